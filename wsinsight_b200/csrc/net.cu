@@ -1,0 +1,533 @@
+// K4: network runtime -- a small layer-graph executor over the tcgen05 conv kernel.
+//
+// Replaces the TorchScript forward + CPU softmax of the reference classification loop
+// (wsinsight/modellib/run_inference.py:537-560) for the zoo CNNs (ResNet34, InceptionV4):
+// the Python side walks the (frozen) TorchScript graph, hands folded conv weights/biases
+// to wsi_net_add_*, and every forward runs only kernels from this library.
+#include "conv.cuh"
+#include "../../include/wsi_b200.h"
+#include <math.h>
+#include <vector>
+
+namespace {
+
+struct Tensor {
+  int H, W, C;
+  __nv_bfloat16* ptr = nullptr;   // [max_batch][H][W][C]; nullptr for the external input
+  bool external = false;
+};
+
+enum OpKind { OP_CONV, OP_MAXPOOL, OP_AVGPOOL, OP_HEAD };
+
+struct Op {
+  OpKind kind;
+  int in, out, res;
+  // conv
+  convk::Args ca;
+  CUtensorMap tmA, tmB;
+  __nv_bfloat16* d_w = nullptr;
+  float* d_bias = nullptr;
+  std::vector<__nv_bfloat16> h_w;
+  std::vector<float> h_bias;
+  int Cin, Cout, KH, KW, stride, pad_h, pad_w, relu, out_c_off, is_stem;
+  int Ktot;
+  // pool
+  int pk, pstride, ppad, count_include_pad;
+  // head
+  int K;
+  float* d_fcw = nullptr;
+  float* d_fcb = nullptr;
+  std::vector<float> h_fcw, h_fcb;
+  double flops_per_image = 0;
+};
+
+struct Net {
+  int max_batch;
+  bool finalized = false;
+  std::vector<Tensor> tensors;
+  std::vector<Op> ops;
+  int num_sms = 148;
+  int launches_per_forward = 0;
+};
+
+// ---------------------------------------------------------------------------
+// pooling / head kernels (NHWC bf16, 8 channels = 16 B per thread)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float bflo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bfhi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+__global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
+                          int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off) {
+  const int cv = C / 8;
+  size_t total = (size_t)B * Ho * Wo * cv;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int c8 = idx % cv;
+  size_t p = idx / cv;
+  int wo = p % Wo;
+  p /= Wo;
+  int ho = p % Ho;
+  int n = p / Ho;
+  float m[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = -INFINITY;
+  for (int dy = 0; dy < k; ++dy) {
+    int y = ho * s - pad + dy;
+    if (y < 0 || y >= H) continue;
+    for (int dx = 0; dx < k; ++dx) {
+      int x = wo * s - pad + dx;
+      if (x < 0 || x >= W) continue;
+      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * H + y) * W + x) * C) + c8);
+      m[0] = fmaxf(m[0], bflo(v.x)); m[1] = fmaxf(m[1], bfhi(v.x));
+      m[2] = fmaxf(m[2], bflo(v.y)); m[3] = fmaxf(m[3], bfhi(v.y));
+      m[4] = fmaxf(m[4], bflo(v.z)); m[5] = fmaxf(m[5], bfhi(v.z));
+      m[6] = fmaxf(m[6], bflo(v.w)); m[7] = fmaxf(m[7], bfhi(v.w));
+    }
+  }
+  uint4 o;
+  o.x = convk::pack_bf16(m[0], m[1]);
+  o.y = convk::pack_bf16(m[2], m[3]);
+  o.z = convk::pack_bf16(m[4], m[5]);
+  o.w = convk::pack_bf16(m[6], m[7]);
+  reinterpret_cast<uint4*>(out + (((size_t)n * Ho + ho) * Wo + wo) * out_C + out_c_off)[c8] = o;
+}
+
+__global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
+                          int count_include_pad, int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C,
+                          int out_c_off) {
+  const int cv = C / 8;
+  size_t total = (size_t)B * Ho * Wo * cv;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int c8 = idx % cv;
+  size_t p = idx / cv;
+  int wo = p % Wo;
+  p /= Wo;
+  int ho = p % Ho;
+  int n = p / Ho;
+  float m[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = 0.f;
+  int cnt = 0;
+  for (int dy = 0; dy < k; ++dy) {
+    int y = ho * s - pad + dy;
+    if (y < 0 || y >= H) continue;
+    for (int dx = 0; dx < k; ++dx) {
+      int x = wo * s - pad + dx;
+      if (x < 0 || x >= W) continue;
+      ++cnt;
+      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * H + y) * W + x) * C) + c8);
+      m[0] += bflo(v.x); m[1] += bfhi(v.x); m[2] += bflo(v.y); m[3] += bfhi(v.y);
+      m[4] += bflo(v.z); m[5] += bfhi(v.z); m[6] += bflo(v.w); m[7] += bfhi(v.w);
+    }
+  }
+  float d = count_include_pad ? (float)(k * k) : (float)cnt;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = m[i] / d;
+  uint4 o;
+  o.x = convk::pack_bf16(m[0], m[1]);
+  o.y = convk::pack_bf16(m[2], m[3]);
+  o.z = convk::pack_bf16(m[4], m[5]);
+  o.w = convk::pack_bf16(m[6], m[7]);
+  reinterpret_cast<uint4*>(out + (((size_t)n * Ho + ho) * Wo + wo) * out_C + out_c_off)[c8] = o;
+}
+
+// K4d: global average pool + FC + softmax (K>1) / sigmoid (K==1); one CTA per image.
+// run_inference.py:548-551 does the softmax on the CPU; here it is fused into the tail.
+constexpr int HEAD_THREADS = 256;
+constexpr int HEAD_MAXK = 16;
+__global__ void __launch_bounds__(HEAD_THREADS)
+    k_head(const __nv_bfloat16* __restrict__ in, int HW, int C, const float* __restrict__ fcw,
+           const float* __restrict__ fcb, int K, float* __restrict__ probs) {
+  extern __shared__ float s_feat[];   // C pooled features
+  __shared__ float s_red[HEAD_MAXK][HEAD_THREADS / 32];
+  __shared__ float s_logit[HEAD_MAXK];
+  const int n = blockIdx.x;
+  const __nv_bfloat16* x = in + (size_t)n * HW * C;
+  for (int c = threadIdx.x; c < C; c += HEAD_THREADS) {
+    float s = 0.f;
+    for (int p = 0; p < HW; ++p) s += __bfloat162float(x[(size_t)p * C + c]);
+    s_feat[c] = s / (float)HW;
+  }
+  __syncthreads();
+  for (int k = 0; k < K; ++k) {
+    float s = 0.f;
+    for (int c = threadIdx.x; c < C; c += HEAD_THREADS) s += s_feat[c] * fcw[(size_t)k * C + c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) s_red[k][threadIdx.x >> 5] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < K) {
+    float s = fcb[threadIdx.x];
+    for (int w = 0; w < HEAD_THREADS / 32; ++w) s += s_red[threadIdx.x][w];
+    s_logit[threadIdx.x] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (K == 1) {
+      probs[n] = 1.0f / (1.0f + expf(-s_logit[0]));
+    } else {
+      float mx = s_logit[0];
+      for (int k = 1; k < K; ++k) mx = fmaxf(mx, s_logit[k]);
+      float e[HEAD_MAXK], sum = 0.f;
+      for (int k = 0; k < K; ++k) {
+        e[k] = expf(s_logit[k] - mx);
+        sum += e[k];
+      }
+      for (int k = 0; k < K; ++k) probs[(size_t)n * K + k] = e[k] / sum;
+    }
+  }
+}
+
+void pick_box(int Wo, int Ho, int* bw, int* bh, int* bn) {
+  int w = 8;
+  while (w > 1 && (Wo % w) != 0) w >>= 1;
+  int h = 8;
+  while (h > 1 && (Ho % h) != 0) h >>= 1;
+  *bw = w;
+  *bh = h;
+  *bn = 128 / (w * h);
+}
+
+int pick_ntile(int Cout) {
+  // largest multiple of 32 that is <= 256 and divides Cout
+  for (int n = 256; n >= 32; n -= 32)
+    if (Cout % n == 0) return n;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int wsi_net_create(int max_batch, void** net_out) {
+  WSI_ARG_CHECK(net_out && max_batch > 0, "wsi_net_create: bad arguments");
+  Net* n = new Net();
+  n->max_batch = max_batch;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0) n->num_sms = sms;
+  *net_out = n;
+  return WSI_OK;
+}
+
+int wsi_net_add_tensor(void* net, int H, int W, int C, int external, int* id_out) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && id_out && !n->finalized, "wsi_net_add_tensor: bad state");
+  WSI_ARG_CHECK(H > 0 && W > 0 && C > 0, "wsi_net_add_tensor: bad shape");
+  Tensor t;
+  t.H = H; t.W = W; t.C = C; t.external = external != 0;
+  n->tensors.push_back(t);
+  *id_out = (int)n->tensors.size() - 1;
+  return WSI_OK;
+}
+
+// generic conv: w is host fp32 OIHW [Cout][Cin][KH][KW]; bias host fp32 [Cout] or NULL
+int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const float* w_oihw, const float* bias,
+                     int Cin, int Cout, int KH, int KW, int stride, int pad_h, int pad_w, int relu,
+                     int residual_id) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized && w_oihw, "wsi_net_add_conv: bad state");
+  WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size() && out_id >= 0 && out_id < (int)n->tensors.size(),
+                "wsi_net_add_conv: bad tensor id");
+  const Tensor& ti = n->tensors[in_id];
+  const Tensor& to = n->tensors[out_id];
+  WSI_ARG_CHECK(ti.C == Cin, "wsi_net_add_conv: Cin %d != tensor C %d", Cin, ti.C);
+  WSI_ARG_CHECK(Cin % 8 == 0, "wsi_net_add_conv: Cin must be a multiple of 8 (got %d)", Cin);
+  const int Ho = (ti.H + 2 * pad_h - KH) / stride + 1, Wo = (ti.W + 2 * pad_w - KW) / stride + 1;
+  WSI_ARG_CHECK(Ho == to.H && Wo == to.W, "wsi_net_add_conv: output shape %dx%d != tensor %dx%d", Ho, Wo, to.H,
+                to.W);
+  WSI_ARG_CHECK(out_c_off >= 0 && out_c_off + Cout <= to.C && out_c_off % 8 == 0 && to.C % 8 == 0,
+                "wsi_net_add_conv: bad channel offset");
+  WSI_ARG_CHECK(pick_ntile(Cout) > 0, "wsi_net_add_conv: Cout %d must be a multiple of 32", Cout);
+  if (residual_id >= 0) {
+    WSI_ARG_CHECK(residual_id < (int)n->tensors.size(), "wsi_net_add_conv: bad residual id");
+    const Tensor& tr = n->tensors[residual_id];
+    WSI_ARG_CHECK(tr.H == to.H && tr.W == to.W && tr.C == Cout && out_c_off == 0,
+                  "wsi_net_add_conv: residual shape mismatch");
+  }
+  Op op;
+  op.kind = OP_CONV;
+  op.in = in_id; op.out = out_id; op.res = residual_id;
+  op.Cin = Cin; op.Cout = Cout; op.KH = KH; op.KW = KW; op.stride = stride; op.pad_h = pad_h; op.pad_w = pad_w;
+  op.relu = relu; op.out_c_off = out_c_off; op.is_stem = 0;
+  const int chunks = (Cin + 63) / 64;
+  op.Ktot = KH * KW * chunks * 64;
+  op.h_w.assign((size_t)Cout * op.Ktot, __float2bfloat16(0.f));
+  for (int o = 0; o < Cout; ++o)
+    for (int c = 0; c < Cin; ++c)
+      for (int y = 0; y < KH; ++y)
+        for (int x = 0; x < KW; ++x) {
+          float v = w_oihw[(((size_t)o * Cin + c) * KH + y) * KW + x];
+          size_t k = ((size_t)(y * KW + x) * chunks + c / 64) * 64 + (c % 64);
+          op.h_w[(size_t)o * op.Ktot + k] = __float2bfloat16(v);
+        }
+  op.h_bias.assign(Cout, 0.f);
+  if (bias) memcpy(op.h_bias.data(), bias, sizeof(float) * Cout);
+  op.flops_per_image = 2.0 * Ho * Wo * (double)Cout * Cin * KH * KW;
+  n->ops.push_back(std::move(op));
+  return WSI_OK;
+}
+
+// ResNet stem: 7x7 stride 2 pad 3 conv on the 3-channel image.  The input tensor is the
+// preprocess kernel's padded NHWC4 layout [B][S+6][Wp][4] (3-pixel zero border, Wp even).
+int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* w_oihw, const float* bias, int Cout,
+                        int relu) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized && w_oihw, "wsi_net_add_stem7x7: bad state");
+  WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size() && out_id >= 0 && out_id < (int)n->tensors.size(),
+                "wsi_net_add_stem7x7: bad tensor id");
+  const Tensor& ti = n->tensors[in_id];
+  const Tensor& to = n->tensors[out_id];
+  WSI_ARG_CHECK(ti.C == 4 && (ti.W % 2) == 0, "wsi_net_add_stem7x7: input must be padded NHWC4 with even width");
+  const int S = ti.H - 6;
+  WSI_ARG_CHECK(S > 0 && S % 2 == 0 && ti.W == S + 6, "wsi_net_add_stem7x7: padded geometry must be (S+6)x(S+6)");
+  WSI_ARG_CHECK(to.H == S / 2 && to.W == S / 2 && to.C == Cout, "wsi_net_add_stem7x7: bad output tensor");
+  WSI_ARG_CHECK(pick_ntile(Cout) > 0, "wsi_net_add_stem7x7: Cout must be a multiple of 32");
+  Op op;
+  op.kind = OP_CONV;
+  op.in = in_id; op.out = out_id; op.res = -1;
+  op.Cin = 3; op.Cout = Cout; op.KH = 7; op.KW = 7; op.stride = 2; op.pad_h = 3; op.pad_w = 3;
+  op.relu = relu; op.out_c_off = 0; op.is_stem = 1;
+  op.Ktot = 7 * 32;
+  // K layout: chunk kh x [px 0..7][ch 0..3]; px==7 and ch==3 carry zero weights
+  op.h_w.assign((size_t)Cout * op.Ktot, __float2bfloat16(0.f));
+  for (int o = 0; o < Cout; ++o)
+    for (int c = 0; c < 3; ++c)
+      for (int y = 0; y < 7; ++y)
+        for (int x = 0; x < 7; ++x) {
+          float v = w_oihw[(((size_t)o * 3 + c) * 7 + y) * 7 + x];
+          size_t k = (size_t)y * 32 + x * 4 + c;
+          op.h_w[(size_t)o * op.Ktot + k] = __float2bfloat16(v);
+        }
+  op.h_bias.assign(Cout, 0.f);
+  if (bias) memcpy(op.h_bias.data(), bias, sizeof(float) * Cout);
+  op.flops_per_image = 2.0 * to.H * to.W * (double)Cout * 3 * 49;
+  n->ops.push_back(std::move(op));
+  return WSI_OK;
+}
+
+int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max, int k, int stride, int pad,
+                     int count_include_pad) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized, "wsi_net_add_pool: bad state");
+  WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size() && out_id >= 0 && out_id < (int)n->tensors.size(),
+                "wsi_net_add_pool: bad tensor id");
+  const Tensor& ti = n->tensors[in_id];
+  const Tensor& to = n->tensors[out_id];
+  const int Ho = (ti.H + 2 * pad - k) / stride + 1, Wo = (ti.W + 2 * pad - k) / stride + 1;
+  WSI_ARG_CHECK(Ho == to.H && Wo == to.W, "wsi_net_add_pool: output shape mismatch");
+  WSI_ARG_CHECK(ti.C % 8 == 0 && to.C % 8 == 0 && out_c_off % 8 == 0 && out_c_off + ti.C <= to.C,
+                "wsi_net_add_pool: channel layout");
+  Op op;
+  op.kind = is_max ? OP_MAXPOOL : OP_AVGPOOL;
+  op.in = in_id; op.out = out_id; op.res = -1;
+  op.pk = k; op.pstride = stride; op.ppad = pad; op.count_include_pad = count_include_pad;
+  op.out_c_off = out_c_off;
+  n->ops.push_back(std::move(op));
+  return WSI_OK;
+}
+
+int wsi_net_add_head(void* net, int in_id, const float* fc_w, const float* fc_b, int K) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized && fc_w, "wsi_net_add_head: bad state");
+  WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size(), "wsi_net_add_head: bad tensor id");
+  WSI_ARG_CHECK(K >= 1 && K <= HEAD_MAXK, "wsi_net_add_head: K out of range");
+  const Tensor& ti = n->tensors[in_id];
+  Op op;
+  op.kind = OP_HEAD;
+  op.in = in_id; op.out = -1; op.res = -1;
+  op.K = K;
+  op.h_fcw.assign(fc_w, fc_w + (size_t)K * ti.C);
+  op.h_fcb.assign(K, 0.f);
+  if (fc_b) memcpy(op.h_fcb.data(), fc_b, sizeof(float) * K);
+  op.flops_per_image = 2.0 * K * ti.C;
+  n->ops.push_back(std::move(op));
+  return WSI_OK;
+}
+
+int wsi_net_finalize(void* net) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized, "wsi_net_finalize: bad state");
+  const int B = n->max_batch;
+  for (auto& t : n->tensors) {
+    if (t.external) continue;
+    size_t bytes = (size_t)B * t.H * t.W * t.C * sizeof(__nv_bfloat16);
+    WSI_CUDA_CHECK(cudaMalloc(&t.ptr, bytes));
+    WSI_CUDA_CHECK(cudaMemset(t.ptr, 0, bytes));
+  }
+  int max_smem = 0;
+  for (auto& op : n->ops) {
+    if (op.kind == OP_CONV) {
+      const Tensor& ti = n->tensors[op.in];
+      const Tensor& to = n->tensors[op.out];
+      WSI_CUDA_CHECK(cudaMalloc(&op.d_w, op.h_w.size() * sizeof(__nv_bfloat16)));
+      WSI_CUDA_CHECK(cudaMemcpy(op.d_w, op.h_w.data(), op.h_w.size() * sizeof(__nv_bfloat16),
+                                cudaMemcpyHostToDevice));
+      WSI_CUDA_CHECK(cudaMalloc(&op.d_bias, op.h_bias.size() * sizeof(float)));
+      WSI_CUDA_CHECK(cudaMemcpy(op.d_bias, op.h_bias.data(), op.h_bias.size() * sizeof(float),
+                                cudaMemcpyHostToDevice));
+      convk::Args& a = op.ca;
+      memset(&a, 0, sizeof(a));
+      pick_box(to.W, to.H, &a.bw, &a.bh, &a.bn);
+      a.tiles_w = wsi_cdiv(to.W, a.bw);
+      a.tiles_h = wsi_cdiv(to.H, a.bh);
+      a.Ho = to.H; a.Wo = to.W;
+      a.stride = op.stride; a.pad_h = op.pad_h; a.pad_w = op.pad_w; a.KH = op.KH; a.KW = op.KW;
+      a.cin_chunks = (op.Cin + 63) / 64;
+      a.is_stem = op.is_stem;
+      a.N_tile = pick_ntile(op.Cout);
+      a.tiles_N = op.Cout / a.N_tile;
+      const size_t stage_bytes = convk::A_BYTES + (size_t)a.N_tile * 128;
+      int stages = (int)((200 * 1024) / stage_bytes);
+      if (stages > 8) stages = 8;
+      if (stages < 2) stages = 2;
+      a.stages = stages;
+      a.out_C = to.C; a.out_c_off = op.out_c_off;
+      a.res_C = op.res >= 0 ? n->tensors[op.res].C : 0;
+      a.relu = op.relu;
+      a.bias = op.d_bias;
+      int smem = (int)convk::smem_bytes(a.N_tile, a.stages);
+      if (smem > max_smem) max_smem = smem;
+      // weights: [Cout][Ktot] K-major, box 64 x N_tile, 128B swizzle
+      {
+        uint64_t dims[2] = {(uint64_t)op.Ktot, (uint64_t)op.Cout};
+        uint64_t strides[1] = {(uint64_t)op.Ktot * 2};
+        uint32_t box[2] = {(uint32_t)(op.is_stem ? 32 : 64), (uint32_t)a.N_tile};
+        uint32_t es[2] = {1, 1};
+        int rc = wsi_make_tmap(&op.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op.d_w, dims, strides, box, es,
+                               op.is_stem ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+      }
+      // activations: base pointer patched per forward for external inputs (map re-encoded then)
+      if (!ti.external) {
+        int rc = wsi_net_encode_input_map(net, (int)(&op - &n->ops[0]), ti.ptr);
+        if (rc) return rc;
+      }
+    } else if (op.kind == OP_HEAD) {
+      WSI_CUDA_CHECK(cudaMalloc(&op.d_fcw, op.h_fcw.size() * sizeof(float)));
+      WSI_CUDA_CHECK(cudaMemcpy(op.d_fcw, op.h_fcw.data(), op.h_fcw.size() * sizeof(float), cudaMemcpyHostToDevice));
+      WSI_CUDA_CHECK(cudaMalloc(&op.d_fcb, op.h_fcb.size() * sizeof(float)));
+      WSI_CUDA_CHECK(cudaMemcpy(op.d_fcb, op.h_fcb.data(), op.h_fcb.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+  }
+  if (max_smem > 0)
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  n->launches_per_forward = (int)n->ops.size();
+  n->finalized = true;
+  return WSI_OK;
+}
+
+// (re)encode the A-operand tensor map of conv op `op_index` for input base pointer `base`
+int wsi_net_encode_input_map(void* net, int op_index, const void* base) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && op_index >= 0 && op_index < (int)n->ops.size(), "wsi_net_encode_input_map: bad op");
+  Op& op = n->ops[op_index];
+  WSI_ARG_CHECK(op.kind == OP_CONV && base, "wsi_net_encode_input_map: not a conv");
+  const Tensor& ti = n->tensors[op.in];
+  const convk::Args& a = op.ca;
+  const uint64_t B = (uint64_t)n->max_batch;
+  if (op.is_stem) {
+    // overlapping-window view of the padded NHWC4 image: element (k, wo, row, n) lives at
+    // base + n*H*rowb + row*rowb + wo*16 + k*2  (k < 32: 8 pixels x 4 channels from pixel 2*wo)
+    const uint64_t rowb = (uint64_t)ti.W * 8;   // 4 ch x bf16
+    uint64_t dims[4] = {32, (uint64_t)a.Wo, (uint64_t)ti.H, B};
+    uint64_t strides[3] = {16, rowb, (uint64_t)ti.H * rowb};
+    uint32_t box[4] = {32, (uint32_t)a.bw, (uint32_t)(a.bh * 2), (uint32_t)a.bn};
+    uint32_t es[4] = {1, 1, 2, 1};
+    return wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, es,
+                         CU_TENSOR_MAP_SWIZZLE_64B);
+  }
+  uint64_t dims[4] = {(uint64_t)ti.C, (uint64_t)ti.W, (uint64_t)ti.H, B};
+  uint64_t strides[3] = {(uint64_t)ti.C * 2, (uint64_t)ti.W * ti.C * 2, (uint64_t)ti.H * ti.W * ti.C * 2};
+  uint32_t box[4] = {64, (uint32_t)(a.bw * a.stride), (uint32_t)(a.bh * a.stride), (uint32_t)a.bn};
+  uint32_t es[4] = {1, (uint32_t)a.stride, (uint32_t)a.stride, 1};
+  return wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, es,
+                       CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && n->finalized, "wsi_net_forward: net not finalized");
+  WSI_ARG_CHECK(B >= 1 && B <= n->max_batch, "wsi_net_forward: batch %d out of range (max %d)", B, n->max_batch);
+  for (size_t i = 0; i < n->ops.size(); ++i) {
+    Op& op = n->ops[i];
+    const Tensor& ti = n->tensors[op.in];
+    const __nv_bfloat16* in_ptr = ti.external ? (const __nv_bfloat16*)d_input : ti.ptr;
+    WSI_ARG_CHECK(in_ptr, "wsi_net_forward: missing input pointer");
+    if (op.kind == OP_CONV) {
+      if (ti.external) {
+        int rc = wsi_net_encode_input_map(net, (int)i, in_ptr);
+        if (rc) return rc;
+      }
+      const Tensor& to = n->tensors[op.out];
+      convk::Args a = op.ca;
+      a.B = B;
+      a.tiles_n = wsi_cdiv(B, a.bn);
+      a.out = to.ptr;
+      a.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
+      const long long total = (long long)a.tiles_w * a.tiles_h * a.tiles_n * a.tiles_N;
+      int grid = (int)(total < n->num_sms ? total : n->num_sms);
+      size_t smem = convk::smem_bytes(a.N_tile, a.stages);
+      convk::k_conv_igemm<<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, a);
+    } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
+      const Tensor& to = n->tensors[op.out];
+      size_t total = (size_t)B * to.H * to.W * (ti.C / 8);
+      int blocks = (int)((total + 255) / 256);
+      if (op.kind == OP_MAXPOOL)
+        k_maxpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, to.H, to.W,
+                                              to.ptr, to.C, op.out_c_off);
+      else
+        k_avgpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
+                                              op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off);
+    } else if (op.kind == OP_HEAD) {
+      WSI_ARG_CHECK(d_probs, "wsi_net_forward: null probs");
+      k_head<<<B, HEAD_THREADS, ti.C * sizeof(float), stream>>>(in_ptr, ti.H * ti.W, ti.C, op.d_fcw, op.d_fcb, op.K,
+                                                                d_probs);
+    }
+  }
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
+int wsi_net_tensor_ptr(void* net, int id, void** ptr, int* hwc3) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && id >= 0 && id < (int)n->tensors.size() && ptr, "wsi_net_tensor_ptr: bad id");
+  *ptr = n->tensors[id].ptr;
+  if (hwc3) {
+    hwc3[0] = n->tensors[id].H; hwc3[1] = n->tensors[id].W; hwc3[2] = n->tensors[id].C;
+  }
+  return WSI_OK;
+}
+
+int wsi_net_num_launches(void* net) {
+  Net* n = (Net*)net;
+  return n ? n->launches_per_forward : 0;
+}
+
+double wsi_net_flops_per_image(void* net) {
+  Net* n = (Net*)net;
+  double f = 0;
+  if (n)
+    for (auto& op : n->ops) f += op.flops_per_image;
+  return f;
+}
+
+void wsi_net_destroy(void* net) {
+  Net* n = (Net*)net;
+  if (!n) return;
+  for (auto& t : n->tensors)
+    if (t.ptr) cudaFree(t.ptr);
+  for (auto& op : n->ops) {
+    if (op.d_w) cudaFree(op.d_w);
+    if (op.d_bias) cudaFree(op.d_bias);
+    if (op.d_fcw) cudaFree(op.d_fcw);
+    if (op.d_fcb) cudaFree(op.d_fcb);
+  }
+  delete n;
+}
+
+}  // extern "C"

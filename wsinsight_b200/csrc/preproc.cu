@@ -1,0 +1,350 @@
+// K3: fused patch data path  (crop RGBA->RGB, PIL-exact antialiased bilinear resize,
+// ToTensor, Normalize) from a device-resident slide into bf16 NHWC4 batches.
+//
+// Replaces (reference, huangch/wsinsight):
+//   wsinsight/modellib/data.py:270-281        read_region(...).convert("RGB")  (zero padded OOB)
+//   wsinsight/modellib/transforms.py:22-38    torchvision Resize / ToTensor / Normalize
+//   wsinsight/modellib/run_inference.py:288-299,543  default collate + H2D copy
+//
+// The source window of each patch is staged into shared memory by TMA
+// (cp.async.bulk.tensor, zero fill outside the slide == the reference's padding); the
+// resample follows Pillow's Resample.c in 22-bit fixed point with a uint8 intermediate
+// after the horizontal pass, so the u8 result is bit-exact with PIL; x/255, (x-mean)/std
+// are done in fp32 exactly like torchvision and rounded once to bf16 (RNE).
+#include "common.cuh"
+#include "../../include/wsi_b200.h"
+#include <math.h>
+#include <vector>
+
+namespace {
+
+constexpr int PRECISION_BITS = 32 - 8 - 2;
+constexpr int PP_THREADS = 256;
+constexpr int PP_BOX_W = 256;        // source pixels per TMA box row (1024 B)
+constexpr int PP_MAX_INTER_ROWS = 64;
+
+struct Taps {
+  std::vector<int> lo, cnt, coef;
+  int ksize = 0;
+};
+
+// Pillow precompute_coeffs() for the BILINEAR (triangle, support 1) filter + normalize_coeffs_8bpc()
+Taps make_taps(int in_size, int out_size) {
+  Taps t;
+  double scale = (double)in_size / (double)out_size;
+  double filterscale = scale < 1.0 ? 1.0 : scale;
+  double support = 1.0 * filterscale;
+  int ksize = (int)ceil(support) * 2 + 1;
+  t.ksize = ksize;
+  t.lo.resize(out_size);
+  t.cnt.resize(out_size);
+  t.coef.assign((size_t)out_size * ksize, 0);
+  std::vector<double> w(ksize);
+  double ss = 1.0 / filterscale;
+  for (int xx = 0; xx < out_size; ++xx) {
+    double center = (xx + 0.5) * scale;
+    int lo = (int)(center - support + 0.5);
+    if (lo < 0) lo = 0;
+    int hi = (int)(center + support + 0.5);
+    if (hi > in_size) hi = in_size;
+    int n = hi - lo;
+    double ww = 0.0;
+    for (int x = 0; x < n; ++x) {
+      double v = (x + lo - center + 0.5) * ss;
+      if (v < 0) v = -v;
+      double wv = v < 1.0 ? 1.0 - v : 0.0;
+      w[x] = wv;
+      ww += wv;
+    }
+    for (int x = 0; x < n; ++x) {
+      if (ww != 0.0) w[x] /= ww;
+      double q = w[x] * (double)(1 << PRECISION_BITS);
+      t.coef[(size_t)xx * ksize + x] = (int)(w[x] < 0 ? -0.5 + q : 0.5 + q);
+    }
+    t.lo[xx] = lo;
+    t.cnt[xx] = n;
+  }
+  return t;
+}
+
+struct Plan {
+  int ps, S, ksize;
+  int TR, nbands, ngroups, G;
+  int box_w, box_h;               // TMA box (pixels, rows)
+  int max_src_rows;               // intermediate rows per band
+  int out_H, out_W, pad_top, pad_left;
+  float mean[3], stdv[3];
+  int has_norm;
+  int *d_lo, *d_cnt, *d_coef;     // taps (same table for both axes: square patches)
+  size_t smem_bytes;
+  CUtensorMap tmap;
+};
+
+struct PPArgs {
+  const int* lo;
+  const int* cnt;
+  const int* coef;
+  const int32_t* coords;   // (n,2) top-left x,y
+  __nv_bfloat16* out;
+  int ps, S, ksize, TR, G, ngroups, box_w, box_h, max_src_rows;
+  int out_H, out_W, pad_top, pad_left;
+  float m0, m1, m2, s0, s1, s2;
+  int has_norm;
+};
+
+__device__ __forceinline__ uint32_t clip8(int v) {
+  v >>= PRECISION_BITS;
+  return (uint32_t)min(max(v, 0), 255);
+}
+
+// grid: (n_patches, nbands); one CTA = TR output rows x S output columns of one patch
+__global__ void __launch_bounds__(PP_THREADS)
+    k_preprocess(const __grid_constant__ CUtensorMap tmap, PPArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint32_t* s_src = reinterpret_cast<uint32_t*>(smem);                          // box_h x box_w RGBA
+  uint32_t* s_int = s_src + (size_t)a.box_h * a.box_w;                          // max_src_rows x S (RGBx u8)
+  __shared__ __align__(8) uint64_t s_bar;
+
+  const int patch = blockIdx.x;
+  const int r0 = blockIdx.y * a.TR;
+  const int r1 = min(r0 + a.TR, a.S);
+  const int px = a.coords[2 * patch + 0], py = a.coords[2 * patch + 1];
+  const int y_lo = a.lo[r0];
+  const int y_hi = a.lo[r1 - 1] + a.cnt[r1 - 1];
+  const int nrows = y_hi - y_lo;
+
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(&s_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  uint32_t phase = 0;
+
+  // horizontal pass: source rows [y_lo, y_hi) x output columns, chunked by TMA boxes
+  for (int yc = 0; yc < nrows; yc += a.box_h) {
+    const int rows_here = min(a.box_h, nrows - yc);
+    for (int g = 0; g < a.ngroups; ++g) {
+      const int xx0 = g * a.G, xx1 = min(xx0 + a.G, a.S);
+      const int xs0 = a.lo[xx0];
+      if (threadIdx.x == 0) {
+        ptx::mbar_arrive_expect_tx(&s_bar, (uint32_t)(a.box_h * a.box_w * 4));
+        ptx::tma_load_2d(s_src, &tmap, &s_bar, px + xs0, py + y_lo + yc);
+      }
+      ptx::mbar_wait(&s_bar, phase);
+      phase ^= 1;
+      const int ncols = xx1 - xx0;
+      for (int i = threadIdx.x; i < rows_here * ncols; i += PP_THREADS) {
+        const int rr = i / ncols, xx = xx0 + (i - rr * ncols);
+        const int lo = a.lo[xx] - xs0, n = a.cnt[xx];
+        const int* k = a.coef + (size_t)xx * a.ksize;
+        const uint32_t* src = s_src + rr * a.box_w + lo;
+        int s0 = 1 << (PRECISION_BITS - 1), s1 = s0, s2 = s0;
+        for (int t = 0; t < n; ++t) {
+          const uint32_t p = src[t];
+          const int c = k[t];
+          s0 += (int)(p & 0xff) * c;
+          s1 += (int)((p >> 8) & 0xff) * c;
+          s2 += (int)((p >> 16) & 0xff) * c;
+        }
+        s_int[(yc + rr) * a.S + xx] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
+      }
+      __syncthreads();   // s_src is reused by the next box; s_int rows complete
+    }
+  }
+
+  // vertical pass + ToTensor + Normalize + bf16 NHWC4 store
+  const int nout = (r1 - r0) * a.S;
+  for (int i = threadIdx.x; i < nout; i += PP_THREADS) {
+    const int ry = i / a.S, xx = i - ry * a.S;
+    const int yy = r0 + ry;
+    const int lo = a.lo[yy] - y_lo, n = a.cnt[yy];
+    const int* k = a.coef + (size_t)yy * a.ksize;
+    int s0 = 1 << (PRECISION_BITS - 1), s1 = s0, s2 = s0;
+    for (int t = 0; t < n; ++t) {
+      const uint32_t p = s_int[(lo + t) * a.S + xx];
+      const int c = k[t];
+      s0 += (int)(p & 0xff) * c;
+      s1 += (int)((p >> 8) & 0xff) * c;
+      s2 += (int)((p >> 16) & 0xff) * c;
+    }
+    float f0 = __fdiv_rn((float)clip8(s0), 255.0f);
+    float f1 = __fdiv_rn((float)clip8(s1), 255.0f);
+    float f2 = __fdiv_rn((float)clip8(s2), 255.0f);
+    if (a.has_norm) {
+      f0 = __fdiv_rn(__fsub_rn(f0, a.m0), a.s0);
+      f1 = __fdiv_rn(__fsub_rn(f1, a.m1), a.s1);
+      f2 = __fdiv_rn(__fsub_rn(f2, a.m2), a.s2);
+    }
+    __nv_bfloat162 lo2 = __floats2bfloat162_rn(f0, f1);
+    __nv_bfloat162 hi2 = __floats2bfloat162_rn(f2, 0.0f);
+    uint2 v;
+    v.x = *reinterpret_cast<uint32_t*>(&lo2);
+    v.y = *reinterpret_cast<uint32_t*>(&hi2);
+    size_t o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
+    reinterpret_cast<uint2*>(a.out)[o] = v;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long long slide_h,
+                            long long pitch_bytes, int patch_size, int out_size, const float* mean,
+                            const float* stdv, int out_H, int out_W, int pad_top, int pad_left,
+                            void** plan_out) {
+  WSI_ARG_CHECK(d_slide_rgba && plan_out, "wsi_preproc_plan_create: null pointer");
+  WSI_ARG_CHECK(((uintptr_t)d_slide_rgba & 15) == 0 && (pitch_bytes & 15) == 0 && pitch_bytes >= slide_w * 4,
+                "wsi_preproc_plan_create: slide base/pitch must be 16-byte aligned RGBA");
+  WSI_ARG_CHECK(patch_size >= 1 && out_size >= 1 && out_size <= 1024, "wsi_preproc_plan_create: bad sizes");
+  WSI_ARG_CHECK(out_H >= pad_top + out_size && out_W >= pad_left + out_size && pad_top >= 0 && pad_left >= 0,
+                "wsi_preproc_plan_create: output geometry too small");
+  Plan* p = new Plan();
+  p->ps = patch_size;
+  p->S = out_size;
+  p->out_H = out_H;
+  p->out_W = out_W;
+  p->pad_top = pad_top;
+  p->pad_left = pad_left;
+  p->has_norm = (mean && stdv) ? 1 : 0;
+  for (int c = 0; c < 3; ++c) {
+    p->mean[c] = mean ? mean[c] : 0.f;
+    p->stdv[c] = stdv ? stdv[c] : 1.f;
+  }
+  Taps t = make_taps(patch_size, out_size);
+  p->ksize = t.ksize;
+  const int S = out_size;
+  // rows per band so that the u8 intermediate stays <= PP_MAX_INTER_ROWS source rows
+  int TR = 16;
+  for (;;) {
+    int worst = 0;
+    for (int r0 = 0; r0 < S; r0 += TR) {
+      int r1 = r0 + TR < S ? r0 + TR : S;
+      int rows = t.lo[r1 - 1] + t.cnt[r1 - 1] - t.lo[r0];
+      if (rows > worst) worst = rows;
+    }
+    p->max_src_rows = worst;
+    if (worst <= PP_MAX_INTER_ROWS || TR == 1) break;
+    TR = TR / 2;
+  }
+  p->TR = TR;
+  p->nbands = (S + TR - 1) / TR;
+  // output-column groups whose source span fits one TMA box row
+  int box_w = patch_size + 8;
+  box_w = (box_w + 3) / 4 * 4;
+  if (box_w > PP_BOX_W) box_w = PP_BOX_W;
+  int G = S;
+  for (;;) {
+    int worst = 0;
+    for (int x0 = 0; x0 < S; x0 += G) {
+      int x1 = x0 + G < S ? x0 + G : S;
+      int span = t.lo[x1 - 1] + t.cnt[x1 - 1] - t.lo[x0];
+      if (span > worst) worst = span;
+    }
+    if (worst <= box_w || G == 1) {
+      if (worst > box_w) {
+        delete p;
+        wsi_set_error("wsi_preproc_plan_create: filter support %d exceeds TMA box %d", worst, box_w);
+        return WSI_ERR_UNSUPPORTED;
+      }
+      break;
+    }
+    G = (G + 1) / 2;
+  }
+  p->G = G;
+  p->ngroups = (S + G - 1) / G;
+  p->box_w = box_w;
+  int box_h = (32 * 1024) / (box_w * 4);
+  if (box_h > p->max_src_rows) box_h = p->max_src_rows;
+  if (box_h > 256) box_h = 256;
+  if (box_h < 1) box_h = 1;
+  p->box_h = box_h;
+  p->smem_bytes = (size_t)box_h * box_w * 4 + (size_t)p->max_src_rows * S * 4;
+  if (p->smem_bytes > 200 * 1024) {
+    delete p;
+    wsi_set_error("wsi_preproc_plan_create: shared memory budget exceeded (%zu)", p->smem_bytes);
+    return WSI_ERR_UNSUPPORTED;
+  }
+  size_t nb = (size_t)S * sizeof(int);
+  if (cudaMalloc(&p->d_lo, nb) != cudaSuccess || cudaMalloc(&p->d_cnt, nb) != cudaSuccess ||
+      cudaMalloc(&p->d_coef, nb * t.ksize) != cudaSuccess) {
+    delete p;
+    wsi_set_error("wsi_preproc_plan_create: cudaMalloc failed");
+    return WSI_ERR_NOMEM;
+  }
+  cudaMemcpy(p->d_lo, t.lo.data(), nb, cudaMemcpyHostToDevice);
+  cudaMemcpy(p->d_cnt, t.cnt.data(), nb, cudaMemcpyHostToDevice);
+  cudaMemcpy(p->d_coef, t.coef.data(), nb * t.ksize, cudaMemcpyHostToDevice);
+  uint64_t dims[2] = {(uint64_t)slide_w, (uint64_t)slide_h};
+  uint64_t strides[1] = {(uint64_t)pitch_bytes};
+  uint32_t box[2] = {(uint32_t)box_w, (uint32_t)box_h};
+  uint32_t es[2] = {1, 1};
+  int rc = wsi_make_tmap(&p->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, d_slide_rgba, dims, strides, box, es,
+                         CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc) {
+    cudaFree(p->d_lo);
+    cudaFree(p->d_cnt);
+    cudaFree(p->d_coef);
+    delete p;
+    return rc;
+  }
+  cudaError_t e = cudaFuncSetAttribute(k_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e != cudaSuccess) {
+    wsi_set_error("wsi_preproc_plan_create: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    return WSI_ERR_CUDA;
+  }
+  *plan_out = p;
+  return WSI_OK;
+}
+
+int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_bf16, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(plan && d_coords_xy && d_out_bf16, "wsi_preproc_run: null pointer");
+  if (n <= 0) return WSI_OK;
+  Plan* p = (Plan*)plan;
+  PPArgs a;
+  a.lo = p->d_lo;
+  a.cnt = p->d_cnt;
+  a.coef = p->d_coef;
+  a.coords = d_coords_xy;
+  a.out = (__nv_bfloat16*)d_out_bf16;
+  a.ps = p->ps;
+  a.S = p->S;
+  a.ksize = p->ksize;
+  a.TR = p->TR;
+  a.G = p->G;
+  a.ngroups = p->ngroups;
+  a.box_w = p->box_w;
+  a.box_h = p->box_h;
+  a.max_src_rows = p->max_src_rows;
+  a.out_H = p->out_H;
+  a.out_W = p->out_W;
+  a.pad_top = p->pad_top;
+  a.pad_left = p->pad_left;
+  a.m0 = p->mean[0]; a.m1 = p->mean[1]; a.m2 = p->mean[2];
+  a.s0 = p->stdv[0]; a.s1 = p->stdv[1]; a.s2 = p->stdv[2];
+  a.has_norm = p->has_norm;
+  dim3 grid(n, p->nbands);
+  k_preprocess<<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
+int wsi_preproc_plan_info(void* plan, int* info8) {
+  WSI_ARG_CHECK(plan && info8, "wsi_preproc_plan_info: null pointer");
+  Plan* p = (Plan*)plan;
+  info8[0] = p->TR; info8[1] = p->nbands; info8[2] = p->G; info8[3] = p->ngroups;
+  info8[4] = p->box_w; info8[5] = p->box_h; info8[6] = p->max_src_rows; info8[7] = (int)p->smem_bytes;
+  return WSI_OK;
+}
+
+void wsi_preproc_plan_destroy(void* plan) {
+  if (!plan) return;
+  Plan* p = (Plan*)plan;
+  cudaFree(p->d_lo);
+  cudaFree(p->d_cnt);
+  cudaFree(p->d_coef);
+  delete p;
+}
+
+}  // extern "C"

@@ -1,0 +1,476 @@
+// K1: tissue segmentation of a slide thumbnail, K2: in-tissue patch-grid filter.
+//
+// Replaces (reference, huangch/wsinsight):
+//   wsinsight/patchlib/segment.py:54-97   cv.cvtColor/medianBlur/threshold, skimage
+//                                         binary_closing/remove_small_objects/remove_small_holes
+//   wsinsight/patchlib/patch.py:57-130    cv.findContours + Shapely union/difference
+//   wsinsight/patchlib/patch.py:210-242   itertools grid + STRtree.query(contains) + sort
+//
+// All arithmetic is integer and bit-exact with the CPU oracle (oracle/segment.py,
+// oracle/patchgrid.py).  HBM/latency-bound byte work: no tensor cores here.
+#include "common.cuh"
+#include "../../include/wsi_b200.h"
+
+namespace {
+
+// ----------------------------------------------------------------------------
+// K1a: RGB -> HSV saturation (OpenCV 8-bit formula) -> (S > thresh) -> k x k box
+// count with replicate border >= (k*k+1)/2   [== medianBlur(S,k) > thresh]
+// ----------------------------------------------------------------------------
+__constant__ int c_sdiv[256];
+
+constexpr int K1_TW = 64;
+constexpr int K1_TH = 16;
+
+__global__ void __launch_bounds__(K1_TW* K1_TH / 4)
+    k_sat_median_thresh(const uint8_t* __restrict__ rgb, int H, int W, int pitch, int k, int thresh,
+                        uint8_t* __restrict__ out) {
+  extern __shared__ uint8_t s_b[];  // (TH+2r) x (TW+2r) thresholded bits
+  const int r = k >> 1;
+  const int sw = K1_TW + 2 * r, sh = K1_TH + 2 * r;
+  const int x0 = blockIdx.x * K1_TW - r, y0 = blockIdx.y * K1_TH - r;
+  for (int i = threadIdx.x; i < sw * sh; i += blockDim.x) {
+    int ly = i / sw, lx = i - ly * sw;
+    int gx = min(max(x0 + lx, 0), W - 1);   // BORDER_REPLICATE
+    int gy = min(max(y0 + ly, 0), H - 1);
+    const uint8_t* p = rgb + (size_t)gy * pitch + (size_t)gx * 3;
+    int R = p[0], G = p[1], B = p[2];
+    int v = max(R, max(G, B));
+    int d = v - min(R, min(G, B));
+    int s = (d * c_sdiv[v] + (1 << 11)) >> 12;
+    s_b[i] = (s > thresh) ? 1 : 0;
+  }
+  __syncthreads();
+  const int need = (k * k + 1) >> 1;
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += blockDim.x) {
+    int ly = i / K1_TW, lx = i - ly * K1_TW;
+    int gx = blockIdx.x * K1_TW + lx, gy = blockIdx.y * K1_TH + ly;
+    if (gx >= W || gy >= H) continue;
+    int cnt = 0;
+    for (int dy = 0; dy < k; ++dy) {
+      const uint8_t* row = s_b + (ly + dy) * sw + lx;
+      for (int dx = 0; dx < k; ++dx) cnt += row[dx];
+    }
+    out[(size_t)gy * W + gx] = cnt >= need ? 1 : 0;
+  }
+}
+
+// ----------------------------------------------------------------------------
+// K1b: closing with ones(k,k):  dilation offsets [-(k-1)/2 .. k/2] (outside = 0)
+// then erosion offsets [-(k/2) .. (k-1)/2] (outside = 1)  (scipy / skimage convention)
+// ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    k_closing(const uint8_t* __restrict__ in, int H, int W, int k, uint8_t* __restrict__ out) {
+  extern __shared__ uint8_t s_m[];
+  const int dlo = (k - 1) >> 1, elo = k >> 1;
+  const int halo = k - 1;
+  const int iw = K1_TW + 2 * halo, ih = K1_TH + 2 * halo;      // input tile
+  const int dw = K1_TW + halo, dh = K1_TH + halo;              // dilated tile
+  uint8_t* s_in = s_m;
+  uint8_t* s_d = s_m + iw * ih;
+  const int bx = blockIdx.x * K1_TW, by = blockIdx.y * K1_TH;
+  // input tile origin: (bx - elo - dlo, by - elo - dlo)
+  for (int i = threadIdx.x; i < iw * ih; i += blockDim.x) {
+    int ly = i / iw, lx = i - ly * iw;
+    int gx = bx - elo - dlo + lx, gy = by - elo - dlo + ly;
+    s_in[i] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? in[(size_t)gy * W + gx] : 0;
+  }
+  __syncthreads();
+  // dilated tile origin: (bx - elo, by - elo); positions outside the image read as 1 for the erosion
+  for (int i = threadIdx.x; i < dw * dh; i += blockDim.x) {
+    int ly = i / dw, lx = i - ly * dw;
+    int gx = bx - elo + lx, gy = by - elo + ly;
+    uint8_t v;
+    if (gx < 0 || gx >= W || gy < 0 || gy >= H) {
+      v = 1;
+    } else {
+      v = 0;
+      for (int dy = 0; dy < k; ++dy) {
+        const uint8_t* row = s_in + (ly + dy) * iw + lx;
+        for (int dx = 0; dx < k; ++dx) v |= row[dx];
+      }
+    }
+    s_d[i] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += blockDim.x) {
+    int ly = i / K1_TW, lx = i - ly * K1_TW;
+    int gx = bx + lx, gy = by + ly;
+    if (gx >= W || gy >= H) continue;
+    uint8_t v = 1;
+    for (int dy = 0; dy < k; ++dy) {
+      const uint8_t* row = s_d + (ly + dy) * dw + lx;
+      for (int dx = 0; dx < k; ++dx) v &= row[dx];
+    }
+    out[(size_t)gy * W + gx] = v;
+  }
+}
+
+// ----------------------------------------------------------------------------
+// K1c: connected components by lock-free union-find (min-label roots).
+// One labelling handles both classes at once: a pixel merges with a neighbour of
+// the same value.  conn8_fg adds the diagonal neighbours for foreground pixels
+// (OpenCV contour convention: 8-connected foreground, 4-connected background).
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ int uf_find(const int* L, int x) {
+  int p = L[x];
+  while (p != x) {
+    x = p;
+    p = L[x];
+  }
+  return x;
+}
+__device__ __forceinline__ void uf_union(int* L, int a, int b) {
+  bool done;
+  do {
+    a = uf_find(L, a);
+    b = uf_find(L, b);
+    if (a < b) {
+      int old = atomicMin(&L[b], a);
+      done = (old == b);
+      b = old;
+    } else if (b < a) {
+      int old = atomicMin(&L[a], b);
+      done = (old == a);
+      a = old;
+    } else {
+      done = true;
+    }
+  } while (!done);
+}
+
+constexpr int CC_TW = 32, CC_TH = 16;   // 512-pixel tiles, 1 thread per pixel
+
+// Phase 1: tile-local union-find in shared memory, then publish global ids of the local roots.
+__global__ void __launch_bounds__(CC_TW* CC_TH)
+    k_ccl_local(const uint8_t* __restrict__ mask, int H, int W, int conn8_fg, int* __restrict__ L) {
+  __shared__ int s_L[CC_TW * CC_TH];
+  __shared__ uint8_t s_v[CC_TW * CC_TH];
+  const int lx = threadIdx.x % CC_TW, ly = threadIdx.x / CC_TW;
+  const int gx = blockIdx.x * CC_TW + lx, gy = blockIdx.y * CC_TH + ly;
+  const bool in = gx < W && gy < H;
+  const int t = threadIdx.x;
+  uint8_t v = in ? mask[(size_t)gy * W + gx] : 2;   // 2 = outside, never merges
+  s_v[t] = v;
+  s_L[t] = t;
+  __syncthreads();
+  if (in) {
+    if (lx > 0 && s_v[t - 1] == v) uf_union(s_L, t, t - 1);
+    if (ly > 0 && s_v[t - CC_TW] == v) uf_union(s_L, t, t - CC_TW);
+    if (conn8_fg && v == 1 && ly > 0) {
+      if (lx > 0 && s_v[t - CC_TW - 1] == 1) uf_union(s_L, t, t - CC_TW - 1);
+      if (lx < CC_TW - 1 && s_v[t - CC_TW + 1] == 1) uf_union(s_L, t, t - CC_TW + 1);
+    }
+  }
+  __syncthreads();
+  if (in) {
+    int rt = uf_find(s_L, t);
+    int rx = rt % CC_TW, ry = rt / CC_TW;
+    L[(size_t)gy * W + gx] = (blockIdx.y * CC_TH + ry) * W + blockIdx.x * CC_TW + rx;
+  }
+}
+
+// Phase 2: merge across tile borders (and optionally tie border background to the frame node H*W).
+__global__ void k_ccl_border(const uint8_t* __restrict__ mask, int H, int W, int conn8_fg, int frame,
+                             int* __restrict__ L) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= H * W) return;
+  int gy = idx / W, gx = idx - gy * W;
+  uint8_t v = mask[idx];
+  bool left_edge = (gx % CC_TW) == 0, top_edge = (gy % CC_TH) == 0, right_edge = (gx % CC_TW) == CC_TW - 1;
+  if (left_edge && gx > 0 && mask[idx - 1] == v) uf_union(L, idx, idx - 1);
+  if (top_edge && gy > 0 && mask[idx - W] == v) uf_union(L, idx, idx - W);
+  if (conn8_fg && v == 1 && gy > 0) {
+    if ((top_edge || left_edge) && gx > 0 && mask[idx - W - 1] == 1) uf_union(L, idx, idx - W - 1);
+    if ((top_edge || right_edge) && gx < W - 1 && mask[idx - W + 1] == 1) uf_union(L, idx, idx - W + 1);
+  }
+  if (frame && v == 0 && (gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1)) uf_union(L, idx, H * W);
+}
+
+__global__ void k_set_int(int* p, int v) { *p = v; }
+
+__global__ void k_ccl_flatten(int n, int* __restrict__ L) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  L[idx] = uf_find(L, idx);
+}
+
+// area[root] += 1 for pixels of class `cls`; warp-aggregated so that big components cost
+// one atomic per warp instead of 32.
+__global__ void k_ccl_area(const uint8_t* __restrict__ mask, const int* __restrict__ L, int n, int cls,
+                           int* __restrict__ area) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  bool act = idx < n && mask[idx] == cls;
+  int root = act ? L[idx] : -1 - (int)(threadIdx.x & 31);
+  unsigned peers = __match_any_sync(0xffffffffu, root);
+  if (act && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&area[root], __popc(peers));
+}
+
+// cls==1: remove foreground components with area < thr; cls==0: fill background components with area < thr
+__global__ void k_ccl_apply(uint8_t* __restrict__ mask, const int* __restrict__ L, const int* __restrict__ area,
+                            int n, int cls, int thr) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  if (mask[idx] == cls && area[L[idx]] < thr) mask[idx] = 1 - cls;
+}
+
+// outermost: a foreground component is outermost iff one of its pixels is on the image border or
+// 4-adjacent to the background component tied to the frame node.
+__global__ void k_outer_flag(const uint8_t* __restrict__ mask, const int* __restrict__ L, int H, int W,
+                             int* __restrict__ flag) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= H * W || mask[idx] != 1) return;
+  int gy = idx / W, gx = idx - gy * W;
+  const int fr = L[H * W];
+  bool o = gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1;
+  if (!o) {
+    o = (mask[idx - 1] == 0 && L[idx - 1] == fr) || (mask[idx + 1] == 0 && L[idx + 1] == fr) ||
+        (mask[idx - W] == 0 && L[idx - W] == fr) || (mask[idx + W] == 0 && L[idx + W] == fr);
+  }
+  if (o) flag[L[idx]] = 1;
+}
+__global__ void k_outer_apply(const uint8_t* __restrict__ mask, const int* __restrict__ L,
+                              const int* __restrict__ flag, int n, uint8_t* __restrict__ outer) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  outer[idx] = (mask[idx] == 1 && flag[L[idx]]) ? 1 : 0;
+}
+
+// ----------------------------------------------------------------------------
+// K2: patch-grid filter + order-preserving compaction
+// ----------------------------------------------------------------------------
+struct GridArgs {
+  const uint8_t* outer;
+  int Ht, Wt;
+  long long W, H;
+  int half, step, ni, nj;
+};
+
+__device__ __forceinline__ int outer_at(const GridArgs& g, long long i, long long j) {
+  return (i >= 0 && i < g.Ht && j >= 0 && j < g.Wt) ? g.outer[i * g.Wt + j] : 0;
+}
+
+// exact integer point-in-region test (oracle/patchgrid.py::raster_rule)
+__device__ __forceinline__ bool grid_inside(const GridArgs& g, int cand) {
+  const int ci = cand / g.nj, cj = cand - ci * g.nj;
+  const long long cx = g.half + (long long)ci * g.step;
+  const long long cy = g.half + (long long)cj * g.step;
+  const long long nu = cx * g.Wt, nv = cy * g.Ht;
+  const long long j = nu / g.W, i = nv / g.H;
+  const long long ru = nu - j * g.W, rv = nv - i * g.H;
+  const int a = outer_at(g, i, j), b = outer_at(g, i, j + 1), c = outer_at(g, i + 1, j),
+            d = outer_at(g, i + 1, j + 1);
+  if (ru > 0 && rv > 0) {
+    const int cnt = a + b + c + d;
+    if (cnt == 4) return true;
+    if (cnt != 3) return false;
+    const long long lu = ru * g.H, lv = rv * g.W, wh = g.W * g.H;
+    if (!a) return lu + lv > wh;
+    if (!b) return lv > lu;
+    if (!c) return lu > lv;
+    return lu + lv < wh;
+  }
+  if (ru == 0 && rv > 0)
+    return a && c && (b || d) && (outer_at(g, i, j - 1) || outer_at(g, i + 1, j - 1));
+  if (ru > 0 && rv == 0)
+    return a && b && (c || d) && (outer_at(g, i - 1, j) || outer_at(g, i - 1, j + 1));
+  return a && b && c && outer_at(g, i - 1, j) && outer_at(g, i, j - 1);
+}
+
+constexpr int GRID_THREADS = 256;
+
+__global__ void __launch_bounds__(GRID_THREADS) k_grid_count(GridArgs g, int ncand, int* __restrict__ blk) {
+  __shared__ int s_w[GRID_THREADS / 32];
+  int cand = blockIdx.x * GRID_THREADS + threadIdx.x;
+  bool in = cand < ncand && grid_inside(g, cand);
+  unsigned bal = __ballot_sync(0xffffffffu, in);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = __popc(bal);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+    for (int w = 0; w < GRID_THREADS / 32; ++w) s += s_w[w];
+    blk[blockIdx.x] = s;
+  }
+}
+
+// single-block exclusive scan over the per-block counts; total -> *count
+__global__ void __launch_bounds__(1024) k_grid_scan(int* __restrict__ blk, int nblk, int* __restrict__ count) {
+  __shared__ int s_part[1024];
+  const int per = (nblk + 1023) / 1024;
+  const int b0 = threadIdx.x * per, b1 = min(b0 + per, nblk);
+  int s = 0;
+  for (int i = b0; i < b1; ++i) s += blk[i];
+  s_part[threadIdx.x] = s;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {   // Hillis-Steele inclusive scan
+    int v = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0;
+    __syncthreads();
+    s_part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = s_part[threadIdx.x] - s;
+  for (int i = b0; i < b1; ++i) {
+    int c = blk[i];
+    blk[i] = run;
+    run += c;
+  }
+  if (threadIdx.x == 1023) *count = s_part[1023];
+}
+
+__global__ void __launch_bounds__(GRID_THREADS)
+    k_grid_write(GridArgs g, int ncand, const int* __restrict__ blk, int capacity, int32_t* __restrict__ coords) {
+  __shared__ int s_w[GRID_THREADS / 32];
+  int cand = blockIdx.x * GRID_THREADS + threadIdx.x;
+  bool in = cand < ncand && grid_inside(g, cand);
+  unsigned bal = __ballot_sync(0xffffffffu, in);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) s_w[warp] = __popc(bal);
+  __syncthreads();
+  int base = blk[blockIdx.x];
+  for (int w = 0; w < warp; ++w) base += s_w[w];
+  if (in) {
+    int pos = base + __popc(bal & ((1u << lane) - 1u));
+    if (pos < capacity) {
+      const int ci = cand / g.nj, cj = cand - ci * g.nj;
+      coords[2 * pos + 0] = ci * g.step;   // (half + ci*step) - half
+      coords[2 * pos + 1] = cj * g.step;
+    }
+  }
+}
+
+bool g_sdiv_ready = false;
+
+int upload_sdiv() {
+  if (g_sdiv_ready) return WSI_OK;
+  int h[256];
+  h[0] = 0;
+  for (int i = 1; i < 256; ++i) {
+    double v = (double)(255 << 12) / (double)i;
+    h[i] = (int)__builtin_rint(v);
+  }
+  WSI_CUDA_CHECK(cudaMemcpyToSymbol(c_sdiv, h, sizeof(h)));
+  g_sdiv_ready = true;
+  return WSI_OK;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" {
+
+size_t wsi_seg_workspace_bytes(int H, int W) {
+  size_t n = (size_t)H * W;
+  // tmp mask + labels (n+1) + area/flag (n+1)
+  return align_up(n, 256) + 2 * align_up((n + 1) * sizeof(int), 256) + 256;
+}
+
+int wsi_seg_tissue_u8(const uint8_t* d_rgb, int H, int W, int pitch_bytes, int median_filter_size,
+                      int binary_threshold, int closing_kernel_size, int min_object_size_px,
+                      int min_hole_size_px, uint8_t* d_mask, uint8_t* d_outer, void* d_ws, size_t ws_bytes,
+                      void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_rgb && d_mask && d_ws, "wsi_seg_tissue_u8: null pointer");
+  WSI_ARG_CHECK(H > 0 && W > 0 && pitch_bytes >= 3 * W, "wsi_seg_tissue_u8: bad geometry %dx%d pitch %d", H, W,
+                pitch_bytes);
+  WSI_ARG_CHECK((long long)H * W < (1ll << 30), "wsi_seg_tissue_u8: thumbnail too large");
+  // same message as the reference's ValueError (segment.py:68-72)
+  WSI_ARG_CHECK(median_filter_size > 1 && (median_filter_size % 2) == 1,
+                "median_filter_size must be greater than 1 and odd, but got %d", median_filter_size);
+  WSI_ARG_CHECK(median_filter_size <= 31, "median_filter_size > 31 unsupported");
+  WSI_ARG_CHECK(closing_kernel_size >= 1 && closing_kernel_size <= 32, "closing_kernel_size out of range");
+  WSI_ARG_CHECK(ws_bytes >= wsi_seg_workspace_bytes(H, W), "wsi_seg_tissue_u8: workspace too small");
+  int rc = upload_sdiv();
+  if (rc) return rc;
+
+  const int n = H * W;
+  uint8_t* tmp = (uint8_t*)d_ws;
+  int* L = (int*)((uint8_t*)d_ws + align_up((size_t)n, 256));
+  int* aux = (int*)((uint8_t*)L + align_up(((size_t)n + 1) * sizeof(int), 256));
+
+  dim3 tgrid(wsi_cdiv(W, K1_TW), wsi_cdiv(H, K1_TH));
+  {
+    int r = median_filter_size / 2;
+    size_t smem = (size_t)(K1_TW + 2 * r) * (K1_TH + 2 * r);
+    if (smem > 48 * 1024)
+      WSI_CUDA_CHECK(cudaFuncSetAttribute(k_sat_median_thresh, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)smem));
+    k_sat_median_thresh<<<tgrid, K1_TW * K1_TH / 4, smem, stream>>>(d_rgb, H, W, pitch_bytes, median_filter_size,
+                                                                    binary_threshold, tmp);
+  }
+  {
+    int k = closing_kernel_size, halo = k - 1;
+    size_t smem = (size_t)(K1_TW + 2 * halo) * (K1_TH + 2 * halo) + (size_t)(K1_TW + halo) * (K1_TH + halo);
+    if (smem > 48 * 1024)
+      WSI_CUDA_CHECK(cudaFuncSetAttribute(k_closing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_closing<<<tgrid, 256, smem, stream>>>(tmp, H, W, k, d_mask);
+  }
+  dim3 cgrid(wsi_cdiv(W, CC_TW), wsi_cdiv(H, CC_TH));
+  const int nb = wsi_cdiv(n, 256), nb1 = wsi_cdiv(n + 1, 256);
+  // remove_small_objects (4-conn foreground, area < min) then remove_small_holes (4-conn background)
+  for (int pass = 0; pass < 2; ++pass) {
+    const int cls = pass == 0 ? 1 : 0;
+    const int thr = pass == 0 ? min_object_size_px : min_hole_size_px;
+    if (thr <= 0) continue;
+    k_ccl_local<<<cgrid, CC_TW * CC_TH, 0, stream>>>(d_mask, H, W, 0, L);
+    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, H, W, 0, 0, L);
+    k_ccl_flatten<<<nb, 256, 0, stream>>>(n, L);
+    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, ((size_t)n + 1) * sizeof(int), stream));
+    k_ccl_area<<<nb, 256, 0, stream>>>(d_mask, L, n, cls, aux);
+    k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, L, aux, n, cls, thr);
+  }
+  if (d_outer) {
+    k_ccl_local<<<cgrid, CC_TW * CC_TH, 0, stream>>>(d_mask, H, W, 1, L);
+    k_set_int<<<1, 1, 0, stream>>>(L + n, n);   // frame node: label[n] = n
+    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, H, W, 1, 1, L);
+    k_ccl_flatten<<<nb1, 256, 0, stream>>>(n + 1, L);
+    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, ((size_t)n + 1) * sizeof(int), stream));
+    k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, L, H, W, aux);
+    k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, L, aux, n, d_outer);
+  }
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
+size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int half, int step) {
+  if (step <= 0) return 0;
+  long long ni = slide_w > half ? (slide_w - half + step - 1) / step : 0;
+  long long nj = slide_h > half ? (slide_h - half + step - 1) / step : 0;
+  long long nblk = (ni * nj + GRID_THREADS - 1) / GRID_THREADS;
+  return (size_t)(nblk + 1) * sizeof(int) + 256;
+}
+
+int wsi_patch_grid(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, long long slide_h, int half,
+                   int step, int32_t* d_coords_xy, int capacity, int* d_count, int* h_tile_dim, void* d_ws,
+                   size_t ws_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_outer && d_coords_xy && d_count && d_ws, "wsi_patch_grid: null pointer");
+  WSI_ARG_CHECK(Ht > 0 && Wt > 0 && slide_w > 0 && slide_h > 0, "wsi_patch_grid: bad geometry");
+  WSI_ARG_CHECK(step > 0, "wsi_patch_grid: step must be positive (overlap must be in (-inf, 1))");
+  WSI_ARG_CHECK(half >= 0, "wsi_patch_grid: negative half patch size");
+  // exactness bound for the int64 cross products: W*H, ru*H, rv*W < 2^62
+  WSI_ARG_CHECK(slide_w < (1ll << 30) && slide_h < (1ll << 30), "wsi_patch_grid: slide too large");
+  long long ni = slide_w > half ? (slide_w - half + step - 1) / step : 0;   // len(range(half, W, step))
+  long long nj = slide_h > half ? (slide_h - half + step - 1) / step : 0;
+  WSI_ARG_CHECK(ni * nj < (1ll << 31) - GRID_THREADS, "wsi_patch_grid: too many candidates");
+  if (h_tile_dim) {
+    h_tile_dim[0] = (int)ni;
+    h_tile_dim[1] = (int)nj;
+  }
+  const int ncand = (int)(ni * nj);
+  if (ncand == 0) {
+    WSI_CUDA_CHECK(cudaMemsetAsync(d_count, 0, sizeof(int), stream));
+    return WSI_OK;
+  }
+  const int nblk = wsi_cdiv(ncand, GRID_THREADS);
+  WSI_ARG_CHECK(ws_bytes >= (size_t)(nblk + 1) * sizeof(int), "wsi_patch_grid: workspace too small");
+  GridArgs g{d_outer, Ht, Wt, slide_w, slide_h, half, step, (int)ni, (int)nj};
+  int* blk = (int*)d_ws;
+  k_grid_count<<<nblk, GRID_THREADS, 0, stream>>>(g, ncand, blk);
+  k_grid_scan<<<1, 1024, 0, stream>>>(blk, nblk, d_count);
+  k_grid_write<<<nblk, GRID_THREADS, 0, stream>>>(g, ncand, blk, capacity, d_coords_xy);
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
+}  // extern "C"
