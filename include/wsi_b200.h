@@ -1,0 +1,147 @@
+/* wsi_b200.h -- C ABI of libwsi_b200.so: the sm_100a kernels behind the WSInsight
+ * patch-classification hot path (tissue segmentation + patchify -> crop/resize/normalize ->
+ * CNN forward -> per-patch probabilities).
+ *
+ * The reference (huangch/wsinsight) is pure Python and has no FFI of its own; each entry
+ * point below names the reference call site (file:line under /root/reference) whose
+ * arithmetic it replaces.  The Python host layer (wsinsight_b200/patchlib, modellib) binds
+ * these with ctypes and mirrors the reference's Python signatures; INTEGRATION.md shows the
+ * stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every `d_` pointer is DEVICE memory, every `h_`
+ *     pointer is host memory; `stream` is a cudaStream_t passed as void*.
+ *   - return 0 on success, a negative WSI_ERR_* code otherwise; the message is
+ *     retrievable with wsi_last_error() (thread-local).  Nothing throws.
+ *   - work is enqueued on `stream` and NOT synchronised unless stated.
+ *   - there is no CPU fallback anywhere in this library.
+ */
+#ifndef WSI_B200_H_
+#define WSI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WSI_OK 0
+#define WSI_ERR_CUDA (-1)
+#define WSI_ERR_ARG (-2)
+#define WSI_ERR_UNSUPPORTED (-3)
+#define WSI_ERR_NOMEM (-4)
+
+/* ---- library ------------------------------------------------------------------------- */
+const char* wsi_last_error(void);
+/* "wsi_b200 <version> sm_100a" */
+const char* wsi_version(void);
+/* number of kernels this library has launched in this process (all streams) */
+long long wsi_launch_count(void);
+
+/* ---- K1: tissue segmentation --------------------------------------------------------- */
+/* Replaces segment_tissue(), wsinsight/patchlib/segment.py:13-97:
+ *   cv.cvtColor(RGB2HSV)[...,1] (:54,65) -> cv.medianBlur(k) (:77) -> cv.threshold (:80-83)
+ *   -> skimage binary_closing(ones(c,c)) (:87-89) -> remove_small_objects (:92)
+ *   -> remove_small_holes (:95).
+ * d_rgb: H x W x 3 u8, row pitch `pitch_bytes`.  d_mask: H x W u8 (0/1), the function's result.
+ * d_outer (optional, may be NULL): H x W u8, mask restricted to the OUTERMOST 8-connected
+ * components (what get_multipolygon_from_binary_arr, patchlib/patch.py:35-130, keeps after its
+ * sequential union/difference of cv.findContours(RETR_CCOMP) contours); input of wsi_patch_grid.
+ * Errors: median_filter_size <= 1 or even -> WSI_ERR_ARG with the reference's ValueError text
+ * (segment.py:68-72). */
+size_t wsi_seg_workspace_bytes(int H, int W);
+int wsi_seg_tissue_u8(const uint8_t* d_rgb, int H, int W, int pitch_bytes, int median_filter_size,
+                      int binary_threshold, int closing_kernel_size, int min_object_size_px,
+                      int min_hole_size_px, uint8_t* d_mask, uint8_t* d_outer, void* d_ws,
+                      size_t ws_bytes, void* stream);
+
+/* Batched form for a cohort of thumbnails (BASELINE config 4): slide s has geometry
+ * (h_H[s], h_W[s], h_pitch[s]) and lives at d_rgb + h_rgb_off[s]; mask/outer at
+ * d_mask + h_mask_off[s].  Thresholds are per slide (they depend on the thumbnail mpp,
+ * wsinsight/patchlib/pipeline.py:107-112).  Every stage is ONE launch over all slides. */
+size_t wsi_seg_batch_workspace_bytes(int n, const int* h_H, const int* h_W);
+int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W,
+                            const int* h_pitch, const long long* h_rgb_off,
+                            const long long* h_mask_off, int median_filter_size,
+                            int binary_threshold, int closing_kernel_size,
+                            const int* h_min_object_px, const int* h_min_hole_px, uint8_t* d_mask,
+                            uint8_t* d_outer, void* d_ws, size_t ws_bytes, void* stream);
+
+/* ---- K2: in-tissue patch grid --------------------------------------------------------- */
+/* Replaces get_patch_coordinates_within_polygon(), wsinsight/patchlib/patch.py:174-242
+ * (itertools grid :218-225, STRtree.query(contains) :227-233, ordering :236, -half :240) and the
+ * polygon it is given (patch.py:57-130).  Candidates are centroids (half + i*step, half + j*step)
+ * with half + i*step < slide_w, half + j*step < slide_h; kept candidates are written as top-left
+ * (x, y) int32 pairs in the reference's order (x-major, y fastest).  *d_count receives the number
+ * kept (may exceed `capacity`; only `capacity` pairs are written).  h_tile_dim[2] (optional)
+ * receives (n_i, n_j) == tile_dim of wsinsight/patchlib/pipeline.py:370-382. */
+size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int half, int step);
+int wsi_patch_grid(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, long long slide_h,
+                   int half, int step, int32_t* d_coords_xy, int capacity, int* d_count,
+                   int* h_tile_dim, void* d_ws, size_t ws_bytes, void* stream);
+
+/* ---- K3: fused patch data path --------------------------------------------------------- */
+/* Replaces WholeSlideImagePatches._get_patch_from_wsi (wsinsight/modellib/data.py:270-281:
+ * read_region -> RGBA, zero padded out of bounds -> convert("RGB")), the torchvision Compose of
+ * wsinsight/modellib/transforms.py:22-38 (Resize = PIL antialiased bilinear, ToTensor, Normalize)
+ * and the default collate + H2D copy of wsinsight/modellib/run_inference.py:288-299,543.
+ * The slide is a device-resident RGBA u8 image (16-byte aligned base and pitch).  Output:
+ * bf16 [n][out_H][out_W][4] (channel 3 = 0) with the S x S patch at (pad_top, pad_left); border
+ * elements are never written (zero the buffer once).  mean/stdv may both be NULL (no Normalize). */
+int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long long slide_h,
+                            long long pitch_bytes, int patch_size, int out_size,
+                            const float* mean, const float* stdv, int out_H, int out_W,
+                            int pad_top, int pad_left, void** plan_out);
+int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_bf16, void* stream);
+/* debug/parity: the u8 result of the resize alone, [n][S][S][4] (RGB0) */
+int wsi_preproc_run_u8(void* plan, const int32_t* d_coords_xy, int n, uint8_t* d_out_u8,
+                       void* stream);
+int wsi_preproc_plan_info(void* plan, int* info8);
+void wsi_preproc_plan_destroy(void* plan);
+
+/* ---- K4: CNN forward ------------------------------------------------------------------- */
+/* Replaces `model(batch_imgs.to(device))` + CPU softmax/sigmoid of the classification loop,
+ * wsinsight/modellib/run_inference.py:537-560, for zoo CNNs whose TorchScript graph
+ * (wsinsight/modellib/models.py:51-108) has been lowered by the host to a list of
+ * conv(+bias,+residual,+ReLU) / pool / head ops over NHWC bf16 tensors.  Convolutions are
+ * tcgen05/TMEM implicit GEMMs fed by TMA; weights are given as host fp32 OIHW with BatchNorm
+ * already folded (what torch.jit.freeze leaves, scripts/convert_to_torchscript.py:38-50). */
+int wsi_net_create(int max_batch, void** net_out);
+int wsi_net_add_tensor(void* net, int H, int W, int C, int external, int* id_out);
+int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const float* h_w_oihw,
+                     const float* h_bias, int Cin, int Cout, int KH, int KW, int stride, int pad_h,
+                     int pad_w, int relu, int residual_id);
+int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* h_w_oihw,
+                        const float* h_bias, int Cout, int relu);
+int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max, int k, int stride,
+                     int pad, int count_include_pad);
+int wsi_net_add_head(void* net, int in_id, const float* h_fc_w, const float* h_fc_b, int K);
+int wsi_net_finalize(void* net);
+/* d_input: the external input tensor (bf16 NHWC, layout of wsi_preproc_run); d_probs: f32 [B][K]
+ * (softmax over K when K > 1, sigmoid when K == 1, run_inference.py:548-551). */
+int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void* stream);
+int wsi_net_encode_input_map(void* net, int op_index, const void* d_base);
+int wsi_net_tensor_ptr(void* net, int id, void** d_ptr, int* h_hwc3);
+int wsi_net_num_launches(void* net);
+double wsi_net_flops_per_image(void* net);
+void wsi_net_destroy(void* net);
+
+/* ---- utilities -------------------------------------------------------------------------- */
+/* Synthetic device-resident slide (bench/test input generator): fills an RGBA u8
+ * image from a counter-based hash: smooth value-noise "tissue" field, H&E-like colours on a
+ * near-white background, per-pixel noise.  The same function evaluated on the host is
+ * wsi_synth_slide_host (used to regenerate sampled patches for the CPU baseline). */
+int wsi_synth_slide(uint8_t* d_rgba, long long W, long long H, long long pitch_bytes,
+                    unsigned seed, void* stream);
+int wsi_synth_slide_host(uint8_t* h_rgba, long long x0, long long y0, int w, int h,
+                         long long W, long long H, unsigned seed);
+/* Box-average thumbnail of an RGBA slide -> RGB u8 Ht x Wt (bench input for K1; PIL-LANCZOS
+ * thumbnail parity is a "next" row). */
+int wsi_box_thumbnail(const uint8_t* d_rgba, long long W, long long H, long long pitch_bytes,
+                      uint8_t* d_rgb, int Ht, int Wt, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WSI_B200_H_ */

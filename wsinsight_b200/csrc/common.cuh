@@ -11,13 +11,17 @@
 // error reporting: every extern "C" entry returns 0 or a negative code and
 // leaves a message retrievable with wsi_last_error(); nothing throws.
 // ---------------------------------------------------------------------------
+#ifndef WSI_OK
 #define WSI_OK 0
 #define WSI_ERR_CUDA (-1)
 #define WSI_ERR_ARG (-2)
 #define WSI_ERR_UNSUPPORTED (-3)
 #define WSI_ERR_NOMEM (-4)
+#endif
 
 void wsi_set_error(const char* fmt, ...);
+// bump the library-wide launch counter (wsi_launch_count()) by n kernels
+void wsi_count_launch(int n);
 
 #define WSI_CUDA_CHECK(expr)                                                         \
   do {                                                                               \

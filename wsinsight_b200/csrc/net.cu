@@ -489,6 +489,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
                                                                 d_probs);
     }
   }
+  wsi_count_launch((int)n->ops.size());
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
 }

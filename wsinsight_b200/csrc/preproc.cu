@@ -86,6 +86,7 @@ struct PPArgs {
   const int* coef;
   const int32_t* coords;   // (n,2) top-left x,y
   __nv_bfloat16* out;
+  uint32_t* out_u8;        // debug/parity: resized RGB0 u8 [n][S][S] (out is ignored when set)
   int ps, S, ksize, TR, G, ngroups, box_w, box_h, max_src_rows;
   int out_H, out_W, pad_top, pad_left;
   float m0, m1, m2, s0, s1, s2;
@@ -166,6 +167,10 @@ __global__ void __launch_bounds__(PP_THREADS)
       s0 += (int)(p & 0xff) * c;
       s1 += (int)((p >> 8) & 0xff) * c;
       s2 += (int)((p >> 16) & 0xff) * c;
+    }
+    if (a.out_u8) {
+      a.out_u8[((size_t)patch * a.S + yy) * a.S + xx] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
+      continue;
     }
     float f0 = __fdiv_rn((float)clip8(s0), 255.0f);
     float f1 = __fdiv_rn((float)clip8(s1), 255.0f);
@@ -297,12 +302,14 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
   return WSI_OK;
 }
 
-int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_bf16, void* stream_) {
+static int preproc_launch(void* plan, const int32_t* d_coords_xy, int n, void* d_out_bf16, uint8_t* d_out_u8,
+                          void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  WSI_ARG_CHECK(plan && d_coords_xy && d_out_bf16, "wsi_preproc_run: null pointer");
+  WSI_ARG_CHECK(plan && d_coords_xy && (d_out_bf16 || d_out_u8), "wsi_preproc_run: null pointer");
   if (n <= 0) return WSI_OK;
   Plan* p = (Plan*)plan;
   PPArgs a;
+  a.out_u8 = (uint32_t*)d_out_u8;
   a.lo = p->d_lo;
   a.cnt = p->d_cnt;
   a.coef = p->d_coef;
@@ -326,8 +333,19 @@ int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_b
   a.has_norm = p->has_norm;
   dim3 grid(n, p->nbands);
   k_preprocess<<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
+  wsi_count_launch(1);
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
+}
+
+int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_bf16, void* stream_) {
+  WSI_ARG_CHECK(d_out_bf16, "wsi_preproc_run: null output");
+  return preproc_launch(plan, d_coords_xy, n, d_out_bf16, nullptr, stream_);
+}
+
+int wsi_preproc_run_u8(void* plan, const int32_t* d_coords_xy, int n, uint8_t* d_out_u8, void* stream_) {
+  WSI_ARG_CHECK(d_out_u8, "wsi_preproc_run_u8: null output");
+  return preproc_launch(plan, d_coords_xy, n, nullptr, d_out_u8, stream_);
 }
 
 int wsi_preproc_plan_info(void* plan, int* info8) {

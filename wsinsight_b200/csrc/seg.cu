@@ -1,4 +1,4 @@
-// K1: tissue segmentation of a slide thumbnail, K2: in-tissue patch-grid filter.
+// K1: tissue segmentation of slide thumbnails (batched over a cohort), K2: in-tissue patch-grid filter.
 //
 // Replaces (reference, huangch/wsinsight):
 //   wsinsight/patchlib/segment.py:54-97   cv.cvtColor/medianBlur/threshold, skimage
@@ -7,11 +7,42 @@
 //   wsinsight/patchlib/patch.py:210-242   itertools grid + STRtree.query(contains) + sort
 //
 // All arithmetic is integer and bit-exact with the CPU oracle (oracle/segment.py,
-// oracle/patchgrid.py).  HBM/latency-bound byte work: no tensor cores here.
+// oracle/patchgrid.py).  HBM/latency-bound byte work: no tensor cores here.  Every stage is one
+// launch over ALL thumbnails of the cohort (flat tile / pixel index -> slide by binary search over
+// a prefix table), so a 64-slide cohort costs the same number of launches as one slide.
 #include "common.cuh"
 #include "../../include/wsi_b200.h"
+#include <vector>
 
 namespace {
+
+struct SegSlide {
+  int H, W, pitch;
+  int min_obj, min_hole;
+  int tiles_x;            // tiles per row for the 64x16 tiling (K1a/K1b)
+  int ctiles_x;           // tiles per row for the 32x16 tiling (CCL)
+  int pad_;
+  long long rgb_off;      // bytes from d_rgb
+  long long mask_off;     // bytes from d_mask / d_outer / tmp
+  long long lab_off;      // ints from L / aux: slide s owns n_s + 1 entries (last = frame node)
+};
+
+struct SegBatch {
+  const SegSlide* slides;      // device
+  const long long* tile_base;  // [n+1] prefix of 64x16 tiles
+  const long long* ctile_base; // [n+1] prefix of 32x16 tiles
+  const long long* px_base;    // [n+1] prefix of pixels
+  int n;
+};
+
+__device__ __forceinline__ int find_slide(const long long* __restrict__ base, int n, long long idx) {
+  int lo = 0, hi = n - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (base[mid] <= idx) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
 
 // ----------------------------------------------------------------------------
 // K1a: RGB -> HSV saturation (OpenCV 8-bit formula) -> (S > thresh) -> k x k box
@@ -21,30 +52,38 @@ __constant__ int c_sdiv[256];
 
 constexpr int K1_TW = 64;
 constexpr int K1_TH = 16;
+constexpr int K1_THREADS = 256;
 
-__global__ void __launch_bounds__(K1_TW* K1_TH / 4)
-    k_sat_median_thresh(const uint8_t* __restrict__ rgb, int H, int W, int pitch, int k, int thresh,
-                        uint8_t* __restrict__ out) {
+__global__ void __launch_bounds__(K1_THREADS)
+    k_sat_median_thresh(const uint8_t* __restrict__ rgb_all, SegBatch sb, int k, int thresh,
+                        uint8_t* __restrict__ out_all) {
   extern __shared__ uint8_t s_b[];  // (TH+2r) x (TW+2r) thresholded bits
+  const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.tile_base[s]);
+  const int ty = tile / sl.tiles_x, tx = tile - ty * sl.tiles_x;
+  const uint8_t* __restrict__ rgb = rgb_all + sl.rgb_off;
+  uint8_t* __restrict__ out = out_all + sl.mask_off;
+  const int H = sl.H, W = sl.W;
   const int r = k >> 1;
   const int sw = K1_TW + 2 * r, sh = K1_TH + 2 * r;
-  const int x0 = blockIdx.x * K1_TW - r, y0 = blockIdx.y * K1_TH - r;
-  for (int i = threadIdx.x; i < sw * sh; i += blockDim.x) {
+  const int x0 = tx * K1_TW - r, y0 = ty * K1_TH - r;
+  for (int i = threadIdx.x; i < sw * sh; i += K1_THREADS) {
     int ly = i / sw, lx = i - ly * sw;
     int gx = min(max(x0 + lx, 0), W - 1);   // BORDER_REPLICATE
     int gy = min(max(y0 + ly, 0), H - 1);
-    const uint8_t* p = rgb + (size_t)gy * pitch + (size_t)gx * 3;
+    const uint8_t* p = rgb + (size_t)gy * sl.pitch + (size_t)gx * 3;
     int R = p[0], G = p[1], B = p[2];
     int v = max(R, max(G, B));
     int d = v - min(R, min(G, B));
-    int s = (d * c_sdiv[v] + (1 << 11)) >> 12;
-    s_b[i] = (s > thresh) ? 1 : 0;
+    int sat = (d * c_sdiv[v] + (1 << 11)) >> 12;
+    s_b[i] = (sat > thresh) ? 1 : 0;
   }
   __syncthreads();
   const int need = (k * k + 1) >> 1;
-  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += blockDim.x) {
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += K1_THREADS) {
     int ly = i / K1_TW, lx = i - ly * K1_TW;
-    int gx = blockIdx.x * K1_TW + lx, gy = blockIdx.y * K1_TH + ly;
+    int gx = tx * K1_TW + lx, gy = ty * K1_TH + ly;
     if (gx >= W || gy >= H) continue;
     int cnt = 0;
     for (int dy = 0; dy < k; ++dy) {
@@ -59,25 +98,32 @@ __global__ void __launch_bounds__(K1_TW* K1_TH / 4)
 // K1b: closing with ones(k,k):  dilation offsets [-(k-1)/2 .. k/2] (outside = 0)
 // then erosion offsets [-(k/2) .. (k-1)/2] (outside = 1)  (scipy / skimage convention)
 // ----------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-    k_closing(const uint8_t* __restrict__ in, int H, int W, int k, uint8_t* __restrict__ out) {
+__global__ void __launch_bounds__(K1_THREADS)
+    k_closing(const uint8_t* __restrict__ in_all, SegBatch sb, int k, uint8_t* __restrict__ out_all) {
   extern __shared__ uint8_t s_m[];
+  const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.tile_base[s]);
+  const int ty = tile / sl.tiles_x, tx = tile - ty * sl.tiles_x;
+  const uint8_t* __restrict__ in = in_all + sl.mask_off;
+  uint8_t* __restrict__ out = out_all + sl.mask_off;
+  const int H = sl.H, W = sl.W;
   const int dlo = (k - 1) >> 1, elo = k >> 1;
   const int halo = k - 1;
   const int iw = K1_TW + 2 * halo, ih = K1_TH + 2 * halo;      // input tile
   const int dw = K1_TW + halo, dh = K1_TH + halo;              // dilated tile
   uint8_t* s_in = s_m;
   uint8_t* s_d = s_m + iw * ih;
-  const int bx = blockIdx.x * K1_TW, by = blockIdx.y * K1_TH;
+  const int bx = tx * K1_TW, by = ty * K1_TH;
   // input tile origin: (bx - elo - dlo, by - elo - dlo)
-  for (int i = threadIdx.x; i < iw * ih; i += blockDim.x) {
+  for (int i = threadIdx.x; i < iw * ih; i += K1_THREADS) {
     int ly = i / iw, lx = i - ly * iw;
     int gx = bx - elo - dlo + lx, gy = by - elo - dlo + ly;
     s_in[i] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? in[(size_t)gy * W + gx] : 0;
   }
   __syncthreads();
   // dilated tile origin: (bx - elo, by - elo); positions outside the image read as 1 for the erosion
-  for (int i = threadIdx.x; i < dw * dh; i += blockDim.x) {
+  for (int i = threadIdx.x; i < dw * dh; i += K1_THREADS) {
     int ly = i / dw, lx = i - ly * dw;
     int gx = bx - elo + lx, gy = by - elo + ly;
     uint8_t v;
@@ -93,7 +139,7 @@ __global__ void __launch_bounds__(256)
     s_d[i] = v;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += blockDim.x) {
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += K1_THREADS) {
     int ly = i / K1_TW, lx = i - ly * K1_TW;
     int gx = bx + lx, gy = by + ly;
     if (gx >= W || gy >= H) continue;
@@ -111,6 +157,8 @@ __global__ void __launch_bounds__(256)
 // One labelling handles both classes at once: a pixel merges with a neighbour of
 // the same value.  conn8_fg adds the diagonal neighbours for foreground pixels
 // (OpenCV contour convention: 8-connected foreground, 4-connected background).
+// Labels are slide-local pixel indices; the extra node n_s of each slide is the
+// implicit zero frame around the image.
 // ----------------------------------------------------------------------------
 __device__ __forceinline__ int uf_find(const int* L, int x) {
   int p = L[x];
@@ -141,13 +189,20 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b) {
 
 constexpr int CC_TW = 32, CC_TH = 16;   // 512-pixel tiles, 1 thread per pixel
 
-// Phase 1: tile-local union-find in shared memory, then publish global ids of the local roots.
+// Phase 1: tile-local union-find in shared memory, then publish slide-local ids of the local roots.
 __global__ void __launch_bounds__(CC_TW* CC_TH)
-    k_ccl_local(const uint8_t* __restrict__ mask, int H, int W, int conn8_fg, int* __restrict__ L) {
+    k_ccl_local(const uint8_t* __restrict__ mask_all, SegBatch sb, int conn8_fg, int* __restrict__ L_all) {
   __shared__ int s_L[CC_TW * CC_TH];
   __shared__ uint8_t s_v[CC_TW * CC_TH];
+  const int s = find_slide(sb.ctile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.ctile_base[s]);
+  const int ty = tile / sl.ctiles_x, tx = tile - ty * sl.ctiles_x;
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W;
   const int lx = threadIdx.x % CC_TW, ly = threadIdx.x / CC_TW;
-  const int gx = blockIdx.x * CC_TW + lx, gy = blockIdx.y * CC_TH + ly;
+  const int gx = tx * CC_TW + lx, gy = ty * CC_TH + ly;
   const bool in = gx < W && gy < H;
   const int t = threadIdx.x;
   uint8_t v = in ? mask[(size_t)gy * W + gx] : 2;   // 2 = outside, never merges
@@ -166,74 +221,115 @@ __global__ void __launch_bounds__(CC_TW* CC_TH)
   if (in) {
     int rt = uf_find(s_L, t);
     int rx = rt % CC_TW, ry = rt / CC_TW;
-    L[(size_t)gy * W + gx] = (blockIdx.y * CC_TH + ry) * W + blockIdx.x * CC_TW + rx;
+    L[(size_t)gy * W + gx] = (ty * CC_TH + ry) * W + tx * CC_TW + rx;
   }
+  if (blockIdx.x == sb.ctile_base[s] && t == 0) L[H * W] = H * W;   // frame node
 }
 
-// Phase 2: merge across tile borders (and optionally tie border background to the frame node H*W).
-__global__ void k_ccl_border(const uint8_t* __restrict__ mask, int H, int W, int conn8_fg, int frame,
-                             int* __restrict__ L) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= H * W) return;
-  int gy = idx / W, gx = idx - gy * W;
-  uint8_t v = mask[idx];
-  bool left_edge = (gx % CC_TW) == 0, top_edge = (gy % CC_TH) == 0, right_edge = (gx % CC_TW) == CC_TW - 1;
+// Phase 2: merge across tile borders (and optionally tie border background to the frame node).
+__global__ void __launch_bounds__(256)
+    k_ccl_border(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int conn8_fg, int frame,
+                 int* __restrict__ L_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= total) return;
+  const int s = find_slide(sb.px_base, sb.n, g);
+  const SegSlide sl = sb.slides[s];
+  const int idx = (int)(g - sb.px_base[s]);
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W;
+  const int gy = idx / W, gx = idx - gy * W;
+  const bool left_edge = (gx % CC_TW) == 0, top_edge = (gy % CC_TH) == 0, right_edge = (gx % CC_TW) == CC_TW - 1;
+  const bool img_border = gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1;
+  if (!(left_edge || top_edge || right_edge || img_border)) return;
+  const uint8_t v = mask[idx];
   if (left_edge && gx > 0 && mask[idx - 1] == v) uf_union(L, idx, idx - 1);
   if (top_edge && gy > 0 && mask[idx - W] == v) uf_union(L, idx, idx - W);
   if (conn8_fg && v == 1 && gy > 0) {
     if ((top_edge || left_edge) && gx > 0 && mask[idx - W - 1] == 1) uf_union(L, idx, idx - W - 1);
     if ((top_edge || right_edge) && gx < W - 1 && mask[idx - W + 1] == 1) uf_union(L, idx, idx - W + 1);
   }
-  if (frame && v == 0 && (gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1)) uf_union(L, idx, H * W);
+  if (frame && v == 0 && img_border) uf_union(L, idx, H * W);
 }
 
-__global__ void k_set_int(int* p, int v) { *p = v; }
-
-__global__ void k_ccl_flatten(int n, int* __restrict__ L) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
-  L[idx] = uf_find(L, idx);
-}
-
-// area[root] += 1 for pixels of class `cls`; warp-aggregated so that big components cost
-// one atomic per warp instead of 32.
-__global__ void k_ccl_area(const uint8_t* __restrict__ mask, const int* __restrict__ L, int n, int cls,
-                           int* __restrict__ area) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  bool act = idx < n && mask[idx] == cls;
-  int root = act ? L[idx] : -1 - (int)(threadIdx.x & 31);
+// Phase 3: flatten + per-root area of class `cls` pixels (warp-aggregated atomics).
+__global__ void __launch_bounds__(256)
+    k_ccl_flatten_area(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int cls,
+                       int* __restrict__ L_all, int* __restrict__ area_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = g < total;
+  int root = -1 - (int)(threadIdx.x & 31);
+  bool act = false;
+  int* area = nullptr;
+  if (live) {
+    const int s = find_slide(sb.px_base, sb.n, g);
+    const SegSlide sl = sb.slides[s];
+    const int idx = (int)(g - sb.px_base[s]);
+    int* L = L_all + sl.lab_off;
+    const int r = uf_find(L, idx);
+    L[idx] = r;
+    act = (mask_all + sl.mask_off)[idx] == cls;
+    if (act) {
+      // key must be unique across slides inside one warp: use the global label slot
+      root = (int)(sl.lab_off + r);
+      area = area_all;
+    }
+  }
+  if (cls < 0) return;   // flatten only (warp-uniform)
   unsigned peers = __match_any_sync(0xffffffffu, root);
   if (act && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&area[root], __popc(peers));
 }
 
 // cls==1: remove foreground components with area < thr; cls==0: fill background components with area < thr
-__global__ void k_ccl_apply(uint8_t* __restrict__ mask, const int* __restrict__ L, const int* __restrict__ area,
-                            int n, int cls, int thr) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
-  if (mask[idx] == cls && area[L[idx]] < thr) mask[idx] = 1 - cls;
+__global__ void __launch_bounds__(256)
+    k_ccl_apply(uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
+                const int* __restrict__ area_all, int cls) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= total) return;
+  const int s = find_slide(sb.px_base, sb.n, g);
+  const SegSlide sl = sb.slides[s];
+  const int idx = (int)(g - sb.px_base[s]);
+  uint8_t* mask = mask_all + sl.mask_off;
+  const int thr = cls ? sl.min_obj : sl.min_hole;
+  if (thr <= 0) return;
+  // L may not be fully flattened for pixels processed by other blocks of the fused flatten/area pass
+  // when this kernel runs (it is: separate launch), so one lookup suffices.
+  if (mask[idx] == cls && area_all[sl.lab_off + L_all[sl.lab_off + idx]] < thr) mask[idx] = 1 - cls;
 }
 
 // outermost: a foreground component is outermost iff one of its pixels is on the image border or
-// 4-adjacent to the background component tied to the frame node.
-__global__ void k_outer_flag(const uint8_t* __restrict__ mask, const int* __restrict__ L, int H, int W,
-                             int* __restrict__ flag) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= H * W || mask[idx] != 1) return;
-  int gy = idx / W, gx = idx - gy * W;
-  const int fr = L[H * W];
+// 4-adjacent to the background component tied to the frame node.  (L flattened, incl. frame node.)
+__global__ void __launch_bounds__(256)
+    k_outer_flag(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
+                 int* __restrict__ flag_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= total) return;
+  const int s = find_slide(sb.px_base, sb.n, g);
+  const SegSlide sl = sb.slides[s];
+  const int idx = (int)(g - sb.px_base[s]);
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  if (mask[idx] != 1) return;
+  const int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W;
+  const int gy = idx / W, gx = idx - gy * W;
   bool o = gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1;
   if (!o) {
+    const int fr = uf_find(L, H * W);
     o = (mask[idx - 1] == 0 && L[idx - 1] == fr) || (mask[idx + 1] == 0 && L[idx + 1] == fr) ||
         (mask[idx - W] == 0 && L[idx - W] == fr) || (mask[idx + W] == 0 && L[idx + W] == fr);
   }
-  if (o) flag[L[idx]] = 1;
+  if (o) flag_all[sl.lab_off + L[idx]] = 1;
 }
-__global__ void k_outer_apply(const uint8_t* __restrict__ mask, const int* __restrict__ L,
-                              const int* __restrict__ flag, int n, uint8_t* __restrict__ outer) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
-  outer[idx] = (mask[idx] == 1 && flag[L[idx]]) ? 1 : 0;
+__global__ void __launch_bounds__(256)
+    k_outer_apply(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
+                  const int* __restrict__ flag_all, uint8_t* __restrict__ outer_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= total) return;
+  const int s = find_slide(sb.px_base, sb.n, g);
+  const SegSlide sl = sb.slides[s];
+  const int idx = (int)(g - sb.px_base[s]);
+  const uint8_t m = (mask_all + sl.mask_off)[idx];
+  (outer_all + sl.mask_off)[idx] = (m == 1 && flag_all[sl.lab_off + L_all[sl.lab_off + idx]]) ? 1 : 0;
 }
 
 // ----------------------------------------------------------------------------
@@ -297,7 +393,7 @@ __global__ void __launch_bounds__(GRID_THREADS) k_grid_count(GridArgs g, int nca
 __global__ void __launch_bounds__(1024) k_grid_scan(int* __restrict__ blk, int nblk, int* __restrict__ count) {
   __shared__ int s_part[1024];
   const int per = (nblk + 1023) / 1024;
-  const int b0 = threadIdx.x * per, b1 = min(b0 + per, nblk);
+  const int b0 = min(threadIdx.x * per, nblk), b1 = min(b0 + per, nblk);
   int s = 0;
   for (int i = b0; i < b1; ++i) s += blk[i];
   s_part[threadIdx.x] = s;
@@ -332,8 +428,10 @@ __global__ void __launch_bounds__(GRID_THREADS)
     int pos = base + __popc(bal & ((1u << lane) - 1u));
     if (pos < capacity) {
       const int ci = cand / g.nj, cj = cand - ci * g.nj;
-      coords[2 * pos + 0] = ci * g.step;   // (half + ci*step) - half
-      coords[2 * pos + 1] = cj * g.step;
+      int2 xy;
+      xy.x = ci * g.step;   // (half + ci*step) - half
+      xy.y = cj * g.step;
+      reinterpret_cast<int2*>(coords)[pos] = xy;
     }
   }
 }
@@ -355,81 +453,166 @@ int upload_sdiv() {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+struct BatchLayout {
+  size_t off_desc, off_tile, off_ctile, off_px, off_tmp, off_L, off_aux, total;
+  long long npx, ntiles, nctiles;
+};
+
+BatchLayout batch_layout(int n, const int* H, const int* W) {
+  BatchLayout b;
+  b.npx = 0;
+  b.ntiles = 0;
+  b.nctiles = 0;
+  for (int s = 0; s < n; ++s) {
+    b.npx += (long long)H[s] * W[s];
+    b.ntiles += (long long)wsi_cdiv(W[s], K1_TW) * wsi_cdiv(H[s], K1_TH);
+    b.nctiles += (long long)wsi_cdiv(W[s], CC_TW) * wsi_cdiv(H[s], CC_TH);
+  }
+  size_t o = 0;
+  b.off_desc = o;  o += align_up(sizeof(SegSlide) * n, 256);
+  b.off_tile = o;  o += align_up(sizeof(long long) * (n + 1), 256);
+  b.off_ctile = o; o += align_up(sizeof(long long) * (n + 1), 256);
+  b.off_px = o;    o += align_up(sizeof(long long) * (n + 1), 256);
+  b.off_tmp = o;   o += align_up((size_t)b.npx, 256);
+  b.off_L = o;     o += align_up(((size_t)b.npx + n) * sizeof(int), 256);
+  b.off_aux = o;   o += align_up(((size_t)b.npx + n) * sizeof(int), 256);
+  b.total = o;
+  return b;
+}
+
 }  // namespace
 
 extern "C" {
 
-size_t wsi_seg_workspace_bytes(int H, int W) {
-  size_t n = (size_t)H * W;
-  // tmp mask + labels (n+1) + area/flag (n+1)
-  return align_up(n, 256) + 2 * align_up((n + 1) * sizeof(int), 256) + 256;
+size_t wsi_seg_batch_workspace_bytes(int n, const int* h_H, const int* h_W) {
+  if (n <= 0 || !h_H || !h_W) return 0;
+  return batch_layout(n, h_H, h_W).total;
+}
+
+size_t wsi_seg_workspace_bytes(int H, int W) { return wsi_seg_batch_workspace_bytes(1, &H, &W); }
+
+int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W, const int* h_pitch,
+                            const long long* h_rgb_off, const long long* h_mask_off, int median_filter_size,
+                            int binary_threshold, int closing_kernel_size, const int* h_min_object_px,
+                            const int* h_min_hole_px, uint8_t* d_mask, uint8_t* d_outer, void* d_ws, size_t ws_bytes,
+                            void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_rgb && d_mask && d_ws && h_H && h_W && h_pitch && h_rgb_off && h_mask_off && h_min_object_px &&
+                    h_min_hole_px,
+                "wsi_seg_tissue: null pointer");
+  WSI_ARG_CHECK(n > 0, "wsi_seg_tissue: empty batch");
+  // same message as the reference's ValueError (segment.py:68-72)
+  WSI_ARG_CHECK(median_filter_size > 1 && (median_filter_size % 2) == 1,
+                "median_filter_size must be greater than 1 and odd, but got %d", median_filter_size);
+  WSI_ARG_CHECK(median_filter_size <= 31, "median_filter_size > 31 unsupported");
+  WSI_ARG_CHECK(closing_kernel_size >= 1 && closing_kernel_size <= 32, "closing_kernel_size out of range");
+  for (int s = 0; s < n; ++s) {
+    WSI_ARG_CHECK(h_H[s] > 0 && h_W[s] > 0 && h_pitch[s] >= 3 * h_W[s], "wsi_seg_tissue: bad geometry %dx%d pitch %d",
+                  h_H[s], h_W[s], h_pitch[s]);
+    WSI_ARG_CHECK((long long)h_H[s] * h_W[s] < (1ll << 30), "wsi_seg_tissue: thumbnail too large");
+  }
+  const BatchLayout bl = batch_layout(n, h_H, h_W);
+  WSI_ARG_CHECK(ws_bytes >= bl.total, "wsi_seg_tissue: workspace too small (%zu < %zu)", ws_bytes, bl.total);
+  WSI_ARG_CHECK(bl.npx + n < (1ll << 31), "wsi_seg_tissue: cohort too large for one call");
+  int rc = upload_sdiv();
+  if (rc) return rc;
+
+  // descriptor tables (host staging -> workspace head)
+  std::vector<SegSlide> hs(n);
+  std::vector<long long> tb(n + 1), cb(n + 1), pb(n + 1);
+  tb[0] = cb[0] = pb[0] = 0;
+  for (int s = 0; s < n; ++s) {
+    SegSlide& d = hs[s];
+    d.H = h_H[s]; d.W = h_W[s]; d.pitch = h_pitch[s];
+    d.min_obj = h_min_object_px[s]; d.min_hole = h_min_hole_px[s];
+    d.tiles_x = wsi_cdiv(d.W, K1_TW);
+    d.ctiles_x = wsi_cdiv(d.W, CC_TW);
+    d.pad_ = 0;
+    d.rgb_off = h_rgb_off[s];
+    d.mask_off = h_mask_off[s];
+    d.lab_off = pb[s] + s;
+    tb[s + 1] = tb[s] + (long long)d.tiles_x * wsi_cdiv(d.H, K1_TH);
+    cb[s + 1] = cb[s] + (long long)d.ctiles_x * wsi_cdiv(d.H, CC_TH);
+    pb[s + 1] = pb[s] + (long long)d.H * d.W;
+  }
+  uint8_t* ws = (uint8_t*)d_ws;
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_desc, hs.data(), sizeof(SegSlide) * n, cudaMemcpyHostToDevice, stream));
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_tile, tb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
+                                 stream));
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_ctile, cb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
+                                 stream));
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_px, pb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
+                                 stream));
+  SegBatch sb;
+  sb.slides = (const SegSlide*)(ws + bl.off_desc);
+  sb.tile_base = (const long long*)(ws + bl.off_tile);
+  sb.ctile_base = (const long long*)(ws + bl.off_ctile);
+  sb.px_base = (const long long*)(ws + bl.off_px);
+  sb.n = n;
+  // tmp shares the mask offsets: it must be addressable with mask_off, so it is only usable when the
+  // caller's mask layout fits the npx-byte scratch; otherwise the median output goes through d_outer.
+  long long max_mask_end = 0;
+  for (int s = 0; s < n; ++s) {
+    long long e = h_mask_off[s] + (long long)h_H[s] * h_W[s];
+    if (e > max_mask_end) max_mask_end = e;
+    WSI_ARG_CHECK(h_mask_off[s] >= 0, "wsi_seg_tissue: negative mask offset");
+  }
+  WSI_ARG_CHECK(max_mask_end <= bl.npx, "wsi_seg_tissue: mask offsets must pack the cohort densely");
+  uint8_t* tmp = ws + bl.off_tmp;
+  int* L = (int*)(ws + bl.off_L);
+  int* aux = (int*)(ws + bl.off_aux);
+  const long long total = bl.npx;
+  const size_t lab_bytes = ((size_t)bl.npx + n) * sizeof(int);
+  const int nb = wsi_cdiv(total, 256);
+  int launches = 0;
+  {
+    int r = median_filter_size / 2;
+    size_t smem = (size_t)(K1_TW + 2 * r) * (K1_TH + 2 * r);
+    k_sat_median_thresh<<<(unsigned)bl.ntiles, K1_THREADS, smem, stream>>>(d_rgb, sb, median_filter_size,
+                                                                           binary_threshold, tmp);
+    ++launches;
+  }
+  {
+    int k = closing_kernel_size, halo = k - 1;
+    size_t smem = (size_t)(K1_TW + 2 * halo) * (K1_TH + 2 * halo) + (size_t)(K1_TW + halo) * (K1_TH + halo);
+    k_closing<<<(unsigned)bl.ntiles, K1_THREADS, smem, stream>>>(tmp, sb, k, d_mask);
+    ++launches;
+  }
+  // remove_small_objects (4-conn foreground, area < min) then remove_small_holes (4-conn background)
+  for (int pass = 0; pass < 2; ++pass) {
+    const int cls = pass == 0 ? 1 : 0;
+    bool any = false;
+    for (int s = 0; s < n; ++s) any = any || ((cls ? h_min_object_px[s] : h_min_hole_px[s]) > 0);
+    if (!any) continue;
+    k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, 0, L);
+    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, sb, total, 0, 0, L);
+    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
+    k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, cls, L, aux);
+    k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls);
+    launches += 4;
+  }
+  if (d_outer) {
+    k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, 1, L);
+    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, sb, total, 1, 1, L);
+    k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
+    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
+    k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux);
+    k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer);
+    launches += 5;
+  }
+  wsi_count_launch(launches);
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
 }
 
 int wsi_seg_tissue_u8(const uint8_t* d_rgb, int H, int W, int pitch_bytes, int median_filter_size,
                       int binary_threshold, int closing_kernel_size, int min_object_size_px,
                       int min_hole_size_px, uint8_t* d_mask, uint8_t* d_outer, void* d_ws, size_t ws_bytes,
                       void* stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
-  WSI_ARG_CHECK(d_rgb && d_mask && d_ws, "wsi_seg_tissue_u8: null pointer");
-  WSI_ARG_CHECK(H > 0 && W > 0 && pitch_bytes >= 3 * W, "wsi_seg_tissue_u8: bad geometry %dx%d pitch %d", H, W,
-                pitch_bytes);
-  WSI_ARG_CHECK((long long)H * W < (1ll << 30), "wsi_seg_tissue_u8: thumbnail too large");
-  // same message as the reference's ValueError (segment.py:68-72)
-  WSI_ARG_CHECK(median_filter_size > 1 && (median_filter_size % 2) == 1,
-                "median_filter_size must be greater than 1 and odd, but got %d", median_filter_size);
-  WSI_ARG_CHECK(median_filter_size <= 31, "median_filter_size > 31 unsupported");
-  WSI_ARG_CHECK(closing_kernel_size >= 1 && closing_kernel_size <= 32, "closing_kernel_size out of range");
-  WSI_ARG_CHECK(ws_bytes >= wsi_seg_workspace_bytes(H, W), "wsi_seg_tissue_u8: workspace too small");
-  int rc = upload_sdiv();
-  if (rc) return rc;
-
-  const int n = H * W;
-  uint8_t* tmp = (uint8_t*)d_ws;
-  int* L = (int*)((uint8_t*)d_ws + align_up((size_t)n, 256));
-  int* aux = (int*)((uint8_t*)L + align_up(((size_t)n + 1) * sizeof(int), 256));
-
-  dim3 tgrid(wsi_cdiv(W, K1_TW), wsi_cdiv(H, K1_TH));
-  {
-    int r = median_filter_size / 2;
-    size_t smem = (size_t)(K1_TW + 2 * r) * (K1_TH + 2 * r);
-    if (smem > 48 * 1024)
-      WSI_CUDA_CHECK(cudaFuncSetAttribute(k_sat_median_thresh, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)smem));
-    k_sat_median_thresh<<<tgrid, K1_TW * K1_TH / 4, smem, stream>>>(d_rgb, H, W, pitch_bytes, median_filter_size,
-                                                                    binary_threshold, tmp);
-  }
-  {
-    int k = closing_kernel_size, halo = k - 1;
-    size_t smem = (size_t)(K1_TW + 2 * halo) * (K1_TH + 2 * halo) + (size_t)(K1_TW + halo) * (K1_TH + halo);
-    if (smem > 48 * 1024)
-      WSI_CUDA_CHECK(cudaFuncSetAttribute(k_closing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_closing<<<tgrid, 256, smem, stream>>>(tmp, H, W, k, d_mask);
-  }
-  dim3 cgrid(wsi_cdiv(W, CC_TW), wsi_cdiv(H, CC_TH));
-  const int nb = wsi_cdiv(n, 256), nb1 = wsi_cdiv(n + 1, 256);
-  // remove_small_objects (4-conn foreground, area < min) then remove_small_holes (4-conn background)
-  for (int pass = 0; pass < 2; ++pass) {
-    const int cls = pass == 0 ? 1 : 0;
-    const int thr = pass == 0 ? min_object_size_px : min_hole_size_px;
-    if (thr <= 0) continue;
-    k_ccl_local<<<cgrid, CC_TW * CC_TH, 0, stream>>>(d_mask, H, W, 0, L);
-    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, H, W, 0, 0, L);
-    k_ccl_flatten<<<nb, 256, 0, stream>>>(n, L);
-    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, ((size_t)n + 1) * sizeof(int), stream));
-    k_ccl_area<<<nb, 256, 0, stream>>>(d_mask, L, n, cls, aux);
-    k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, L, aux, n, cls, thr);
-  }
-  if (d_outer) {
-    k_ccl_local<<<cgrid, CC_TW * CC_TH, 0, stream>>>(d_mask, H, W, 1, L);
-    k_set_int<<<1, 1, 0, stream>>>(L + n, n);   // frame node: label[n] = n
-    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, H, W, 1, 1, L);
-    k_ccl_flatten<<<nb1, 256, 0, stream>>>(n + 1, L);
-    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, ((size_t)n + 1) * sizeof(int), stream));
-    k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, L, H, W, aux);
-    k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, L, aux, n, d_outer);
-  }
-  WSI_CUDA_CHECK(cudaGetLastError());
-  return WSI_OK;
+  const long long zero = 0;
+  return wsi_seg_tissue_batch_u8(d_rgb, 1, &H, &W, &pitch_bytes, &zero, &zero, median_filter_size, binary_threshold,
+                                 closing_kernel_size, &min_object_size_px, &min_hole_size_px, d_mask, d_outer, d_ws,
+                                 ws_bytes, stream_);
 }
 
 size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int half, int step) {
@@ -453,6 +636,7 @@ int wsi_patch_grid(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, lo
   long long ni = slide_w > half ? (slide_w - half + step - 1) / step : 0;   // len(range(half, W, step))
   long long nj = slide_h > half ? (slide_h - half + step - 1) / step : 0;
   WSI_ARG_CHECK(ni * nj < (1ll << 31) - GRID_THREADS, "wsi_patch_grid: too many candidates");
+  WSI_ARG_CHECK((ni - 1) * step < (1ll << 31) && (nj - 1) * step < (1ll << 31), "wsi_patch_grid: int32 overflow");
   if (h_tile_dim) {
     h_tile_dim[0] = (int)ni;
     h_tile_dim[1] = (int)nj;
@@ -469,6 +653,7 @@ int wsi_patch_grid(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, lo
   k_grid_count<<<nblk, GRID_THREADS, 0, stream>>>(g, ncand, blk);
   k_grid_scan<<<1, 1024, 0, stream>>>(blk, nblk, d_count);
   k_grid_write<<<nblk, GRID_THREADS, 0, stream>>>(g, ncand, blk, capacity, d_coords_xy);
+  wsi_count_launch(3);
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
 }
