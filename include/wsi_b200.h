@@ -68,6 +68,11 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
                             const int* h_min_object_px, const int* h_min_hole_px, uint8_t* d_mask,
                             uint8_t* d_outer, void* d_ws, size_t ws_bytes, void* stream);
 
+/* Outermost-component restriction of an existing 0/1 mask (the polygon stage alone):
+ * get_multipolygon_from_binary_arr(), wsinsight/patchlib/patch.py:35-130. */
+int wsi_outermost_u8(const uint8_t* d_mask, int H, int W, uint8_t* d_outer, void* d_ws,
+                     size_t ws_bytes, void* stream);
+
 /* ---- K2: in-tissue patch grid --------------------------------------------------------- */
 /* Replaces get_patch_coordinates_within_polygon(), wsinsight/patchlib/patch.py:174-242
  * (itertools grid :218-225, STRtree.query(contains) :227-233, ordering :236, -half :240) and the

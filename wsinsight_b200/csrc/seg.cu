@@ -491,6 +491,78 @@ size_t wsi_seg_batch_workspace_bytes(int n, const int* h_H, const int* h_W) {
 
 size_t wsi_seg_workspace_bytes(int H, int W) { return wsi_seg_batch_workspace_bytes(1, &H, &W); }
 
+static int seg_prepare(int n, const int* h_H, const int* h_W, const int* h_pitch, const long long* h_rgb_off,
+                       const long long* h_mask_off, const int* h_min_object_px, const int* h_min_hole_px, void* d_ws,
+                       size_t ws_bytes, cudaStream_t stream, SegBatch* sb_out, BatchLayout* bl_out) {
+  WSI_ARG_CHECK(n > 0, "wsi_seg_tissue: empty batch");
+  for (int s = 0; s < n; ++s) {
+    WSI_ARG_CHECK(h_H[s] > 0 && h_W[s] > 0, "wsi_seg_tissue: bad geometry %dx%d", h_H[s], h_W[s]);
+    WSI_ARG_CHECK((long long)h_H[s] * h_W[s] < (1ll << 30), "wsi_seg_tissue: thumbnail too large");
+  }
+  const BatchLayout bl = batch_layout(n, h_H, h_W);
+  WSI_ARG_CHECK(ws_bytes >= bl.total, "wsi_seg_tissue: workspace too small (%zu < %zu)", ws_bytes, bl.total);
+  WSI_ARG_CHECK(bl.npx + n < (1ll << 31), "wsi_seg_tissue: cohort too large for one call");
+  // descriptor tables (host staging -> workspace head)
+  std::vector<SegSlide> hs(n);
+  std::vector<long long> tb(n + 1), cb(n + 1), pb(n + 1);
+  tb[0] = cb[0] = pb[0] = 0;
+  long long max_mask_end = 0;
+  for (int s = 0; s < n; ++s) {
+    SegSlide& d = hs[s];
+    d.H = h_H[s]; d.W = h_W[s]; d.pitch = h_pitch ? h_pitch[s] : 0;
+    d.min_obj = h_min_object_px ? h_min_object_px[s] : 0;
+    d.min_hole = h_min_hole_px ? h_min_hole_px[s] : 0;
+    d.tiles_x = wsi_cdiv(d.W, K1_TW);
+    d.ctiles_x = wsi_cdiv(d.W, CC_TW);
+    d.pad_ = 0;
+    d.rgb_off = h_rgb_off ? h_rgb_off[s] : 0;
+    d.mask_off = h_mask_off[s];
+    d.lab_off = pb[s] + s;
+    tb[s + 1] = tb[s] + (long long)d.tiles_x * wsi_cdiv(d.H, K1_TH);
+    cb[s + 1] = cb[s] + (long long)d.ctiles_x * wsi_cdiv(d.H, CC_TH);
+    pb[s + 1] = pb[s] + (long long)d.H * d.W;
+    WSI_ARG_CHECK(h_mask_off[s] >= 0, "wsi_seg_tissue: negative mask offset");
+    const long long e = h_mask_off[s] + (long long)d.H * d.W;
+    if (e > max_mask_end) max_mask_end = e;
+  }
+  // the median scratch is addressed with the mask offsets, so masks must pack the cohort densely
+  WSI_ARG_CHECK(max_mask_end <= bl.npx, "wsi_seg_tissue: mask offsets must pack the cohort densely");
+  uint8_t* ws = (uint8_t*)d_ws;
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_desc, hs.data(), sizeof(SegSlide) * n, cudaMemcpyHostToDevice, stream));
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_tile, tb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
+                                 stream));
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_ctile, cb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
+                                 stream));
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_px, pb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
+                                 stream));
+  sb_out->slides = (const SegSlide*)(ws + bl.off_desc);
+  sb_out->tile_base = (const long long*)(ws + bl.off_tile);
+  sb_out->ctile_base = (const long long*)(ws + bl.off_ctile);
+  sb_out->px_base = (const long long*)(ws + bl.off_px);
+  sb_out->n = n;
+  *bl_out = bl;
+  return WSI_OK;
+}
+
+// 8-connected foreground labelling + frame adjacency -> outermost-component mask
+static int seg_outermost(const SegBatch& sb, const BatchLayout& bl, const uint8_t* d_mask, uint8_t* d_outer, void* d_ws,
+                         cudaStream_t stream) {
+  uint8_t* ws = (uint8_t*)d_ws;
+  int* L = (int*)(ws + bl.off_L);
+  int* aux = (int*)(ws + bl.off_aux);
+  const long long total = bl.npx;
+  const size_t lab_bytes = ((size_t)bl.npx + sb.n) * sizeof(int);
+  const int nb = wsi_cdiv(total, 256);
+  k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, 1, L);
+  k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, sb, total, 1, 1, L);
+  k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
+  WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
+  k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux);
+  k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer);
+  wsi_count_launch(5);
+  return WSI_OK;
+}
+
 int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W, const int* h_pitch,
                             const long long* h_rgb_off, const long long* h_mask_off, int median_filter_size,
                             int binary_threshold, int closing_kernel_size, const int* h_min_object_px,
@@ -500,64 +572,21 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
   WSI_ARG_CHECK(d_rgb && d_mask && d_ws && h_H && h_W && h_pitch && h_rgb_off && h_mask_off && h_min_object_px &&
                     h_min_hole_px,
                 "wsi_seg_tissue: null pointer");
-  WSI_ARG_CHECK(n > 0, "wsi_seg_tissue: empty batch");
   // same message as the reference's ValueError (segment.py:68-72)
   WSI_ARG_CHECK(median_filter_size > 1 && (median_filter_size % 2) == 1,
                 "median_filter_size must be greater than 1 and odd, but got %d", median_filter_size);
   WSI_ARG_CHECK(median_filter_size <= 31, "median_filter_size > 31 unsupported");
   WSI_ARG_CHECK(closing_kernel_size >= 1 && closing_kernel_size <= 32, "closing_kernel_size out of range");
-  for (int s = 0; s < n; ++s) {
-    WSI_ARG_CHECK(h_H[s] > 0 && h_W[s] > 0 && h_pitch[s] >= 3 * h_W[s], "wsi_seg_tissue: bad geometry %dx%d pitch %d",
-                  h_H[s], h_W[s], h_pitch[s]);
-    WSI_ARG_CHECK((long long)h_H[s] * h_W[s] < (1ll << 30), "wsi_seg_tissue: thumbnail too large");
-  }
-  const BatchLayout bl = batch_layout(n, h_H, h_W);
-  WSI_ARG_CHECK(ws_bytes >= bl.total, "wsi_seg_tissue: workspace too small (%zu < %zu)", ws_bytes, bl.total);
-  WSI_ARG_CHECK(bl.npx + n < (1ll << 31), "wsi_seg_tissue: cohort too large for one call");
+  for (int s = 0; s < n; ++s)
+    WSI_ARG_CHECK(h_pitch[s] >= 3 * h_W[s], "wsi_seg_tissue: pitch %d < 3*W (%d)", h_pitch[s], h_W[s]);
   int rc = upload_sdiv();
   if (rc) return rc;
-
-  // descriptor tables (host staging -> workspace head)
-  std::vector<SegSlide> hs(n);
-  std::vector<long long> tb(n + 1), cb(n + 1), pb(n + 1);
-  tb[0] = cb[0] = pb[0] = 0;
-  for (int s = 0; s < n; ++s) {
-    SegSlide& d = hs[s];
-    d.H = h_H[s]; d.W = h_W[s]; d.pitch = h_pitch[s];
-    d.min_obj = h_min_object_px[s]; d.min_hole = h_min_hole_px[s];
-    d.tiles_x = wsi_cdiv(d.W, K1_TW);
-    d.ctiles_x = wsi_cdiv(d.W, CC_TW);
-    d.pad_ = 0;
-    d.rgb_off = h_rgb_off[s];
-    d.mask_off = h_mask_off[s];
-    d.lab_off = pb[s] + s;
-    tb[s + 1] = tb[s] + (long long)d.tiles_x * wsi_cdiv(d.H, K1_TH);
-    cb[s + 1] = cb[s] + (long long)d.ctiles_x * wsi_cdiv(d.H, CC_TH);
-    pb[s + 1] = pb[s] + (long long)d.H * d.W;
-  }
-  uint8_t* ws = (uint8_t*)d_ws;
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_desc, hs.data(), sizeof(SegSlide) * n, cudaMemcpyHostToDevice, stream));
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_tile, tb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
-                                 stream));
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_ctile, cb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
-                                 stream));
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_px, pb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
-                                 stream));
   SegBatch sb;
-  sb.slides = (const SegSlide*)(ws + bl.off_desc);
-  sb.tile_base = (const long long*)(ws + bl.off_tile);
-  sb.ctile_base = (const long long*)(ws + bl.off_ctile);
-  sb.px_base = (const long long*)(ws + bl.off_px);
-  sb.n = n;
-  // tmp shares the mask offsets: it must be addressable with mask_off, so it is only usable when the
-  // caller's mask layout fits the npx-byte scratch; otherwise the median output goes through d_outer.
-  long long max_mask_end = 0;
-  for (int s = 0; s < n; ++s) {
-    long long e = h_mask_off[s] + (long long)h_H[s] * h_W[s];
-    if (e > max_mask_end) max_mask_end = e;
-    WSI_ARG_CHECK(h_mask_off[s] >= 0, "wsi_seg_tissue: negative mask offset");
-  }
-  WSI_ARG_CHECK(max_mask_end <= bl.npx, "wsi_seg_tissue: mask offsets must pack the cohort densely");
+  BatchLayout bl;
+  rc = seg_prepare(n, h_H, h_W, h_pitch, h_rgb_off, h_mask_off, h_min_object_px, h_min_hole_px, d_ws, ws_bytes, stream,
+                   &sb, &bl);
+  if (rc) return rc;
+  uint8_t* ws = (uint8_t*)d_ws;
   uint8_t* tmp = ws + bl.off_tmp;
   int* L = (int*)(ws + bl.off_L);
   int* aux = (int*)(ws + bl.off_aux);
@@ -591,16 +620,11 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
     k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls);
     launches += 4;
   }
-  if (d_outer) {
-    k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, 1, L);
-    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, sb, total, 1, 1, L);
-    k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
-    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
-    k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux);
-    k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer);
-    launches += 5;
-  }
   wsi_count_launch(launches);
+  if (d_outer) {
+    rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, stream);
+    if (rc) return rc;
+  }
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
 }
@@ -613,6 +637,21 @@ int wsi_seg_tissue_u8(const uint8_t* d_rgb, int H, int W, int pitch_bytes, int m
   return wsi_seg_tissue_batch_u8(d_rgb, 1, &H, &W, &pitch_bytes, &zero, &zero, median_filter_size, binary_threshold,
                                  closing_kernel_size, &min_object_size_px, &min_hole_size_px, d_mask, d_outer, d_ws,
                                  ws_bytes, stream_);
+}
+
+int wsi_outermost_u8(const uint8_t* d_mask, int H, int W, uint8_t* d_outer, void* d_ws, size_t ws_bytes,
+                     void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_mask && d_outer && d_ws, "wsi_outermost_u8: null pointer");
+  const long long zero = 0;
+  SegBatch sb;
+  BatchLayout bl;
+  int rc = seg_prepare(1, &H, &W, nullptr, nullptr, &zero, nullptr, nullptr, d_ws, ws_bytes, stream, &sb, &bl);
+  if (rc) return rc;
+  rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, stream);
+  if (rc) return rc;
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
 }
 
 size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int half, int step) {
