@@ -39,6 +39,9 @@ const char* wsi_version(void);
 /* number of kernels this library has launched in this process (all streams) */
 long long wsi_launch_count(void);
 
+/* device-to-device copy on `stream` (debug access to activations owned by the library) */
+int wsi_memcpy_d2d(void* d_dst, const void* d_src, size_t bytes, void* stream);
+
 /* ---- K1: tissue segmentation --------------------------------------------------------- */
 /* Replaces segment_tissue(), wsinsight/patchlib/segment.py:13-97:
  *   cv.cvtColor(RGB2HSV)[...,1] (:54,65) -> cv.medianBlur(k) (:77) -> cv.threshold (:80-83)

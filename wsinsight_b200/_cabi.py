@@ -32,6 +32,7 @@ _PROTOS = {
     "wsi_last_error": (C.c_char_p, []),
     "wsi_version": (C.c_char_p, []),
     "wsi_launch_count": (c_ll, []),
+    "wsi_memcpy_d2d": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "wsi_seg_workspace_bytes": (c_size_t, [c_int, c_int]),
     "wsi_seg_tissue_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

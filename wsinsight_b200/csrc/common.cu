@@ -68,6 +68,12 @@ const char* wsi_last_error(void) { return t_err; }
 
 const char* wsi_version(void) { return "wsi_b200 0.1.0 sm_100a"; }
 
+int wsi_memcpy_d2d(void* d_dst, const void* d_src, size_t bytes, void* stream) {
+  WSI_ARG_CHECK(d_dst && d_src, "wsi_memcpy_d2d: null pointer");
+  WSI_CUDA_CHECK(cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return WSI_OK;
+}
+
 long long wsi_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 }  // extern "C"

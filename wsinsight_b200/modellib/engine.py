@@ -1,0 +1,221 @@
+"""B200 network: lowered IR -> ``wsi_net_*`` handle -> probabilities.
+
+Replaces the TorchScript forward + CPU softmax of the reference classification loop
+(``wsinsight/modellib/run_inference.py:537-560``).  The object is callable like the module the
+reference gets from ``get_pretrained_torch_module`` (``models.py:93-108``) but takes the bf16
+NHWC batches written by the fused preprocess kernel and returns fp32 probabilities
+(softmax for K > 1, sigmoid for K == 1) computed on the device.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import List
+
+import numpy as np
+
+from .. import _cabi
+from ..errors import UnknownArchitectureError
+from .lowering import IRNode, lower_torchscript
+
+
+def _fptr(t):
+    """ctypes float* of a contiguous fp32 CPU tensor (or None)."""
+    if t is None:
+        return None
+    return C.cast(t.data_ptr(), _cabi.c_float_p)
+
+
+def _topo_order(nodes: List[IRNode]) -> List[int]:
+    order, state = [], [0] * len(nodes)
+
+    def visit(i):
+        stack = [(i, 0)]
+        while stack:
+            j, phase = stack.pop()
+            if phase == 0:
+                if state[j]:
+                    continue
+                state[j] = 1
+                stack.append((j, 1))
+                deps = list(nodes[j].inputs) + ([nodes[j].residual] if nodes[j].residual is not None else [])
+                for d in reversed(deps):
+                    if not state[d]:
+                        stack.append((d, 0))
+            else:
+                order.append(j)
+
+    for i in range(len(nodes)):
+        visit(i)
+    return order
+
+
+class B200Network:
+    """A classification CNN resident on one B200, executed only by libwsi_b200 kernels."""
+
+    def __init__(self, nodes: List[IRNode], max_batch: int, device=None):
+        torch = _cabi.require_cuda()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.max_batch = int(max_batch)
+        self.nodes = nodes
+        self._h = C.c_void_p()
+        lib = _cabi.load()
+        with torch.cuda.device(self.device):
+            _cabi.call("wsi_net_create", self.max_batch, C.byref(self._h))
+            try:
+                self._build(nodes)
+                _cabi.call("wsi_net_finalize", self._h)
+            except Exception:
+                lib.wsi_net_destroy(self._h)
+                self._h = C.c_void_p()
+                raise
+        self.num_launches = int(lib.wsi_net_num_launches(self._h))
+        self.flops_per_image = float(lib.wsi_net_flops_per_image(self._h))
+
+    # -- construction ---------------------------------------------------------
+    @classmethod
+    def from_torchscript(cls, path_or_module, num_classes=None, input_size: int = 224, max_batch: int = 1024,
+                         device=None):
+        nodes = lower_torchscript(path_or_module, input_size)
+        net = cls(nodes, max_batch, device)
+        if num_classes is not None and net.num_classes != int(num_classes):
+            raise UnknownArchitectureError(
+                f"model emits {net.num_classes} classes but the configuration says {num_classes}")
+        return net
+
+    def _add_tensor(self, h, w, c, external=False) -> int:
+        tid = C.c_int()
+        _cabi.call("wsi_net_add_tensor", self._h, int(h), int(w), int(c), 1 if external else 0, C.byref(tid))
+        return tid.value
+
+    def _build(self, nodes):
+        inp = nodes[0]
+        self.input_size = int(inp.shape[1])
+        first_convs = [n for n in nodes if n.kind == "conv" and n.inputs == [0]]
+        if len(first_convs) != 1 or nodes[0].n_uses != 1:
+            raise UnknownArchitectureError("the network input must feed exactly one convolution")
+        stem = first_convs[0]
+        kh, kw = int(stem.weight.shape[2]), int(stem.weight.shape[3])
+        if not (kh == 7 and kw == 7 and stem.stride == 2 and tuple(stem.pad) == (3, 3) and stem.residual is None):
+            raise UnknownArchitectureError(
+                f"first convolution {kh}x{kw}/s{stem.stride} is not supported yet (7x7/2 pad 3 only)")
+        S = self.input_size
+        if S % 2:
+            raise UnknownArchitectureError("the 7x7/2 stem needs an even input size")
+        # layout the preprocess kernel must write: [B][S+6][S+6][4] bf16, patch at (3,3)
+        self.input_layout = dict(out_H=S + 6, out_W=S + 6, pad_top=3, pad_left=3, channels=4)
+        # tensor assignment: cat members write into the cat tensor at a channel offset
+        tensor_of, c_off = {}, {}
+        tensor_of[0] = self._add_tensor(S + 6, S + 6, 4, external=True)
+        c_off[0] = 0
+        for i, n in enumerate(nodes):
+            if n.kind == "cat":
+                c, h, w = n.shape
+                tid = self._add_tensor(h, w, c)
+                tensor_of[i], c_off[i] = tid, 0
+                off = 0
+                for p in n.inputs:
+                    if nodes[p].kind not in ("conv", "pool") or nodes[p].n_uses != 1 or p in tensor_of:
+                        raise UnknownArchitectureError("cat input must be a single-use conv/pool output")
+                    if off % 8 or nodes[p].shape[0] % 8:
+                        raise UnknownArchitectureError("cat channel offsets must be multiples of 8")
+                    tensor_of[p], c_off[p] = tid, off
+                    off += nodes[p].shape[0]
+        for i, n in enumerate(nodes):
+            if n.kind in ("conv", "pool") and i not in tensor_of:
+                c, h, w = n.shape
+                tensor_of[i], c_off[i] = self._add_tensor(h, w, c), 0
+        self.num_classes = None
+        self._keep = []
+        for i in _topo_order(nodes):
+            n = nodes[i]
+            if n.kind in ("input", "cat"):
+                continue
+            x = n.inputs[0]
+            if c_off.get(x, 0) != 0 or (nodes[x].kind in ("conv", "pool") and
+                                        nodes[x].shape[0] != self._tensor_channels(nodes, tensor_of, x)):
+                raise UnknownArchitectureError("reading a channel slice of a concat buffer is not supported")
+            if n.kind == "conv":
+                cout, cin = int(n.weight.shape[0]), int(n.weight.shape[1])
+                w = n.weight.contiguous()
+                b = n.bias.contiguous() if n.bias is not None else None
+                self._keep += [w, b]
+                if n is stem:
+                    _cabi.call("wsi_net_add_stem7x7", self._h, tensor_of[x], tensor_of[i], _fptr(w), _fptr(b), cout,
+                               1 if n.relu else 0)
+                else:
+                    res = tensor_of[n.residual] if n.residual is not None else -1
+                    if n.residual is not None and c_off.get(n.residual, 0) != 0:
+                        raise UnknownArchitectureError("residual read from a concat slice")
+                    _cabi.call("wsi_net_add_conv", self._h, tensor_of[x], tensor_of[i], c_off[i], _fptr(w), _fptr(b),
+                               cin, cout, int(w.shape[2]), int(w.shape[3]), int(n.stride), int(n.pad[0]),
+                               int(n.pad[1]), 1 if n.relu else 0, res)
+            elif n.kind == "pool":
+                _cabi.call("wsi_net_add_pool", self._h, tensor_of[x], tensor_of[i], c_off[i], 1 if n.pool_max else 0,
+                           int(n.k), int(n.pstride), int(n.ppad), 1 if n.count_include_pad else 0)
+            elif n.kind == "head":
+                w = n.fc_w.contiguous()
+                b = n.fc_b.contiguous() if n.fc_b is not None else None
+                self._keep += [w, b]
+                self.num_classes = int(w.shape[0])
+                _cabi.call("wsi_net_add_head", self._h, tensor_of[x], _fptr(w), _fptr(b), self.num_classes)
+        if self.num_classes is None:
+            raise UnknownArchitectureError("no classifier head found")
+        self._tensor_of = tensor_of
+
+    @staticmethod
+    def _tensor_channels(nodes, tensor_of, x):
+        tid = tensor_of[x]
+        for i, n in enumerate(nodes):
+            if tensor_of.get(i) == tid and n.kind == "cat":
+                return n.shape[0]
+        return nodes[x].shape[0]
+
+    # -- execution --------------------------------------------------------------
+    def alloc_input(self, batch: int):
+        """Zeroed bf16 input buffer in the layout ``wsi_preproc_run`` writes (borders stay zero)."""
+        import torch
+
+        lay = self.input_layout
+        return torch.zeros((int(batch), lay["out_H"], lay["out_W"], lay["channels"]), dtype=torch.bfloat16,
+                           device=self.device)
+
+    def forward_into(self, x, probs, stream=None):
+        """Enqueue the forward of ``x`` (bf16 [B][S+6][S+6][4]) writing fp32 probs [B][K]."""
+        import torch
+
+        b = int(x.shape[0])
+        assert x.dtype == torch.bfloat16 and x.is_contiguous() and x.device == self.device
+        assert probs.dtype == torch.float32 and probs.is_contiguous() and probs.numel() >= b * self.num_classes
+        with torch.cuda.device(self.device):
+            _cabi.call("wsi_net_forward", self._h, x.data_ptr(), b, probs.data_ptr(), _cabi.stream_ptr(stream))
+
+    def __call__(self, x):
+        import torch
+
+        probs = torch.empty((int(x.shape[0]), self.num_classes), dtype=torch.float32, device=self.device)
+        self.forward_into(x, probs)
+        return probs.squeeze(1) if self.num_classes == 1 else probs
+
+    def activation(self, node_index: int, batch: int):
+        """Debug: bf16 activation tensor [batch][H][W][C] of IR node ``node_index`` after a forward."""
+        import torch
+
+        ptr, hwc = C.c_void_p(), (C.c_int * 3)()
+        _cabi.call("wsi_net_tensor_ptr", self._h, self._tensor_of[node_index], C.byref(ptr), hwc)
+        h, w, c = int(hwc[0]), int(hwc[1]), int(hwc[2])
+        out = torch.empty((batch, h, w, c), dtype=torch.bfloat16, device=self.device)
+        with torch.cuda.device(self.device):
+            _cabi.call("wsi_memcpy_d2d", out.data_ptr(), ptr.value, batch * h * w * c * 2, _cabi.stream_ptr())
+        return out
+
+    def close(self):
+        if self._h:
+            _cabi.load().wsi_net_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

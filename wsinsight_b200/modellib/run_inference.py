@@ -1,0 +1,171 @@
+"""Patch classification over precomputed patch files (classification branch only).
+
+Mirror of ``wsinsight/modellib/run_inference.py``: signature :45-65, per-slide loop :205-225,
+classification loop :537-560, CSV assembly :565-607,732-733.  The reference moves fp32 NCHW
+batches host->device, runs the TorchScript module through cuDNN and does softmax on the CPU;
+here each batch is two library calls on one stream (fused preprocess, network forward with the
+softmax in the tail kernel) and one device->host copy of the probabilities per slide.
+
+Multi-GPU: the reference wraps the model in ``nn.DataParallel`` (:173-174).  Here ranks of a
+``torch.distributed`` job each take a contiguous range of the x-major sorted patch list (an
+x-band of the slide) and rank 0 gathers the ``(N_r, K)`` probabilities with one collective.
+"""
+
+from __future__ import annotations
+
+import logging
+from pathlib import Path
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from .. import _cabi
+from ..errors import PatchDirectoryNotFound, ResultsDirectoryNotFound
+from .data import WholeSlideImagePatches, _read_patch_coords
+from .models import Model, get_pretrained_torch_module
+from .transforms import make_compose_from_transform_config
+
+logger = logging.getLogger(__name__)
+
+
+def shard_range(n: int, rank: int, world: int):
+    """Contiguous range [lo, hi) of rank ``rank``: N*r/R .. N*(r+1)/R."""
+    return (n * rank) // world, (n * (rank + 1)) // world
+
+
+def classify_patches_device(slide, coords_xywh: np.ndarray, net, transform, batch_size: int, device_coords=None,
+                            probs_out=None):
+    """Hot loop for one slide on one GPU: returns a CUDA fp32 (N, K) tensor of probabilities.
+
+    Everything is enqueued on the current stream; nothing synchronises until the caller reads
+    the result.  (reference: run_inference.py:537-560)
+    """
+    torch = _cabi.require_cuda()
+    n = len(coords_xywh)
+    K = net.num_classes
+    probs = probs_out if probs_out is not None else torch.empty((n, K), dtype=torch.float32, device=net.device)
+    if n == 0:
+        return probs
+    dset = WholeSlideImagePatches(slide, coords_xywh, transform, batch_size, net.input_layout, device_coords)
+    s = 0
+    for batch, bc in dset:
+        b = int(batch.shape[0])
+        net.forward_into(batch, probs[s:s + b])
+        s += b
+    return probs
+
+
+def gather_probs(probs_local, n_total: int, rank: int, world: int):
+    """Gather per-rank (N_r, K) probability shards on rank 0 (NCCL on GPUs, gloo on CPU).
+
+    Shards follow :func:`shard_range`, so ranks may differ by one row: shards are padded to the
+    largest, all-gathered, and trimmed.  Returns the (N, K) tensor on rank 0, ``None`` elsewhere.
+    """
+    import torch
+    import torch.distributed as dist
+
+    if world == 1:
+        return probs_local
+    K = int(probs_local.shape[1])
+    sizes = [shard_range(n_total, r, world) for r in range(world)]
+    mx = max(hi - lo for lo, hi in sizes)
+    pad = torch.zeros((mx, K), dtype=probs_local.dtype, device=probs_local.device)
+    pad[: probs_local.shape[0]] = probs_local
+    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == 0 else None
+    dist.gather(pad, bufs, dst=0)
+    if rank != 0:
+        return None
+    return torch.cat([bufs[r][: hi - lo] for r, (lo, hi) in enumerate(sizes)], dim=0)
+
+
+def write_slide_csv(path, coords_xywh: np.ndarray, probs: np.ndarray, class_names: List[str]) -> None:
+    """CSV assembly of run_inference.py:568-607,732-733: minx,miny,width,height,prob_<class>..."""
+    import pandas as pd
+
+    df = pd.DataFrame(dict(minx=coords_xywh[:, 0], miny=coords_xywh[:, 1], width=coords_xywh[:, 2],
+                           height=coords_xywh[:, 3]))
+    probs = np.asarray(probs)
+    if probs.ndim == 1:
+        probs = probs[:, None]
+    for i, c in enumerate(class_names):
+        df[f"prob_{c}"] = probs[:, i]
+    Path(path).parent.mkdir(parents=True, exist_ok=True)
+    df.to_csv(path, index=False)
+
+
+def run_inference(
+    wsi_dir,
+    slide_paths,
+    results_dir,
+    references_dir=None,
+    qupath_detection_dir=None,
+    qupath_geojson_detection_dir=None,
+    qupath_geojson_annotation_dir=None,
+    qupath_name_as_class: bool = False,
+    model_info: Model = None,
+    halo_size_px: int = 46,
+    batch_size: int = 32,
+    num_workers: int = 4,
+    speedup: bool = False,
+    stain_normalization: bool = False,
+    object_based: bool = False,
+    object_detection: Optional[str] = None,
+    mixed_precision: bool = False,
+    stitch_workers: Optional[int] = None,
+    slides: Optional[Dict[str, object]] = None,
+):
+    """Reference signature (run_inference.py:45-65).  ``slides`` maps slide path -> opened
+    :class:`~wsinsight_b200.wsi.DeviceSlide` (decoders are out of scope).  ``num_workers`` is
+    accepted and ignored: there are no DataLoader workers on this path.
+
+    Returns ``(failed_patching, failed_inference)`` like the reference.
+    """
+    if references_dir or qupath_detection_dir or qupath_geojson_detection_dir or qupath_geojson_annotation_dir \
+            or object_based or object_detection or stain_normalization:
+        raise NotImplementedError("QuPath / reference-annotation / object-based / stain-normalisation branches "
+                                  "are outside the B200 hot path")
+    from ..patchlib.io import load_patch_file
+
+    results_dir = Path(results_dir)
+    if not results_dir.exists():
+        raise ResultsDirectoryNotFound(results_dir)
+    patch_dir = results_dir / "patches"
+    if not patch_dir.exists():
+        raise PatchDirectoryNotFound("Results dir must include 'patches' dir")
+    model_output_dir = results_dir / "model-outputs-csv"
+    model_output_dir.mkdir(exist_ok=True)
+    slides = slides or {}
+    patch_paths = sorted(list(patch_dir.glob("*.h5")) + list(patch_dir.glob("*.h5.npz")))
+    failed_patching = [str(p) for p in (slide_paths or [])
+                       if not any(Path(str(q).replace(".npz", "")).stem == Path(str(p)).stem for q in patch_paths)]
+    failed_inference: List[str] = []
+    transform = make_compose_from_transform_config(model_info.config.transform)
+    net = None
+    for patch_path in patch_paths:
+        meta = load_patch_file(patch_path)
+        wsi_path = str(meta["slide_path"])
+        slide_csv = model_output_dir / (Path(wsi_path).stem + ".csv")
+        if slide_csv.exists():
+            logger.info(f"Output CSV exists... skipping. {slide_csv}")
+            continue
+        slide = slides.get(wsi_path)
+        if slide is None:
+            failed_inference.append(wsi_path)
+            logger.error(f"slide {wsi_path} is not open on the device")
+            continue
+        try:
+            coords = _read_patch_coords(patch_path)
+            if len(coords) == 0:
+                continue
+            if net is None:
+                S = transform.out_size(int(coords[0, 2]))
+                from .engine import B200Network
+
+                net = B200Network.from_torchscript(model_info.model_path, model_info.config.num_classes,
+                                                   input_size=S, max_batch=batch_size, device=slide.rgba.device)
+            probs = classify_patches_device(slide, coords, net, transform, batch_size)
+            write_slide_csv(slide_csv, coords, probs.cpu().numpy(), model_info.config.class_names)
+        except Exception as e:  # noqa: BLE001 - slide-granular isolation, as upstream :268-280
+            failed_inference.append(wsi_path)
+            logger.error(f"Failed inference on {wsi_path}", exc_info=e)
+    return failed_patching, failed_inference
