@@ -132,6 +132,13 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
 int wsi_net_encode_input_map(void* net, int op_index, const void* d_base);
 int wsi_net_tensor_ptr(void* net, int id, void** d_ptr, int* h_hwc3);
 int wsi_net_num_launches(void* net);
+/* Per-op CUDA-event timing on the launching stream (bench roofline).  `slots` = number of most
+ * recent forwards kept (0 disables).  wsi_net_profile_read synchronises the device and returns the
+ * summed duration (ms) of each op over the recorded forwards, the op's flops per image and its kind
+ * (0 conv, 1 max-pool, 2 avg-pool, 3 head). */
+int wsi_net_set_profiling(void* net, int slots);
+int wsi_net_profile_read(void* net, double* h_op_ms, double* h_op_flops, int* h_op_kind, int max_ops,
+                         int* h_forwards);
 double wsi_net_flops_per_image(void* net);
 void wsi_net_destroy(void* net);
 

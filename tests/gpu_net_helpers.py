@@ -1,0 +1,61 @@
+"""Helpers for the GPU network tests: drive single layers through the raw C ABI."""
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from wsinsight_b200 import _cabi
+
+
+def bf16_round(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.bfloat16).float()
+
+
+def run_single_conv(x_nchw, w, b, stride, pad, relu=False, residual=None, max_batch=None):
+    """x: fp32 NCHW (values already bf16-representable).  Returns fp32 NCHW output of the B200 conv."""
+    lib = _cabi.load()
+    B, Cin, H, W = x_nchw.shape
+    Cout, _, KH, KW = w.shape
+    ph, pw = (pad, pad) if isinstance(pad, int) else pad
+    Ho, Wo = (H + 2 * ph - KH) // stride + 1, (W + 2 * pw - KW) // stride + 1
+    net = C.c_void_p()
+    _cabi.call("wsi_net_create", int(max_batch or B), C.byref(net))
+    try:
+        tin, tout, tres = C.c_int(), C.c_int(), C.c_int(-1)
+        _cabi.call("wsi_net_add_tensor", net, H, W, Cin, 1, C.byref(tin))
+        _cabi.call("wsi_net_add_tensor", net, Ho, Wo, Cout, 0, C.byref(tout))
+        res_id = -1
+        if residual is not None:
+            _cabi.call("wsi_net_add_tensor", net, Ho, Wo, Cout, 0, C.byref(tres))
+            res_id = tres.value
+        wc = w.contiguous().float().cpu()
+        bc = b.contiguous().float().cpu() if b is not None else None
+        _cabi.call("wsi_net_add_conv", net, tin.value, tout.value, 0, C.cast(wc.data_ptr(), _cabi.c_float_p),
+                   C.cast(bc.data_ptr(), _cabi.c_float_p) if bc is not None else None, Cin, Cout, KH, KW, stride, ph, pw,
+                   1 if relu else 0, res_id)
+        _cabi.call("wsi_net_finalize", net)
+        xd = x_nchw.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+        if residual is not None:
+            ptr, hwc = C.c_void_p(), (C.c_int * 3)()
+            _cabi.call("wsi_net_tensor_ptr", net, res_id, C.byref(ptr), hwc)
+            rd = residual.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+            _cabi.call("wsi_memcpy_d2d", ptr, rd.data_ptr(), rd.numel() * 2, _cabi.stream_ptr())
+        _cabi.call("wsi_net_forward", net, xd.data_ptr(), B, None, _cabi.stream_ptr())
+        ptr, hwc = C.c_void_p(), (C.c_int * 3)()
+        _cabi.call("wsi_net_tensor_ptr", net, tout.value, C.byref(ptr), hwc)
+        out = torch.empty((B, Ho, Wo, Cout), dtype=torch.bfloat16, device="cuda")
+        _cabi.call("wsi_memcpy_d2d", out.data_ptr(), ptr, out.numel() * 2, _cabi.stream_ptr())
+        torch.cuda.synchronize()
+        return out.float().permute(0, 3, 1, 2).cpu()
+    finally:
+        lib.wsi_net_destroy(net)
+
+
+def conv_reference(x, w, b, stride, pad, relu=False, residual=None):
+    y = torch.nn.functional.conv2d(x.double(), w.double(), None if b is None else b.double(), stride=stride, padding=pad)
+    if residual is not None:
+        y = y + residual.double()
+    if relu:
+        y = torch.relu(y)
+    return y.float()

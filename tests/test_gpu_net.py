@@ -1,0 +1,133 @@
+"""GPU numerics: tcgen05 implicit-GEMM convolutions and the full ResNet34 forward vs fp32 torch."""
+
+import numpy as np
+import pytest
+import torch
+
+from gpu_net_helpers import bf16_round, conv_reference, run_single_conv
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(got, want, what, rtol=2e-2):
+    err = (got - want).abs()
+    scale = want.abs().mean().item() + 1e-6
+    # outputs are stored as bf16: allow bf16 rounding (2^-8 relative) plus accumulation-order noise
+    tol = 1.0 / 128.0 * want.abs() + rtol * scale * 0.25
+    bad = (err > tol)
+    assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.numel()} bad, max err {err.max().item():.4g}, "
+                           f"mean|want| {scale:.4g}, first bad {bad.nonzero()[:4].tolist()}, "
+                           f"got {got[bad][:4].tolist()} want {want[bad][:4].tolist()}")
+
+
+# (B, Cin, H, Cout, k, stride, pad): the distinct ResNet34 layer shapes + ragged/odd cases
+CASES = [
+    (4, 64, 56, 64, 3, 1, 1),      # layer1
+    (8, 64, 56, 128, 3, 2, 1),     # layer2.0.conv1
+    (8, 64, 56, 128, 1, 2, 0),     # layer2.0.downsample
+    (8, 128, 28, 128, 3, 1, 1),    # layer2
+    (32, 128, 28, 256, 3, 2, 1),   # layer3.0.conv1
+    (32, 256, 14, 256, 3, 1, 1),   # layer3
+    (128, 256, 14, 512, 3, 2, 1),  # layer4.0.conv1
+    (128, 256, 14, 512, 1, 2, 0),  # layer4.0.downsample
+    (128, 512, 7, 512, 3, 1, 1),   # layer4
+    (3, 64, 56, 64, 3, 1, 1),      # batch not a multiple of the box
+    (5, 32, 17, 96, 3, 1, 1),      # Cin < 64, odd spatial size
+    (130, 96, 7, 32, 1, 1, 0),     # batch tail beyond one 128-image box
+]
+
+
+@pytest.mark.parametrize("B,Cin,H,Cout,k,stride,pad", CASES)
+def test_single_conv_vs_torch(B, Cin, H, Cout, k, stride, pad):
+    g = torch.Generator().manual_seed(B * 1000 + Cin + H + Cout + k)
+    x = bf16_round(torch.randn((B, Cin, H, H), generator=g))
+    w = bf16_round(torch.randn((Cout, Cin, k, k), generator=g) / (Cin * k * k) ** 0.5)
+    b = torch.randn(Cout, generator=g) * 0.1
+    got = run_single_conv(x, w, b, stride, pad)
+    want = conv_reference(x, w, b, stride, pad)
+    _check(got, want, f"conv {B}x{Cin}x{H} -> {Cout} k{k} s{stride}")
+
+
+def test_conv_residual_relu_epilogue():
+    g = torch.Generator().manual_seed(7)
+    x = bf16_round(torch.randn((8, 64, 28, 28), generator=g))
+    w = bf16_round(torch.randn((64, 64, 3, 3), generator=g) / 24.0)
+    b = torch.randn(64, generator=g) * 0.1
+    r = bf16_round(torch.randn((8, 64, 28, 28), generator=g))
+    got = run_single_conv(x, w, b, 1, 1, relu=True, residual=r)
+    want = conv_reference(x, w, b, 1, 1, relu=True, residual=r)
+    _check(got, want, "conv+residual+relu")
+    assert got.min().item() >= 0
+
+
+def test_conv_asymmetric_kernels():
+    g = torch.Generator().manual_seed(9)
+    for (kh, kw, ph, pw) in [(1, 7, 0, 3), (7, 1, 3, 0), (1, 3, 0, 1), (3, 1, 1, 0)]:
+        x = bf16_round(torch.randn((16, 64, 17, 17), generator=g))
+        w = bf16_round(torch.randn((64, 64, kh, kw), generator=g) / (64 * kh * kw) ** 0.5)
+        got = run_single_conv(x, w, None, 1, (ph, pw))
+        want = conv_reference(x, w, None, 1, (ph, pw))
+        _check(got, want, f"conv {kh}x{kw}")
+
+
+def _resnet_inputs(B, S, seed):
+    g = torch.Generator().manual_seed(seed)
+    # normalised-image-like values, exactly bf16 representable (what the preprocess kernel emits)
+    return bf16_round(torch.randn((B, 3, S, S), generator=g) * 1.5)
+
+
+def _padded_nhwc4(x):
+    B, _, S, _ = x.shape
+    buf = torch.zeros((B, S + 6, S + 6, 4), dtype=torch.bfloat16, device="cuda")
+    buf[:, 3:3 + S, 3:3 + S, :3] = x.permute(0, 2, 3, 1).to(torch.bfloat16).cuda()
+    return buf
+
+
+def test_resnet34_layerwise_and_probs():
+    """Full ResNet34 forward vs torchvision fp32 on identical random-init weights.
+
+    north_star tolerance: |dp| <= 2e-3 and >= 99.9 % argmax agreement.
+    """
+    from oracle.forward import forward_probs, make_resnet34
+    from wsinsight_b200.modellib.engine import B200Network
+
+    m = make_resnet34(2, 0)
+    B = 64
+    x = _resnet_inputs(B, 224, 1)
+    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(m)), 2, input_size=224, max_batch=B)
+    assert abs(net.flops_per_image / 1e9 - 7.326) < 0.15 or net.flops_per_image > 7e9
+    probs = net(_padded_nhwc4(x)).cpu()
+    # layer-wise diagnostics against fp32 torch (loose: activations are stored in bf16)
+    with torch.no_grad():
+        a = torch.relu(m.bn1(m.conv1(x)))
+        stem = net.activation(1, B).float().permute(0, 3, 1, 2).cpu()
+        rel = ((stem - a).abs().mean() / a.abs().mean()).item()
+        assert rel < 1e-2, f"stem relative error {rel}"
+        a = m.maxpool(a)
+        pool = net.activation(2, B).float().permute(0, 3, 1, 2).cpu()
+        rel = ((pool - a).abs().mean() / a.abs().mean()).item()
+        assert rel < 1e-2, f"maxpool relative error {rel}"
+        a1 = m.layer1(a)
+        idx = [i for i, n in enumerate(net.nodes) if n.kind == "conv"][6]     # last conv of layer1
+        l1 = net.activation(idx, B).float().permute(0, 3, 1, 2).cpu()
+        rel = ((l1 - a1).abs().mean() / a1.abs().mean()).item()
+        assert rel < 2e-2, f"layer1 relative error {rel}"
+    want = forward_probs(m, x)
+    dp = (probs - want).abs().max().item()
+    agree = (probs.argmax(1) == want.argmax(1)).float().mean().item()
+    assert torch.allclose(probs.sum(1), torch.ones(B), atol=1e-5)
+    assert dp <= 2e-3, f"max |dp| = {dp}"
+    assert agree >= 0.999, f"argmax agreement {agree}"
+
+
+def test_resnet34_batch_tail_and_k1_sigmoid():
+    from oracle.forward import forward_probs, make_resnet34
+    from wsinsight_b200.modellib.engine import B200Network
+
+    m = make_resnet34(1, 3)
+    x = _resnet_inputs(5, 224, 2)
+    net = B200Network.from_torchscript(torch.jit.script(m), 1, input_size=224, max_batch=8)
+    p = net(_padded_nhwc4(x)).cpu()
+    want = forward_probs(m, x)
+    assert p.shape == want.shape == (5,)
+    assert (p - want).abs().max().item() <= 2e-3

@@ -62,6 +62,9 @@ _PROTOS = {
     "wsi_net_encode_input_map": (c_int, [c_void_p, c_int, c_void_p]),
     "wsi_net_tensor_ptr": (c_int, [c_void_p, c_int, C.POINTER(c_void_p), c_int_p]),
     "wsi_net_num_launches": (c_int, [c_void_p]),
+    "wsi_net_set_profiling": (c_int, [c_void_p, c_int]),
+    "wsi_net_profile_read": (c_int, [c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), c_int_p, c_int,
+                                     c_int_p]),
     "wsi_net_flops_per_image": (C.c_double, [c_void_p]),
     "wsi_net_destroy": (None, [c_void_p]),
     "wsi_synth_slide": (c_int, [c_void_p, c_ll, c_ll, c_ll, C.c_uint, c_void_p]),

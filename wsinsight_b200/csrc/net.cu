@@ -48,6 +48,10 @@ struct Net {
   std::vector<Op> ops;
   int num_sms = 148;
   int launches_per_forward = 0;
+  // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
+  int prof_slots = 0;
+  long long prof_forwards = 0;
+  std::vector<cudaEvent_t> prof_ev;   // [prof_slots][ops + 1]
 };
 
 // ---------------------------------------------------------------------------
@@ -453,8 +457,12 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
   Net* n = (Net*)net;
   WSI_ARG_CHECK(n && n->finalized, "wsi_net_forward: net not finalized");
   WSI_ARG_CHECK(B >= 1 && B <= n->max_batch, "wsi_net_forward: batch %d out of range (max %d)", B, n->max_batch);
+  cudaEvent_t* pev = nullptr;
+  if (n->prof_slots > 0)
+    pev = n->prof_ev.data() + (size_t)(n->prof_forwards % n->prof_slots) * (n->ops.size() + 1);
   for (size_t i = 0; i < n->ops.size(); ++i) {
     Op& op = n->ops[i];
+    if (pev) cudaEventRecord(pev[i], stream);
     const Tensor& ti = n->tensors[op.in];
     const __nv_bfloat16* in_ptr = ti.external ? (const __nv_bfloat16*)d_input : ti.ptr;
     WSI_ARG_CHECK(in_ptr, "wsi_net_forward: missing input pointer");
@@ -489,8 +497,50 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
                                                                 d_probs);
     }
   }
+  if (pev) {
+    cudaEventRecord(pev[n->ops.size()], stream);
+    n->prof_forwards++;
+  }
   wsi_count_launch((int)n->ops.size());
   WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
+int wsi_net_set_profiling(void* net, int slots) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && n->finalized && slots >= 0, "wsi_net_set_profiling: bad arguments");
+  for (auto e : n->prof_ev) cudaEventDestroy(e);
+  n->prof_ev.clear();
+  n->prof_slots = slots;
+  n->prof_forwards = 0;
+  n->prof_ev.resize((size_t)slots * (n->ops.size() + 1));
+  for (auto& e : n->prof_ev) WSI_CUDA_CHECK(cudaEventCreate(&e));
+  return WSI_OK;
+}
+
+// Sum of per-op durations (ms) over the forwards recorded since wsi_net_set_profiling (at most `slots`
+// most recent); synchronises the device.  h_op_kind: 0 conv, 1 maxpool, 2 avgpool, 3 head.
+int wsi_net_profile_read(void* net, double* h_op_ms, double* h_op_flops, int* h_op_kind, int max_ops, int* h_forwards) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && h_op_ms && h_forwards, "wsi_net_profile_read: bad arguments");
+  WSI_CUDA_CHECK(cudaDeviceSynchronize());
+  const int nops = (int)n->ops.size();
+  WSI_ARG_CHECK(max_ops >= nops, "wsi_net_profile_read: need room for %d ops", nops);
+  const long long cnt = n->prof_forwards < n->prof_slots ? n->prof_forwards : n->prof_slots;
+  for (int i = 0; i < nops; ++i) {
+    h_op_ms[i] = 0;
+    if (h_op_flops) h_op_flops[i] = n->ops[i].flops_per_image;
+    if (h_op_kind) h_op_kind[i] = (int)n->ops[i].kind;
+  }
+  for (long long s = 0; s < cnt; ++s) {
+    cudaEvent_t* ev = n->prof_ev.data() + (size_t)s * (nops + 1);
+    for (int i = 0; i < nops; ++i) {
+      float ms = 0;
+      WSI_CUDA_CHECK(cudaEventElapsedTime(&ms, ev[i], ev[i + 1]));
+      h_op_ms[i] += ms;
+    }
+  }
+  *h_forwards = (int)cnt;
   return WSI_OK;
 }
 
@@ -520,6 +570,7 @@ double wsi_net_flops_per_image(void* net) {
 void wsi_net_destroy(void* net) {
   Net* n = (Net*)net;
   if (!n) return;
+  for (auto e : n->prof_ev) cudaEventDestroy(e);
   for (auto& t : n->tensors)
     if (t.ptr) cudaFree(t.ptr);
   for (auto& op : n->ops) {

@@ -209,6 +209,19 @@ class B200Network:
             _cabi.call("wsi_memcpy_d2d", out.data_ptr(), ptr.value, batch * h * w * c * 2, _cabi.stream_ptr())
         return out
 
+    def set_profiling(self, slots: int):
+        _cabi.call("wsi_net_set_profiling", self._h, int(slots))
+
+    def profile(self):
+        """Per-op event timings: list of dict(kind, ms_total, flops_per_image) + number of forwards."""
+        nmax = 512
+        ms, fl, kd, nf = (C.c_double * nmax)(), (C.c_double * nmax)(), (C.c_int * nmax)(), C.c_int()
+        _cabi.call("wsi_net_profile_read", self._h, ms, fl, kd, nmax, C.byref(nf))
+        kinds = {0: "conv", 1: "maxpool", 2: "avgpool", 3: "head"}
+        ops = [dict(kind=kinds[int(kd[i])], ms_total=float(ms[i]), flops_per_image=float(fl[i]))
+               for i in range(self.num_launches)]
+        return ops, int(nf.value)
+
     def close(self):
         if self._h:
             _cabi.load().wsi_net_destroy(self._h)

@@ -54,6 +54,8 @@ def _pair(v):
 
 def _const(value):
     node = value.node()
+    if node.kind() == "prim::ListConstruct":      # serialised graphs rebuild constant lists
+        return [_const(i) for i in node.inputs()]
     if node.kind() != "prim::Constant":
         raise UnknownArchitectureError(f"expected a constant for {value.debugName()}, got {node.kind()}")
     return value.toIValue()
