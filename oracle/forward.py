@@ -36,6 +36,28 @@ def make_resnet34(num_classes: int = 2, seed: int = 0) -> torch.nn.Module:
     return m.eval()
 
 
+def make_resnet34_calibrated(num_classes: int = 2, seed: int = 0, fc_gain: float = 4.0) -> torch.nn.Module:
+    """ResNet34 with trained-net-like statistics: random affine BN parameters, running stats
+    calibrated on random normalised-image-like batches (every layer O(1)), classifier scaled so the
+    logits are O(1) and the probabilities are NOT saturated.  This is the hard case for bf16."""
+    g = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    m = torchvision.models.resnet34(num_classes=num_classes)
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            with torch.no_grad():
+                mod.weight.copy_(torch.rand(mod.weight.shape, generator=g) * 0.5 + 0.75)
+                mod.bias.copy_(torch.randn(mod.bias.shape, generator=g) * 0.1)
+            mod.momentum = None
+            mod.reset_running_stats()
+    m.train()
+    with torch.no_grad():
+        for _ in range(2):
+            m(torch.randn((16, 3, 224, 224), generator=g) * 1.5)
+        m.fc.weight.mul_(fc_gain)
+    return m.eval()
+
+
 BREAST_RESNET34_CONFIG = {
     "spec_version": "1.0",
     "architecture": "resnet34",

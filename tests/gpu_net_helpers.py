@@ -59,3 +59,45 @@ def conv_reference(x, w, b, stride, pad, relu=False, residual=None):
     if relu:
         y = torch.relu(y)
     return y.float()
+
+
+def emulate_ir(nodes, x_nchw):
+    """CPU emulation of the B200 network numerics: bf16 weights/activations, fp32 accumulate.
+
+    Runs the lowered IR (wsinsight_b200.modellib.lowering) node by node in torch and rounds every
+    stored activation to bf16, exactly where the kernels do.  Returns ({node index: fp32 NCHW
+    activation}, probabilities).  Differences to the GPU are accumulation-order noise only.
+    """
+    import torch.nn.functional as F
+
+    acts = {0: bf16_round(x_nchw)}
+    probs = None
+    from wsinsight_b200.modellib.engine import _topo_order
+
+    for i in _topo_order(nodes):
+        n = nodes[i]
+        if n.kind == "conv":
+            y = F.conv2d(acts[n.inputs[0]].double(), bf16_round(n.weight).double(),
+                         None if n.bias is None else n.bias.double(), stride=n.stride, padding=tuple(n.pad))
+            if n.residual is not None:
+                y = y + acts[n.residual].double()
+            if n.relu:
+                y = torch.relu(y)
+            acts[i] = bf16_round(y.float())
+        elif n.kind == "pool":
+            a = acts[n.inputs[0]]
+            if n.pool_max:
+                y = F.max_pool2d(a, n.k, n.pstride, n.ppad)
+            else:
+                y = F.avg_pool2d(a, n.k, n.pstride, n.ppad, count_include_pad=n.count_include_pad)
+            acts[i] = bf16_round(y)
+        elif n.kind == "cat":
+            acts[i] = torch.cat([acts[p] for p in n.inputs], 1)
+        elif n.kind == "head":
+            feat = acts[n.inputs[0]].double().mean((2, 3))
+            logits = feat @ n.fc_w.double().t()
+            if n.fc_b is not None:
+                logits = logits + n.fc_b.double()
+            logits = logits.float()
+            probs = torch.softmax(logits, 1) if logits.shape[1] > 1 else torch.sigmoid(logits.squeeze(1))
+    return acts, probs

@@ -120,14 +120,39 @@ def test_resnet34_layerwise_and_probs():
     assert agree >= 0.999, f"argmax agreement {agree}"
 
 
-def test_resnet34_batch_tail_and_k1_sigmoid():
-    from oracle.forward import forward_probs, make_resnet34
+def _torch_bf16_probs(m, x):
+    """The 'best library' comparator: the same model through PyTorch/cuDNN in bf16 channels_last."""
+    import copy
+    from oracle.forward import head
+    mb = copy.deepcopy(m).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    with torch.no_grad():
+        return head(mb(x.cuda().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)).float()).cpu()
+
+
+@pytest.mark.parametrize("K,B,maxb", [(2, 48, 48), (1, 5, 8)])
+def test_resnet34_calibrated_unsaturated(K, B, maxb):
+    """Hard case: BN-calibrated random net with mid-range probabilities (no saturation), batch tail,
+    K == 1 sigmoid head.  bf16 weights/activations alone move such probabilities by ~1e-2
+    (PyTorch's own bf16 path moves them more), so the check is: (a) the kernels match a CPU
+    emulation with identical rounding points, (b) the error vs fp32 is no worse than cuDNN bf16."""
+    from gpu_net_helpers import emulate_ir
+    from oracle.forward import forward_probs, make_resnet34_calibrated
     from wsinsight_b200.modellib.engine import B200Network
 
-    m = make_resnet34(1, 3)
-    x = _resnet_inputs(5, 224, 2)
-    net = B200Network.from_torchscript(torch.jit.script(m), 1, input_size=224, max_batch=8)
+    m = make_resnet34_calibrated(K, 0)
+    x = _resnet_inputs(B, 224, 5)
+    net = B200Network.from_torchscript(torch.jit.script(m), K, input_size=224, max_batch=maxb)
     p = net(_padded_nhwc4(x)).cpu()
     want = forward_probs(m, x)
-    assert p.shape == want.shape == (5,)
-    assert (p - want).abs().max().item() <= 2e-3
+    assert p.shape == want.shape
+    acts, pe = emulate_ir(net.nodes, x)
+    last = [i for i, n in enumerate(net.nodes) if n.kind == "conv"][-1]
+    a = net.activation(last, B).float().permute(0, 3, 1, 2).cpu()
+    rel = ((a - acts[last]).abs().mean() / acts[last].abs().mean()).item()
+    assert rel < 2e-2, f"last conv vs bf16 emulation: relative mean error {rel}"
+    d_emul = (p - pe).abs().max().item()
+    d_fp32 = (p - want).abs().max().item()
+    d_lib = (_torch_bf16_probs(m, x) - want).abs().max().item()
+    print(f"K={K}: max|p-emul|={d_emul:.3e} max|p-fp32|={d_fp32:.3e} cuDNN-bf16 max|p-fp32|={d_lib:.3e}")
+    assert d_emul <= 3e-2
+    assert d_fp32 <= max(2e-3, 1.25 * d_lib), (d_fp32, d_lib)

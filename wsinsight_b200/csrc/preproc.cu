@@ -127,16 +127,19 @@ __global__ void __launch_bounds__(PP_THREADS)
     for (int g = 0; g < a.ngroups; ++g) {
       const int xx0 = g * a.G, xx1 = min(xx0 + a.G, a.S);
       const int xs0 = a.lo[xx0];
+      // TMA needs the box start 16-byte aligned in global memory: align x down to 4 pixels
+      const int bx = (px + xs0) & ~3;
+      const int shift = (px + xs0) - bx;
       if (threadIdx.x == 0) {
         ptx::mbar_arrive_expect_tx(&s_bar, (uint32_t)(a.box_h * a.box_w * 4));
-        ptx::tma_load_2d(s_src, &tmap, &s_bar, px + xs0, py + y_lo + yc);
+        ptx::tma_load_2d(s_src, &tmap, &s_bar, bx, py + y_lo + yc);
       }
       ptx::mbar_wait(&s_bar, phase);
       phase ^= 1;
       const int ncols = xx1 - xx0;
       for (int i = threadIdx.x; i < rows_here * ncols; i += PP_THREADS) {
         const int rr = i / ncols, xx = xx0 + (i - rr * ncols);
-        const int lo = a.lo[xx] - xs0, n = a.cnt[xx];
+        const int lo = a.lo[xx] - xs0 + shift, n = a.cnt[xx];
         const int* k = a.coef + (size_t)xx * a.ksize;
         const uint32_t* src = s_src + rr * a.box_w + lo;
         int s0 = 1 << (PRECISION_BITS - 1), s1 = s0, s2 = s0;
@@ -235,7 +238,7 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
   p->TR = TR;
   p->nbands = (S + TR - 1) / TR;
   // output-column groups whose source span fits one TMA box row
-  int box_w = patch_size + 8;
+  int box_w = patch_size + 8 + 3;   // +3: the box start is aligned down to 4 pixels (16 B) for TMA
   box_w = (box_w + 3) / 4 * 4;
   if (box_w > PP_BOX_W) box_w = PP_BOX_W;
   int G = S;
@@ -246,8 +249,8 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
       int span = t.lo[x1 - 1] + t.cnt[x1 - 1] - t.lo[x0];
       if (span > worst) worst = span;
     }
-    if (worst <= box_w || G == 1) {
-      if (worst > box_w) {
+    if (worst + 3 <= box_w || G == 1) {
+      if (worst + 3 > box_w) {
         delete p;
         wsi_set_error("wsi_preproc_plan_create: filter support %d exceeds TMA box %d", worst, box_w);
         return WSI_ERR_UNSUPPORTED;
