@@ -1,0 +1,513 @@
+#!/usr/bin/env python
+"""bench.py -- patches/s of the WSInsight patch-classification hot path on B200.
+
+Workload (BASELINE.json configs[1]): breast-tumor-resnet34.tcga-brca on a synthetic
+100 000 x 80 000 slide at 0.5 um/px, bf16, batch 1024.  One "step" = one batch of 1024
+in-tissue patches: fused crop/resize/normalise kernel + ResNet34 forward (softmax in the tail
+kernel).
+
+  value  patches/s with the slide resident in HBM (device-timed, CUDA events, max over ranks)
+  e2e    patches/s through the host-buffer entry (wsi_hostpipe_*): every step copies the
+         batch's RGBA pixels from pinned host memory and reads the probabilities back
+  roofline      the tcgen05 convolution kernel against the measured bf16 peak
+  cpu_baseline  the reference's CPU path (PIL/torchvision transform + fp32 TorchScript ResNet34)
+                timed on the same box's host cores on a bounded sample (rank 0, N=1)
+
+``--impl reference`` times only that CPU path (see ``reference_arm``).
+Launch: ``python bench.py [--gpus N --steps K --warmup W]`` or, for N>1, under torchrun.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+METRIC = "patches/sec (ResNet34 224^2, bf16)"
+UNIT = "patches/s"
+RESNET34_GFLOP = 7.326  # convs + FC, 2*MACs, per 224^2 patch
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--slide", default="100000x80000", help="WxH of the synthetic slide (level 0 pixels)")
+    ap.add_argument("--mpp", type=float, default=0.5)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--per-op", action="store_true", help="print the per-layer event timings to stderr")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def workload_name(w, h, mpp, batch):
+    return (f"breast-tumor-resnet34.tcga-brca on a synthetic {w}x{h} slide at {mpp} um/px, "
+            f"patch 350px@0.25um -> 224^2, batch {batch}")
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: sample nvidia-smi DURING the timed region (B200_PROFILING.md "clocks" line)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def mark(self):
+        return time.perf_counter()
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.lines:
+            if not (t0 <= t <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the reference's own CPU path for this hot path (test/bench infrastructure: oracle/)
+# ------------------------------------------------------------------------------------------------
+def host_patches(coords_xy, ps, slide_w, slide_h, seed):
+    """Regenerate RGBA patch windows of the synthetic slide on the HOST (same counter-based
+    generator as the device slide; zero padded outside the slide like read_region)."""
+    import numpy as np
+
+    from wsinsight_b200.wsi import synth_window_host
+
+    out = np.zeros((len(coords_xy), ps, ps, 4), dtype=np.uint8)
+    for i, (x, y) in enumerate(coords_xy):
+        x, y = int(x), int(y)
+        x1, y1 = min(x + ps, slide_w), min(y + ps, slide_h)
+        if x1 > x and y1 > y:
+            out[i, : y1 - y, : x1 - x] = synth_window_host(x, y, x1 - x, y1 - y, slide_w, slide_h, seed)
+    return out
+
+
+class CpuReference:
+    """PIL convert + torchvision Compose(Resize, ToTensor, Normalize) + frozen TorchScript ResNet34
+    fp32 + CPU softmax, batch 32 (wsinsight/modellib/data.py:270-314, transforms.py:22-38,
+    run_inference.py:288-299,537-560), all host threads."""
+
+    def __init__(self, batch=None):
+        import torch
+
+        from oracle import forward as oforward
+
+        self.cores = len(os.sched_getaffinity(0))
+        torch.set_num_threads(self.cores)
+        # reference default batch is 32 (cli/run.py:369-376); many-core hosts get a larger batch so
+        # that the intra-op thread pool of the fp32 forward is not starved
+        self.batch = batch if batch is not None else (32 if self.cores <= 16 else 128)
+        self.cfg = oforward.BREAST_RESNET34_CONFIG
+        model = oforward.make_resnet34(2, 0)
+        self.ts = torch.jit.freeze(torch.jit.script(model))
+        from concurrent.futures import ThreadPoolExecutor
+
+        self.pool = ThreadPoolExecutor(max_workers=min(self.cores, 8))   # reference default: min(cpus, 8) workers
+        tf = self.cfg["transform"]
+        self.size = tf[0]["arguments"]["size"]
+        self.mean, self.std = tf[2]["arguments"]["mean"], tf[2]["arguments"]["std"]
+
+    def step(self, rgba_batch):
+        """One batch: per-patch PIL transform on worker threads + forward + softmax."""
+        import torch
+
+        from oracle import forward as oforward
+        from oracle import preprocess
+
+        fn = lambda p: preprocess.preprocess_lib(p, self.size, self.mean, self.std)  # noqa: E731
+        x = torch.stack(list(self.pool.map(fn, rgba_batch)), 0)   # PIL releases the GIL: ~DataLoader workers
+        with torch.no_grad():
+            return oforward.head(self.ts(x))
+
+
+def sample_grid_coords(slide_w, slide_h, ps, n, seed=0):
+    """Seeded sample of patch-grid positions (x-major grid of pipeline.py:359-382, zero overlap)."""
+    import numpy as np
+
+    half = round(ps / 2)
+    ni, nj = len(range(half, slide_w, ps)), len(range(half, slide_h, ps))
+    rng = np.random.default_rng(seed)
+    idx = rng.choice(ni * nj, size=min(n, ni * nj), replace=False)
+    idx.sort()
+    return np.stack([(idx // nj) * ps, (idx % nj) * ps], 1).astype(np.int64)
+
+
+def time_cpu_reference(ref, coords_xy, ps, slide_w, slide_h, seed, steps, warmup, budget_s=None):
+    """Time `steps` batches of ref.batch patches after `warmup` (stop early once budget_s is spent)."""
+    b = ref.batch
+    need = (steps + warmup) * b
+    reps = -(-need // len(coords_xy))
+    import numpy as np
+
+    coords = np.concatenate([coords_xy] * reps)[:need]
+    times = []
+    for s in range(steps + warmup):
+        patches = host_patches(coords[s * b:(s + 1) * b], ps, slide_w, slide_h, seed)
+        t0 = time.perf_counter()
+        ref.step(patches)
+        dt = time.perf_counter() - t0
+        if s >= warmup:
+            times.append(dt)
+            if budget_s is not None and sum(times) >= budget_s and len(times) >= 2:
+                break
+    return times
+
+
+def reference_arm(args, rank, world):
+    """`--impl reference`: the reference's CPU implementation of the path on this box's host cores.
+
+    The reference package itself cannot be imported in this image; this executes the
+    same PIL / torchvision / TorchScript calls its data path and classification loop make
+    (oracle/preprocess.py, oracle/forward.py).  Rank 0 alone runs."""
+    if rank != 0:
+        return
+    w, h = (int(v) for v in args.slide.lower().split("x"))
+    ps = int(round(350 * 0.25 / args.mpp))
+    ref = CpuReference()
+    coords = sample_grid_coords(w, h, ps, (args.steps + args.warmup) * ref.batch, seed=0)
+    t_all0 = time.perf_counter()
+    times = time_cpu_reference(ref, coords, ps, w, h, 0, args.steps, args.warmup)
+    total = sum(times)
+    val = len(times) * ref.batch / total
+    sample = (f"{len(times)} timed batches of {ref.batch} patches ({ps}px RGBA -> 224^2) at seeded grid positions of "
+              f"the {w}x{h} synthetic slide, regenerated on the host; PIL/torchvision transform on min(cores,8) worker threads + frozen "
+              f"TorchScript ResNet34 fp32 + softmax, {ref.cores} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": len(times),
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(w, h, args.mpp, args.batch), "batch_per_step": ref.batch,
+                   "note": "bounded sample of the same workload; CPU batch 32 (reference default) or 128 on >16 cores"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.perf_counter() - t_all0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def load_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm_gbs": float(d["hbm_gbs"]), "tf_burst": float(d["bf16_tflops"]),
+                "tf_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback"}
+
+
+def b200_arm(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as ge
+
+    ge.build()
+    from oracle import forward as oforward   # only the model factory + config record (random-init weights)
+    from wsinsight_b200 import _cabi
+    from wsinsight_b200.modellib.data import PreprocessPlan
+    from wsinsight_b200.modellib.engine import B200Network
+    from wsinsight_b200.modellib.run_inference import HostPatchClassifier, shard_range
+    from wsinsight_b200.modellib.transforms import make_compose_from_transform_config
+    from wsinsight_b200.patchlib import segment_and_patch_slides_device
+    from wsinsight_b200.wsi import DeviceSlide
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _cabi.load()
+    peaks = load_peaks()
+    W, H = (int(v) for v in args.slide.lower().split("x"))
+    B, K, Wm = args.batch, args.steps, args.warmup
+    cfg = oforward.BREAST_RESNET34_CONFIG
+    transform = make_compose_from_transform_config(cfg["transform"])
+
+    def ev():
+        return torch.cuda.Event(enable_timing=True)
+
+    # ---- setup: slide in HBM, tissue segmentation + patchify (timed as its own stage) ----
+    t0 = time.perf_counter()
+    slide = DeviceSlide.synthetic(W, H, mpp=args.mpp, seed=0, device=dev)
+    thumb = slide.thumbnail_device((2048, 2048))
+    torch.cuda.synchronize()
+    t_gen = time.perf_counter() - t0
+    seg_ms = []
+    for i in range(4):
+        e0, e1 = ev(), ev()
+        e0.record()
+        res = segment_and_patch_slides_device([slide], cfg["patch_size_pixels"], cfg["spacing_um_px"], thumbs=[thumb])[0]
+        e1.record()
+        torch.cuda.synchronize()
+        seg_ms.append(e0.elapsed_time(e1))
+    ps = res.patch_size
+    coords_all = res.coords
+    n_total = int(coords_all.shape[0])
+    lo, hi = shard_range(n_total, rank, world)
+    coords = coords_all[lo:hi].contiguous()
+    n_local = int(coords.shape[0])
+    assert n_local >= B, f"rank {rank}: only {n_local} in-tissue patches for batch {B}"
+    nb_local = n_local // B
+
+    model = oforward.make_resnet34(2, 0)
+    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(model)), 2, input_size=224, max_batch=B,
+                                       device=dev)
+    lay = net.input_layout
+    plan = PreprocessPlan(slide, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"])
+    xin = net.alloc_input(B)
+    probs = torch.empty((nb_local * B, 2), dtype=torch.float32, device=dev)
+
+    def step(i):
+        b = i % nb_local
+        plan.run(coords[b * B:(b + 1) * B], xin)
+        net.forward_into(xin, probs[b * B:(b + 1) * B])
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timed region ----
+    for i in range(Wm):
+        step(i)
+    net.set_profiling(K)
+    pp_ev = [(ev(), ev()) for _ in range(K)]
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.3)
+    barrier()
+    launches0 = int(lib.wsi_launch_count())
+    c0 = sampler.mark()
+    e0, e1 = ev(), ev()
+    e0.record()
+    for i in range(K):
+        b = (Wm + i) % nb_local
+        pp_ev[i][0].record()
+        plan.run(coords[b * B:(b + 1) * B], xin)
+        pp_ev[i][1].record()
+        net.forward_into(xin, probs[b * B:(b + 1) * B])
+    e1.record()
+    barrier()
+    c1 = sampler.mark()
+    launches = int(lib.wsi_launch_count()) - launches0
+    ms = e0.elapsed_time(e1)
+    ops, nfwd = net.profile()
+    net.set_profiling(0)
+    pp_ms = sum(a.elapsed_time(b) for a, b in pp_ev)
+    tms = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_max = float(tms.item())
+    value = world * K * B / (ms_max * 1e-3)
+
+    # ---- e2e: host buffers through wsi_hostpipe_* ----
+    e2e = None
+    if not args.no_e2e:
+        hp = HostPatchClassifier(net, ps, transform, B, depth=2)
+        nbuf = min(4, nb_local)
+        host = []
+        for j in range(nbuf):
+            rgba, hprobs = hp.alloc_host_batch(B)
+            cj = coords[j * B:(j + 1) * B].cpu().numpy()
+            for i, (x, y) in enumerate(cj):
+                x1, y1 = min(x + ps, W), min(y + ps, H)
+                rgba[i, : y1 - y, : x1 - x].copy_(slide.rgba[y:y1, x:x1])
+            host.append((rgba, hprobs))
+        torch.cuda.synchronize()
+        for i in range(max(Wm, 2)):
+            hp.submit(*host[i % nbuf])
+        hp.sync()
+        h2d0, d2h0 = hp.bytes_copied()
+        barrier()
+        cs = hp.compute_stream
+        s0, s1 = ev(), ev()
+        tw0 = time.perf_counter()
+        s0.record(cs)
+        for i in range(K):
+            hp.submit(*host[(Wm + i) % nbuf])
+        s1.record(cs)
+        hp.sync()
+        tw1 = time.perf_counter()
+        barrier()
+        h2d1, d2h1 = hp.bytes_copied()
+        # the timed region ends when the last probabilities are on the host: take the larger of
+        # the device-event span and the host wall clock around submit..sync
+        e_ms = max(s0.elapsed_time(s1), (tw1 - tw0) * 1e3)
+        t2 = torch.tensor([e_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e_ms = float(t2.item())
+        # parity of the two entries on identical patches (device-resident vs host-buffer path)
+        ref_p = probs[: nbuf * B].cpu() if Wm + K >= nbuf else None
+        e2e = {"value": world * K * B / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // K,
+               "d2h_bytes_per_step": (d2h1 - d2h0) // K, "ms_per_step": e_ms / K, "in_flight": 2}
+        if ref_p is not None:
+            got = torch.cat([h[1] for h in host], 0)
+            e2e["max_abs_diff_vs_resident_path"] = float((got - ref_p).abs().max().item())
+        hp.close()
+    sampler.stop()
+    clocks = sampler.summary(c0, c1)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    if args.per_op:
+        for i, o in enumerate(ops):
+            tf = o["flops_per_image"] * B * nfwd / max(o["ms_total"], 1e-9) / 1e9
+            sys.stderr.write(f"op {i:3d} {o['kind']:8s} ms/step {o['ms_total'] / nfwd:8.4f}  GFLOP/img "
+                             f"{o['flops_per_image'] / 1e9:7.4f}  TFLOP/s {tf:8.1f}\n")
+    # ---- roofline of the dominant kernel: k_conv_igemm (tensor pipe) ----
+    conv_ms = sum(o["ms_total"] for o in ops if o["kind"] == "conv")
+    conv_fl = sum(o["flops_per_image"] for o in ops if o["kind"] == "conv")
+    n_conv = sum(1 for o in ops if o["kind"] == "conv")
+    other_ms = sum(o["ms_total"] for o in ops if o["kind"] != "conv")
+    achieved = conv_fl * B * nfwd / (conv_ms * 1e-3) / 1e12
+    roofline = {"kernel": "convk::k_conv_igemm (36 launches per step)", "bound": "tensor", "achieved": achieved,
+                "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
+                "traffic": None, "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
+                "flops_per_launch_avg": conv_fl * B / n_conv, "avg_launch_ms": conv_ms / (n_conv * nfwd),
+                "share_of_step": conv_ms / ms}
+    pp_bytes = ps * ps * 4 + 224 * 224 * 3 * 2     # read ps^2 RGBA + write S^2 x 3 bf16
+    stages = {
+        "preprocess": {"ms_per_step": pp_ms / K, "bound": "hbm", "achieved_gbs": pp_bytes * B * K / (pp_ms * 1e-3) / 1e9,
+                       "peak_gbs": peaks["hbm_gbs"], "frac": pp_bytes * B * K / (pp_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                       "bytes_per_patch": pp_bytes},
+        "conv": {"ms_per_step": conv_ms / nfwd},
+        "pool_head": {"ms_per_step": other_ms / nfwd},
+        "seg_patchify_ms_per_slide": min(seg_ms), "seg_patchify_ms_runs": seg_ms,
+        "slide_generation_s": t_gen, "in_tissue_patches": n_total, "patch_size": ps,
+    }
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(W, H, args.mpp, B), "batch_per_gpu": B, "global_batch": B * world,
+                   "patches_sharded": "contiguous x-bands of the x-major patch list, no data-path collective",
+                   "l2": "inputs larger than L2 (125 MB of source pixels + GBs of activations per step; "
+                         "consecutive steps read different patches)",
+                   "weights": "random-init torchvision resnet34(num_classes=2), jit.script+freeze, BN folded"},
+        "roofline": roofline, "stages": stages, "clocks": clocks, "gpu_launches": launches,
+        "tensor_pipe_frac_of_step": value / world * RESNET34_GFLOP * 1e9 / (peaks["tf_sustained"] * 1e12),
+    }
+    if e2e is not None:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args, coords_all, ps, W, H, thumb, res)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, coords_all, ps, W, H, thumb, res):
+    """Bounded CPU sample of the same workload on this box's host cores (rank 0, N=1)."""
+    import numpy as np
+
+    from oracle import patchgrid, segment
+
+    ref = CpuReference()
+    n = int(coords_all.shape[0])
+    rng = np.random.default_rng(0)
+    idx = np.sort(rng.choice(n, size=min(n, ref.batch * 40), replace=False))
+    coords = coords_all[idx].cpu().numpy().astype(np.int64)
+    times = time_cpu_reference(ref, coords, ps, W, H, 0, steps=38, warmup=2, budget_s=args.cpu_seconds)
+    val = len(times) * ref.batch / sum(times)
+    out = {"value": val, "unit": UNIT, "cores": ref.cores, "kind": "port",
+           "sample": (f"{len(times)} timed batches of {ref.batch} in-tissue patches ({ps}px RGBA -> 224^2, seeded sample of the "
+                      f"slide's patch list, pixels regenerated on the host); PIL/torchvision transform on "
+                      f"min(cores,8) worker threads + frozen TorchScript ResNet34 fp32 + softmax, {ref.cores} threads"),
+           "ms_per_batch": 1e3 * sum(times) / len(times), "batch": ref.batch}
+    # seg + patchify on the CPU (cv2 + scipy restatement + contour/point-in-polygon), same thumbnail
+    th = thumb.cpu().numpy()
+    t0 = time.perf_counter()
+    mask = segment.segment_tissue(th, 7, 7, 6, res.min_object_size_px, res.min_hole_size_px)
+    t1 = time.perf_counter()
+    xy = patchgrid.patch_coordinates(mask, W, H, ps, res.half_patch_size)
+    t2 = time.perf_counter()
+    out["seg_patchify_ms_per_slide"] = (t2 - t0) * 1e3
+    out["seg_ms"] = (t1 - t0) * 1e3
+    out["patchify_ms"] = (t2 - t1) * 1e3
+    out["seg_patchify_coords_equal_gpu"] = bool(np.array_equal(np.asarray(xy).astype(np.int64),
+                                                               coords_all.cpu().numpy().astype(np.int64)))
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # plain `python bench.py --gpus N`: re-launch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"),
+               str(Path(__file__).resolve())] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    b200_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

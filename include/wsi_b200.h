@@ -132,6 +132,9 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
 int wsi_net_encode_input_map(void* net, int op_index, const void* d_base);
 int wsi_net_tensor_ptr(void* net, int id, void** d_ptr, int* h_hwc3);
 int wsi_net_num_launches(void* net);
+/* geometry (H, W, C) of the external input tensor the preprocess kernel must write; K of the head */
+int wsi_net_input_geometry(void* net, int* h_hwc3);
+int wsi_net_num_classes(void* net);
 /* Per-op CUDA-event timing on the launching stream (bench roofline).  `slots` = number of most
  * recent forwards kept (0 disables).  wsi_net_profile_read synchronises the device and returns the
  * summed duration (ms) of each op over the recorded forwards, the op's flops per image and its kind
@@ -141,6 +144,29 @@ int wsi_net_profile_read(void* net, double* h_op_ms, double* h_op_flops, int* h_
                          int* h_forwards);
 double wsi_net_flops_per_image(void* net);
 void wsi_net_destroy(void* net);
+
+/* ---- host-buffer entry of the classification loop ------------------------------------------ */
+/* Replaces one iteration of `for batch_imgs, batch_coords in loader:` in
+ * wsinsight/modellib/run_inference.py:539-556 when the pixels are in HOST memory (what
+ * read_region returns, wsinsight/modellib/data.py:276-280): h_rgba holds n RGBA u8 patches of
+ * patch_size x patch_size pixels, patch i at h_rgba + i*patch_size*patch_pitch_bytes, rows
+ * patch_pitch_bytes apart (multiple of 16).  submit() enqueues H2D copy -> fused preprocess ->
+ * network forward -> D2H copy of the n x K probabilities into h_probs and returns at once; up to
+ * `depth` batches are in flight (copy of batch i+1 overlaps the kernels of batch i).  h_rgba must
+ * stay valid until the next sync(); h_probs is valid after sync().  Use pinned host memory
+ * (wsi_host_alloc_pinned) or the copies degrade to staged synchronous ones. */
+int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, int out_size,
+                        const float* mean, const float* stdv, int max_batch, int depth,
+                        void** pipe_out);
+int wsi_hostpipe_submit(void* pipe, const uint8_t* h_rgba, int n, float* h_probs);
+int wsi_hostpipe_sync(void* pipe);
+/* cudaStream_t the kernels of the pipe run on (for event timing by the caller) */
+void* wsi_hostpipe_compute_stream(void* pipe);
+/* bytes copied host->device / device->host since creation */
+int wsi_hostpipe_bytes(void* pipe, long long* h2d_bytes, long long* d2h_bytes);
+void wsi_hostpipe_destroy(void* pipe);
+int wsi_host_alloc_pinned(size_t bytes, void** h_ptr);
+int wsi_host_free_pinned(void* h_ptr);
 
 /* ---- utilities -------------------------------------------------------------------------- */
 /* Synthetic device-resident slide (bench/test input generator): fills an RGBA u8

@@ -61,12 +61,14 @@ def conv_reference(x, w, b, stride, pad, relu=False, residual=None):
     return y.float()
 
 
-def emulate_ir(nodes, x_nchw):
+def emulate_ir(nodes, x_nchw, accum=torch.float64):
     """CPU emulation of the B200 network numerics: bf16 weights/activations, fp32 accumulate.
 
     Runs the lowered IR (wsinsight_b200.modellib.lowering) node by node in torch and rounds every
     stored activation to bf16, exactly where the kernels do.  Returns ({node index: fp32 NCHW
-    activation}, probabilities).  Differences to the GPU are accumulation-order noise only.
+    activation}, probabilities).  Differences to the GPU are accumulation-order noise only; that
+    noise is amplified layer by layer (a bf16 rounding flip is 2^-8 relative), so callers calibrate
+    their tolerance by running the emulation twice, with ``accum`` fp64 and fp32.
     """
     import torch.nn.functional as F
 
@@ -77,10 +79,10 @@ def emulate_ir(nodes, x_nchw):
     for i in _topo_order(nodes):
         n = nodes[i]
         if n.kind == "conv":
-            y = F.conv2d(acts[n.inputs[0]].double(), bf16_round(n.weight).double(),
-                         None if n.bias is None else n.bias.double(), stride=n.stride, padding=tuple(n.pad))
+            y = F.conv2d(acts[n.inputs[0]].to(accum), bf16_round(n.weight).to(accum),
+                         None if n.bias is None else n.bias.to(accum), stride=n.stride, padding=tuple(n.pad))
             if n.residual is not None:
-                y = y + acts[n.residual].double()
+                y = y + acts[n.residual].to(accum)
             if n.relu:
                 y = torch.relu(y)
             acts[i] = bf16_round(y.float())

@@ -146,13 +146,20 @@ def test_resnet34_calibrated_unsaturated(K, B, maxb):
     want = forward_probs(m, x)
     assert p.shape == want.shape
     acts, pe = emulate_ir(net.nodes, x)
-    last = [i for i, n in enumerate(net.nodes) if n.kind == "conv"][-1]
-    a = net.activation(last, B).float().permute(0, 3, 1, 2).cpu()
-    rel = ((a - acts[last]).abs().mean() / acts[last].abs().mean()).item()
-    assert rel < 2e-2, f"last conv vs bf16 emulation: relative mean error {rel}"
+    # noise floor: the same emulation accumulating in fp32 instead of fp64 (rounding flips amplify
+    # through 36 layers: ~4e-2 at the last conv of this net for pure accumulation-order noise; the tensor-core accumulation
+    # order differs more from fp64 than a CPU fp32 sum does, hence the factor)
+    acts32, pe32 = emulate_ir(net.nodes, x, accum=torch.float32)
+    convs = [i for i, n in enumerate(net.nodes) if n.kind == "conv"]
+    for i in convs:
+        a = net.activation(i, B).float().permute(0, 3, 1, 2).cpu()
+        den = acts[i].abs().mean()
+        rel = ((a - acts[i]).abs().mean() / den).item()
+        floor = ((acts32[i] - acts[i]).abs().mean() / den).item()
+        assert rel <= max(1e-3, 5 * floor), f"conv node {i}: rel err {rel} vs emulation noise floor {floor}"
     d_emul = (p - pe).abs().max().item()
     d_fp32 = (p - want).abs().max().item()
     d_lib = (_torch_bf16_probs(m, x) - want).abs().max().item()
     print(f"K={K}: max|p-emul|={d_emul:.3e} max|p-fp32|={d_fp32:.3e} cuDNN-bf16 max|p-fp32|={d_lib:.3e}")
-    assert d_emul <= 3e-2
+    assert d_emul <= max(3e-2, 2.5 * (pe32 - pe).abs().max().item())
     assert d_fp32 <= max(2e-3, 1.25 * d_lib), (d_fp32, d_lib)

@@ -62,6 +62,17 @@ _PROTOS = {
     "wsi_net_encode_input_map": (c_int, [c_void_p, c_int, c_void_p]),
     "wsi_net_tensor_ptr": (c_int, [c_void_p, c_int, C.POINTER(c_void_p), c_int_p]),
     "wsi_net_num_launches": (c_int, [c_void_p]),
+    "wsi_net_input_geometry": (c_int, [c_void_p, c_int_p]),
+    "wsi_net_num_classes": (c_int, [c_void_p]),
+    "wsi_hostpipe_create": (c_int, [c_void_p, c_int, c_ll, c_int, c_float_p, c_float_p, c_int, c_int,
+                                    C.POINTER(c_void_p)]),
+    "wsi_hostpipe_submit": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "wsi_hostpipe_sync": (c_int, [c_void_p]),
+    "wsi_hostpipe_compute_stream": (c_void_p, [c_void_p]),
+    "wsi_hostpipe_bytes": (c_int, [c_void_p, c_ll_p, c_ll_p]),
+    "wsi_hostpipe_destroy": (None, [c_void_p]),
+    "wsi_host_alloc_pinned": (c_int, [c_size_t, C.POINTER(c_void_p)]),
+    "wsi_host_free_pinned": (c_int, [c_void_p]),
     "wsi_net_set_profiling": (c_int, [c_void_p, c_int]),
     "wsi_net_profile_read": (c_int, [c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), c_int_p, c_int,
                                      c_int_p]),

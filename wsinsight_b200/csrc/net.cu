@@ -554,6 +554,26 @@ int wsi_net_tensor_ptr(void* net, int id, void** ptr, int* hwc3) {
   return WSI_OK;
 }
 
+int wsi_net_input_geometry(void* net, int* hwc3) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && hwc3, "wsi_net_input_geometry: null pointer");
+  for (auto& t : n->tensors)
+    if (t.external) {
+      hwc3[0] = t.H; hwc3[1] = t.W; hwc3[2] = t.C;
+      return WSI_OK;
+    }
+  wsi_set_error("wsi_net_input_geometry: the network has no external input tensor");
+  return WSI_ERR_ARG;
+}
+
+int wsi_net_num_classes(void* net) {
+  Net* n = (Net*)net;
+  if (n)
+    for (auto& op : n->ops)
+      if (op.kind == OP_HEAD) return op.K;
+  return 0;
+}
+
 int wsi_net_num_launches(void* net) {
   Net* n = (Net*)net;
   return n ? n->launches_per_forward : 0;

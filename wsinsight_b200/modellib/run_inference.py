@@ -169,3 +169,70 @@ def run_inference(
             failed_inference.append(wsi_path)
             logger.error(f"Failed inference on {wsi_path}", exc_info=e)
     return failed_patching, failed_inference
+
+
+class HostPatchClassifier:
+    """Host-buffer form of the classification loop (run_inference.py:539-556).
+
+    ``submit(rgba, probs)`` takes a pinned uint8 CPU tensor ``(n, ps, pitch_px, 4)`` holding the
+    RGBA pixels ``read_region`` returned for ``n`` patches (rows padded to a multiple of 4 pixels)
+    and a pinned fp32 CPU tensor ``(n, K)`` that receives the probabilities after ``sync()``.
+    H2D copy, fused preprocess, forward and D2H copy run inside ``libwsi_b200`` on its own two
+    streams with ``depth`` batches in flight.
+    """
+
+    def __init__(self, net, patch_size: int, transform, max_batch: int, depth: int = 2):
+        import ctypes as C
+
+        torch = _cabi.require_cuda()
+        self.net, self.patch_size, self.max_batch = net, int(patch_size), int(max_batch)
+        self.pitch_px = (self.patch_size + 3) // 4 * 4
+        self.S = transform.out_size(patch_size)
+        self._h = C.c_void_p()
+        mean = _cabi.float_array(transform.mean) if transform.mean is not None else None
+        std = _cabi.float_array(transform.std) if transform.std is not None else None
+        with torch.cuda.device(net.device):
+            _cabi.call("wsi_hostpipe_create", net._h, self.patch_size, self.pitch_px * 4, self.S, mean, std,
+                       self.max_batch, int(depth), C.byref(self._h))
+
+    def alloc_host_batch(self, n: int = None):
+        """Pinned ``(n, ps, pitch_px, 4)`` uint8 and ``(n, K)`` fp32 host tensors."""
+        import torch
+
+        n = self.max_batch if n is None else int(n)
+        return (torch.zeros((n, self.patch_size, self.pitch_px, 4), dtype=torch.uint8).pin_memory(),
+                torch.zeros((n, self.net.num_classes), dtype=torch.float32).pin_memory())
+
+    def submit(self, rgba, probs):
+        n = int(rgba.shape[0])
+        assert rgba.dtype.is_floating_point is False and rgba.is_contiguous() and not rgba.is_cuda
+        assert tuple(rgba.shape[1:]) == (self.patch_size, self.pitch_px, 4)
+        assert probs.is_contiguous() and not probs.is_cuda and probs.numel() >= n * self.net.num_classes
+        _cabi.call("wsi_hostpipe_submit", self._h, rgba.data_ptr(), n, probs.data_ptr())
+
+    def sync(self):
+        _cabi.call("wsi_hostpipe_sync", self._h)
+
+    @property
+    def compute_stream(self):
+        import torch
+
+        return torch.cuda.ExternalStream(int(_cabi.load().wsi_hostpipe_compute_stream(self._h)), device=self.net.device)
+
+    def bytes_copied(self):
+        import ctypes as C
+
+        a, b = C.c_longlong(), C.c_longlong()
+        _cabi.call("wsi_hostpipe_bytes", self._h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
+
+    def close(self):
+        if self._h:
+            _cabi.load().wsi_hostpipe_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
