@@ -131,6 +131,13 @@ int wsi_net_finalize(void* net);
 int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void* stream);
 int wsi_net_encode_input_map(void* net, int op_index, const void* d_base);
 int wsi_net_tensor_ptr(void* net, int id, void** d_ptr, int* h_hwc3);
+/* Copy `batch` images between a dense bf16 [batch][H][W][C] device buffer and tensor `id`; the
+ * library may store a tensor with a one-pixel zero border (tensors touched by the flat 3x3 kernel),
+ * so raw wsi_net_tensor_ptr access is only meaningful through these two. */
+int wsi_net_read_tensor(void* net, int id, int batch, void* d_dense_out, void* stream);
+int wsi_net_write_tensor(void* net, int id, int batch, const void* d_dense_in, void* stream);
+/* 1 if op `op_index` is a conv that runs on the flat-slab kernel */
+int wsi_net_op_is_flat(void* net, int op_index);
 int wsi_net_num_launches(void* net);
 /* geometry (H, W, C) of the external input tensor the preprocess kernel must write; K of the head */
 int wsi_net_input_geometry(void* net, int* h_hwc3);

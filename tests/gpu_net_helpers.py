@@ -12,7 +12,7 @@ def bf16_round(t: torch.Tensor) -> torch.Tensor:
     return t.to(torch.bfloat16).float()
 
 
-def run_single_conv(x_nchw, w, b, stride, pad, relu=False, residual=None, max_batch=None):
+def run_single_conv(x_nchw, w, b, stride, pad, relu=False, residual=None, max_batch=None, expect_flat=None):
     """x: fp32 NCHW (values already bf16-representable).  Returns fp32 NCHW output of the B200 conv."""
     lib = _cabi.load()
     B, Cin, H, W = x_nchw.shape
@@ -23,7 +23,9 @@ def run_single_conv(x_nchw, w, b, stride, pad, relu=False, residual=None, max_ba
     _cabi.call("wsi_net_create", int(max_batch or B), C.byref(net))
     try:
         tin, tout, tres = C.c_int(), C.c_int(), C.c_int(-1)
-        _cabi.call("wsi_net_add_tensor", net, H, W, Cin, 1, C.byref(tin))
+        # the input is an internal tensor filled through wsi_net_write_tensor, so that eligible shapes
+        # take the flat-slab kernel exactly as they do inside a network
+        _cabi.call("wsi_net_add_tensor", net, H, W, Cin, 0, C.byref(tin))
         _cabi.call("wsi_net_add_tensor", net, Ho, Wo, Cout, 0, C.byref(tout))
         res_id = -1
         if residual is not None:
@@ -36,16 +38,15 @@ def run_single_conv(x_nchw, w, b, stride, pad, relu=False, residual=None, max_ba
                    1 if relu else 0, res_id)
         _cabi.call("wsi_net_finalize", net)
         xd = x_nchw.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+        _cabi.call("wsi_net_write_tensor", net, tin.value, B, xd.data_ptr(), _cabi.stream_ptr())
         if residual is not None:
-            ptr, hwc = C.c_void_p(), (C.c_int * 3)()
-            _cabi.call("wsi_net_tensor_ptr", net, res_id, C.byref(ptr), hwc)
             rd = residual.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
-            _cabi.call("wsi_memcpy_d2d", ptr, rd.data_ptr(), rd.numel() * 2, _cabi.stream_ptr())
-        _cabi.call("wsi_net_forward", net, xd.data_ptr(), B, None, _cabi.stream_ptr())
-        ptr, hwc = C.c_void_p(), (C.c_int * 3)()
-        _cabi.call("wsi_net_tensor_ptr", net, tout.value, C.byref(ptr), hwc)
+            _cabi.call("wsi_net_write_tensor", net, res_id, B, rd.data_ptr(), _cabi.stream_ptr())
+        _cabi.call("wsi_net_forward", net, None, B, None, _cabi.stream_ptr())
         out = torch.empty((B, Ho, Wo, Cout), dtype=torch.bfloat16, device="cuda")
-        _cabi.call("wsi_memcpy_d2d", out.data_ptr(), ptr, out.numel() * 2, _cabi.stream_ptr())
+        _cabi.call("wsi_net_read_tensor", net, tout.value, B, out.data_ptr(), _cabi.stream_ptr())
+        if expect_flat is not None:
+            assert bool(lib.wsi_net_op_is_flat(net, 0)) == expect_flat
         torch.cuda.synchronize()
         return out.float().permute(0, 3, 1, 2).cpu()
     finally:

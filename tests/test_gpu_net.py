@@ -48,6 +48,44 @@ def test_single_conv_vs_torch(B, Cin, H, Cout, k, stride, pad):
     _check(got, want, f"conv {B}x{Cin}x{H} -> {Cout} k{k} s{stride}")
 
 
+# 3x3/s1/p1 shapes that must take the flat-slab kernel (convf::k_conv_flat): ragged last tile, several
+# images per tile, Cin of 1/2 chunks, resident and streamed weights, Cout not a power of two
+FLAT_CASES = [
+    (2, 64, 56, 64),     # layer1: weights resident
+    (5, 128, 28, 128),   # layer2: 2 chunks, streamed weights
+    (3, 64, 35, 96),     # Inception-A branch shape
+    (1, 64, 24, 32),     # smallest eligible width, one image
+    (9, 192, 30, 64),    # 3 chunks
+]
+
+
+@pytest.mark.parametrize("B,Cin,H,Cout", FLAT_CASES)
+@pytest.mark.parametrize("relu_res", [False, True])
+def test_flat_conv_vs_torch(B, Cin, H, Cout, relu_res):
+    g = torch.Generator().manual_seed(B * 77 + Cin + H + Cout)
+    x = bf16_round(torch.randn((B, Cin, H, H), generator=g))
+    w = bf16_round(torch.randn((Cout, Cin, 3, 3), generator=g) / (Cin * 9) ** 0.5)
+    b = torch.randn(Cout, generator=g) * 0.1
+    r = bf16_round(torch.randn((B, Cout, H, H), generator=g)) if relu_res else None
+    got = run_single_conv(x, w, b, 1, 1, relu=relu_res, residual=r, expect_flat=True)
+    want = conv_reference(x, w, b, 1, 1, relu=relu_res, residual=r)
+    _check(got, want, f"flat conv {B}x{Cin}x{H} -> {Cout}")
+
+
+def test_flat_conv_matches_per_tap_kernel(monkeypatch):
+    """Same conv through both kernels: the flat-slab path and the per-tap TMA path agree bit for bit
+    up to fp32 accumulation order (identical operands, identical rounding point)."""
+    g = torch.Generator().manual_seed(11)
+    x = bf16_round(torch.randn((6, 64, 56, 56), generator=g))
+    w = bf16_round(torch.randn((64, 64, 3, 3), generator=g) / 24.0)
+    b = torch.randn(64, generator=g) * 0.1
+    flat = run_single_conv(x, w, b, 1, 1, relu=True, expect_flat=True)
+    monkeypatch.setenv("WSI_B200_NO_FLAT", "1")
+    tap = run_single_conv(x, w, b, 1, 1, relu=True, expect_flat=False)
+    assert (flat - tap).abs().max().item() <= 2.0 ** -7 * max(1.0, tap.abs().max().item())
+    assert (flat != tap).float().mean().item() < 1e-2
+
+
 def test_conv_residual_relu_epilogue():
     g = torch.Generator().manual_seed(7)
     x = bf16_round(torch.randn((8, 64, 28, 28), generator=g))

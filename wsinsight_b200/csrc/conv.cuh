@@ -37,6 +37,7 @@ struct Args {
   int stages;
   int out_C, out_c_off;                      // channels of the destination tensor / concat offset
   int res_C;                                 // channels of the residual tensor (0 = none)
+  int out_pad, res_pad;                      // one-pixel zero border of the destination / residual tensor (0|1)
   int relu;
   const __nv_bfloat16* residual;
   const float* bias;                         // [tiles_N * N_tile]
@@ -187,7 +188,8 @@ __global__ void __launch_bounds__(THREADS, 1)
       const int tn = mt / a.tiles_h;
       const int wo = tw * a.bw + w_l, ho = th * a.bh + h_l, n = tn * a.bn + n_l;
       const bool valid = (wo < a.Wo) && (ho < a.Ho) && (n < a.B);
-      const size_t pix = ((size_t)n * a.Ho + ho) * a.Wo + wo;
+      const size_t pix = ((size_t)n * (a.Ho + 2 * a.out_pad) + ho + a.out_pad) * (a.Wo + 2 * a.out_pad) + wo + a.out_pad;
+      const size_t rpix = ((size_t)n * (a.Ho + 2 * a.res_pad) + ho + a.res_pad) * (a.Wo + 2 * a.res_pad) + wo + a.res_pad;
       ptx::mbar_wait(&tfull[acc], acc_phase);
       ptx::tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256);
@@ -208,7 +210,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + b.w;
           }
           if (a.res_C) {
-            const uint4* rp = reinterpret_cast<const uint4*>(a.residual + pix * a.res_C + ch);
+            const uint4* rp = reinterpret_cast<const uint4*>(a.residual + rpix * a.res_C + ch);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               uint4 rv = __ldg(rp + i);

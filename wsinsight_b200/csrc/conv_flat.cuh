@@ -1,0 +1,256 @@
+// K4a': 3x3 / stride 1 / pad 1 convolution over a zero-PADDED NHWC activation, as a tcgen05
+// implicit GEMM whose nine taps are fed from ONE shared-memory slab per tile.
+//
+// Why: with per-tap TMA im2col boxes (conv.cuh) the input is re-read nine times from L2 and the
+// 128-byte-granular 4-D boxes cap the A-operand feed (ncu, profiles/r01_ncu_conv_baseline_summary.txt:
+// layer1 moves 5.55 GB L2->SM per launch for a 411 MB input; tensor pipe 19 % active).  Here the
+// activation is stored with a one-pixel zero border, [B][H+2][W+2][C], so that in FLAT pixel
+// index p = (n*(H+2) + h)*(W+2) + w the input of tap (kh,kw) for output p is simply row
+// p + (kh-1)*(W+2) + (kw-1): a pure row shift.  One contiguous 2-D TMA load brings rows
+// [q0 - (W+2) - 1, q0 + T*128 + (W+2) + 1) of a 64-channel chunk into a slab; every tap is an
+// MMA whose A descriptor START ADDRESS is moved by (kh*(W+2) + kw) rows.  tcgen05 applies the
+// 128B swizzle on absolute shared-memory address bits, so any 128-byte-row start works
+// (tools/umma_desc_probe.cu, profiles/r01_umma_desc_probe.txt).  Outputs are computed for every
+// padded position; border positions are simply not stored (they stay zero = the next conv's padding).
+//
+// T = 2 M-tiles (256 output positions) share each weight k-block, halving the B-operand feed;
+// small weight sets (<= 80 KB: ResNet layer1) stay RESIDENT in shared memory for the whole kernel.
+//
+// Warp roles as conv.cuh: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue.
+#pragma once
+#include "conv.cuh"
+
+namespace convf {
+
+constexpr int THREADS = 192;
+
+struct Args {
+  int Hp, Wp, H, W, B;          // padded / interior geometry (input == output == residual geometry)
+  long long total_rows;         // B * Hp * Wp flat positions
+  int num_tiles;                // super-tiles of T*128 positions
+  int T;                        // M-tiles per super-tile (1 or 2)
+  int N;                        // Cout (UMMA N, multiple of 16, <= 128)
+  int chunks;                   // Cin / 64
+  int resident_b;               // all 9*chunks weight k-blocks stay in smem
+  int slab_rows;                // rows per slab (multiple of 8)
+  int slab_loads, slab_box_rows;
+  int stagesA, stagesB;         // slab ring / weight ring (stagesB == 9*chunks when resident)
+  int relu, has_res;
+  int out_C, out_c_off;         // channels of the destination tensor / concat offset
+  const __nv_bfloat16* residual;
+  const float* bias;
+  __nv_bfloat16* out;
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+    k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const Args a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+  const int slab_bytes = a.slab_rows * 128;
+  const int b_bytes = a.N * 128;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + (size_t)a.stagesA * slab_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)a.stagesB * b_bytes);
+  uint64_t* aFull = bars;
+  uint64_t* aEmpty = aFull + a.stagesA;
+  uint64_t* bFull = aEmpty + a.stagesA;
+  uint64_t* bEmpty = bFull + a.stagesB;
+  uint64_t* tfull = bEmpty + a.stagesB;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int TM = a.T * 128;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmapA);
+    ptx::prefetch_tmap(&tmapB);
+    for (int s = 0; s < a.stagesA; ++s) {
+      ptx::mbar_init(&aFull[s], 1);
+      ptx::mbar_init(&aEmpty[s], 1);
+    }
+    for (int s = 0; s < a.stagesB; ++s) {
+      ptx::mbar_init(&bFull[s], 1);
+      ptx::mbar_init(&bEmpty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      bool first = true;
+      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+        const long long q0 = (long long)tile * TM;
+        const int row0 = (int)(q0 - a.Wp - 1);
+        for (int c = 0; c < a.chunks; ++c) {
+          ptx::mbar_wait(&aEmpty[sa], pa ^ 1);
+          ptx::mbar_arrive_expect_tx(&aFull[sa], (uint32_t)slab_bytes);
+          for (int i = 0; i < a.slab_loads; ++i)
+            ptx::tma_load_2d(sA + (size_t)sa * slab_bytes + (size_t)i * a.slab_box_rows * 128, &tmapA, &aFull[sa],
+                             c * 64, row0 + i * a.slab_box_rows);
+          if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
+          if (a.resident_b) {
+            if (first)
+              for (int tap = 0; tap < 9; ++tap) {
+                const int kb = tap * a.chunks + c;
+                ptx::mbar_arrive_expect_tx(&bFull[kb], (uint32_t)b_bytes);
+                ptx::tma_load_2d(sB + (size_t)kb * b_bytes, &tmapB, &bFull[kb], kb * 64, 0);
+              }
+          } else {
+            for (int tap = 0; tap < 9; ++tap) {
+              const int kb = tap * a.chunks + c;
+              ptx::mbar_wait(&bEmpty[sb], pb ^ 1);
+              ptx::mbar_arrive_expect_tx(&bFull[sb], (uint32_t)b_bytes);
+              ptx::tma_load_2d(sB + (size_t)sb * b_bytes, &tmapB, &bFull[sb], kb * 64, 0);
+              if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
+            }
+          }
+        }
+        first = false;
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = ptx::make_idesc_bf16(128, a.N);
+      int sa = 0, sb = 0, acc = 0;
+      uint32_t pa = 0, pb = 0, pacc = 0;
+      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+        ptx::mbar_wait(&tempty[acc], pacc ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * a.T * a.N);
+        for (int c = 0; c < a.chunks; ++c) {
+          ptx::mbar_wait(&aFull[sa], pa);
+          ptx::tc_fence_after();
+          const uint32_t slab = ptx::smem_u32(sA + (size_t)sa * slab_bytes);
+          for (int tap = 0; tap < 9; ++tap) {
+            const int kh = tap / 3, kw = tap - kh * 3;
+            uint32_t bAddr;
+            if (a.resident_b) {
+              const int kb = tap * a.chunks + c;
+              ptx::mbar_wait(&bFull[kb], 0);      // completes once; parity 0 stays satisfied afterwards
+              bAddr = ptx::smem_u32(sB + (size_t)kb * b_bytes);
+            } else {
+              ptx::mbar_wait(&bFull[sb], pb);
+              bAddr = ptx::smem_u32(sB + (size_t)sb * b_bytes);
+            }
+            ptx::tc_fence_after();
+            const uint64_t dB = ptx::make_sw128_desc(bAddr);
+            const uint32_t shift = (uint32_t)((kh * a.Wp + kw) * 128);
+            for (int t = 0; t < a.T; ++t) {
+              const uint64_t dA = ptx::make_sw128_desc(slab + shift + (uint32_t)(t * 128 * 128));
+              for (int k = 0; k < 4; ++k)
+                ptx::umma_bf16(d_tmem + (uint32_t)(t * a.N), dA + (uint64_t)(2 * k), dB + (uint64_t)(2 * k), idesc,
+                               (c | tap | k) != 0);
+            }
+            if (!a.resident_b) {
+              ptx::umma_commit(&bEmpty[sb]);
+              if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
+            }
+          }
+          ptx::umma_commit(&aEmpty[sa]);
+          if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
+        }
+        ptx::umma_commit(&tfull[acc]);
+        if (++acc == 2) { acc = 0; pacc ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int img = a.Hp * a.Wp;
+    int acc = 0;
+    uint32_t pacc = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+      const long long q0 = (long long)tile * TM;
+      ptx::mbar_wait(&tfull[acc], pacc);
+      ptx::tc_fence_after();
+      for (int t = 0; t < a.T; ++t) {
+        const long long p = q0 + t * 128 + row;
+        const int n = (int)(p / img);
+        const int rem = (int)(p - (long long)n * img);
+        const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
+        const bool valid = (n < a.B) && (hp >= 1) && (hp <= a.H) && (wp >= 1) && (wp <= a.W);
+        const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + t) * a.N);
+        for (int c0 = 0; c0 < a.N; c0 += 32) {
+          uint32_t r[32];
+          ptx::tmem_ld_32x32b_x32(t_addr + (uint32_t)c0, r);
+          ptx::tmem_ld_wait();
+          if (valid) {
+            const float4* b4 = reinterpret_cast<const float4*>(a.bias + c0);
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float4 b = __ldg(b4 + i);
+              v[4 * i + 0] = __uint_as_float(r[4 * i + 0]) + b.x;
+              v[4 * i + 1] = __uint_as_float(r[4 * i + 1]) + b.y;
+              v[4 * i + 2] = __uint_as_float(r[4 * i + 2]) + b.z;
+              v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + b.w;
+            }
+            if (a.has_res) {
+              const uint4* rp = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N + c0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                uint4 rv = __ldg(rp + i);
+                v[8 * i + 0] += convk::bf16_lo(rv.x); v[8 * i + 1] += convk::bf16_hi(rv.x);
+                v[8 * i + 2] += convk::bf16_lo(rv.y); v[8 * i + 3] += convk::bf16_hi(rv.y);
+                v[8 * i + 4] += convk::bf16_lo(rv.z); v[8 * i + 5] += convk::bf16_hi(rv.z);
+                v[8 * i + 6] += convk::bf16_lo(rv.w); v[8 * i + 7] += convk::bf16_hi(rv.w);
+              }
+            }
+            if (a.relu) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.0f);
+            }
+            uint4* op = reinterpret_cast<uint4*>(a.out + (size_t)p * a.out_C + a.out_c_off + c0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              uint4 o;
+              o.x = convk::pack_bf16(v[8 * i + 0], v[8 * i + 1]);
+              o.y = convk::pack_bf16(v[8 * i + 2], v[8 * i + 3]);
+              o.z = convk::pack_bf16(v[8 * i + 4], v[8 * i + 5]);
+              o.w = convk::pack_bf16(v[8 * i + 6], v[8 * i + 7]);
+              op[i] = o;
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+      if (++acc == 2) { acc = 0; pacc ^= 1; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+static inline size_t smem_bytes(const Args& a) {
+  return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * a.N * 128 +
+         (size_t)(2 * a.stagesA + 2 * a.stagesB + 4) * 8 + 16;
+}
+
+}  // namespace convf

@@ -4,17 +4,22 @@
 // (wsinsight/modellib/run_inference.py:537-560) for the zoo CNNs (ResNet34, InceptionV4):
 // the Python side walks the (frozen) TorchScript graph, hands folded conv weights/biases
 // to wsi_net_add_*, and every forward runs only kernels from this library.
-#include "conv.cuh"
+#include "conv_flat.cuh"
 #include "../../include/wsi_b200.h"
 #include <math.h>
+#include <stdlib.h>
 #include <vector>
 
 namespace {
 
 struct Tensor {
   int H, W, C;
-  __nv_bfloat16* ptr = nullptr;   // [max_batch][H][W][C]; nullptr for the external input
+  __nv_bfloat16* ptr = nullptr;   // [max_batch][H+2*pad][W+2*pad][C]; nullptr for the external input
   bool external = false;
+  int pad = 0;                    // one-pixel zero border (tensors touched by the flat 3x3 conv kernel)
+  int Hp() const { return H + 2 * pad; }
+  int Wp() const { return W + 2 * pad; }
+  size_t interior_offset() const { return ((size_t)pad * Wp() + pad) * C; }   // elements to pixel (0,0)
 };
 
 enum OpKind { OP_CONV, OP_MAXPOOL, OP_AVGPOOL, OP_HEAD };
@@ -24,6 +29,8 @@ struct Op {
   int in, out, res;
   // conv
   convk::Args ca;
+  convf::Args fa;
+  bool flat = false;              // 3x3/s1/p1 over padded tensors -> convf::k_conv_flat
   CUtensorMap tmA, tmB;
   __nv_bfloat16* d_w = nullptr;
   float* d_bias = nullptr;
@@ -47,6 +54,7 @@ struct Net {
   std::vector<Tensor> tensors;
   std::vector<Op> ops;
   int num_sms = 148;
+  bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
   int prof_slots = 0;
@@ -60,8 +68,9 @@ struct Net {
 __device__ __forceinline__ float bflo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bfhi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
+// ip / op: one-pixel zero border of the input / output tensor (0|1); `in`/`out` point at the buffer start
 __global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
-                          int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off) {
+                          int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int ip, int op) {
   const int cv = C / 8;
   size_t total = (size_t)B * Ho * Wo * cv;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -81,7 +90,7 @@ __global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
     for (int dx = 0; dx < k; ++dx) {
       int x = wo * s - pad + dx;
       if (x < 0 || x >= W) continue;
-      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * H + y) * W + x) * C) + c8);
+      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * (H + 2 * ip) + y + ip) * (W + 2 * ip) + x + ip) * C) + c8);
       m[0] = fmaxf(m[0], bflo(v.x)); m[1] = fmaxf(m[1], bfhi(v.x));
       m[2] = fmaxf(m[2], bflo(v.y)); m[3] = fmaxf(m[3], bfhi(v.y));
       m[4] = fmaxf(m[4], bflo(v.z)); m[5] = fmaxf(m[5], bfhi(v.z));
@@ -93,12 +102,12 @@ __global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
   o.y = convk::pack_bf16(m[2], m[3]);
   o.z = convk::pack_bf16(m[4], m[5]);
   o.w = convk::pack_bf16(m[6], m[7]);
-  reinterpret_cast<uint4*>(out + (((size_t)n * Ho + ho) * Wo + wo) * out_C + out_c_off)[c8] = o;
+  reinterpret_cast<uint4*>(out + (((size_t)n * (Ho + 2 * op) + ho + op) * (Wo + 2 * op) + wo + op) * out_C + out_c_off)[c8] = o;
 }
 
 __global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
                           int count_include_pad, int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C,
-                          int out_c_off) {
+                          int out_c_off, int ip, int op) {
   const int cv = C / 8;
   size_t total = (size_t)B * Ho * Wo * cv;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -120,7 +129,7 @@ __global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
       int x = wo * s - pad + dx;
       if (x < 0 || x >= W) continue;
       ++cnt;
-      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * H + y) * W + x) * C) + c8);
+      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * (H + 2 * ip) + y + ip) * (W + 2 * ip) + x + ip) * C) + c8);
       m[0] += bflo(v.x); m[1] += bfhi(v.x); m[2] += bflo(v.y); m[3] += bfhi(v.y);
       m[4] += bflo(v.z); m[5] += bfhi(v.z); m[6] += bflo(v.w); m[7] += bfhi(v.w);
     }
@@ -133,7 +142,7 @@ __global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
   o.y = convk::pack_bf16(m[2], m[3]);
   o.z = convk::pack_bf16(m[4], m[5]);
   o.w = convk::pack_bf16(m[6], m[7]);
-  reinterpret_cast<uint4*>(out + (((size_t)n * Ho + ho) * Wo + wo) * out_C + out_c_off)[c8] = o;
+  reinterpret_cast<uint4*>(out + (((size_t)n * (Ho + 2 * op) + ho + op) * (Wo + 2 * op) + wo + op) * out_C + out_c_off)[c8] = o;
 }
 
 // K4d: global average pool + FC + softmax (K>1) / sigmoid (K==1); one CTA per image.
@@ -184,6 +193,22 @@ __global__ void __launch_bounds__(HEAD_THREADS)
   }
 }
 
+// dense [B][H][W][C] <-> interior of a padded [B][H+2p][W+2p][C] tensor, 16 bytes per thread
+__global__ void k_copy_interior(const uint4* __restrict__ src, uint4* __restrict__ dst, int B, int H, int W, int C8,
+                                int pad, int to_padded) {
+  size_t total = (size_t)B * H * W * C8;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int c = idx % C8;
+  size_t p = idx / C8;
+  int w = p % W;
+  p /= W;
+  int h = p % H;
+  int n = p / H;
+  size_t pi = (((size_t)n * (H + 2 * pad) + h + pad) * (W + 2 * pad) + w + pad) * C8 + c;
+  if (to_padded) dst[pi] = src[idx]; else dst[idx] = src[pi];
+}
+
 void pick_box(int Wo, int Ho, int* bw, int* bh, int* bn) {
   int w = 8;
   while (w > 1 && (Wo % w) != 0) w >>= 1;
@@ -213,6 +238,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   cudaGetDevice(&dev);
   int sms = 0;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0) n->num_sms = sms;
+  const char* nf = getenv("WSI_B200_NO_FLAT");
+  n->flat_enabled = !(nf && nf[0] == '1');
   *net_out = n;
   return WSI_OK;
 }
@@ -356,13 +383,34 @@ int wsi_net_finalize(void* net) {
   Net* n = (Net*)net;
   WSI_ARG_CHECK(n && !n->finalized, "wsi_net_finalize: bad state");
   const int B = n->max_batch;
+  // which convs run on the flat-slab kernel, and which tensors therefore carry a zero border
+  for (auto& op : n->ops) {
+    op.flat = false;
+    if (op.kind != OP_CONV || op.is_stem || !n->flat_enabled) continue;
+    const Tensor& ti = n->tensors[op.in];
+    bool ok = op.KH == 3 && op.KW == 3 && op.stride == 1 && op.pad_h == 1 && op.pad_w == 1 && op.Cin % 64 == 0 &&
+              ti.C == op.Cin && op.Cout % 32 == 0 && op.Cout <= 128 && !ti.external && ti.W >= 24 && ti.H >= 8;
+    if (op.res >= 0 && (n->tensors[op.res].C != op.Cout || n->tensors[op.res].external)) ok = false;
+    op.flat = ok;
+  }
+  for (auto& op : n->ops)
+    if (op.flat) {
+      n->tensors[op.in].pad = 1;
+      n->tensors[op.out].pad = 1;
+      if (op.res >= 0) n->tensors[op.res].pad = 1;
+    }
+  for (auto& op : n->ops)
+    if (op.kind == OP_HEAD && n->tensors[op.in].pad) {
+      wsi_set_error("wsi_net_finalize: the head cannot read a padded tensor");
+      return WSI_ERR_UNSUPPORTED;
+    }
   for (auto& t : n->tensors) {
     if (t.external) continue;
-    size_t bytes = (size_t)B * t.H * t.W * t.C * sizeof(__nv_bfloat16);
+    size_t bytes = (size_t)B * t.Hp() * t.Wp() * t.C * sizeof(__nv_bfloat16);
     WSI_CUDA_CHECK(cudaMalloc(&t.ptr, bytes));
     WSI_CUDA_CHECK(cudaMemset(t.ptr, 0, bytes));
   }
-  int max_smem = 0;
+  int max_smem = 0, max_smem_flat = 0;
   for (auto& op : n->ops) {
     if (op.kind == OP_CONV) {
       const Tensor& ti = n->tensors[op.in];
@@ -373,6 +421,49 @@ int wsi_net_finalize(void* net) {
       WSI_CUDA_CHECK(cudaMalloc(&op.d_bias, op.h_bias.size() * sizeof(float)));
       WSI_CUDA_CHECK(cudaMemcpy(op.d_bias, op.h_bias.data(), op.h_bias.size() * sizeof(float),
                                 cudaMemcpyHostToDevice));
+      if (op.flat) {
+        convf::Args& f = op.fa;
+        memset(&f, 0, sizeof(f));
+        f.Hp = ti.Hp(); f.Wp = ti.Wp(); f.H = ti.H; f.W = ti.W;
+        f.N = op.Cout;
+        f.chunks = op.Cin / 64;
+        f.T = 2;
+        f.resident_b = (size_t)9 * f.chunks * f.N * 128 <= 80 * 1024;
+        f.stagesB = f.resident_b ? 9 * f.chunks : 4;
+        const int rows_needed = f.T * 128 + 2 * f.Wp + 2;
+        f.slab_loads = (rows_needed + 255) / 256;
+        f.slab_box_rows = ((rows_needed + f.slab_loads - 1) / f.slab_loads + 7) / 8 * 8;
+        f.slab_rows = f.slab_loads * f.slab_box_rows;
+        const long long budget = 220 * 1024 - 2048 - (long long)f.stagesB * f.N * 128;
+        f.stagesA = (int)(budget / ((long long)f.slab_rows * 128));
+        if (f.stagesA > 4) f.stagesA = 4;
+        WSI_ARG_CHECK(f.stagesA >= 2 && f.slab_box_rows <= 256, "wsi_net_finalize: flat conv does not fit shared memory");
+        f.relu = op.relu;
+        f.has_res = op.res >= 0;
+        f.bias = op.d_bias;
+        f.out_C = to.C; f.out_c_off = op.out_c_off;
+        int smem = (int)convf::smem_bytes(f);
+        if (smem > max_smem_flat) max_smem_flat = smem;
+        {
+          uint64_t dims[2] = {(uint64_t)op.Ktot, (uint64_t)op.Cout};
+          uint64_t strides[1] = {(uint64_t)op.Ktot * 2};
+          uint32_t box[2] = {64, (uint32_t)f.N};
+          uint32_t es[2] = {1, 1};
+          int rc = wsi_make_tmap(&op.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op.d_w, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+        }
+        {
+          uint64_t dims[2] = {(uint64_t)ti.C, (uint64_t)B * ti.Hp() * ti.Wp()};
+          uint64_t strides[1] = {(uint64_t)ti.C * 2};
+          uint32_t box[2] = {64, (uint32_t)f.slab_box_rows};
+          uint32_t es[2] = {1, 1};
+          int rc = wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ti.ptr, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+        }
+        continue;
+      }
       convk::Args& a = op.ca;
       memset(&a, 0, sizeof(a));
       pick_box(to.W, to.H, &a.bw, &a.bh, &a.bn);
@@ -391,6 +482,8 @@ int wsi_net_finalize(void* net) {
       a.stages = stages;
       a.out_C = to.C; a.out_c_off = op.out_c_off;
       a.res_C = op.res >= 0 ? n->tensors[op.res].C : 0;
+      a.out_pad = to.pad;
+      a.res_pad = op.res >= 0 ? n->tensors[op.res].pad : 0;
       a.relu = op.relu;
       a.bias = op.d_bias;
       int smem = (int)convk::smem_bytes(a.N_tile, a.stages);
@@ -419,6 +512,8 @@ int wsi_net_finalize(void* net) {
   }
   if (max_smem > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  if (max_smem_flat > 0)
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
   n->launches_per_forward = (int)n->ops.size();
   n->finalized = true;
   return WSI_OK;
@@ -444,8 +539,11 @@ int wsi_net_encode_input_map(void* net, int op_index, const void* base) {
     return wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, es,
                          CU_TENSOR_MAP_SWIZZLE_64B);
   }
+  // a padded tensor is addressed from its interior pixel (0,0) with the padded pitches; TMA's
+  // out-of-bounds zero fill then stands in for the border exactly as for a dense tensor
+  base = (const __nv_bfloat16*)base + ti.interior_offset();
   uint64_t dims[4] = {(uint64_t)ti.C, (uint64_t)ti.W, (uint64_t)ti.H, B};
-  uint64_t strides[3] = {(uint64_t)ti.C * 2, (uint64_t)ti.W * ti.C * 2, (uint64_t)ti.H * ti.W * ti.C * 2};
+  uint64_t strides[3] = {(uint64_t)ti.C * 2, (uint64_t)ti.Wp() * ti.C * 2, (uint64_t)ti.Hp() * ti.Wp() * ti.C * 2};
   uint32_t box[4] = {64, (uint32_t)(a.bw * a.stride), (uint32_t)(a.bh * a.stride), (uint32_t)a.bn};
   uint32_t es[4] = {1, (uint32_t)a.stride, (uint32_t)a.stride, 1};
   return wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, es,
@@ -472,6 +570,17 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         if (rc) return rc;
       }
       const Tensor& to = n->tensors[op.out];
+      if (op.flat) {
+        convf::Args f = op.fa;
+        f.B = B;
+        f.total_rows = (long long)B * f.Hp * f.Wp;
+        f.num_tiles = (int)((f.total_rows + f.T * 128 - 1) / (f.T * 128));
+        f.out = to.ptr;
+        f.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
+        int grid = f.num_tiles < n->num_sms ? f.num_tiles : n->num_sms;
+        convf::k_conv_flat<<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, f);
+        continue;
+      }
       convk::Args a = op.ca;
       a.B = B;
       a.tiles_n = wsi_cdiv(B, a.bn);
@@ -487,10 +596,11 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       int blocks = (int)((total + 255) / 256);
       if (op.kind == OP_MAXPOOL)
         k_maxpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, to.H, to.W,
-                                              to.ptr, to.C, op.out_c_off);
+                                              to.ptr, to.C, op.out_c_off, ti.pad, to.pad);
       else
         k_avgpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
-                                              op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off);
+                                              op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.pad,
+                                              to.pad);
     } else if (op.kind == OP_HEAD) {
       WSI_ARG_CHECK(d_probs, "wsi_net_forward: null probs");
       k_head<<<B, HEAD_THREADS, ti.C * sizeof(float), stream>>>(in_ptr, ti.H * ti.W, ti.C, op.d_fcw, op.d_fcb, op.K,
@@ -552,6 +662,37 @@ int wsi_net_tensor_ptr(void* net, int id, void** ptr, int* hwc3) {
     hwc3[0] = n->tensors[id].H; hwc3[1] = n->tensors[id].W; hwc3[2] = n->tensors[id].C;
   }
   return WSI_OK;
+}
+
+// copy `batch` images between a dense bf16 [batch][H][W][C] device buffer and tensor `id` (whatever its padding)
+static int copy_tensor(void* net, int id, int batch, void* d_dense, int to_tensor, void* stream_) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && n->finalized && id >= 0 && id < (int)n->tensors.size() && d_dense, "wsi_net_read/write_tensor: bad arguments");
+  const Tensor& t = n->tensors[id];
+  WSI_ARG_CHECK(t.ptr && batch >= 1 && batch <= n->max_batch && t.C % 8 == 0, "wsi_net_read/write_tensor: bad tensor");
+  size_t total = (size_t)batch * t.H * t.W * (t.C / 8);
+  int blocks = (int)((total + 255) / 256);
+  if (to_tensor)
+    k_copy_interior<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const uint4*)d_dense, (uint4*)t.ptr, batch, t.H, t.W, t.C / 8, t.pad, 1);
+  else
+    k_copy_interior<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const uint4*)t.ptr, (uint4*)d_dense, batch, t.H, t.W, t.C / 8, t.pad, 0);
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
+int wsi_net_read_tensor(void* net, int id, int batch, void* d_dense_out, void* stream) {
+  return copy_tensor(net, id, batch, d_dense_out, 0, stream);
+}
+
+int wsi_net_write_tensor(void* net, int id, int batch, const void* d_dense_in, void* stream) {
+  return copy_tensor(net, id, batch, (void*)d_dense_in, 1, stream);
+}
+
+// 1 if conv op `op_index` runs on the flat-slab kernel (convf::k_conv_flat)
+int wsi_net_op_is_flat(void* net, int op_index) {
+  Net* n = (Net*)net;
+  if (!n || op_index < 0 || op_index >= (int)n->ops.size()) return 0;
+  return n->ops[op_index].flat ? 1 : 0;
 }
 
 int wsi_net_input_geometry(void* net, int* hwc3) {

@@ -206,7 +206,8 @@ class B200Network:
         h, w, c = int(hwc[0]), int(hwc[1]), int(hwc[2])
         out = torch.empty((batch, h, w, c), dtype=torch.bfloat16, device=self.device)
         with torch.cuda.device(self.device):
-            _cabi.call("wsi_memcpy_d2d", out.data_ptr(), ptr.value, batch * h * w * c * 2, _cabi.stream_ptr())
+            _cabi.call("wsi_net_read_tensor", self._h, self._tensor_of[node_index], int(batch), out.data_ptr(),
+                       _cabi.stream_ptr())
         return out
 
     def set_profiling(self, slots: int):
