@@ -51,6 +51,44 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
+// Epilogue of one 64-column chunk of a 128-row accumulator tile, staged for a TMA store:
+// TMEM -> registers -> (+bias, +residual from its smem staging, ReLU) -> bf16 -> shared memory in the
+// SWIZZLE_128B layout of a [128 rows][64 ch] box (16-byte chunk c of row r lives at r*128 + ((c ^ (r&7))<<4)),
+// so that a quarter warp covers all 32 banks and ONE bulk tensor store writes the tile with full
+// 128-byte lines (the per-thread 16-byte stores at a row pitch it replaces were the bottleneck of
+// every layer with N <= 128).  `keep` false writes zeros (border rows of the padded flat layout).
+__device__ __forceinline__ void epi_chunk64(uint32_t t_addr, int row, bool keep, uint32_t s_out, uint32_t s_res,
+                                            const float* s_bias, int relu) {
+  uint32_t r[64];
+  ptx::tmem_ld_32x32b_x32(t_addr, r);
+  ptx::tmem_ld_32x32b_x32(t_addr + 32u, r + 32);
+  ptx::tmem_ld_wait();
+  const uint32_t row_base = (uint32_t)row * 128u;
+  const uint32_t sw = (uint32_t)row & 7u;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
+    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
+    float v0 = __uint_as_float(r[8 * c + 0]) + b0.x, v1 = __uint_as_float(r[8 * c + 1]) + b0.y;
+    float v2 = __uint_as_float(r[8 * c + 2]) + b0.z, v3 = __uint_as_float(r[8 * c + 3]) + b0.w;
+    float v4 = __uint_as_float(r[8 * c + 4]) + b1.x, v5 = __uint_as_float(r[8 * c + 5]) + b1.y;
+    float v6 = __uint_as_float(r[8 * c + 6]) + b1.z, v7 = __uint_as_float(r[8 * c + 7]) + b1.w;
+    const uint32_t off = row_base + (((uint32_t)c ^ sw) << 4);
+    if (s_res) {
+      const uint4 rv = ptx::ld_shared_v4(s_res + off);
+      v0 += bf16_lo(rv.x); v1 += bf16_hi(rv.x); v2 += bf16_lo(rv.y); v3 += bf16_hi(rv.y);
+      v4 += bf16_lo(rv.z); v5 += bf16_hi(rv.z); v6 += bf16_lo(rv.w); v7 += bf16_hi(rv.w);
+    }
+    if (relu) {
+      v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
+      v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
+    }
+    uint32_t o0 = pack_bf16(v0, v1), o1 = pack_bf16(v2, v3), o2 = pack_bf16(v4, v5), o3 = pack_bf16(v6, v7);
+    if (!keep) o0 = o1 = o2 = o3 = 0u;
+    ptx::st_shared_v4(s_out + off, o0, o1, o2, o3);
+  }
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_igemm(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                  const Args a) {
@@ -97,20 +135,20 @@ __global__ void __launch_bounds__(THREADS, 1)
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int nt = tile % a.tiles_N;
-        int mt = tile / a.tiles_N;
-        const int tw = mt % a.tiles_w;
-        mt /= a.tiles_w;
-        const int th = mt % a.tiles_h;
-        const int tn = mt / a.tiles_h;
-        const int wo0 = tw * a.bw, ho0 = th * a.bh, n0 = tn * a.bn;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&empty[stage], phase ^ 1);
+    // ===================== TMA producer (whole warp loops, one elected lane issues) =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int nt = tile % a.tiles_N;
+      int mt = tile / a.tiles_N;
+      const int tw = mt % a.tiles_w;
+      mt /= a.tiles_w;
+      const int th = mt % a.tiles_h;
+      const int tn = mt / a.tiles_h;
+      const int wo0 = tw * a.bw, ho0 = th * a.bh, n0 = tn * a.bn;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(&empty[stage], phase ^ 1);
+        if (ptx::elect_one()) {
           ptx::mbar_arrive_expect_tx(&full[stage], (uint32_t)((BLOCK_M + a.N_tile) * kbytes));
           void* dA = sA + (size_t)stage * A_BYTES;
           void* dB = sB + (size_t)stage * B_BYTES;
@@ -126,48 +164,51 @@ __global__ void __launch_bounds__(THREADS, 1)
                              ho0 * a.stride + kh - a.pad_h, n0);
             ptx::tma_load_2d(dB, &tmapB, &full[stage], kb * BLOCK_K, nt * a.N_tile);
           }
-          if (++stage == a.stages) {
-            stage = 0;
-            phase ^= 1;
-          }
+        }
+        __syncwarp();
+        if (++stage == a.stages) {
+          stage = 0;
+          phase ^= 1;
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, a.N_tile);
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        ptx::mbar_wait(&tempty[acc], acc_phase ^ 1);
+    // ===================== MMA issuer (whole warp loops; tcgen05 under elect.sync) =====================
+    const uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, a.N_tile);
+    const uint32_t hi = a.is_stem ? ptx::sw64_desc_hi() : ptx::sw128_desc_hi();
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(&tempty[acc], acc_phase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(&full[stage], phase);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&full[stage], phase);
-          ptx::tc_fence_after();
-          const uint32_t aA = ptx::smem_u32(sA + (size_t)stage * A_BYTES);
-          const uint32_t aB = ptx::smem_u32(sB + (size_t)stage * B_BYTES);
-          const uint64_t dA = a.is_stem ? ptx::make_sw64_desc(aA) : ptx::make_sw128_desc(aA);
-          const uint64_t dB = a.is_stem ? ptx::make_sw64_desc(aB) : ptx::make_sw128_desc(aB);
-          const int nk = a.is_stem ? 2 : 4;
-          for (int k = 0; k < nk; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in 16-byte units
-            ptx::umma_bf16(d_tmem, dA + (uint64_t)(2 * k), dB + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+        const uint32_t a_lo = ptx::desc_lo(ptx::smem_u32(sA + (size_t)stage * A_BYTES));
+        const uint32_t b_lo = ptx::desc_lo(ptx::smem_u32(sB + (size_t)stage * B_BYTES));
+        if (ptx::elect_one()) {
+          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in 16-byte units
+          ptx::umma_bf16_lohi(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != 0));
+          ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+          if (!a.is_stem) {
+            ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+            ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
           }
           ptx::umma_commit(&empty[stage]);   // frees the smem slot once these MMAs retire
-          if (++stage == a.stages) {
-            stage = 0;
-            phase ^= 1;
-          }
+          if (kb == num_kb - 1) ptx::umma_commit(&tfull[acc]);   // accumulator ready for the epilogue
         }
-        ptx::umma_commit(&tfull[acc]);       // accumulator ready for the epilogue
-        if (++acc == 2) {
-          acc = 0;
-          acc_phase ^= 1;
+        __syncwarp();
+        if (++stage == a.stages) {
+          stage = 0;
+          phase ^= 1;
         }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
       }
     }
   } else {

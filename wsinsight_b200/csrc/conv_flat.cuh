@@ -37,13 +37,16 @@ struct Args {
   int stagesA, stagesB;         // slab ring / weight ring (stagesB == 9*chunks when resident)
   int relu, has_res;
   int out_C, out_c_off;         // channels of the destination tensor / concat offset
+  int tma_epi;                  // N % 64 == 0: epilogue staged in smem and written by TMA stores
+  int nOut, nRes;               // staging buffers (16 KB each) for output chunks / residual chunks
   const __nv_bfloat16* residual;
   const float* bias;
   __nv_bfloat16* out;
 };
 
 __global__ void __launch_bounds__(THREADS, 1)
-    k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, const Args a) {
+    k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
+                const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapR, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -51,14 +54,18 @@ __global__ void __launch_bounds__(THREADS, 1)
   const int b_bytes = a.N * 128;
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)a.stagesA * slab_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)a.stagesB * b_bytes);
+  uint8_t* sOut = sB + (size_t)a.stagesB * b_bytes;                 // nOut x 16 KB (1024-aligned)
+  uint8_t* sRes = sOut + (size_t)a.nOut * 16384;                    // nRes x 16 KB
+  float* sBias = reinterpret_cast<float*>(sRes + (size_t)a.nRes * 16384);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 128);
   uint64_t* aFull = bars;
   uint64_t* aEmpty = aFull + a.stagesA;
   uint64_t* bFull = aEmpty + a.stagesA;
   uint64_t* bEmpty = bFull + a.stagesB;
   uint64_t* tfull = bEmpty + a.stagesB;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* resFull = tempty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resFull + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int TM = a.T * 128;
@@ -77,6 +84,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
       ptx::mbar_init(&tempty[s], 4);
+      ptx::mbar_init(&resFull[s], 1);
     }
     ptx::fence_barrier_init();
   }
@@ -91,7 +99,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    {
       int sa = 0, sb = 0;
       uint32_t pa = 0, pb = 0;
       bool first = true;
@@ -100,24 +108,31 @@ __global__ void __launch_bounds__(THREADS, 1)
         const int row0 = (int)(q0 - a.Wp - 1);
         for (int c = 0; c < a.chunks; ++c) {
           ptx::mbar_wait(&aEmpty[sa], pa ^ 1);
-          ptx::mbar_arrive_expect_tx(&aFull[sa], (uint32_t)slab_bytes);
-          for (int i = 0; i < a.slab_loads; ++i)
-            ptx::tma_load_2d(sA + (size_t)sa * slab_bytes + (size_t)i * a.slab_box_rows * 128, &tmapA, &aFull[sa],
-                             c * 64, row0 + i * a.slab_box_rows);
+          if (ptx::elect_one()) {
+            ptx::mbar_arrive_expect_tx(&aFull[sa], (uint32_t)slab_bytes);
+            for (int i = 0; i < a.slab_loads; ++i)
+              ptx::tma_load_2d(sA + (size_t)sa * slab_bytes + (size_t)i * a.slab_box_rows * 128, &tmapA, &aFull[sa],
+                               c * 64, row0 + i * a.slab_box_rows);
+          }
+          __syncwarp();
           if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
           if (a.resident_b) {
-            if (first)
+            if (first && ptx::elect_one())
               for (int tap = 0; tap < 9; ++tap) {
                 const int kb = tap * a.chunks + c;
                 ptx::mbar_arrive_expect_tx(&bFull[kb], (uint32_t)b_bytes);
                 ptx::tma_load_2d(sB + (size_t)kb * b_bytes, &tmapB, &bFull[kb], kb * 64, 0);
               }
+            __syncwarp();
           } else {
             for (int tap = 0; tap < 9; ++tap) {
               const int kb = tap * a.chunks + c;
               ptx::mbar_wait(&bEmpty[sb], pb ^ 1);
-              ptx::mbar_arrive_expect_tx(&bFull[sb], (uint32_t)b_bytes);
-              ptx::tma_load_2d(sB + (size_t)sb * b_bytes, &tmapB, &bFull[sb], kb * 64, 0);
+              if (ptx::elect_one()) {
+                ptx::mbar_arrive_expect_tx(&bFull[sb], (uint32_t)b_bytes);
+                ptx::tma_load_2d(sB + (size_t)sb * b_bytes, &tmapB, &bFull[sb], kb * 64, 0);
+              }
+              __syncwarp();
               if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
             }
           }
@@ -127,49 +142,64 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = ptx::make_idesc_bf16(128, a.N);
-      int sa = 0, sb = 0, acc = 0;
-      uint32_t pa = 0, pb = 0, pacc = 0;
-      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        ptx::mbar_wait(&tempty[acc], pacc ^ 1);
-        ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * a.T * a.N);
-        for (int c = 0; c < a.chunks; ++c) {
-          ptx::mbar_wait(&aFull[sa], pa);
-          ptx::tc_fence_after();
-          const uint32_t slab = ptx::smem_u32(sA + (size_t)sa * slab_bytes);
-          for (int tap = 0; tap < 9; ++tap) {
-            const int kh = tap / 3, kw = tap - kh * 3;
-            uint32_t bAddr;
-            if (a.resident_b) {
-              const int kb = tap * a.chunks + c;
-              ptx::mbar_wait(&bFull[kb], 0);      // completes once; parity 0 stays satisfied afterwards
-              bAddr = ptx::smem_u32(sB + (size_t)kb * b_bytes);
-            } else {
-              ptx::mbar_wait(&bFull[sb], pb);
-              bAddr = ptx::smem_u32(sB + (size_t)sb * b_bytes);
-            }
-            ptx::tc_fence_after();
-            const uint64_t dB = ptx::make_sw128_desc(bAddr);
-            const uint32_t shift = (uint32_t)((kh * a.Wp + kw) * 128);
-            for (int t = 0; t < a.T; ++t) {
-              const uint64_t dA = ptx::make_sw128_desc(slab + shift + (uint32_t)(t * 128 * 128));
-              for (int k = 0; k < 4; ++k)
-                ptx::umma_bf16(d_tmem + (uint32_t)(t * a.N), dA + (uint64_t)(2 * k), dB + (uint64_t)(2 * k), idesc,
-                               (c | tap | k) != 0);
-            }
-            if (!a.resident_b) {
-              ptx::umma_commit(&bEmpty[sb]);
-              if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
-            }
+    // The whole warp runs the loop (warp-uniform control flow); the tcgen05 instructions sit under
+    // elect.sync so that ptxas emits them straight-line (an `if (lane == 0)` region makes it wrap
+    // every UTCHMMA in an elect/branch loop: ~100 cycles per MMA, 3x the N=64 MMA itself).
+    const uint32_t idesc = ptx::make_idesc_bf16(128, a.N);
+    const uint32_t hi = ptx::sw128_desc_hi();
+    int sa = 0, sb = 0, acc = 0;
+    uint32_t pa = 0, pb = 0, pacc = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(&tempty[acc], pacc ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * a.T * a.N);
+      for (int c = 0; c < a.chunks; ++c) {
+        ptx::mbar_wait(&aFull[sa], pa);
+        const uint32_t slab_lo = ptx::desc_lo(ptx::smem_u32(sA + (size_t)sa * slab_bytes));
+        for (int tap = 0; tap < 9; ++tap) {
+          const int kh = tap / 3, kw = tap - kh * 3;
+          uint32_t b_lo;
+          if (a.resident_b) {
+            const int kb = tap * a.chunks + c;
+            ptx::mbar_wait(&bFull[kb], 0);      // completes once; parity 0 stays satisfied afterwards
+            b_lo = ptx::desc_lo(ptx::smem_u32(sB + (size_t)kb * b_bytes));
+          } else {
+            ptx::mbar_wait(&bFull[sb], pb);
+            b_lo = ptx::desc_lo(ptx::smem_u32(sB + (size_t)sb * b_bytes));
           }
-          ptx::umma_commit(&aEmpty[sa]);
-          if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
+          ptx::tc_fence_after();
+          const uint32_t a_lo = slab_lo + (uint32_t)((kh * a.Wp + kw) * 8);   // rows * 128 B >> 4
+          if (ptx::elect_one()) {
+            if (a.T == 2) {
+              const uint32_t first = (uint32_t)((c | tap) != 0);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, first);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+              const uint32_t d1 = d_tmem + (uint32_t)a.N, a1 = a_lo + 1024u;   // second M-tile: +128 rows
+              ptx::umma_bf16_lohi(d1, a1 + 0, b_lo + 0, hi, idesc, first);
+              ptx::umma_bf16_lohi(d1, a1 + 2, b_lo + 2, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
+            } else {
+              const uint32_t first = (uint32_t)((c | tap) != 0);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, first);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+            }
+            if (!a.resident_b) ptx::umma_commit(&bEmpty[sb]);
+            if (tap == 8) ptx::umma_commit(&aEmpty[sa]);
+            if (tap == 8 && c == a.chunks - 1) ptx::umma_commit(&tfull[acc]);
+          }
+          __syncwarp();
+          if (!a.resident_b) {
+            if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
+          }
         }
-        ptx::umma_commit(&tfull[acc]);
-        if (++acc == 2) { acc = 0; pacc ^= 1; }
+        if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
       }
+      if (++acc == 2) { acc = 0; pacc ^= 1; }
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
@@ -178,6 +208,68 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int img = a.Hp * a.Wp;
     int acc = 0;
     uint32_t pacc = 0;
+    if (a.tma_epi) {
+      const int et = (int)threadIdx.x - 64;            // 0..127 among the epilogue warps
+      const bool leader = et == 0;
+      const int cn = a.N >> 6;                          // 64-column chunks per accumulator tile
+      const int per_tile = a.T * cn;
+      if (et < a.N) sBias[et] = a.bias[et];
+      // residual chunk k of this CTA -> (super-tile, t, j); issued by the leader nRes chunks ahead
+      auto issue_res = [&](int k) {
+        const int tile = blockIdx.x + (k / per_tile) * gridDim.x;
+        if (tile >= a.num_tiles) return;
+        const int w = k % per_tile, t = w / cn, j = w - t * cn;
+        const int b = k % a.nRes;
+        ptx::mbar_arrive_expect_tx(&resFull[b], 16384u);
+        ptx::tma_load_2d(sRes + (size_t)b * 16384, &tmapR, &resFull[b], 64 * j, (int)((long long)tile * TM + t * 128));
+      };
+      if (leader && a.has_res)
+        for (int k = 0; k < a.nRes; ++k) issue_res(k);
+      ptx::named_bar_sync(1, 128);                      // bias staged
+      int k = 0;
+      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+        const long long q0 = (long long)tile * TM;
+        ptx::mbar_wait(&tfull[acc], pacc);
+        ptx::tc_fence_after();
+        for (int t = 0; t < a.T; ++t) {
+          const long long p = q0 + t * 128 + row;
+          const int n = (int)(p / img);
+          const int rem = (int)(p - (long long)n * img);
+          const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
+          const bool valid = (n < a.B) && (hp >= 1) && (hp <= a.H) && (wp >= 1) && (wp <= a.W);
+          for (int j = 0; j < cn; ++j, ++k) {
+            const int ob = a.nOut == 2 ? (k & 1) : 0;
+            if (leader) {
+              if (a.nOut == 2) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<0>();
+            }
+            ptx::named_bar_sync(1, 128);                // staging buffer ob is free again
+            uint32_t s_res = 0;
+            if (a.has_res) {
+              const int rb = k % a.nRes;
+              ptx::mbar_wait(&resFull[rb], (uint32_t)((k / a.nRes) & 1));
+              s_res = ptx::smem_u32(sRes + (size_t)rb * 16384);
+            }
+            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + t) * a.N + 64 * j);
+            convk::epi_chunk64(t_addr, row, valid, ptx::smem_u32(sOut + (size_t)ob * 16384), s_res, sBias + 64 * j,
+                               a.relu);
+            if (t == a.T - 1 && j == cn - 1) {          // accumulator stage fully read: hand it back
+              ptx::tc_fence_before();
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+            }
+            ptx::fence_proxy_async();
+            ptx::named_bar_sync(1, 128);                // tile chunk staged, residual buffer consumed
+            if (leader) {
+              ptx::tma_store_2d(&tmapO, sOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)(q0 + t * 128));
+              ptx::bulk_commit();
+              if (a.has_res) issue_res(k + a.nRes);
+            }
+          }
+        }
+        if (++acc == 2) { acc = 0; pacc ^= 1; }
+      }
+      if (leader) ptx::bulk_wait<0>();
+    } else
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
       const long long q0 = (long long)tile * TM;
       ptx::mbar_wait(&tfull[acc], pacc);
@@ -250,7 +342,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
 static inline size_t smem_bytes(const Args& a) {
   return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * a.N * 128 +
-         (size_t)(2 * a.stagesA + 2 * a.stagesB + 4) * 8 + 16;
+         (size_t)(a.nOut + a.nRes) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
 }
 
 }  // namespace convf

@@ -31,7 +31,7 @@ struct Op {
   convk::Args ca;
   convf::Args fa;
   bool flat = false;              // 3x3/s1/p1 over padded tensors -> convf::k_conv_flat
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmO, tmR;
   __nv_bfloat16* d_w = nullptr;
   float* d_bias = nullptr;
   std::vector<__nv_bfloat16> h_w;
@@ -434,14 +434,48 @@ int wsi_net_finalize(void* net) {
         f.slab_loads = (rows_needed + 255) / 256;
         f.slab_box_rows = ((rows_needed + f.slab_loads - 1) / f.slab_loads + 7) / 8 * 8;
         f.slab_rows = f.slab_loads * f.slab_box_rows;
-        const long long budget = 220 * 1024 - 2048 - (long long)f.stagesB * f.N * 128;
-        f.stagesA = (int)(budget / ((long long)f.slab_rows * 128));
-        if (f.stagesA > 4) f.stagesA = 4;
+        f.tma_epi = (op.Cout % 64 == 0) ? 1 : 0;
+        // shared-memory plan: prefer resident weights and double-buffered epilogue staging; give up
+        // the second output staging buffer, then weight residency, before dropping below 2 slabs
+        const int want_res = (f.tma_epi && op.res >= 0) ? 2 : 0;
+        const int plans[4][2] = {{1, 2}, {1, 1}, {0, 2}, {0, 1}};   // {resident weights, nOut}
+        for (auto& pl : plans) {
+          if (pl[0] && !f.resident_b) continue;
+          const int sB = pl[0] ? 9 * f.chunks : 4;
+          const int nOut = f.tma_epi ? pl[1] : 0;
+          const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(nOut + want_res) * 16384;
+          int sA = (int)(budget / ((long long)f.slab_rows * 128));
+          if (sA > 4) sA = 4;
+          f.stagesA = sA; f.stagesB = sB; f.nOut = nOut; f.nRes = want_res;
+          if (sA >= 2) {
+            f.resident_b = pl[0];
+            break;
+          }
+        }
         WSI_ARG_CHECK(f.stagesA >= 2 && f.slab_box_rows <= 256, "wsi_net_finalize: flat conv does not fit shared memory");
         f.relu = op.relu;
         f.has_res = op.res >= 0;
         f.bias = op.d_bias;
         f.out_C = to.C; f.out_c_off = op.out_c_off;
+        op.tmO = op.tmB;
+        op.tmR = op.tmB;
+        if (f.tma_epi) {
+          uint64_t dims[2] = {(uint64_t)to.C, (uint64_t)B * to.Hp() * to.Wp()};
+          uint64_t strides[1] = {(uint64_t)to.C * 2};
+          uint32_t box[2] = {64, 128};
+          uint32_t es[2] = {1, 1};
+          int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+          if (op.res >= 0) {
+            const Tensor& tr = n->tensors[op.res];
+            uint64_t rdims[2] = {(uint64_t)tr.C, (uint64_t)B * tr.Hp() * tr.Wp()};
+            uint64_t rstrides[1] = {(uint64_t)tr.C * 2};
+            rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr, rdims, rstrides, box, es,
+                               CU_TENSOR_MAP_SWIZZLE_128B);
+            if (rc) return rc;
+          }
+        }
         int smem = (int)convf::smem_bytes(f);
         if (smem > max_smem_flat) max_smem_flat = smem;
         {
@@ -578,7 +612,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         f.out = to.ptr;
         f.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
         int grid = f.num_tiles < n->num_sms ? f.num_tiles : n->num_sms;
-        convf::k_conv_flat<<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, f);
+        convf::k_conv_flat<<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmR, f);
         continue;
       }
       convk::Args a = op.ca;
