@@ -38,7 +38,8 @@ def _nvcc() -> str:
 
 def _digest() -> str:
     h = hashlib.sha256()
-    for name in SOURCES + HEADERS:
+    names = sorted({*SOURCES, *HEADERS, *(f.name for f in CSRC.glob("*.cu*"))})
+    for name in names:
         h.update((CSRC / name).read_bytes())
     h.update(" ".join(NVCC_FLAGS).encode())
     return h.hexdigest()

@@ -44,6 +44,88 @@ struct Args {
   __nv_bfloat16* out;
 };
 
+// MMA issue loop of the flat kernel, specialised on T (M-tiles per super-tile) and weight residency so
+// that the nine taps unroll into straight-line UTCHMMA sequences: the issuing warp, not the tensor pipe,
+// was the limiter (ncu: ~975 cycles per tap for 256-512 cycles of MMA work) while the loop carried
+// runtime branches, constant reloads and one elect region per tap.
+struct MmaCtx {
+  uint32_t sA_lo, sB_lo;          // descriptor low words of slab 0 / weight block 0
+  uint32_t slab_step, b_step;     // (bytes >> 4) between slabs / weight blocks
+  uint32_t row_step;              // Wp * 8: one image row of the padded layout in descriptor units
+  uint32_t tmem_base, idesc, hi;
+  int N, chunks, stagesA, stagesB, num_tiles;
+  uint64_t *aFull, *aEmpty, *bFull, *bEmpty, *tfull, *tempty;
+};
+
+template <int T>
+__device__ __forceinline__ void issue_tap(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                                          uint32_t accum_first, uint32_t N) {
+  ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, accum_first);
+  ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+  ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+  ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+  if (T == 2) {
+    const uint32_t d1 = d_tmem + N, a1 = a_lo + 1024u;   // second M-tile: +128 rows of 128 B (>> 4)
+    ptx::umma_bf16_lohi(d1, a1 + 0, b_lo + 0, hi, idesc, accum_first);
+    ptx::umma_bf16_lohi(d1, a1 + 2, b_lo + 2, hi, idesc, 1u);
+    ptx::umma_bf16_lohi(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
+    ptx::umma_bf16_lohi(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
+  }
+}
+
+template <int T, bool RESIDENT>
+__device__ __forceinline__ void mma_loop(const MmaCtx& m) {
+  int sa = 0, sb = 0, acc = 0;
+  uint32_t pa = 0, pb = 0, pacc = 0;
+  bool first_tile = true;
+  for (int tile = blockIdx.x; tile < m.num_tiles; tile += gridDim.x) {
+    ptx::mbar_wait(&m.tempty[acc], pacc ^ 1);
+    const uint32_t d_tmem = m.tmem_base + (uint32_t)(acc * T) * (uint32_t)m.N;
+    for (int c = 0; c < m.chunks; ++c) {
+      ptx::mbar_wait(&m.aFull[sa], pa);
+      const uint32_t slab_lo = m.sA_lo + (uint32_t)sa * m.slab_step;
+      const bool last_c = c == m.chunks - 1;
+      if (RESIDENT) {
+        if (first_tile)
+          for (int tap = 0; tap < 9; ++tap) ptx::mbar_wait(&m.bFull[tap * m.chunks + c], 0);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const uint32_t a_lo = slab_lo + (uint32_t)(tap / 3) * m.row_step + (uint32_t)(tap % 3) * 8u;
+            const uint32_t b_lo = m.sB_lo + (uint32_t)(tap * m.chunks + c) * m.b_step;
+            issue_tap<T>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
+          }
+          ptx::umma_commit(&m.aEmpty[sa]);
+          if (last_c) ptx::umma_commit(&m.tfull[acc]);
+        }
+        __syncwarp();
+      } else {
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          ptx::mbar_wait(&m.bFull[sb], pb);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            const uint32_t a_lo = slab_lo + (uint32_t)(tap / 3) * m.row_step + (uint32_t)(tap % 3) * 8u;
+            const uint32_t b_lo = m.sB_lo + (uint32_t)sb * m.b_step;
+            issue_tap<T>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
+            ptx::umma_commit(&m.bEmpty[sb]);
+            if (tap == 8) {
+              ptx::umma_commit(&m.aEmpty[sa]);
+              if (last_c) ptx::umma_commit(&m.tfull[acc]);
+            }
+          }
+          __syncwarp();
+          if (++sb == m.stagesB) { sb = 0; pb ^= 1; }
+        }
+      }
+      if (++sa == m.stagesA) { sa = 0; pa ^= 1; }
+    }
+    first_tile = false;
+    if (++acc == 2) { acc = 0; pacc ^= 1; }
+  }
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                 const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapR, const Args a) {
@@ -145,61 +227,21 @@ __global__ void __launch_bounds__(THREADS, 1)
     // The whole warp runs the loop (warp-uniform control flow); the tcgen05 instructions sit under
     // elect.sync so that ptxas emits them straight-line (an `if (lane == 0)` region makes it wrap
     // every UTCHMMA in an elect/branch loop: ~100 cycles per MMA, 3x the N=64 MMA itself).
-    const uint32_t idesc = ptx::make_idesc_bf16(128, a.N);
-    const uint32_t hi = ptx::sw128_desc_hi();
-    int sa = 0, sb = 0, acc = 0;
-    uint32_t pa = 0, pb = 0, pacc = 0;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-      ptx::mbar_wait(&tempty[acc], pacc ^ 1);
-      ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * a.T * a.N);
-      for (int c = 0; c < a.chunks; ++c) {
-        ptx::mbar_wait(&aFull[sa], pa);
-        const uint32_t slab_lo = ptx::desc_lo(ptx::smem_u32(sA + (size_t)sa * slab_bytes));
-        for (int tap = 0; tap < 9; ++tap) {
-          const int kh = tap / 3, kw = tap - kh * 3;
-          uint32_t b_lo;
-          if (a.resident_b) {
-            const int kb = tap * a.chunks + c;
-            ptx::mbar_wait(&bFull[kb], 0);      // completes once; parity 0 stays satisfied afterwards
-            b_lo = ptx::desc_lo(ptx::smem_u32(sB + (size_t)kb * b_bytes));
-          } else {
-            ptx::mbar_wait(&bFull[sb], pb);
-            b_lo = ptx::desc_lo(ptx::smem_u32(sB + (size_t)sb * b_bytes));
-          }
-          ptx::tc_fence_after();
-          const uint32_t a_lo = slab_lo + (uint32_t)((kh * a.Wp + kw) * 8);   // rows * 128 B >> 4
-          if (ptx::elect_one()) {
-            if (a.T == 2) {
-              const uint32_t first = (uint32_t)((c | tap) != 0);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, first);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
-              const uint32_t d1 = d_tmem + (uint32_t)a.N, a1 = a_lo + 1024u;   // second M-tile: +128 rows
-              ptx::umma_bf16_lohi(d1, a1 + 0, b_lo + 0, hi, idesc, first);
-              ptx::umma_bf16_lohi(d1, a1 + 2, b_lo + 2, hi, idesc, 1u);
-              ptx::umma_bf16_lohi(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
-              ptx::umma_bf16_lohi(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
-            } else {
-              const uint32_t first = (uint32_t)((c | tap) != 0);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, first);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
-              ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
-            }
-            if (!a.resident_b) ptx::umma_commit(&bEmpty[sb]);
-            if (tap == 8) ptx::umma_commit(&aEmpty[sa]);
-            if (tap == 8 && c == a.chunks - 1) ptx::umma_commit(&tfull[acc]);
-          }
-          __syncwarp();
-          if (!a.resident_b) {
-            if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
-          }
-        }
-        if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
-      }
-      if (++acc == 2) { acc = 0; pacc ^= 1; }
+    MmaCtx m;
+    m.sA_lo = ptx::desc_lo(ptx::smem_u32(sA));
+    m.sB_lo = ptx::desc_lo(ptx::smem_u32(sB));
+    m.slab_step = (uint32_t)slab_bytes >> 4;
+    m.b_step = (uint32_t)b_bytes >> 4;
+    m.row_step = (uint32_t)a.Wp * 8u;
+    m.tmem_base = tmem_base;
+    m.idesc = ptx::make_idesc_bf16(128, a.N);
+    m.hi = ptx::sw128_desc_hi();
+    m.N = a.N; m.chunks = a.chunks; m.stagesA = a.stagesA; m.stagesB = a.stagesB; m.num_tiles = a.num_tiles;
+    m.aFull = aFull; m.aEmpty = aEmpty; m.bFull = bFull; m.bEmpty = bEmpty; m.tfull = tfull; m.tempty = tempty;
+    if (a.T == 2) {
+      if (a.resident_b) mma_loop<2, true>(m); else mma_loop<2, false>(m);
+    } else {
+      if (a.resident_b) mma_loop<1, true>(m); else mma_loop<1, false>(m);
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================

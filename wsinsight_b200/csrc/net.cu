@@ -428,6 +428,10 @@ int wsi_net_finalize(void* net) {
         f.N = op.Cout;
         f.chunks = op.Cin / 64;
         f.T = 2;
+        if (const char* e = getenv("WSI_FLAT_T")) f.T = atoi(e) == 1 ? 1 : 2;      // tuning knobs (bench only)
+        int force_nout = 0, force_res = -1;
+        if (const char* e = getenv("WSI_FLAT_NOUT")) force_nout = atoi(e);
+        if (const char* e = getenv("WSI_FLAT_RESIDENT")) force_res = atoi(e);
         f.resident_b = (size_t)9 * f.chunks * f.N * 128 <= 80 * 1024;
         f.stagesB = f.resident_b ? 9 * f.chunks : 4;
         const int rows_needed = f.T * 128 + 2 * f.Wp + 2;
@@ -441,6 +445,8 @@ int wsi_net_finalize(void* net) {
         const int plans[4][2] = {{1, 2}, {1, 1}, {0, 2}, {0, 1}};   // {resident weights, nOut}
         for (auto& pl : plans) {
           if (pl[0] && !f.resident_b) continue;
+          if (force_nout && pl[1] != force_nout) continue;
+          if (force_res >= 0 && pl[0] != force_res) continue;
           const int sB = pl[0] ? 9 * f.chunks : 4;
           const int nOut = f.tma_epi ? pl[1] : 0;
           const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(nOut + want_res) * 16384;
