@@ -309,7 +309,8 @@ def b200_arm(args, rank, world, local_rank):
     net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(model)), 2, input_size=224, max_batch=B,
                                        device=dev)
     lay = net.input_layout
-    plan = PreprocessPlan(slide, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"])
+    plan = PreprocessPlan(slide, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"],
+                          lay["plane_stride_px"])
     xin = net.alloc_input(B)
     probs = torch.empty((nb_local * B, 2), dtype=torch.float32, device=dev)
 

@@ -105,6 +105,10 @@ int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_b
 /* debug/parity: the u8 result of the resize alone, [n][S][S][4] (RGB0) */
 int wsi_preproc_run_u8(void* plan, const int32_t* d_coords_xy, int n, uint8_t* d_out_u8,
                        void* stream);
+/* plane_stride_px > 0 switches the output to the layout the parity-plane stem kernel reads (see
+ * wsi_net_input_layout): two row-parity planes, bf16 [2][max_batch][P][2P][4] with P = out_H/2, planes
+ * plane_stride_px pixels apart; 0 restores [n][out_H][out_W][4]. */
+int wsi_preproc_plan_set_parity_layout(void* plan, long long plane_stride_px);
 int wsi_preproc_plan_info(void* plan, int* info8);
 void wsi_preproc_plan_destroy(void* plan);
 
@@ -142,6 +146,12 @@ int wsi_net_num_launches(void* net);
 /* geometry (H, W, C) of the external input tensor the preprocess kernel must write; K of the head */
 int wsi_net_input_geometry(void* net, int* h_hwc3);
 int wsi_net_num_classes(void* net);
+/* h_info4[0] = layout of the external input: 0 = bf16 [B][H][W][4] (geometry of wsi_net_input_geometry),
+ * 1 = two row-parity planes of pixel pairs, bf16 [2][max_batch][P][P][8] (7x7/2 stems with 64 filters);
+ * h_info4[1] = P; h_info4[2], h_info4[3] = low / high 32 bits of the plane stride in pixels.
+ * wsi_net_input_bytes = bytes to allocate for that buffer (max_batch images + read slack). */
+int wsi_net_input_layout(void* net, int* h_info4);
+size_t wsi_net_input_bytes(void* net);
 /* Per-op CUDA-event timing on the launching stream (bench roofline).  `slots` = number of most
  * recent forwards kept (0 disables).  wsi_net_profile_read synchronises the device and returns the
  * summed duration (ms) of each op over the recorded forwards, the op's flops per image and its kind

@@ -134,7 +134,7 @@ def test_resnet34_layerwise_and_probs():
     x = _resnet_inputs(B, 224, 1)
     net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(m)), 2, input_size=224, max_batch=B)
     assert abs(net.flops_per_image / 1e9 - 7.326) < 0.15 or net.flops_per_image > 7e9
-    probs = net(_padded_nhwc4(x)).cpu()
+    probs = net(net.pack_input(x), B).cpu()
     # layer-wise diagnostics against fp32 torch (loose: activations are stored in bf16)
     with torch.no_grad():
         a = torch.relu(m.bn1(m.conv1(x)))
@@ -180,7 +180,7 @@ def test_resnet34_calibrated_unsaturated(K, B, maxb):
     m = make_resnet34_calibrated(K, 0)
     x = _resnet_inputs(B, 224, 5)
     net = B200Network.from_torchscript(torch.jit.script(m), K, input_size=224, max_batch=maxb)
-    p = net(_padded_nhwc4(x)).cpu()
+    p = net(net.pack_input(x), B).cpu()
     want = forward_probs(m, x)
     assert p.shape == want.shape
     acts, pe = emulate_ir(net.nodes, x)

@@ -19,7 +19,7 @@ for (K, seed, B, maxb) in [(1, 3, 5, 8), (2, 0, 16, 16), (1, 3, 8, 8)]:
     g = torch.Generator().manual_seed(2)
     x = bf16_round(torch.randn((B, 3, 224, 224), generator=g) * 1.5)
     net = B200Network.from_torchscript(torch.jit.script(m), K, input_size=224, max_batch=maxb)
-    p = net(padded(x)).cpu()
+    p = net(net.pack_input(x), B).cpu()
     acts, pe = emulate_ir(net.nodes, x)
     pf = forward_probs(m, x)
     print(f"K={K} seed={seed} B={B} max_batch={maxb}")

@@ -38,6 +38,7 @@ struct Args {
   int out_C, out_c_off;                      // channels of the destination tensor / concat offset
   int res_C;                                 // channels of the residual tensor (0 = none)
   int out_pad, res_pad;                      // one-pixel zero border of the destination / residual tensor (0|1)
+  int out_Hp, out_Wp, res_Hp, res_Wp;        // stored rows / columns of the destination / residual tensor
   int relu;
   const __nv_bfloat16* residual;
   const float* bias;                         // [tiles_N * N_tile]
@@ -229,8 +230,8 @@ __global__ void __launch_bounds__(THREADS, 1)
       const int tn = mt / a.tiles_h;
       const int wo = tw * a.bw + w_l, ho = th * a.bh + h_l, n = tn * a.bn + n_l;
       const bool valid = (wo < a.Wo) && (ho < a.Ho) && (n < a.B);
-      const size_t pix = ((size_t)n * (a.Ho + 2 * a.out_pad) + ho + a.out_pad) * (a.Wo + 2 * a.out_pad) + wo + a.out_pad;
-      const size_t rpix = ((size_t)n * (a.Ho + 2 * a.res_pad) + ho + a.res_pad) * (a.Wo + 2 * a.res_pad) + wo + a.res_pad;
+      const size_t pix = ((size_t)n * a.out_Hp + ho + a.out_pad) * a.out_Wp + wo + a.out_pad;
+      const size_t rpix = ((size_t)n * a.res_Hp + ho + a.res_pad) * a.res_Wp + wo + a.res_pad;
       ptx::mbar_wait(&tfull[acc], acc_phase);
       ptx::tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256);

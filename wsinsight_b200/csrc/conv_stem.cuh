@@ -1,0 +1,215 @@
+// K4b: the 7x7 / stride 2 / pad 3 stem convolution (3 -> Cout=64 channels) as a tcgen05 implicit GEMM
+// that reads its overlapping input windows straight from UNEXPANDED image rows in shared memory.
+//
+// The per-tap kernel (conv.cuh) fed the stem through an "overlapping window" tensor map: every
+// output pixel's 8-pixel window was materialised by TMA, 64 bytes at a time, three times over
+// (ncu: 10 GB L2->SM per launch for a 0.43 GB input, tensor pipe 12 % active, 1.5 ms).  Here:
+//
+//  * the preprocess kernel writes the padded (S+6)^2 x 4-channel image as two ROW-PARITY planes of
+//    16-byte pixel pairs, bf16 [2][maxB][P][P][8] with P = (S+6)/2:  element [s][n][r][x][e] is
+//    padded row 2r+s, column 2x + e/4, channel e%4 (channel 3 = 0);
+//  * in flat pair index q = (n*P + ho)*P + wo the window of output (ho, wo) for tap row kh = 2a+s is
+//    the 64 bytes starting at pair q + a*P of plane s -- a pure shift, and consecutive outputs are
+//    consecutive pairs, i.e. operand rows 16 bytes apart that overlap by 48 bytes;
+//  * that is exactly a K-major NO-SWIZZLE UMMA operand whose core matrices overlap: row pitch 16 B
+//    inside a core matrix, K-direction core stride (LBO) 16 B, 8-row-group stride (SBO) 128 B
+//    (tools/umma_noswz_probe.cu, profiles/r01_umma_noswz_probe.txt: bit-exact on B200).
+//
+// One 1-D bulk copy per parity plane brings (T*128 + 3P + 4) pairs (9.7 KB) for T*128 outputs; the 14
+// k-steps (7 tap rows x 2 pair-pairs, K = 16 each) are MMAs whose A start address moves by a*P + 2*jj
+// pairs.  Weights (28 KB, canonical no-swizzle blocks) stay resident.  Outputs are produced for all P
+// columns of a row (3 of 115 are junk that nobody reads) into a [maxB*P*P][Cout] tensor.
+//
+// Warps: 0 producer, 1 MMA issuer, 2-5 epilogue group 0 (M-tile 0), 6-9 epilogue group 1 (M-tile 1);
+// each group stages its 128x64 tile in swizzled smem and writes it with one TMA store.
+#pragma once
+#include "conv.cuh"
+
+namespace convs {
+
+constexpr int THREADS = 320;
+constexpr int T = 2;             // M-tiles per super-tile
+constexpr int KSTEPS = 14;       // 7 tap rows x 2 (pairs {0,1}, {2,3}); K = 16 per step
+constexpr int N = 64;            // Cout
+constexpr int W_BYTES = KSTEPS * N * 16 * 2;   // 28 KB
+
+struct Args {
+  int P;                         // pairs per padded row == padded rows per parity plane
+  long long total_q;             // B * P * P flat outputs
+  long long plane_pairs;         // maxB * P * P: distance between the two parity planes (pairs)
+  int num_tiles;
+  int slab_pairs;                // pairs per parity slab (multiple of 8)
+  int stages;
+  int relu;
+  const uint8_t* in;             // parity-plane input (bf16 pairs)
+  const uint8_t* w;              // weights in canonical no-swizzle blocks [14][8][2][8][8] bf16
+  const float* bias;
+};
+
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          ptx::smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(ptx::smem_u32(bar))
+      : "memory");
+}
+
+__device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant__ CUtensorMap tmapO, const Args a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+  const int slab_bytes = a.slab_pairs * 16;           // one parity
+  uint8_t* sOut = smem;                               // 4 x 16 KB: [group][buffer], 1024-aligned
+  uint8_t* sW = sOut + 4 * 16384;
+  uint8_t* sA = sW + W_BYTES;                          // stages x 2 parities x slab_bytes
+  float* sBias = reinterpret_cast<float*>(sA + (size_t)a.stages * 2 * slab_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 64);
+  uint64_t* full = bars;
+  uint64_t* empty = full + a.stages;
+  uint64_t* tfull = empty + a.stages;
+  uint64_t* tempty = tfull + 2;
+  uint64_t* wfull = tempty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmapO);
+    for (int s = 0; s < a.stages; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], 8);
+    }
+    ptx::mbar_init(wfull, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 256);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== producer: weights once, then one bulk copy per parity per super-tile =====================
+    if (ptx::elect_one()) {
+      ptx::mbar_arrive_expect_tx(wfull, (uint32_t)W_BYTES);
+      for (int i = 0; i < 2; ++i) bulk_g2s(sW + i * (W_BYTES / 2), a.w + i * (W_BYTES / 2), W_BYTES / 2, wfull);
+    }
+    __syncwarp();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(&empty[stage], phase ^ 1);
+      if (ptx::elect_one()) {
+        const long long q0 = (long long)tile * (T * 128);
+        ptx::mbar_arrive_expect_tx(&full[stage], (uint32_t)(2 * slab_bytes));
+        uint8_t* dst = sA + (size_t)stage * 2 * slab_bytes;
+        bulk_g2s(dst, a.in + q0 * 16, (uint32_t)slab_bytes, &full[stage]);
+        bulk_g2s(dst + slab_bytes, a.in + (a.plane_pairs + q0) * 16, (uint32_t)slab_bytes, &full[stage]);
+      }
+      __syncwarp();
+      if (++stage == a.stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = ptx::make_idesc_bf16(128, N);
+    // no-swizzle K-major descriptors: LBO (K-direction core stride) in bits 16-29, SBO (8-row group) in 32-45
+    const uint32_t a_hi = (uint32_t)(128 >> 4) | (1u << 14);
+    const uint32_t a_lbo = (uint32_t)(16 >> 4) << 16;
+    const uint32_t b_hi = (uint32_t)(256 >> 4) | (1u << 14);
+    const uint32_t b_lbo = (uint32_t)(128 >> 4) << 16;
+    const uint32_t w_lo = ((ptx::smem_u32(sW) & 0x3FFFFu) >> 4) | b_lbo;
+    const uint32_t sA_lo = ((ptx::smem_u32(sA) & 0x3FFFFu) >> 4) | a_lbo;
+    const uint32_t stage_step = (uint32_t)(2 * slab_bytes) >> 4, par_step = (uint32_t)slab_bytes >> 4;
+    const uint32_t P = (uint32_t)a.P;
+    ptx::mbar_wait(wfull, 0);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, pacc = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(&tempty[acc], pacc ^ 1);
+      ptx::mbar_wait(&full[stage], phase);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+        const uint32_t d0 = tmem_base + (uint32_t)(acc * T * N);
+        const uint32_t s_lo = sA_lo + (uint32_t)stage * stage_step;
+#pragma unroll
+        for (int ks = 0; ks < KSTEPS; ++ks) {
+          const int kh = ks >> 1, jj = ks & 1;
+          // pair offset inside the parity slab: a*P rows down, 2*jj pairs right (units of 16 B == descriptor units)
+          const uint32_t a_lo = s_lo + (uint32_t)(kh & 1) * par_step + (uint32_t)(kh >> 1) * P + (uint32_t)(2 * jj);
+          const uint32_t b_lo = w_lo + (uint32_t)ks * (uint32_t)(N * 32 >> 4);
+          umma_lohi2(d0, a_lo, a_hi, b_lo, b_hi, idesc, ks == 0 ? 0u : 1u);
+          umma_lohi2(d0 + (uint32_t)N, a_lo + 128u, a_hi, b_lo, b_hi, idesc, ks == 0 ? 0u : 1u);
+        }
+        ptx::umma_commit(&empty[stage]);
+        ptx::umma_commit(&tfull[acc]);
+      }
+      __syncwarp();
+      if (++stage == a.stages) { stage = 0; phase ^= 1; }
+      if (++acc == 2) { acc = 0; pacc ^= 1; }
+    }
+  } else {
+    // ===================== epilogue: group g = M-tile g of every super-tile =====================
+    const int g = (warp - 2) >> 2;                    // 0 | 1
+    const int q = warp & 3;                           // TMEM lane quarter of this warp
+    const int row = q * 32 + lane;
+    const int gt = ((warp - 2) & 3) * 32 + lane;      // 0..127 inside the group
+    const bool leader = gt == 0;
+    if (g == 0 && gt < N) sBias[gt] = a.bias[gt];
+    ptx::named_bar_sync(3, 256);                      // bias staged (both groups)
+    uint8_t* myOut = sOut + (size_t)g * 2 * 16384;
+    int acc = 0, k = 0;
+    uint32_t pacc = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++k) {
+      const int ob = k & 1;
+      if (leader) ptx::bulk_wait_read<1>();
+      ptx::named_bar_sync(1 + g, 128);                // staging buffer ob of this group is free again
+      ptx::mbar_wait(&tfull[acc], pacc);
+      ptx::tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * T + g) * N);
+      convk::epi_chunk64(t_addr, row, true, ptx::smem_u32(myOut + (size_t)ob * 16384), 0u, sBias, a.relu);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+      ptx::fence_proxy_async();
+      ptx::named_bar_sync(1 + g, 128);                // tile staged
+      if (leader) {
+        ptx::tma_store_2d(&tmapO, myOut + (size_t)ob * 16384, 0, (int)((long long)tile * (T * 128) + g * 128));
+        ptx::bulk_commit();
+      }
+      if (++acc == 2) { acc = 0; pacc ^= 1; }
+    }
+    if (leader) ptx::bulk_wait<0>();
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 256);
+  }
+}
+
+static inline size_t smem_bytes(int slab_pairs, int stages) {
+  return 1024 + 4 * 16384 + W_BYTES + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
+}
+
+}  // namespace convs

@@ -99,7 +99,11 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
   cudaMemcpy(p->d_coords, hc.data(), hc.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
   p->slots.resize(depth);
   const size_t stage_bytes = (size_t)max_batch * patch_size * (size_t)patch_pitch_bytes;
-  const size_t input_bytes = (size_t)max_batch * hwc[0] * hwc[1] * 4 * sizeof(__nv_bfloat16);
+  const size_t input_bytes = wsi_net_input_bytes(net);
+  int lay[4] = {0, 0, 0, 0};
+  rc = wsi_net_input_layout(net, lay);
+  if (rc) return rc;
+  const long long plane_stride_px = lay[0] == 1 ? (((long long)lay[3] << 32) | (unsigned int)lay[2]) : 0;
   for (auto& s : p->slots) {
     if (cudaMalloc(&s.d_stage, stage_bytes) != cudaSuccess || cudaMalloc(&s.d_input, input_bytes) != cudaSuccess ||
         cudaMalloc(&s.d_probs, (size_t)max_batch * p->K * sizeof(float)) != cudaSuccess)
@@ -111,6 +115,7 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
       return fail("event creation failed", WSI_ERR_CUDA);
     rc = wsi_preproc_plan_create(s.d_stage, patch_size, (long long)max_batch * patch_size, patch_pitch_bytes,
                                  patch_size, out_size, mean, stdv, hwc[0], hwc[1], pad, pad, &s.plan);
+    if (!rc) rc = wsi_preproc_plan_set_parity_layout(s.plan, plane_stride_px);
     if (rc) {
       destroy(p);
       return rc;

@@ -5,6 +5,7 @@
 // the Python side walks the (frozen) TorchScript graph, hands folded conv weights/biases
 // to wsi_net_add_*, and every forward runs only kernels from this library.
 #include "conv_flat.cuh"
+#include "conv_stem.cuh"
 #include "../../include/wsi_b200.h"
 #include <math.h>
 #include <stdlib.h>
@@ -17,8 +18,9 @@ struct Tensor {
   __nv_bfloat16* ptr = nullptr;   // [max_batch][H+2*pad][W+2*pad][C]; nullptr for the external input
   bool external = false;
   int pad = 0;                    // one-pixel zero border (tensors touched by the flat 3x3 conv kernel)
-  int Hp() const { return H + 2 * pad; }
-  int Wp() const { return W + 2 * pad; }
+  int xh = 0, xw = 0;             // extra junk rows / columns after the image (output of the flat stem kernel)
+  int Hp() const { return H + 2 * pad + xh; }
+  int Wp() const { return W + 2 * pad + xw; }
   size_t interior_offset() const { return ((size_t)pad * Wp() + pad) * C; }   // elements to pixel (0,0)
 };
 
@@ -30,6 +32,7 @@ struct Op {
   // conv
   convk::Args ca;
   convf::Args fa;
+  convs::Args sa;
   bool flat = false;              // 3x3/s1/p1 over padded tensors -> convf::k_conv_flat
   CUtensorMap tmA, tmB, tmO, tmR;
   __nv_bfloat16* d_w = nullptr;
@@ -68,9 +71,9 @@ struct Net {
 __device__ __forceinline__ float bflo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bfhi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
-// ip / op: one-pixel zero border of the input / output tensor (0|1); `in`/`out` point at the buffer start
+// (iHp, iWp, ip) / (oHp, oWp, op): stored rows, stored columns and border of the input / output tensor; `in`/`out` point at the buffer start
 __global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
-                          int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int ip, int op) {
+                          int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp, int op) {
   const int cv = C / 8;
   size_t total = (size_t)B * Ho * Wo * cv;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -90,7 +93,7 @@ __global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
     for (int dx = 0; dx < k; ++dx) {
       int x = wo * s - pad + dx;
       if (x < 0 || x >= W) continue;
-      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * (H + 2 * ip) + y + ip) * (W + 2 * ip) + x + ip) * C) + c8);
+      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * iHp + y + ip) * iWp + x + ip) * C) + c8);
       m[0] = fmaxf(m[0], bflo(v.x)); m[1] = fmaxf(m[1], bfhi(v.x));
       m[2] = fmaxf(m[2], bflo(v.y)); m[3] = fmaxf(m[3], bfhi(v.y));
       m[4] = fmaxf(m[4], bflo(v.z)); m[5] = fmaxf(m[5], bfhi(v.z));
@@ -102,12 +105,12 @@ __global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
   o.y = convk::pack_bf16(m[2], m[3]);
   o.z = convk::pack_bf16(m[4], m[5]);
   o.w = convk::pack_bf16(m[6], m[7]);
-  reinterpret_cast<uint4*>(out + (((size_t)n * (Ho + 2 * op) + ho + op) * (Wo + 2 * op) + wo + op) * out_C + out_c_off)[c8] = o;
+  reinterpret_cast<uint4*>(out + (((size_t)n * oHp + ho + op) * oWp + wo + op) * out_C + out_c_off)[c8] = o;
 }
 
 __global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
                           int count_include_pad, int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C,
-                          int out_c_off, int ip, int op) {
+                          int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp, int op) {
   const int cv = C / 8;
   size_t total = (size_t)B * Ho * Wo * cv;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -129,7 +132,7 @@ __global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
       int x = wo * s - pad + dx;
       if (x < 0 || x >= W) continue;
       ++cnt;
-      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * (H + 2 * ip) + y + ip) * (W + 2 * ip) + x + ip) * C) + c8);
+      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * iHp + y + ip) * iWp + x + ip) * C) + c8);
       m[0] += bflo(v.x); m[1] += bfhi(v.x); m[2] += bflo(v.y); m[3] += bfhi(v.y);
       m[4] += bflo(v.z); m[5] += bfhi(v.z); m[6] += bflo(v.w); m[7] += bfhi(v.w);
     }
@@ -142,7 +145,7 @@ __global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, in
   o.y = convk::pack_bf16(m[2], m[3]);
   o.z = convk::pack_bf16(m[4], m[5]);
   o.w = convk::pack_bf16(m[6], m[7]);
-  reinterpret_cast<uint4*>(out + (((size_t)n * (Ho + 2 * op) + ho + op) * (Wo + 2 * op) + wo + op) * out_C + out_c_off)[c8] = o;
+  reinterpret_cast<uint4*>(out + (((size_t)n * oHp + ho + op) * oWp + wo + op) * out_C + out_c_off)[c8] = o;
 }
 
 // K4d: global average pool + FC + softmax (K>1) / sigmoid (K==1); one CTA per image.
@@ -195,7 +198,7 @@ __global__ void __launch_bounds__(HEAD_THREADS)
 
 // dense [B][H][W][C] <-> interior of a padded [B][H+2p][W+2p][C] tensor, 16 bytes per thread
 __global__ void k_copy_interior(const uint4* __restrict__ src, uint4* __restrict__ dst, int B, int H, int W, int C8,
-                                int pad, int to_padded) {
+                                int Hp, int Wp, int pad, int to_padded) {
   size_t total = (size_t)B * H * W * C8;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -205,7 +208,7 @@ __global__ void k_copy_interior(const uint4* __restrict__ src, uint4* __restrict
   p /= W;
   int h = p % H;
   int n = p / H;
-  size_t pi = (((size_t)n * (H + 2 * pad) + h + pad) * (W + 2 * pad) + w + pad) * C8 + c;
+  size_t pi = (((size_t)n * Hp + h + pad) * Wp + w + pad) * C8 + c;
   if (to_padded) dst[pi] = src[idx]; else dst[idx] = src[pi];
 }
 
@@ -321,17 +324,27 @@ int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* w_oihw, c
   op.kind = OP_CONV;
   op.in = in_id; op.out = out_id; op.res = -1;
   op.Cin = 3; op.Cout = Cout; op.KH = 7; op.KW = 7; op.stride = 2; op.pad_h = 3; op.pad_w = 3;
-  op.relu = relu; op.out_c_off = 0; op.is_stem = 1;
+  op.relu = relu; op.out_c_off = 0;
+  // Cout == 64 (every ResNet): the parity-plane stem kernel (conv_stem.cuh); otherwise the per-tap kernel
+  op.is_stem = (Cout == convs::N && n->flat_enabled) ? 2 : 1;
   op.Ktot = 7 * 32;
-  // K layout: chunk kh x [px 0..7][ch 0..3]; px==7 and ch==3 carry zero weights
   op.h_w.assign((size_t)Cout * op.Ktot, __float2bfloat16(0.f));
   for (int o = 0; o < Cout; ++o)
     for (int c = 0; c < 3; ++c)
       for (int y = 0; y < 7; ++y)
         for (int x = 0; x < 7; ++x) {
           float v = w_oihw[(((size_t)o * 3 + c) * 7 + y) * 7 + x];
-          size_t k = (size_t)y * 32 + x * 4 + c;
-          op.h_w[(size_t)o * op.Ktot + k] = __float2bfloat16(v);
+          size_t off;
+          if (op.is_stem == 2) {
+            // canonical no-swizzle blocks [ks = 2*kh + jj][n/8][k/8][n%8][k%8], k = 16 per block:
+            // pixel pair j = x/2 = 2*jj + k/8, element (x%2)*4 + c inside the pair
+            const int j = x >> 1, ks = y * 2 + (j >> 1), k16 = (j & 1) * 8 + (x & 1) * 4 + c;
+            off = (size_t)ks * 1024 + (size_t)(o / 8) * 128 + (size_t)(k16 / 8) * 64 + (size_t)(o % 8) * 8 + (k16 % 8);
+          } else {
+            // K layout: chunk kh x [px 0..7][ch 0..3]; px==7 and ch==3 carry zero weights
+            off = (size_t)o * op.Ktot + (size_t)y * 32 + x * 4 + c;
+          }
+          op.h_w[off] = __float2bfloat16(v);
         }
   op.h_bias.assign(Cout, 0.f);
   if (bias) memcpy(op.h_bias.data(), bias, sizeof(float) * Cout);
@@ -400,6 +413,14 @@ int wsi_net_finalize(void* net) {
       if (op.res >= 0) n->tensors[op.res].pad = 1;
     }
   for (auto& op : n->ops)
+    if (op.kind == OP_CONV && op.is_stem == 2) {
+      // the parity-plane stem writes every column / row of its P x P flat grid: P - S/2 junk ones
+      Tensor& to = n->tensors[op.out];
+      const int P = n->tensors[op.in].H / 2;
+      to.xh = P - to.H;
+      to.xw = P - to.W;
+    }
+  for (auto& op : n->ops)
     if (op.kind == OP_HEAD && n->tensors[op.in].pad) {
       wsi_set_error("wsi_net_finalize: the head cannot read a padded tensor");
       return WSI_ERR_UNSUPPORTED;
@@ -410,7 +431,7 @@ int wsi_net_finalize(void* net) {
     WSI_CUDA_CHECK(cudaMalloc(&t.ptr, bytes));
     WSI_CUDA_CHECK(cudaMemset(t.ptr, 0, bytes));
   }
-  int max_smem = 0, max_smem_flat = 0;
+  int max_smem = 0, max_smem_flat = 0, max_smem_stem = 0;
   for (auto& op : n->ops) {
     if (op.kind == OP_CONV) {
       const Tensor& ti = n->tensors[op.in];
@@ -421,6 +442,29 @@ int wsi_net_finalize(void* net) {
       WSI_CUDA_CHECK(cudaMalloc(&op.d_bias, op.h_bias.size() * sizeof(float)));
       WSI_CUDA_CHECK(cudaMemcpy(op.d_bias, op.h_bias.data(), op.h_bias.size() * sizeof(float),
                                 cudaMemcpyHostToDevice));
+      if (op.is_stem == 2) {
+        const int P = ti.H / 2;
+        convs::Args& sa = op.sa;
+        memset(&sa, 0, sizeof(sa));
+        sa.P = P;
+        sa.plane_pairs = (long long)B * P * P;
+        sa.slab_pairs = (convs::T * 128 + 3 * P + 4 + 7) / 8 * 8;
+        sa.stages = 4;
+        sa.relu = op.relu;
+        sa.w = (const uint8_t*)op.d_w;
+        sa.bias = op.d_bias;
+        int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages);
+        WSI_ARG_CHECK(smem <= 227 * 1024, "wsi_net_finalize: stem slab does not fit shared memory (P = %d)", P);
+        if (smem > max_smem_stem) max_smem_stem = smem;
+        uint64_t dims[2] = {(uint64_t)to.C, (uint64_t)B * to.Hp() * to.Wp()};
+        uint64_t strides[1] = {(uint64_t)to.C * 2};
+        uint32_t box[2] = {64, 128};
+        uint32_t es[2] = {1, 1};
+        int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
+                               CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+        continue;
+      }
       if (op.flat) {
         convf::Args& f = op.fa;
         memset(&f, 0, sizeof(f));
@@ -522,8 +566,10 @@ int wsi_net_finalize(void* net) {
       a.stages = stages;
       a.out_C = to.C; a.out_c_off = op.out_c_off;
       a.res_C = op.res >= 0 ? n->tensors[op.res].C : 0;
-      a.out_pad = to.pad;
+      a.out_pad = to.pad; a.out_Hp = to.Hp(); a.out_Wp = to.Wp();
       a.res_pad = op.res >= 0 ? n->tensors[op.res].pad : 0;
+      a.res_Hp = op.res >= 0 ? n->tensors[op.res].Hp() : 0;
+      a.res_Wp = op.res >= 0 ? n->tensors[op.res].Wp() : 0;
       a.relu = op.relu;
       a.bias = op.d_bias;
       int smem = (int)convk::smem_bytes(a.N_tile, a.stages);
@@ -552,6 +598,8 @@ int wsi_net_finalize(void* net) {
   }
   if (max_smem > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  if (max_smem_stem > 0)
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
   if (max_smem_flat > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
   n->launches_per_forward = (int)n->ops.size();
@@ -605,11 +653,20 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
     const __nv_bfloat16* in_ptr = ti.external ? (const __nv_bfloat16*)d_input : ti.ptr;
     WSI_ARG_CHECK(in_ptr, "wsi_net_forward: missing input pointer");
     if (op.kind == OP_CONV) {
-      if (ti.external) {
+      if (ti.external && op.is_stem != 2) {
         int rc = wsi_net_encode_input_map(net, (int)i, in_ptr);
         if (rc) return rc;
       }
       const Tensor& to = n->tensors[op.out];
+      if (op.is_stem == 2) {
+        convs::Args sa = op.sa;
+        sa.in = (const uint8_t*)in_ptr;
+        sa.total_q = (long long)B * sa.P * sa.P;
+        sa.num_tiles = (int)((sa.total_q + convs::T * 128 - 1) / (convs::T * 128));
+        int grid = sa.num_tiles < n->num_sms ? sa.num_tiles : n->num_sms;
+        convs::k_conv_stem<<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages), stream>>>(op.tmO, sa);
+        continue;
+      }
       if (op.flat) {
         convf::Args f = op.fa;
         f.B = B;
@@ -636,11 +693,11 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       int blocks = (int)((total + 255) / 256);
       if (op.kind == OP_MAXPOOL)
         k_maxpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, to.H, to.W,
-                                              to.ptr, to.C, op.out_c_off, ti.pad, to.pad);
+                                              to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
       else
         k_avgpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
-                                              op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.pad,
-                                              to.pad);
+                                              op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.Hp(),
+                                              ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
     } else if (op.kind == OP_HEAD) {
       WSI_ARG_CHECK(d_probs, "wsi_net_forward: null probs");
       k_head<<<B, HEAD_THREADS, ti.C * sizeof(float), stream>>>(in_ptr, ti.H * ti.W, ti.C, op.d_fcw, op.d_fcb, op.K,
@@ -713,9 +770,9 @@ static int copy_tensor(void* net, int id, int batch, void* d_dense, int to_tenso
   size_t total = (size_t)batch * t.H * t.W * (t.C / 8);
   int blocks = (int)((total + 255) / 256);
   if (to_tensor)
-    k_copy_interior<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const uint4*)d_dense, (uint4*)t.ptr, batch, t.H, t.W, t.C / 8, t.pad, 1);
+    k_copy_interior<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const uint4*)d_dense, (uint4*)t.ptr, batch, t.H, t.W, t.C / 8, t.Hp(), t.Wp(), t.pad, 1);
   else
-    k_copy_interior<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const uint4*)t.ptr, (uint4*)d_dense, batch, t.H, t.W, t.C / 8, t.pad, 0);
+    k_copy_interior<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const uint4*)t.ptr, (uint4*)d_dense, batch, t.H, t.W, t.C / 8, t.Hp(), t.Wp(), t.pad, 0);
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
 }
@@ -745,6 +802,33 @@ int wsi_net_input_geometry(void* net, int* hwc3) {
     }
   wsi_set_error("wsi_net_input_geometry: the network has no external input tensor");
   return WSI_ERR_ARG;
+}
+
+// info[0] = layout kind of the external input (0: bf16 [B][H][W][4] with the patch at the stem's padding offset;
+// 1: two row-parity planes of 16-byte pixel pairs, bf16 [2][max_batch][P][P][8], see conv_stem.cuh),
+// info[1] = P, info[2..3] = plane stride in PIXELS (low, high 32 bits)
+int wsi_net_input_layout(void* net, int* info4) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && info4, "wsi_net_input_layout: null pointer");
+  info4[0] = info4[1] = info4[2] = info4[3] = 0;
+  for (auto& op : n->ops)
+    if (op.kind == OP_CONV && op.is_stem == 2 && n->tensors[op.in].external) {
+      const int P = n->tensors[op.in].H / 2;
+      const long long stride_px = (long long)n->max_batch * P * P * 2;
+      info4[0] = 1; info4[1] = P;
+      info4[2] = (int)(stride_px & 0xffffffffll); info4[3] = (int)(stride_px >> 32);
+    }
+  return WSI_OK;
+}
+
+// bytes the caller must allocate for the external input of a max_batch forward (includes the slack the
+// stem's bulk copies may read past the last image)
+size_t wsi_net_input_bytes(void* net) {
+  Net* n = (Net*)net;
+  if (!n) return 0;
+  for (auto& t : n->tensors)
+    if (t.external) return (size_t)n->max_batch * t.H * t.W * t.C * sizeof(__nv_bfloat16) + 32 * 1024;
+  return 0;
 }
 
 int wsi_net_num_classes(void* net) {

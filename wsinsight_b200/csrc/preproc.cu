@@ -75,6 +75,7 @@ struct Plan {
   int out_H, out_W, pad_top, pad_left;
   float mean[3], stdv[3];
   int has_norm;
+  long long plane_stride_px = 0;  // > 0: row-parity plane output layout (conv_stem.cuh)
   int *d_lo, *d_cnt, *d_coef;     // taps (same table for both axes: square patches)
   size_t smem_bytes;
   CUtensorMap tmap;
@@ -91,6 +92,7 @@ struct PPArgs {
   int out_H, out_W, pad_top, pad_left;
   float m0, m1, m2, s0, s1, s2;
   int has_norm;
+  long long plane_stride_px;   // > 0: write two row-parity planes [2][maxB][P][2P] of 4-channel pixels
 };
 
 __device__ __forceinline__ uint32_t clip8(int v) {
@@ -188,7 +190,13 @@ __global__ void __launch_bounds__(PP_THREADS)
     uint2 v;
     v.x = *reinterpret_cast<uint32_t*>(&lo2);
     v.y = *reinterpret_cast<uint32_t*>(&hi2);
-    size_t o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
+    size_t o;
+    if (a.plane_stride_px > 0) {
+      const int y = a.pad_top + yy, P = a.out_H >> 1;
+      o = (size_t)(y & 1) * (size_t)a.plane_stride_px + ((size_t)patch * P + (y >> 1)) * (size_t)a.out_W + (a.pad_left + xx);
+    } else {
+      o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
+    }
     reinterpret_cast<uint2*>(a.out)[o] = v;
   }
 }
@@ -334,6 +342,7 @@ static int preproc_launch(void* plan, const int32_t* d_coords_xy, int n, void* d
   a.m0 = p->mean[0]; a.m1 = p->mean[1]; a.m2 = p->mean[2];
   a.s0 = p->stdv[0]; a.s1 = p->stdv[1]; a.s2 = p->stdv[2];
   a.has_norm = p->has_norm;
+  a.plane_stride_px = p->plane_stride_px;
   dim3 grid(n, p->nbands);
   k_preprocess<<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
   wsi_count_launch(1);
@@ -349,6 +358,15 @@ int wsi_preproc_run(void* plan, const int32_t* d_coords_xy, int n, void* d_out_b
 int wsi_preproc_run_u8(void* plan, const int32_t* d_coords_xy, int n, uint8_t* d_out_u8, void* stream_) {
   WSI_ARG_CHECK(d_out_u8, "wsi_preproc_run_u8: null output");
   return preproc_launch(plan, d_coords_xy, n, nullptr, d_out_u8, stream_);
+}
+
+int wsi_preproc_plan_set_parity_layout(void* plan, long long plane_stride_px) {
+  WSI_ARG_CHECK(plan && plane_stride_px >= 0, "wsi_preproc_plan_set_parity_layout: bad arguments");
+  Plan* p = (Plan*)plan;
+  WSI_ARG_CHECK(plane_stride_px == 0 || (p->out_H == p->out_W && (p->out_H & 1) == 0),
+                "wsi_preproc_plan_set_parity_layout: the padded output must be square with an even side");
+  p->plane_stride_px = plane_stride_px;
+  return WSI_OK;
 }
 
 int wsi_preproc_plan_info(void* plan, int* info8) {

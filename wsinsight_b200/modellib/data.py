@@ -42,7 +42,7 @@ class PreprocessPlan:
     """Owns a ``wsi_preproc_plan`` for one (slide, patch_size, transform, output layout)."""
 
     def __init__(self, slide, patch_size: int, transform: FusedTransform, out_H=None, out_W=None, pad_top=0,
-                 pad_left=0):
+                 pad_left=0, plane_stride_px=0):
         torch = _cabi.require_cuda()
         self.slide = slide
         self.patch_size = int(patch_size)
@@ -57,6 +57,9 @@ class PreprocessPlan:
             _cabi.call("wsi_preproc_plan_create", slide.rgba.data_ptr(), slide.width, slide.height,
                        slide.pitch_bytes, self.patch_size, self.S, mean, std, self.out_H, self.out_W, self.pad_top,
                        self.pad_left, C.byref(self._h))
+            self.plane_stride_px = int(plane_stride_px)
+            if self.plane_stride_px:
+                _cabi.call("wsi_preproc_plan_set_parity_layout", self._h, self.plane_stride_px)
 
     def info(self):
         a = (C.c_int * 8)()
@@ -65,12 +68,16 @@ class PreprocessPlan:
         return dict(zip(keys, [int(v) for v in a]))
 
     def run(self, coords_xy, out, stream=None):
-        """coords_xy: CUDA int32 (n, 2) top-left corners; out: bf16 [>=n][out_H][out_W][4]."""
+        """coords_xy: CUDA int32 (n, 2) top-left corners; out: bf16 buffer, [>=n][out_H][out_W][4] or, with
+        the parity layout, the flat buffer of ``B200Network.alloc_input``."""
         torch = _cabi.require_cuda()
         n = int(coords_xy.shape[0])
         assert coords_xy.dtype == torch.int32 and coords_xy.is_contiguous() and coords_xy.is_cuda
-        assert out.dtype == torch.bfloat16 and out.is_contiguous() and out.shape[0] >= n
-        assert tuple(out.shape[1:]) == (self.out_H, self.out_W, 4)
+        assert out.dtype == torch.bfloat16 and out.is_contiguous()
+        if self.plane_stride_px:
+            assert out.numel() >= 2 * self.plane_stride_px * 4
+        else:
+            assert out.numel() >= n * self.out_H * self.out_W * 4
         with torch.cuda.device(out.device):
             _cabi.call("wsi_preproc_run", self._h, coords_xy.data_ptr(), n, out.data_ptr(), _cabi.stream_ptr(stream))
 
@@ -117,12 +124,12 @@ class WholeSlideImagePatches:
         self.batch_size = int(batch_size)
         lay = input_layout or {}
         self.plan = PreprocessPlan(slide, self.patch_size, transform, lay.get("out_H"), lay.get("out_W"),
-                                   lay.get("pad_top", 0), lay.get("pad_left", 0))
+                                   lay.get("pad_top", 0), lay.get("pad_left", 0), lay.get("plane_stride_px", 0))
         dev = slide.rgba.device
         self.dev_coords = device_coords if device_coords is not None else \
             torch.from_numpy(np.ascontiguousarray(self.coords[:, :2], dtype=np.int32)).to(dev)
-        self._buf = torch.zeros((self.batch_size, self.plan.out_H, self.plan.out_W, 4), dtype=torch.bfloat16,
-                                device=dev)
+        nelem = lay.get("buffer_elems") or self.batch_size * self.plan.out_H * self.plan.out_W * 4
+        self._buf = torch.zeros(int(nelem), dtype=torch.bfloat16, device=dev)
 
     def __len__(self):
         return (len(self.coords) + self.batch_size - 1) // self.batch_size
@@ -131,4 +138,4 @@ class WholeSlideImagePatches:
         for s in range(0, len(self.coords), self.batch_size):
             e = min(s + self.batch_size, len(self.coords))
             self.plan.run(self.dev_coords[s:e], self._buf)
-            yield self._buf[: e - s], self.coords[s:e]
+            yield self._buf, self.coords[s:e]

@@ -69,6 +69,16 @@ class B200Network:
                 lib.wsi_net_destroy(self._h)
                 self._h = C.c_void_p()
                 raise
+        info = (C.c_int * 4)()
+        _cabi.call("wsi_net_input_layout", self._h, info)
+        self.input_bytes = int(lib.wsi_net_input_bytes(self._h))
+        if int(info[0]) == 1:
+            # row-parity planes of pixel pairs (csrc/conv_stem.cuh): bf16 [2][max_batch][P][P][8]
+            self.input_layout.update(kind="parity", P=int(info[1]),
+                                     plane_stride_px=(int(info[3]) << 32) | (int(info[2]) & 0xFFFFFFFF))
+        else:
+            self.input_layout.update(kind="nhwc4", plane_stride_px=0)
+        self.input_layout["buffer_elems"] = self.input_bytes // 2
         self.num_launches = int(lib.wsi_net_num_launches(self._h))
         self.flops_per_image = float(lib.wsi_net_flops_per_image(self._h))
 
@@ -172,28 +182,48 @@ class B200Network:
         return nodes[x].shape[0]
 
     # -- execution --------------------------------------------------------------
-    def alloc_input(self, batch: int):
-        """Zeroed bf16 input buffer in the layout ``wsi_preproc_run`` writes (borders stay zero)."""
+    def alloc_input(self, batch: int = None):
+        """Zeroed flat bf16 input buffer in the layout ``wsi_preproc_run`` writes (borders stay zero).
+
+        Always sized for ``max_batch`` (the parity-plane layout fixes the plane stride) plus read slack."""
+        import torch
+
+        return torch.zeros(self.input_bytes // 2, dtype=torch.bfloat16, device=self.device)
+
+    def pack_input(self, x_nchw):
+        """Test helper: fp32/bf16 ``(B, 3, S, S)`` tensor -> input buffer in this network's layout
+        (what the preprocess kernel would have written for already-normalised pixels)."""
         import torch
 
         lay = self.input_layout
-        return torch.zeros((int(batch), lay["out_H"], lay["out_W"], lay["channels"]), dtype=torch.bfloat16,
-                           device=self.device)
+        b, _, s, _ = x_nchw.shape
+        hp, pt, pl = lay["out_H"], lay["pad_top"], lay["pad_left"]
+        img = torch.zeros((self.max_batch, hp, hp, 4), dtype=torch.bfloat16, device=self.device)
+        img[:b, pt:pt + s, pl:pl + s, :3] = x_nchw.permute(0, 2, 3, 1).to(torch.bfloat16).to(self.device)
+        buf = self.alloc_input()
+        if lay["kind"] == "parity":
+            planes = torch.stack([img[:, 0::2], img[:, 1::2]], 0)      # [2][maxB][P][2P][4]
+            buf[: planes.numel()] = planes.reshape(-1)
+        else:
+            buf[: img.numel()] = img.reshape(-1)
+        return buf
 
-    def forward_into(self, x, probs, stream=None):
-        """Enqueue the forward of ``x`` (bf16 [B][S+6][S+6][4]) writing fp32 probs [B][K]."""
+    def forward_into(self, x, probs, stream=None, batch=None):
+        """Enqueue the forward of the first ``batch`` (default ``len(probs)``) images of input buffer ``x``
+        (layout of :meth:`alloc_input`), writing fp32 probs [B][K]."""
         import torch
 
-        b = int(x.shape[0])
+        b = int(probs.shape[0]) if batch is None else int(batch)
         assert x.dtype == torch.bfloat16 and x.is_contiguous() and x.device == self.device
+        assert x.numel() * 2 >= self.input_bytes, "allocate the input with alloc_input()"
         assert probs.dtype == torch.float32 and probs.is_contiguous() and probs.numel() >= b * self.num_classes
         with torch.cuda.device(self.device):
             _cabi.call("wsi_net_forward", self._h, x.data_ptr(), b, probs.data_ptr(), _cabi.stream_ptr(stream))
 
-    def __call__(self, x):
+    def __call__(self, x, batch: int):
         import torch
 
-        probs = torch.empty((int(x.shape[0]), self.num_classes), dtype=torch.float32, device=self.device)
+        probs = torch.empty((int(batch), self.num_classes), dtype=torch.float32, device=self.device)
         self.forward_into(x, probs)
         return probs.squeeze(1) if self.num_classes == 1 else probs
 

@@ -49,7 +49,7 @@ def classify_patches_device(slide, coords_xywh: np.ndarray, net, transform, batc
     dset = WholeSlideImagePatches(slide, coords_xywh, transform, batch_size, net.input_layout, device_coords)
     s = 0
     for batch, bc in dset:
-        b = int(batch.shape[0])
+        b = len(bc)
         net.forward_into(batch, probs[s:s + b])
         s += b
     return probs
