@@ -23,7 +23,7 @@ namespace convk {
 
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;
-constexpr int THREADS = 192;
+constexpr int THREADS = 320;   // warp 0 producer, warp 1 MMA, warps 2-5 / 6-9 two epilogue groups
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
 
 struct Args {
@@ -39,6 +39,8 @@ struct Args {
   int res_C;                                 // channels of the residual tensor (0 = none)
   int out_pad, res_pad;                      // one-pixel zero border of the destination / residual tensor (0|1)
   int out_Hp, out_Wp, res_Hp, res_Wp;        // stored rows / columns of the destination / residual tensor
+  int tma_epi;                               // N_tile % 64 == 0: smem-staged epilogue + TMA stores, two warp groups
+  int Cout;                                  // tiles_N * N_tile (bias entries staged in smem)
   int relu;
   const __nv_bfloat16* residual;
   const float* bias;                         // [tiles_N * N_tile]
@@ -90,18 +92,51 @@ __device__ __forceinline__ void epi_chunk64(uint32_t t_addr, int row, bool keep,
   }
 }
 
+// Same, with the residual already in registers (8 x 16 B = this thread's 64 channels): used where shared
+// memory has no room for a residual staging ring; the caller issues the global loads one chunk ahead.
+__device__ __forceinline__ void epi_chunk64_regs(uint32_t t_addr, int row, uint32_t s_out, bool has_res,
+                                                 const uint4 (&rv)[8], const float* s_bias, int relu) {
+  uint32_t r[64];
+  ptx::tmem_ld_32x32b_x32(t_addr, r);
+  ptx::tmem_ld_32x32b_x32(t_addr + 32u, r + 32);
+  ptx::tmem_ld_wait();
+  const uint32_t row_base = (uint32_t)row * 128u;
+  const uint32_t sw = (uint32_t)row & 7u;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
+    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
+    float v0 = __uint_as_float(r[8 * c + 0]) + b0.x, v1 = __uint_as_float(r[8 * c + 1]) + b0.y;
+    float v2 = __uint_as_float(r[8 * c + 2]) + b0.z, v3 = __uint_as_float(r[8 * c + 3]) + b0.w;
+    float v4 = __uint_as_float(r[8 * c + 4]) + b1.x, v5 = __uint_as_float(r[8 * c + 5]) + b1.y;
+    float v6 = __uint_as_float(r[8 * c + 6]) + b1.z, v7 = __uint_as_float(r[8 * c + 7]) + b1.w;
+    if (has_res) {
+      v0 += bf16_lo(rv[c].x); v1 += bf16_hi(rv[c].x); v2 += bf16_lo(rv[c].y); v3 += bf16_hi(rv[c].y);
+      v4 += bf16_lo(rv[c].z); v5 += bf16_hi(rv[c].z); v6 += bf16_lo(rv[c].w); v7 += bf16_hi(rv[c].w);
+    }
+    if (relu) {
+      v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
+      v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
+    }
+    ptx::st_shared_v4(s_out + row_base + (((uint32_t)c ^ sw) << 4), pack_bf16(v0, v1), pack_bf16(v2, v3),
+                      pack_bf16(v4, v5), pack_bf16(v6, v7));
+  }
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_igemm(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                 const Args a) {
+                 const __grid_constant__ CUtensorMap tmapO, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x A 16KB][stages x B N_tile*128][barriers]
-  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+  if (ptx::smem_u32(smem_raw) & 1023u) __trap();
+  uint8_t* smem = smem_raw;
   const int B_BYTES = a.N_tile * BLOCK_K * 2;           // stage stride (the stem uses half of each stage)
   const int kbytes = a.is_stem ? 64 : 128;              // bytes of K per smem row
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)a.stages * A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)a.stages * B_BYTES);
+  uint8_t* sOut = sB + (size_t)a.stages * B_BYTES;                       // tma_epi: 2 x 16 KB (one per group)
+  float* sBias = reinterpret_cast<float*>(sOut + (a.tma_epi ? 2 * 16384 : 0));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + (a.tma_epi ? ((a.Cout + 31) & ~31) : 0));
   uint64_t* full = bars;
   uint64_t* empty = bars + a.stages;
   uint64_t* tfull = bars + 2 * a.stages;
@@ -122,7 +157,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4);
+      ptx::mbar_init(&tempty[s], (a.tma_epi && a.N_tile > 64) ? 8 : 4);
     }
     ptx::fence_barrier_init();
   }
@@ -212,8 +247,85 @@ __global__ void __launch_bounds__(THREADS, 1)
         acc_phase ^= 1;
       }
     }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
+  } else if (a.tma_epi) {
+    // ===================== epilogue, two groups of 4 warps (2-5, 6-9) =====================
+    // group g takes the 64-column chunks j = g, g+2, ... of every tile (or, when the tile has a single
+    // chunk, every other tile: accumulator stage g); each chunk is staged swizzled in the group's 16 KB
+    // buffer and written by ONE 4-D TMA store (box = the tile's pixel box x 64 channels; partial
+    // tiles are clipped by the tensor map).  The residual comes straight from global memory, loaded
+    // one chunk ahead (and before the wait on the accumulator) into registers.
+    const int ew = warp - 2, g = ew >> 2;
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int gt = (ew & 3) * 32 + lane;
+    const bool leader = gt == 0;
+    for (int i = (int)threadIdx.x - 64; i < a.Cout; i += 256) sBias[i] = a.bias[i];
+    ptx::named_bar_sync(3, 256);
+    const int cn = a.N_tile >> 6;
+    const int jstep = cn > 1 ? 2 : 1;
+    const uint32_t myOut = ptx::smem_u32(sOut + (size_t)g * 16384);
+    const int w_l = row % a.bw;
+    const int h_l = (row / a.bw) % a.bh;
+    const int n_l = row / (a.bw * a.bh);
+    int acc = 0, k = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++k) {
+      const bool part = cn > 1 ? (g < cn) : ((k & 1) == g);
+      if (part) {
+        const int nt = tile % a.tiles_N;
+        int mt = tile / a.tiles_N;
+        const int tw = mt % a.tiles_w;
+        mt /= a.tiles_w;
+        const int th = mt % a.tiles_h;
+        const int tn = mt / a.tiles_h;
+        const int wo = tw * a.bw + w_l, ho = th * a.bh + h_l, n = tn * a.bn + n_l;
+        const bool do_res = a.res_C && (wo < a.Wo) && (ho < a.Ho) && (n < a.B);
+        const size_t rpix = ((size_t)n * a.res_Hp + ho + a.res_pad) * a.res_Wp + wo + a.res_pad;
+        const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + rpix * a.res_C + nt * a.N_tile);
+        int j = cn > 1 ? g : 0;
+        uint4 rv[8], rn[8];
+        if (do_res) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) rv[i] = __ldg(rbase + 8 * j + i);
+        }
+        ptx::mbar_wait(&tfull[acc], acc_phase);
+        ptx::tc_fence_after();
+        for (; j < cn; j += jstep) {
+          const bool last = j + jstep >= cn;
+          if (do_res && !last) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rn[i] = __ldg(rbase + 8 * (j + jstep) + i);
+          }
+          if (leader) ptx::bulk_wait_read<0>();
+          ptx::named_bar_sync(1 + g, 128);              // the group's staging buffer is free again
+          const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + 64 * j);
+          epi_chunk64_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, a.relu);
+          if (last) {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+          }
+          ptx::fence_proxy_async();
+          ptx::named_bar_sync(1 + g, 128);              // chunk staged
+          if (leader) {
+            ptx::tma_store_4d(&tmapO, sOut + (size_t)g * 16384, a.out_c_off + nt * a.N_tile + 64 * j, tw * a.bw,
+                              th * a.bh, tn * a.bn);
+            ptx::bulk_commit();
+          }
+          if (!last) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rv[i] = rn[i];
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (leader) ptx::bulk_wait<0>();
+  } else if (warp < 6) {
+    // ===================== legacy epilogue (warps 2..5): N_tile not a multiple of 64 =====================
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;             // row of the 128-row tile == pixel in the box
     const int w_l = row % a.bw;
@@ -297,8 +409,13 @@ __global__ void __launch_bounds__(THREADS, 1)
   }
 }
 
-static inline size_t smem_bytes(int N_tile, int stages) {
-  return 1024 + (size_t)stages * (A_BYTES + (size_t)N_tile * BLOCK_K * 2) + (2 * stages + 4) * 8 + 16;
+// no alignment slack: the dynamic shared window of a kernel without static __shared__ starts 1024-aligned
+// (the kernel traps if it ever does not); 4 stages of 48 KB + staging only just fit in 227 KB
+static inline size_t smem_fixed(int tma_epi, int Cout) {
+  return (tma_epi ? 2 * 16384 + (size_t)((Cout + 31) & ~31) * 4 : 0) + 256;
+}
+static inline size_t smem_bytes(int N_tile, int stages, int tma_epi, int Cout) {
+  return smem_fixed(tma_epi, Cout) + (size_t)stages * (A_BYTES + (size_t)N_tile * BLOCK_K * 2);
 }
 
 }  // namespace convk

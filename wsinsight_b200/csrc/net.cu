@@ -559,8 +559,10 @@ int wsi_net_finalize(void* net) {
       a.is_stem = op.is_stem;
       a.N_tile = pick_ntile(op.Cout);
       a.tiles_N = op.Cout / a.N_tile;
+      a.tma_epi = (a.N_tile % 64 == 0) ? 1 : 0;
+      a.Cout = op.Cout;
       const size_t stage_bytes = convk::A_BYTES + (size_t)a.N_tile * 128;
-      int stages = (int)((200 * 1024) / stage_bytes);
+      int stages = (int)((227 * 1024 - convk::smem_fixed(a.tma_epi, a.Cout)) / stage_bytes);
       if (stages > 8) stages = 8;
       if (stages < 2) stages = 2;
       a.stages = stages;
@@ -572,8 +574,20 @@ int wsi_net_finalize(void* net) {
       a.res_Wp = op.res >= 0 ? n->tensors[op.res].Wp() : 0;
       a.relu = op.relu;
       a.bias = op.d_bias;
-      int smem = (int)convk::smem_bytes(a.N_tile, a.stages);
+      int smem = (int)convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout);
       if (smem > max_smem) max_smem = smem;
+      op.tmO = op.tmB;
+      if (a.tma_epi) {
+        // destination seen from its interior pixel (0,0) with the stored pitches: partial pixel boxes and
+        // the zero border are protected by TMA's bounds clipping
+        uint64_t dims[4] = {(uint64_t)to.C, (uint64_t)to.W, (uint64_t)to.H, (uint64_t)B};
+        uint64_t strides[3] = {(uint64_t)to.C * 2, (uint64_t)to.Wp() * to.C * 2, (uint64_t)to.Hp() * to.Wp() * to.C * 2};
+        uint32_t box[4] = {64, (uint32_t)a.bw, (uint32_t)a.bh, (uint32_t)a.bn};
+        uint32_t es[4] = {1, 1, 1, 1};
+        int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, to.ptr + to.interior_offset(), dims, strides,
+                               box, es, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+      }
       // weights: [Cout][Ktot] K-major, box 64 x N_tile, 128B swizzle
       {
         uint64_t dims[2] = {(uint64_t)op.Ktot, (uint64_t)op.Cout};
@@ -685,8 +699,8 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       a.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
       const long long total = (long long)a.tiles_w * a.tiles_h * a.tiles_n * a.tiles_N;
       int grid = (int)(total < n->num_sms ? total : n->num_sms);
-      size_t smem = convk::smem_bytes(a.N_tile, a.stages);
-      convk::k_conv_igemm<<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, a);
+      size_t smem = convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout);
+      convk::k_conv_igemm<<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, a);
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];
       size_t total = (size_t)B * to.H * to.W * (ti.C / 8);
