@@ -38,6 +38,31 @@ UNIT = "patches/s"
 RESNET34_GFLOP = 7.326  # convs + FC, 2*MACs, per 224^2 patch
 
 
+class ModelSpec:
+    """The two zoo models of BASELINE.json: configs[1] (default, the metric's model) and configs[2]."""
+
+    def __init__(self, name):
+        from oracle import forward as oforward
+
+        self.name = name
+        if name == "resnet34":
+            self.cfg = oforward.BREAST_RESNET34_CONFIG
+            self.make = lambda: oforward.make_resnet34(2, 0)
+            self.gflop, self.metric = RESNET34_GFLOP, METRIC
+            self.title, self.weights = "breast-tumor-resnet34.tcga-brca", "torchvision resnet34(num_classes=2), BN folded"
+        else:
+            from oracle import inceptionv4 as oinc
+
+            self.cfg = oinc.TIL_INCEPTIONV4_CONFIG
+            self.make = lambda: oinc.make_inceptionv4(2, 0)
+            self.gflop, self.metric = 24.505, "patches/sec (InceptionV4 299^2, bf16)"
+            self.title, self.weights = "pancancer-lymphocytes-inceptionv4.tcga", "Cadene-layout InceptionV4 without BatchNorm"
+        self.S = int(self.cfg["transform"][0]["arguments"]["size"])
+
+    def patch_px(self, mpp):
+        return int(round(self.cfg["patch_size_pixels"] * self.cfg["spacing_um_px"] / mpp))
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -45,6 +70,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--model", default="resnet34", choices=["resnet34", "inceptionv4"],
+                    help="resnet34 = BASELINE configs[1] (the metric); inceptionv4 = configs[2]")
     ap.add_argument("--slide", default="100000x80000", help="WxH of the synthetic slide (level 0 pixels)")
     ap.add_argument("--mpp", type=float, default=0.5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -54,9 +81,12 @@ def parse_args():
     return ap.parse_args()
 
 
-def workload_name(w, h, mpp, batch):
-    return (f"breast-tumor-resnet34.tcga-brca on a synthetic {w}x{h} slide at {mpp} um/px, "
-            f"patch 350px@0.25um -> 224^2, batch {batch}")
+def workload_name(w, h, mpp, batch, spec=None):
+    if spec is None or spec.name == "resnet34":
+        return (f"breast-tumor-resnet34.tcga-brca on a synthetic {w}x{h} slide at {mpp} um/px, "
+                f"patch 350px@0.25um -> 224^2, batch {batch}")
+    return (f"{spec.title} on a synthetic {w}x{h} slide at {mpp} um/px, patch {spec.cfg['patch_size_pixels']}px@"
+            f"{spec.cfg['spacing_um_px']}um -> {spec.S}^2, batch {batch}")
 
 
 # ------------------------------------------------------------------------------------------------
@@ -141,7 +171,7 @@ class CpuReference:
     fp32 + CPU softmax, batch 32 (wsinsight/modellib/data.py:270-314, transforms.py:22-38,
     run_inference.py:288-299,537-560), all host threads."""
 
-    def __init__(self, batch=None):
+    def __init__(self, batch=None, spec=None):
         import torch
 
         from oracle import forward as oforward
@@ -151,8 +181,9 @@ class CpuReference:
         # reference default batch is 32 (cli/run.py:369-376); many-core hosts get a larger batch so
         # that the intra-op thread pool of the fp32 forward is not starved
         self.batch = batch if batch is not None else (32 if self.cores <= 16 else 128)
-        self.cfg = oforward.BREAST_RESNET34_CONFIG
-        model = oforward.make_resnet34(2, 0)
+        spec = spec or ModelSpec("resnet34")
+        self.cfg = spec.cfg
+        model = spec.make()
         self.ts = torch.jit.freeze(torch.jit.script(model))
         from concurrent.futures import ThreadPoolExecutor
 
@@ -216,21 +247,22 @@ def reference_arm(args, rank, world):
     if rank != 0:
         return
     w, h = (int(v) for v in args.slide.lower().split("x"))
-    ps = int(round(350 * 0.25 / args.mpp))
-    ref = CpuReference()
+    spec = ModelSpec(args.model)
+    ps = spec.patch_px(args.mpp)
+    ref = CpuReference(spec=spec)
     coords = sample_grid_coords(w, h, ps, (args.steps + args.warmup) * ref.batch, seed=0)
     t_all0 = time.perf_counter()
     times = time_cpu_reference(ref, coords, ps, w, h, 0, args.steps, args.warmup)
     total = sum(times)
     val = len(times) * ref.batch / total
-    sample = (f"{len(times)} timed batches of {ref.batch} patches ({ps}px RGBA -> 224^2) at seeded grid positions of "
+    sample = (f"{len(times)} timed batches of {ref.batch} patches ({ps}px RGBA -> {spec.S}^2) at seeded grid positions of "
               f"the {w}x{h} synthetic slide, regenerated on the host; PIL/torchvision transform on min(cores,8) worker threads + frozen "
-              f"TorchScript ResNet34 fp32 + softmax, {ref.cores} threads")
+              f"TorchScript {spec.name} fp32 + softmax, {ref.cores} threads")
     line = {
-        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": len(times),
+        "impl": "reference", "metric": spec.metric, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": len(times),
         "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(w, h, args.mpp, args.batch), "batch_per_step": ref.batch,
+        "config": {"workload": workload_name(w, h, args.mpp, args.batch, spec), "batch_per_step": ref.batch,
                    "note": "bounded sample of the same workload; CPU batch 32 (reference default) or 128 on >16 cores"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -276,7 +308,8 @@ def b200_arm(args, rank, world, local_rank):
     peaks = load_peaks()
     W, H = (int(v) for v in args.slide.lower().split("x"))
     B, K, Wm = args.batch, args.steps, args.warmup
-    cfg = oforward.BREAST_RESNET34_CONFIG
+    spec = ModelSpec(args.model)
+    cfg = spec.cfg
     transform = make_compose_from_transform_config(cfg["transform"])
 
     def ev():
@@ -305,12 +338,12 @@ def b200_arm(args, rank, world, local_rank):
     assert n_local >= B, f"rank {rank}: only {n_local} in-tissue patches for batch {B}"
     nb_local = n_local // B
 
-    model = oforward.make_resnet34(2, 0)
-    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(model)), 2, input_size=224, max_batch=B,
+    model = spec.make()
+    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(model)), 2, input_size=spec.S, max_batch=B,
                                        device=dev)
     lay = net.input_layout
     plan = PreprocessPlan(slide, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"],
-                          lay["plane_stride_px"])
+                          lay["plane_stride_px"], lay["channels"])
     xin = net.alloc_input(B)
     probs = torch.empty((nb_local * B, 2), dtype=torch.float32, device=dev)
 
@@ -422,12 +455,12 @@ def b200_arm(args, rank, world, local_rank):
     n_conv = sum(1 for o in ops if o["kind"] == "conv")
     other_ms = sum(o["ms_total"] for o in ops if o["kind"] != "conv")
     achieved = conv_fl * B * nfwd / (conv_ms * 1e-3) / 1e12
-    roofline = {"kernel": "convk::k_conv_igemm (36 launches per step)", "bound": "tensor", "achieved": achieved,
+    roofline = {"kernel": f"tcgen05 conv kernels: convs::k_conv_stem + convf::k_conv_flat + convk::k_conv_igemm ({n_conv} launches per step)", "bound": "tensor", "achieved": achieved,
                 "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
                 "traffic": None, "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
                 "flops_per_launch_avg": conv_fl * B / n_conv, "avg_launch_ms": conv_ms / (n_conv * nfwd),
                 "share_of_step": conv_ms / ms}
-    pp_bytes = ps * ps * 4 + 224 * 224 * 3 * 2     # read ps^2 RGBA + write S^2 x 3 bf16
+    pp_bytes = ps * ps * 4 + spec.S * spec.S * 3 * 2     # read ps^2 RGBA + write S^2 x 3 bf16
     stages = {
         "preprocess": {"ms_per_step": pp_ms / K, "bound": "hbm", "achieved_gbs": pp_bytes * B * K / (pp_ms * 1e-3) / 1e9,
                        "peak_gbs": peaks["hbm_gbs"], "frac": pp_bytes * B * K / (pp_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
@@ -439,33 +472,33 @@ def b200_arm(args, rank, world, local_rank):
     }
 
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "metric": spec.metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": workload_name(W, H, args.mpp, B), "batch_per_gpu": B, "global_batch": B * world,
+        "config": {"workload": workload_name(W, H, args.mpp, B, spec), "batch_per_gpu": B, "global_batch": B * world,
                    "patches_sharded": "contiguous x-bands of the x-major patch list, no data-path collective",
                    "l2": "inputs larger than L2 (125 MB of source pixels + GBs of activations per step; "
                          "consecutive steps read different patches)",
-                   "weights": "random-init torchvision resnet34(num_classes=2), jit.script+freeze, BN folded"},
+                   "weights": f"random-init {spec.weights}, jit.script+freeze"},
         "roofline": roofline, "stages": stages, "clocks": clocks, "gpu_launches": launches,
-        "tensor_pipe_frac_of_step": value / world * RESNET34_GFLOP * 1e9 / (peaks["tf_sustained"] * 1e12),
+        "tensor_pipe_frac_of_step": value / world * spec.gflop * 1e9 / (peaks["tf_sustained"] * 1e12),
     }
     if e2e is not None:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(args, coords_all, ps, W, H, thumb, res)
+        line["cpu_baseline"] = cpu_baseline(args, coords_all, ps, W, H, thumb, res, spec)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
-def cpu_baseline(args, coords_all, ps, W, H, thumb, res):
+def cpu_baseline(args, coords_all, ps, W, H, thumb, res, spec):
     """Bounded CPU sample of the same workload on this box's host cores (rank 0, N=1)."""
     import numpy as np
 
     from oracle import patchgrid, segment
 
-    ref = CpuReference()
+    ref = CpuReference(spec=spec)
     n = int(coords_all.shape[0])
     rng = np.random.default_rng(0)
     idx = np.sort(rng.choice(n, size=min(n, ref.batch * 40), replace=False))
@@ -473,9 +506,9 @@ def cpu_baseline(args, coords_all, ps, W, H, thumb, res):
     times = time_cpu_reference(ref, coords, ps, W, H, 0, steps=38, warmup=2, budget_s=args.cpu_seconds)
     val = len(times) * ref.batch / sum(times)
     out = {"value": val, "unit": UNIT, "cores": ref.cores, "kind": "port",
-           "sample": (f"{len(times)} timed batches of {ref.batch} in-tissue patches ({ps}px RGBA -> 224^2, seeded sample of the "
+           "sample": (f"{len(times)} timed batches of {ref.batch} in-tissue patches ({ps}px RGBA -> {spec.S}^2, seeded sample of the "
                       f"slide's patch list, pixels regenerated on the host); PIL/torchvision transform on "
-                      f"min(cores,8) worker threads + frozen TorchScript ResNet34 fp32 + softmax, {ref.cores} threads"),
+                      f"min(cores,8) worker threads + frozen TorchScript {spec.name} fp32 + softmax, {ref.cores} threads"),
            "ms_per_batch": 1e3 * sum(times) / len(times), "batch": ref.batch}
     # seg + patchify on the CPU (cv2 + scipy restatement + contour/point-in-polygon), same thumbnail
     th = thumb.cpu().numpy()

@@ -109,6 +109,9 @@ int wsi_preproc_run_u8(void* plan, const int32_t* d_coords_xy, int n, uint8_t* d
  * wsi_net_input_layout): two row-parity planes, bf16 [2][max_batch][P][2P][4] with P = out_H/2, planes
  * plane_stride_px pixels apart; 0 restores [n][out_H][out_W][4]. */
 int wsi_preproc_plan_set_parity_layout(void* plan, long long plane_stride_px);
+/* bf16 channels per output pixel: 4 (default) or 8 (first convolutions that run on the generic kernel);
+ * channels 3.. are zero. */
+int wsi_preproc_plan_set_channels(void* plan, int channels);
 int wsi_preproc_plan_info(void* plan, int* info8);
 void wsi_preproc_plan_destroy(void* plan);
 

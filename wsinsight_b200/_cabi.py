@@ -70,6 +70,7 @@ _PROTOS = {
     "wsi_net_input_layout": (c_int, [c_void_p, c_int_p]),
     "wsi_net_input_bytes": (c_size_t, [c_void_p]),
     "wsi_preproc_plan_set_parity_layout": (c_int, [c_void_p, c_ll]),
+    "wsi_preproc_plan_set_channels": (c_int, [c_void_p, c_int]),
     "wsi_hostpipe_create": (c_int, [c_void_p, c_int, c_ll, c_int, c_float_p, c_float_p, c_int, c_int,
                                     C.POINTER(c_void_p)]),
     "wsi_hostpipe_submit": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),

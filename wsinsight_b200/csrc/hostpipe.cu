@@ -67,7 +67,7 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
   int hwc[3] = {0, 0, 0};
   int rc = wsi_net_input_geometry(net, hwc);
   if (rc) return rc;
-  WSI_ARG_CHECK(hwc[2] == 4 && hwc[0] >= out_size && hwc[1] >= out_size && ((hwc[0] - out_size) % 2) == 0 &&
+  WSI_ARG_CHECK((hwc[2] == 4 || hwc[2] == 8) && hwc[0] >= out_size && hwc[1] >= out_size && ((hwc[0] - out_size) % 2) == 0 &&
                     hwc[0] == hwc[1],
                 "wsi_hostpipe_create: network input %dx%dx%d does not fit out_size %d", hwc[0], hwc[1], hwc[2],
                 out_size);
@@ -116,6 +116,7 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
     rc = wsi_preproc_plan_create(s.d_stage, patch_size, (long long)max_batch * patch_size, patch_pitch_bytes,
                                  patch_size, out_size, mean, stdv, hwc[0], hwc[1], pad, pad, &s.plan);
     if (!rc) rc = wsi_preproc_plan_set_parity_layout(s.plan, plane_stride_px);
+    if (!rc) rc = wsi_preproc_plan_set_channels(s.plan, hwc[2]);
     if (rc) {
       destroy(p);
       return rc;

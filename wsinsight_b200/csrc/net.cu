@@ -212,14 +212,20 @@ __global__ void k_copy_interior(const uint4* __restrict__ src, uint4* __restrict
   if (to_padded) dst[pi] = src[idx]; else dst[idx] = src[pi];
 }
 
-void pick_box(int Wo, int Ho, int* bw, int* bh, int* bn) {
-  int w = 8;
-  while (w > 1 && (Wo % w) != 0) w >>= 1;
-  int h = 8;
-  while (h > 1 && (Ho % h) != 0) h >>= 1;
-  *bw = w;
-  *bh = h;
-  *bn = 128 / (w * h);
+// Pixel box (bw x bh x bn images == 128 GEMM rows) of one M tile: the shape that wastes the fewest rows
+// on partial tiles for this output size and batch; ties go to the wider box (longer contiguous runs).
+void pick_box(int Wo, int Ho, int B, int* bw, int* bh, int* bn) {
+  double best = 1e30;
+  for (int w = 16; w >= 1; w >>= 1)
+    for (int h = 16; h >= 1; h >>= 1) {
+      if (w * h > 128) continue;
+      const int n = 128 / (w * h);
+      const double rows = (double)((Wo + w - 1) / w * w) * ((Ho + h - 1) / h * h) * ((B + n - 1) / n * n);
+      if (rows < best * 0.999) {
+        best = rows;
+        *bw = w; *bh = h; *bn = n;
+      }
+    }
 }
 
 int pick_ntile(int Cout) {
@@ -550,7 +556,7 @@ int wsi_net_finalize(void* net) {
       }
       convk::Args& a = op.ca;
       memset(&a, 0, sizeof(a));
-      pick_box(to.W, to.H, &a.bw, &a.bh, &a.bn);
+      pick_box(to.W, to.H, B, &a.bw, &a.bh, &a.bn);
       a.tiles_w = wsi_cdiv(to.W, a.bw);
       a.tiles_h = wsi_cdiv(to.H, a.bh);
       a.Ho = to.H; a.Wo = to.W;

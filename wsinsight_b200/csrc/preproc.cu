@@ -76,6 +76,7 @@ struct Plan {
   float mean[3], stdv[3];
   int has_norm;
   long long plane_stride_px = 0;  // > 0: row-parity plane output layout (conv_stem.cuh)
+  int channels = 4;               // 4 | 8 bf16 per output pixel (channels >= 3 are zero)
   int *d_lo, *d_cnt, *d_coef;     // taps (same table for both axes: square patches)
   size_t smem_bytes;
   CUtensorMap tmap;
@@ -93,6 +94,7 @@ struct PPArgs {
   float m0, m1, m2, s0, s1, s2;
   int has_norm;
   long long plane_stride_px;   // > 0: write two row-parity planes [2][maxB][P][2P] of 4-channel pixels
+  int channels;                // 4: 8-byte pixels, 8: 16-byte pixels
 };
 
 __device__ __forceinline__ uint32_t clip8(int v) {
@@ -197,7 +199,10 @@ __global__ void __launch_bounds__(PP_THREADS)
     } else {
       o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
     }
-    reinterpret_cast<uint2*>(a.out)[o] = v;
+    if (a.channels == 8)
+      reinterpret_cast<uint4*>(a.out)[o] = make_uint4(v.x, v.y, 0u, 0u);
+    else
+      reinterpret_cast<uint2*>(a.out)[o] = v;
   }
 }
 
@@ -343,6 +348,7 @@ static int preproc_launch(void* plan, const int32_t* d_coords_xy, int n, void* d
   a.s0 = p->stdv[0]; a.s1 = p->stdv[1]; a.s2 = p->stdv[2];
   a.has_norm = p->has_norm;
   a.plane_stride_px = p->plane_stride_px;
+  a.channels = p->channels;
   dim3 grid(n, p->nbands);
   k_preprocess<<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
   wsi_count_launch(1);
@@ -366,6 +372,14 @@ int wsi_preproc_plan_set_parity_layout(void* plan, long long plane_stride_px) {
   WSI_ARG_CHECK(plane_stride_px == 0 || (p->out_H == p->out_W && (p->out_H & 1) == 0),
                 "wsi_preproc_plan_set_parity_layout: the padded output must be square with an even side");
   p->plane_stride_px = plane_stride_px;
+  return WSI_OK;
+}
+
+int wsi_preproc_plan_set_channels(void* plan, int channels) {
+  WSI_ARG_CHECK(plan && (channels == 4 || channels == 8), "wsi_preproc_plan_set_channels: channels must be 4 or 8");
+  Plan* p = (Plan*)plan;
+  WSI_ARG_CHECK(channels == 4 || p->plane_stride_px == 0, "wsi_preproc_plan_set_channels: the parity layout has 4 channels");
+  p->channels = channels;
   return WSI_OK;
 }
 

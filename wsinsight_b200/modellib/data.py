@@ -42,7 +42,7 @@ class PreprocessPlan:
     """Owns a ``wsi_preproc_plan`` for one (slide, patch_size, transform, output layout)."""
 
     def __init__(self, slide, patch_size: int, transform: FusedTransform, out_H=None, out_W=None, pad_top=0,
-                 pad_left=0, plane_stride_px=0):
+                 pad_left=0, plane_stride_px=0, channels=4):
         torch = _cabi.require_cuda()
         self.slide = slide
         self.patch_size = int(patch_size)
@@ -60,6 +60,9 @@ class PreprocessPlan:
             self.plane_stride_px = int(plane_stride_px)
             if self.plane_stride_px:
                 _cabi.call("wsi_preproc_plan_set_parity_layout", self._h, self.plane_stride_px)
+            self.channels = int(channels)
+            if self.channels != 4:
+                _cabi.call("wsi_preproc_plan_set_channels", self._h, self.channels)
 
     def info(self):
         a = (C.c_int * 8)()
@@ -77,7 +80,7 @@ class PreprocessPlan:
         if self.plane_stride_px:
             assert out.numel() >= 2 * self.plane_stride_px * 4
         else:
-            assert out.numel() >= n * self.out_H * self.out_W * 4
+            assert out.numel() >= n * self.out_H * self.out_W * self.channels
         with torch.cuda.device(out.device):
             _cabi.call("wsi_preproc_run", self._h, coords_xy.data_ptr(), n, out.data_ptr(), _cabi.stream_ptr(stream))
 
@@ -124,11 +127,12 @@ class WholeSlideImagePatches:
         self.batch_size = int(batch_size)
         lay = input_layout or {}
         self.plan = PreprocessPlan(slide, self.patch_size, transform, lay.get("out_H"), lay.get("out_W"),
-                                   lay.get("pad_top", 0), lay.get("pad_left", 0), lay.get("plane_stride_px", 0))
+                                   lay.get("pad_top", 0), lay.get("pad_left", 0), lay.get("plane_stride_px", 0),
+                                   lay.get("channels", 4))
         dev = slide.rgba.device
         self.dev_coords = device_coords if device_coords is not None else \
             torch.from_numpy(np.ascontiguousarray(self.coords[:, :2], dtype=np.int32)).to(dev)
-        nelem = lay.get("buffer_elems") or self.batch_size * self.plan.out_H * self.plan.out_W * 4
+        nelem = lay.get("buffer_elems") or self.batch_size * self.plan.out_H * self.plan.out_W * self.plan.channels
         self._buf = torch.zeros(int(nelem), dtype=torch.bfloat16, device=dev)
 
     def __len__(self):

@@ -106,17 +106,22 @@ class B200Network:
             raise UnknownArchitectureError("the network input must feed exactly one convolution")
         stem = first_convs[0]
         kh, kw = int(stem.weight.shape[2]), int(stem.weight.shape[3])
-        if not (kh == 7 and kw == 7 and stem.stride == 2 and tuple(stem.pad) == (3, 3) and stem.residual is None):
-            raise UnknownArchitectureError(
-                f"first convolution {kh}x{kw}/s{stem.stride} is not supported yet (7x7/2 pad 3 only)")
         S = self.input_size
-        if S % 2:
-            raise UnknownArchitectureError("the 7x7/2 stem needs an even input size")
-        # layout the preprocess kernel must write: [B][S+6][S+6][4] bf16, patch at (3,3)
-        self.input_layout = dict(out_H=S + 6, out_W=S + 6, pad_top=3, pad_left=3, channels=4)
-        # tensor assignment: cat members write into the cat tensor at a channel offset
+        stem7 = (kh == 7 and kw == 7 and stem.stride == 2 and tuple(stem.pad) == (3, 3) and stem.residual is None
+                 and S % 2 == 0)
+        if stem.residual is not None:
+            raise UnknownArchitectureError("the first convolution cannot take a residual")
         tensor_of, c_off = {}, {}
-        tensor_of[0] = self._add_tensor(S + 6, S + 6, 4, external=True)
+        if stem7:
+            # ResNet family: the preprocess kernel writes the padded image, patch at (3,3), 4 channels
+            # (as row-parity planes when the 64-filter stem kernel is used, see csrc/conv_stem.cuh)
+            self.input_layout = dict(out_H=S + 6, out_W=S + 6, pad_top=3, pad_left=3, channels=4)
+            tensor_of[0] = self._add_tensor(S + 6, S + 6, 4, external=True)
+        else:
+            # any other first convolution (InceptionV4: 3x3/2, no padding) runs on the generic per-tap kernel
+            # over an 8-channel NHWC image (channels 3..7 zero, weights zero-padded to match)
+            self.input_layout = dict(out_H=S, out_W=S, pad_top=0, pad_left=0, channels=8)
+            tensor_of[0] = self._add_tensor(S, S, 8, external=True)
         c_off[0] = 0
         for i, n in enumerate(nodes):
             if n.kind == "cat":
@@ -150,7 +155,16 @@ class B200Network:
                 w = n.weight.contiguous()
                 b = n.bias.contiguous() if n.bias is not None else None
                 self._keep += [w, b]
-                if n is stem:
+                if n is stem and not stem7:
+                    import torch
+
+                    w8 = torch.zeros((cout, 8, int(w.shape[2]), int(w.shape[3])), dtype=torch.float32)
+                    w8[:, :cin] = w
+                    self._keep.append(w8)
+                    _cabi.call("wsi_net_add_conv", self._h, tensor_of[x], tensor_of[i], c_off[i], _fptr(w8), _fptr(b),
+                               8, cout, int(w.shape[2]), int(w.shape[3]), int(n.stride), int(n.pad[0]),
+                               int(n.pad[1]), 1 if n.relu else 0, -1)
+                elif n is stem:
                     _cabi.call("wsi_net_add_stem7x7", self._h, tensor_of[x], tensor_of[i], _fptr(w), _fptr(b), cout,
                                1 if n.relu else 0)
                 else:
@@ -172,6 +186,7 @@ class B200Network:
         if self.num_classes is None:
             raise UnknownArchitectureError("no classifier head found")
         self._tensor_of = tensor_of
+        self._c_off = c_off
 
     @staticmethod
     def _tensor_channels(nodes, tensor_of, x):
@@ -198,7 +213,7 @@ class B200Network:
         lay = self.input_layout
         b, _, s, _ = x_nchw.shape
         hp, pt, pl = lay["out_H"], lay["pad_top"], lay["pad_left"]
-        img = torch.zeros((self.max_batch, hp, hp, 4), dtype=torch.bfloat16, device=self.device)
+        img = torch.zeros((self.max_batch, hp, hp, lay["channels"]), dtype=torch.bfloat16, device=self.device)
         img[:b, pt:pt + s, pl:pl + s, :3] = x_nchw.permute(0, 2, 3, 1).to(torch.bfloat16).to(self.device)
         buf = self.alloc_input()
         if lay["kind"] == "parity":
@@ -239,6 +254,10 @@ class B200Network:
             _cabi.call("wsi_net_read_tensor", self._h, self._tensor_of[node_index], int(batch), out.data_ptr(),
                        _cabi.stream_ptr())
         return out
+
+    def channel_offset(self, node_index: int) -> int:
+        """Channel offset of IR node ``node_index`` inside its (possibly concat) tensor."""
+        return int(self._c_off.get(node_index, 0))
 
     def set_profiling(self, slots: int):
         _cabi.call("wsi_net_set_profiling", self._h, int(slots))
