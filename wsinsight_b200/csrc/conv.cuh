@@ -41,6 +41,11 @@ struct Args {
   int out_Hp, out_Wp, res_Hp, res_Wp;        // stored rows / columns of the destination / residual tensor
   int tma_epi;                               // N_tile % 64 == 0: smem-staged epilogue + TMA stores, two warp groups
   int Cout;                                  // tiles_N * N_tile (bias entries staged in smem)
+  int cluster;                               // 1, or 2: CTA PAIRS (cta_group::2).  One tcgen05.mma of the leader CTA
+                                             // spans both SMs: M = 256 (two M tiles of the same N tile), each CTA
+                                             // stages its own 128 activation rows and HALF of the weight k-block, so a
+                                             // stage is 16 KB + N_tile*64 B and the ring is 1.5x deeper (the single-CTA
+                                             // ring starved: ncu showed the MMA warp waiting on TMA data 26 % of the time)
   int relu;
   const __nv_bfloat16* residual;
   const float* bias;                         // [tiles_N * N_tile]
@@ -123,6 +128,9 @@ __device__ __forceinline__ void epi_chunk64_regs(uint32_t t_addr, int row, uint3
   }
 }
 
+// CL = 1: one CTA per tile.  CL = 2: CTA pairs (cta_group::2); a separate instantiation because a kernel that
+// contains cta_group::2 instructions can only be launched as 2-CTA clusters.
+template <int CL>
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_igemm(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                  const __grid_constant__ CUtensorMap tmapO, const Args a) {
@@ -130,7 +138,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   // carve: [stages x A 16KB][stages x B N_tile*128][barriers]
   if (ptx::smem_u32(smem_raw) & 1023u) __trap();
   uint8_t* smem = smem_raw;
-  const int B_BYTES = a.N_tile * BLOCK_K * 2;           // stage stride (the stem uses half of each stage)
+  const int B_BYTES = (CL == 2 ? a.N_tile / 2 : a.N_tile) * BLOCK_K * 2;   // per-CTA stage stride (the stem uses half)
   const int kbytes = a.is_stem ? 64 : 128;              // bytes of K per smem row
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)a.stages * A_BYTES;
@@ -145,7 +153,19 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = a.tiles_w * a.tiles_h * a.tiles_n;
-  const int total_tiles = m_tiles * a.tiles_N;
+  // work units: one (M tile, N tile) per CTA and iteration.  In pair mode unit u of the PAIR is
+  // (M-tile pair u / tiles_N, N tile u % tiles_N) and CTA `crank` takes M tile 2*pair + crank, clamped to the
+  // last tile (an odd tile count makes the last pair compute the same tile twice: identical stores).
+  const uint32_t crank = CL == 2 ? ptx::cluster_ctarank() : 0u;
+  const int m_units = CL == 2 ? (m_tiles + 1) / 2 : m_tiles;
+  const int total_units = m_units * a.tiles_N;
+  const int first_unit = CL == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int unit_step = CL == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  auto unit_to_tile = [&](int u, int& nt, int& mt) {
+    nt = u % a.tiles_N;
+    mt = u / a.tiles_N;
+    if (CL == 2) mt = min(2 * mt + (int)crank, m_tiles - 1);
+  };
   const int num_kb = a.is_stem ? 7 : a.KH * a.KW * a.cin_chunks;
 
   if (warp == 0 && lane == 0) {
@@ -157,16 +177,26 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], (a.tma_epi && a.N_tile > 64) ? 8 : 4);
+      ptx::mbar_init(&tempty[s], (uint32_t)(((a.tma_epi && a.N_tile > 64) ? 8 : 4) * CL));
     }
     ptx::fence_barrier_init();
   }
+  if (CL == 2) {
+    __syncthreads();
+    ptx::cluster_sync();                      // both CTAs' barriers exist before the pair-wide TMEM allocation
+  }
   if (warp == 1) {
-    ptx::tmem_alloc(tmem_slot, 512);
-    ptx::tmem_relinquish();
+    if (CL == 2) {
+      ptx::tmem_alloc_2sm(tmem_slot, 512);
+      ptx::tmem_relinquish_2sm();
+    } else {
+      ptx::tmem_alloc(tmem_slot, 512);
+      ptx::tmem_relinquish();
+    }
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (CL == 2) ptx::cluster_sync();   // the peer's barriers are initialised before anything remote happens
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -174,9 +204,9 @@ __global__ void __launch_bounds__(THREADS, 1)
     // ===================== TMA producer (whole warp loops, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int nt = tile % a.tiles_N;
-      int mt = tile / a.tiles_N;
+    for (int u = first_unit; u < total_units; u += unit_step) {
+      int nt, mt;
+      unit_to_tile(u, nt, mt);
       const int tw = mt % a.tiles_w;
       mt /= a.tiles_w;
       const int th = mt % a.tiles_h;
@@ -185,9 +215,21 @@ __global__ void __launch_bounds__(THREADS, 1)
       for (int kb = 0; kb < num_kb; ++kb) {
         ptx::mbar_wait(&empty[stage], phase ^ 1);
         if (ptx::elect_one()) {
-          ptx::mbar_arrive_expect_tx(&full[stage], (uint32_t)((BLOCK_M + a.N_tile) * kbytes));
+          // pair mode: only the leader arms its barrier, for the bytes of BOTH CTAs (2 x (16 KB + half B))
+          if (CL != 2 || crank == 0)
+            ptx::mbar_arrive_expect_tx(&full[stage], (uint32_t)((CL == 2 ? 2 * BLOCK_M : BLOCK_M) + a.N_tile) * kbytes);
           void* dA = sA + (size_t)stage * A_BYTES;
           void* dB = sB + (size_t)stage * B_BYTES;
+          if (CL == 2) {
+            // own 128 activation rows + own half of the weight k-block; completion lands on the LEADER's barrier
+            const int cc = kb % a.cin_chunks;
+            const int tap = kb / a.cin_chunks;
+            const int kw = tap % a.KW, kh = tap / a.KW;
+            const uint32_t lbar = ptx::leader_bar_addr(&full[stage]);
+            ptx::tma_load_4d_2sm(dA, &tmapA, lbar, cc * BLOCK_K, wo0 * a.stride + kw - a.pad_w,
+                                 ho0 * a.stride + kh - a.pad_h, n0);
+            ptx::tma_load_2d_2sm(dB, &tmapB, lbar, kb * BLOCK_K, nt * a.N_tile + (int)crank * (a.N_tile >> 1));
+          } else
           if (a.is_stem) {
             // rows 2*ho + kh of the padded image, 8 pixels x 4 channels starting at pixel 2*wo
             ptx::tma_load_4d(dA, &tmapA, &full[stage], 0, wo0, 2 * ho0 + kb, n0);
@@ -210,13 +252,17 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (whole warp loops; tcgen05 under elect.sync) =====================
-    const uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, a.N_tile);
+    // pair mode: only the leader CTA issues; its M = 256 instruction reads both CTAs' stages and writes
+    // both CTAs' accumulators, and its commits arrive on the barriers of BOTH CTAs.
+    const bool pair = CL == 2;
+    const uint32_t idesc = ptx::make_idesc_bf16(pair ? 2 * BLOCK_M : BLOCK_M, a.N_tile);
     const uint32_t hi = a.is_stem ? ptx::sw64_desc_hi() : ptx::sw128_desc_hi();
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    if (!pair || crank == 0)
+    for (int u = first_unit; u < total_units; u += unit_step) {
       ptx::mbar_wait(&tempty[acc], acc_phase ^ 1);
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
@@ -227,14 +273,23 @@ __global__ void __launch_bounds__(THREADS, 1)
         const uint32_t b_lo = ptx::desc_lo(ptx::smem_u32(sB + (size_t)stage * B_BYTES));
         if (ptx::elect_one()) {
           // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in 16-byte units
-          ptx::umma_bf16_lohi(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != 0));
-          ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
-          if (!a.is_stem) {
-            ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
-            ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+          if (pair) {
+            ptx::umma_bf16_lohi_2sm(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != 0));
+            ptx::umma_bf16_lohi_2sm(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+            ptx::umma_bf16_lohi_2sm(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+            ptx::umma_bf16_lohi_2sm(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+            ptx::umma_commit_2sm(&empty[stage], (uint16_t)3);      // frees the slot in both CTAs
+            if (kb == num_kb - 1) ptx::umma_commit_2sm(&tfull[acc], (uint16_t)3);
+          } else {
+            ptx::umma_bf16_lohi(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != 0));
+            ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+            if (!a.is_stem) {
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+              ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+            }
+            ptx::umma_commit(&empty[stage]);   // frees the smem slot once these MMAs retire
+            if (kb == num_kb - 1) ptx::umma_commit(&tfull[acc]);   // accumulator ready for the epilogue
           }
-          ptx::umma_commit(&empty[stage]);   // frees the smem slot once these MMAs retire
-          if (kb == num_kb - 1) ptx::umma_commit(&tfull[acc]);   // accumulator ready for the epilogue
         }
         __syncwarp();
         if (++stage == a.stages) {
@@ -269,11 +324,11 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int n_l = row / (a.bw * a.bh);
     int acc = 0, k = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++k) {
+    for (int u = first_unit; u < total_units; u += unit_step, ++k) {
       const bool part = cn > 1 ? (g < cn) : ((k & 1) == g);
       if (part) {
-        const int nt = tile % a.tiles_N;
-        int mt = tile / a.tiles_N;
+        int nt, mt;
+        unit_to_tile(u, nt, mt);
         const int tw = mt % a.tiles_w;
         mt /= a.tiles_w;
         const int th = mt % a.tiles_h;
@@ -303,7 +358,9 @@ __global__ void __launch_bounds__(THREADS, 1)
           if (last) {
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+            if (lane == 0) {
+              if (CL == 2) ptx::mbar_arrive_cluster(&tempty[acc], 0u); else ptx::mbar_arrive(&tempty[acc]);
+            }
           }
           ptx::fence_proxy_async();
           ptx::named_bar_sync(1 + g, 128);              // chunk staged
@@ -333,9 +390,9 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int n_l = row / (a.bw * a.bh);
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int nt = tile % a.tiles_N;
-      int mt = tile / a.tiles_N;
+    for (int u = first_unit; u < total_units; u += unit_step) {
+      int nt, mt;
+      unit_to_tile(u, nt, mt);
       const int tw = mt % a.tiles_w;
       mt /= a.tiles_w;
       const int th = mt % a.tiles_h;
@@ -392,7 +449,9 @@ __global__ void __launch_bounds__(THREADS, 1)
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if (CL == 2) ptx::mbar_arrive_cluster(&tempty[acc], 0u); else ptx::mbar_arrive(&tempty[acc]);
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -402,10 +461,11 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (CL == 2) ptx::cluster_sync();   // nobody leaves while the peer may still multicast / arrive here
   if (warp == 1) {
     __syncwarp();
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, 512);
+    if (CL == 2) ptx::tmem_dealloc_2sm(tmem_base, 512); else ptx::tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -414,8 +474,11 @@ __global__ void __launch_bounds__(THREADS, 1)
 static inline size_t smem_fixed(int tma_epi, int Cout) {
   return (tma_epi ? 2 * 16384 + (size_t)((Cout + 31) & ~31) * 4 : 0) + 256;
 }
-static inline size_t smem_bytes(int N_tile, int stages, int tma_epi, int Cout) {
-  return smem_fixed(tma_epi, Cout) + (size_t)stages * (A_BYTES + (size_t)N_tile * BLOCK_K * 2);
+static inline size_t stage_bytes(int N_tile, int cluster) {
+  return A_BYTES + (size_t)(cluster == 2 ? N_tile / 2 : N_tile) * BLOCK_K * 2;
+}
+static inline size_t smem_bytes(int N_tile, int stages, int tma_epi, int Cout, int cluster) {
+  return smem_fixed(tma_epi, Cout) + (size_t)stages * stage_bytes(N_tile, cluster);
 }
 
 }  // namespace convk

@@ -34,6 +34,7 @@ struct Op {
   convf::Args fa;
   convs::Args sa;
   bool flat = false;              // 3x3/s1/p1 over padded tensors -> convf::k_conv_flat
+  int max_pairs = 0;              // co-resident 2-CTA clusters of the per-tap kernel (queried at first launch)
   CUtensorMap tmA, tmB, tmO, tmR;
   __nv_bfloat16* d_w = nullptr;
   float* d_bias = nullptr;
@@ -58,6 +59,7 @@ struct Net {
   std::vector<Op> ops;
   int num_sms = 148;
   bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
+  bool cluster_enabled = true;    // WSI_B200_NO_CLUSTER=1: no CTA pairs / weight multicast in the per-tap kernel
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
   int prof_slots = 0;
@@ -249,6 +251,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0) n->num_sms = sms;
   const char* nf = getenv("WSI_B200_NO_FLAT");
   n->flat_enabled = !(nf && nf[0] == '1');
+  const char* nc = getenv("WSI_B200_NO_CLUSTER");
+  n->cluster_enabled = !(nc && nc[0] == '1');
   *net_out = n;
   return WSI_OK;
 }
@@ -567,7 +571,10 @@ int wsi_net_finalize(void* net) {
       a.tiles_N = op.Cout / a.N_tile;
       a.tma_epi = (a.N_tile % 64 == 0) ? 1 : 0;
       a.Cout = op.Cout;
-      const size_t stage_bytes = convk::A_BYTES + (size_t)a.N_tile * 128;
+      // CTA pairs (cta_group::2, M = 256): N must be a multiple of 32 there and each CTA's half of the weight
+      // block a whole number of 8-row swizzle groups
+      a.cluster = (n->cluster_enabled && !op.is_stem && a.N_tile >= 64 && a.N_tile % 32 == 0) ? 2 : 1;
+      const size_t stage_bytes = convk::stage_bytes(a.N_tile, a.cluster);
       int stages = (int)((227 * 1024 - convk::smem_fixed(a.tma_epi, a.Cout)) / stage_bytes);
       if (stages > 8) stages = 8;
       if (stages < 2) stages = 2;
@@ -580,7 +587,7 @@ int wsi_net_finalize(void* net) {
       a.res_Wp = op.res >= 0 ? n->tensors[op.res].Wp() : 0;
       a.relu = op.relu;
       a.bias = op.d_bias;
-      int smem = (int)convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout);
+      int smem = (int)convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout, a.cluster);
       if (smem > max_smem) max_smem = smem;
       op.tmO = op.tmB;
       if (a.tma_epi) {
@@ -598,7 +605,7 @@ int wsi_net_finalize(void* net) {
       {
         uint64_t dims[2] = {(uint64_t)op.Ktot, (uint64_t)op.Cout};
         uint64_t strides[1] = {(uint64_t)op.Ktot * 2};
-        uint32_t box[2] = {(uint32_t)(op.is_stem ? 32 : 64), (uint32_t)a.N_tile};
+        uint32_t box[2] = {(uint32_t)(op.is_stem ? 32 : 64), (uint32_t)(a.cluster == 2 ? a.N_tile / 2 : a.N_tile)};
         uint32_t es[2] = {1, 1};
         int rc = wsi_make_tmap(&op.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op.d_w, dims, strides, box, es,
                                op.is_stem ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
@@ -617,7 +624,9 @@ int wsi_net_finalize(void* net) {
     }
   }
   if (max_smem > 0)
-    WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  if (max_smem > 0)
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   if (max_smem_stem > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
   if (max_smem_flat > 0)
@@ -705,8 +714,42 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       a.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
       const long long total = (long long)a.tiles_w * a.tiles_h * a.tiles_n * a.tiles_N;
       int grid = (int)(total < n->num_sms ? total : n->num_sms);
-      size_t smem = convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout);
-      convk::k_conv_igemm<<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, a);
+      size_t smem = convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout, a.cluster);
+      if (a.cluster == 2) {
+        // CTA pairs: an even grid of 2-CTA clusters, one pair per two M tiles
+        const long long m_tiles = (long long)a.tiles_w * a.tiles_h * a.tiles_n;
+        const long long units = (m_tiles + 1) / 2 * a.tiles_N;
+        long long pairs = units < n->num_sms / 2 ? units : n->num_sms / 2;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)(2 * pairs));
+        cfg.blockDim = dim3(convk::THREADS);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (op.max_pairs == 0) {
+          // GPCs with an odd SM count cannot host a pair on every SM: size the persistent grid to what is co-resident
+          int nclusters = 0;
+          cudaLaunchConfig_t q = cfg;
+          q.gridDim = dim3((unsigned)(n->num_sms / 2 * 2));
+          if (cudaOccupancyMaxActiveClusters(&nclusters, convk::k_conv_igemm<2>, &q) != cudaSuccess || nclusters <= 0) {
+            cudaGetLastError();
+            nclusters = n->num_sms / 2;
+          }
+          op.max_pairs = nclusters;
+        }
+        if (pairs > op.max_pairs) pairs = op.max_pairs;
+        cfg.gridDim = dim3((unsigned)(2 * pairs));
+        WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convk::k_conv_igemm<2>, op.tmA, op.tmB, op.tmO, a));
+      } else {
+        convk::k_conv_igemm<1><<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, a);
+      }
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];
       size_t total = (size_t)B * to.H * to.W * (ti.C / 8);
