@@ -100,7 +100,8 @@ __device__ __forceinline__ void epi_chunk64(uint32_t t_addr, int row, bool keep,
 // Same, with the residual already in registers (8 x 16 B = this thread's 64 channels): used where shared
 // memory has no room for a residual staging ring; the caller issues the global loads one chunk ahead.
 __device__ __forceinline__ void epi_chunk64_regs(uint32_t t_addr, int row, uint32_t s_out, bool has_res,
-                                                 const uint4 (&rv)[8], const float* s_bias, int relu) {
+                                                 const uint4 (&rv)[8], const float* s_bias, int relu,
+                                                 bool keep = true) {
   uint32_t r[64];
   ptx::tmem_ld_32x32b_x32(t_addr, r);
   ptx::tmem_ld_32x32b_x32(t_addr + 32u, r + 32);
@@ -123,8 +124,9 @@ __device__ __forceinline__ void epi_chunk64_regs(uint32_t t_addr, int row, uint3
       v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
       v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
     }
-    ptx::st_shared_v4(s_out + row_base + (((uint32_t)c ^ sw) << 4), pack_bf16(v0, v1), pack_bf16(v2, v3),
-                      pack_bf16(v4, v5), pack_bf16(v6, v7));
+    uint32_t o0 = pack_bf16(v0, v1), o1 = pack_bf16(v2, v3), o2 = pack_bf16(v4, v5), o3 = pack_bf16(v6, v7);
+    if (!keep) o0 = o1 = o2 = o3 = 0u;   // border rows of the padded flat layout stay zero
+    ptx::st_shared_v4(s_out + row_base + (((uint32_t)c ^ sw) << 4), o0, o1, o2, o3);
   }
 }
 

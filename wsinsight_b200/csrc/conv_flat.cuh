@@ -16,13 +16,16 @@
 // T = 2 M-tiles (256 output positions) share each weight k-block, halving the B-operand feed;
 // small weight sets (<= 80 KB: ResNet layer1) stay RESIDENT in shared memory for the whole kernel.
 //
-// Warp roles as conv.cuh: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue.
+// Warp roles as conv.cuh: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 and 6-9 two epilogue groups
+// (group g owns M-tile g of every super-tile: with N = 64 one group could not drain 128 x 64 accumulators,
+// add the residual and stage the store in the ~1800 cycles the tensor pipe needs for the next tile --
+// ncu: tensor pipe 39 % / 55 % active with / without residual on ResNet34 layer1).
 #pragma once
 #include "conv.cuh"
 
 namespace convf {
 
-constexpr int THREADS = 192;
+constexpr int THREADS = 320;   // warp 0 producer, warp 1 MMA, warps 2-5 / 6-9: epilogue group of M-tile 0 / 1
 
 struct Args {
   int Hp, Wp, H, W, B;          // padded / interior geometry (input == output == residual geometry)
@@ -38,7 +41,8 @@ struct Args {
   int relu, has_res;
   int out_C, out_c_off;         // channels of the destination tensor / concat offset
   int tma_epi;                  // N % 64 == 0: epilogue staged in smem and written by TMA stores
-  int nOut, nRes;               // staging buffers (16 KB each) for output chunks / residual chunks
+  int nOut, nRes;               // output staging buffers (16 KB each) PER epilogue group; nRes unused (residual
+                                // chunks are prefetched from global memory into registers one chunk ahead)
   const __nv_bfloat16* residual;
   const float* bias;
   __nv_bfloat16* out;
@@ -136,9 +140,8 @@ __global__ void __launch_bounds__(THREADS, 1)
   const int b_bytes = a.N * 128;
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)a.stagesA * slab_bytes;
-  uint8_t* sOut = sB + (size_t)a.stagesB * b_bytes;                 // nOut x 16 KB (1024-aligned)
-  uint8_t* sRes = sOut + (size_t)a.nOut * 16384;                    // nRes x 16 KB
-  float* sBias = reinterpret_cast<float*>(sRes + (size_t)a.nRes * 16384);
+  uint8_t* sOut = sB + (size_t)a.stagesB * b_bytes;                 // 2 groups x nOut x 16 KB (1024-aligned)
+  float* sBias = reinterpret_cast<float*>(sOut + (size_t)2 * a.nOut * 16384);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 128);
   uint64_t* aFull = bars;
   uint64_t* aEmpty = aFull + a.stagesA;
@@ -165,7 +168,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4);
+      ptx::mbar_init(&tempty[s], a.tma_epi ? 4 * a.T : 4);
       ptx::mbar_init(&resFull[s], 1);
     }
     ptx::fence_barrier_init();
@@ -251,67 +254,66 @@ __global__ void __launch_bounds__(THREADS, 1)
     int acc = 0;
     uint32_t pacc = 0;
     if (a.tma_epi) {
-      const int et = (int)threadIdx.x - 64;            // 0..127 among the epilogue warps
-      const bool leader = et == 0;
+      const int g = (warp - 2) >> 2;                    // epilogue group == M-tile of the super-tile
+      const int gt = ((warp - 2) & 3) * 32 + lane;      // 0..127 inside the group
+      const bool leader = gt == 0;
       const int cn = a.N >> 6;                          // 64-column chunks per accumulator tile
-      const int per_tile = a.T * cn;
-      if (et < a.N) sBias[et] = a.bias[et];
-      // residual chunk k of this CTA -> (super-tile, t, j); issued by the leader nRes chunks ahead
-      auto issue_res = [&](int k) {
-        const int tile = blockIdx.x + (k / per_tile) * gridDim.x;
-        if (tile >= a.num_tiles) return;
-        const int w = k % per_tile, t = w / cn, j = w - t * cn;
-        const int b = k % a.nRes;
-        ptx::mbar_arrive_expect_tx(&resFull[b], 16384u);
-        ptx::tma_load_2d(sRes + (size_t)b * 16384, &tmapR, &resFull[b], 64 * j, (int)((long long)tile * TM + t * 128));
-      };
-      if (leader && a.has_res)
-        for (int k = 0; k < a.nRes; ++k) issue_res(k);
-      ptx::named_bar_sync(1, 128);                      // bias staged
-      int k = 0;
-      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        const long long q0 = (long long)tile * TM;
-        ptx::mbar_wait(&tfull[acc], pacc);
-        ptx::tc_fence_after();
-        for (int t = 0; t < a.T; ++t) {
-          const long long p = q0 + t * 128 + row;
+      for (int i = (int)threadIdx.x - 64; i < a.N; i += 256) sBias[i] = a.bias[i];
+      ptx::named_bar_sync(3, 256);                      // bias staged (both groups)
+      if (g < a.T) {
+        uint8_t* myOut = sOut + (size_t)g * a.nOut * 16384;
+        int k = 0;
+        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+          const long long q0 = (long long)tile * TM + g * 128;
+          const long long p = q0 + row;
           const int n = (int)(p / img);
           const int rem = (int)(p - (long long)n * img);
           const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
           const bool valid = (n < a.B) && (hp >= 1) && (hp <= a.H) && (wp >= 1) && (wp <= a.W);
+          const bool do_res = a.has_res && p < a.total_rows;
+          const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N);
+          uint4 rv[8], rn[8];
+          if (do_res) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rv[i] = __ldg(rbase + i);
+          }
+          ptx::mbar_wait(&tfull[acc], pacc);
+          ptx::tc_fence_after();
           for (int j = 0; j < cn; ++j, ++k) {
+            const bool last = j == cn - 1;
+            if (do_res && !last) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) rn[i] = __ldg(rbase + 8 * (j + 1) + i);
+            }
             const int ob = a.nOut == 2 ? (k & 1) : 0;
             if (leader) {
               if (a.nOut == 2) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<0>();
             }
-            ptx::named_bar_sync(1, 128);                // staging buffer ob is free again
-            uint32_t s_res = 0;
-            if (a.has_res) {
-              const int rb = k % a.nRes;
-              ptx::mbar_wait(&resFull[rb], (uint32_t)((k / a.nRes) & 1));
-              s_res = ptx::smem_u32(sRes + (size_t)rb * 16384);
-            }
-            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + t) * a.N + 64 * j);
-            convk::epi_chunk64(t_addr, row, valid, ptx::smem_u32(sOut + (size_t)ob * 16384), s_res, sBias + 64 * j,
-                               a.relu);
-            if (t == a.T - 1 && j == cn - 1) {          // accumulator stage fully read: hand it back
+            ptx::named_bar_sync(1 + g, 128);            // the group's staging buffer ob is free again
+            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + g) * a.N + 64 * j);
+            convk::epi_chunk64_regs(t_addr, row, ptx::smem_u32(myOut + (size_t)ob * 16384), do_res, rv, sBias + 64 * j,
+                                    a.relu, valid);
+            if (last) {                                 // this group's accumulator tile fully read: hand it back
               ptx::tc_fence_before();
               __syncwarp();
               if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
             }
             ptx::fence_proxy_async();
-            ptx::named_bar_sync(1, 128);                // tile chunk staged, residual buffer consumed
+            ptx::named_bar_sync(1 + g, 128);            // chunk staged
             if (leader) {
-              ptx::tma_store_2d(&tmapO, sOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)(q0 + t * 128));
+              ptx::tma_store_2d(&tmapO, myOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)q0);
               ptx::bulk_commit();
-              if (a.has_res) issue_res(k + a.nRes);
+            }
+            if (!last) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) rv[i] = rn[i];
             }
           }
+          if (++acc == 2) { acc = 0; pacc ^= 1; }
         }
-        if (++acc == 2) { acc = 0; pacc ^= 1; }
+        if (leader) ptx::bulk_wait<0>();
       }
-      if (leader) ptx::bulk_wait<0>();
-    } else
+    } else if (warp < 6)
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
       const long long q0 = (long long)tile * TM;
       ptx::mbar_wait(&tfull[acc], pacc);
@@ -384,7 +386,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
 static inline size_t smem_bytes(const Args& a) {
   return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * a.N * 128 +
-         (size_t)(a.nOut + a.nRes) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
+         (size_t)(2 * a.nOut) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
 }
 
 }  // namespace convf

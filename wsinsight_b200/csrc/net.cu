@@ -73,81 +73,54 @@ struct Net {
 __device__ __forceinline__ float bflo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bfhi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
-// (iHp, iWp, ip) / (oHp, oWp, op): stored rows, stored columns and border of the input / output tensor; `in`/`out` point at the buffer start
-__global__ void k_maxpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
-                          int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp, int op) {
-  const int cv = C / 8;
-  size_t total = (size_t)B * Ho * Wo * cv;
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  int c8 = idx % cv;
-  size_t p = idx / cv;
-  int wo = p % Wo;
-  p /= Wo;
-  int ho = p % Ho;
-  int n = p / Ho;
-  float m[8];
+// (iHp, iWp, ip) / (oHp, oWp, op): stored rows, stored columns and border of the input / output tensor; `in`/`out` point at the buffer start.
+// One CTA per output row (n, ho); threadIdx.x walks the 16-byte channel vectors, threadIdx.y the output columns:
+// no integer division on the data path, 32-bit offsets inside an image row, the k x k window re-read from L1.
+template <bool IS_MAX>
+__global__ void __launch_bounds__(256)
+    k_pool(const __nv_bfloat16* __restrict__ in, int H, int W, int C, int k, int s, int pad, int count_include_pad,
+           int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp,
+           int oWp, int op) {
+  const int cv = C >> 3;
+  const int n = blockIdx.x / Ho, ho = blockIdx.x - n * Ho;
+  const int y0 = max(ho * s - pad, 0), y1 = min(ho * s - pad + k, H);
+  const uint4* img = reinterpret_cast<const uint4*>(in + (size_t)n * iHp * iWp * C);
+  uint4* orow = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + ho + op) * oWp + op) * out_C + out_c_off);
+  const int ocv = out_C >> 3;
+  for (int wo = threadIdx.y; wo < Wo; wo += blockDim.y) {
+    const int x0 = max(wo * s - pad, 0), x1 = min(wo * s - pad + k, W);
+    const float d = count_include_pad ? (float)(k * k) : (float)((y1 - y0) * (x1 - x0));
+    for (int c8 = threadIdx.x; c8 < cv; c8 += blockDim.x) {
+      float m[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) m[i] = -INFINITY;
-  for (int dy = 0; dy < k; ++dy) {
-    int y = ho * s - pad + dy;
-    if (y < 0 || y >= H) continue;
-    for (int dx = 0; dx < k; ++dx) {
-      int x = wo * s - pad + dx;
-      if (x < 0 || x >= W) continue;
-      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * iHp + y + ip) * iWp + x + ip) * C) + c8);
-      m[0] = fmaxf(m[0], bflo(v.x)); m[1] = fmaxf(m[1], bfhi(v.x));
-      m[2] = fmaxf(m[2], bflo(v.y)); m[3] = fmaxf(m[3], bfhi(v.y));
-      m[4] = fmaxf(m[4], bflo(v.z)); m[5] = fmaxf(m[5], bfhi(v.z));
-      m[6] = fmaxf(m[6], bflo(v.w)); m[7] = fmaxf(m[7], bfhi(v.w));
+      for (int i = 0; i < 8; ++i) m[i] = IS_MAX ? -INFINITY : 0.f;
+      for (int y = y0; y < y1; ++y) {
+        const uint4* row = img + ((size_t)(y + ip) * iWp + ip) * cv + c8;
+        for (int x = x0; x < x1; ++x) {
+          const uint4 v = __ldg(row + (size_t)x * cv);
+          if (IS_MAX) {
+            m[0] = fmaxf(m[0], bflo(v.x)); m[1] = fmaxf(m[1], bfhi(v.x));
+            m[2] = fmaxf(m[2], bflo(v.y)); m[3] = fmaxf(m[3], bfhi(v.y));
+            m[4] = fmaxf(m[4], bflo(v.z)); m[5] = fmaxf(m[5], bfhi(v.z));
+            m[6] = fmaxf(m[6], bflo(v.w)); m[7] = fmaxf(m[7], bfhi(v.w));
+          } else {
+            m[0] += bflo(v.x); m[1] += bfhi(v.x); m[2] += bflo(v.y); m[3] += bfhi(v.y);
+            m[4] += bflo(v.z); m[5] += bfhi(v.z); m[6] += bflo(v.w); m[7] += bfhi(v.w);
+          }
+        }
+      }
+      if (!IS_MAX) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) m[i] = m[i] / d;
+      }
+      uint4 o;
+      o.x = convk::pack_bf16(m[0], m[1]);
+      o.y = convk::pack_bf16(m[2], m[3]);
+      o.z = convk::pack_bf16(m[4], m[5]);
+      o.w = convk::pack_bf16(m[6], m[7]);
+      orow[(size_t)wo * ocv + c8] = o;
     }
   }
-  uint4 o;
-  o.x = convk::pack_bf16(m[0], m[1]);
-  o.y = convk::pack_bf16(m[2], m[3]);
-  o.z = convk::pack_bf16(m[4], m[5]);
-  o.w = convk::pack_bf16(m[6], m[7]);
-  reinterpret_cast<uint4*>(out + (((size_t)n * oHp + ho + op) * oWp + wo + op) * out_C + out_c_off)[c8] = o;
-}
-
-__global__ void k_avgpool(const __nv_bfloat16* __restrict__ in, int B, int H, int W, int C, int k, int s, int pad,
-                          int count_include_pad, int Ho, int Wo, __nv_bfloat16* __restrict__ out, int out_C,
-                          int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp, int op) {
-  const int cv = C / 8;
-  size_t total = (size_t)B * Ho * Wo * cv;
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  int c8 = idx % cv;
-  size_t p = idx / cv;
-  int wo = p % Wo;
-  p /= Wo;
-  int ho = p % Ho;
-  int n = p / Ho;
-  float m[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) m[i] = 0.f;
-  int cnt = 0;
-  for (int dy = 0; dy < k; ++dy) {
-    int y = ho * s - pad + dy;
-    if (y < 0 || y >= H) continue;
-    for (int dx = 0; dx < k; ++dx) {
-      int x = wo * s - pad + dx;
-      if (x < 0 || x >= W) continue;
-      ++cnt;
-      uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)n * iHp + y + ip) * iWp + x + ip) * C) + c8);
-      m[0] += bflo(v.x); m[1] += bfhi(v.x); m[2] += bflo(v.y); m[3] += bfhi(v.y);
-      m[4] += bflo(v.z); m[5] += bfhi(v.z); m[6] += bflo(v.w); m[7] += bfhi(v.w);
-    }
-  }
-  float d = count_include_pad ? (float)(k * k) : (float)cnt;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) m[i] = m[i] / d;
-  uint4 o;
-  o.x = convk::pack_bf16(m[0], m[1]);
-  o.y = convk::pack_bf16(m[2], m[3]);
-  o.z = convk::pack_bf16(m[4], m[5]);
-  o.w = convk::pack_bf16(m[6], m[7]);
-  reinterpret_cast<uint4*>(out + (((size_t)n * oHp + ho + op) * oWp + wo + op) * out_C + out_c_off)[c8] = o;
 }
 
 // K4d: global average pool + FC + softmax (K>1) / sigmoid (K==1); one CTA per image.
@@ -495,7 +468,7 @@ int wsi_net_finalize(void* net) {
         f.tma_epi = (op.Cout % 64 == 0) ? 1 : 0;
         // shared-memory plan: prefer resident weights and double-buffered epilogue staging; give up
         // the second output staging buffer, then weight residency, before dropping below 2 slabs
-        const int want_res = (f.tma_epi && op.res >= 0) ? 2 : 0;
+        const int want_res = 0;   // the residual is prefetched into registers (no smem ring)
         const int plans[4][2] = {{1, 2}, {1, 1}, {0, 2}, {0, 1}};   // {resident weights, nOut}
         for (auto& pl : plans) {
           if (pl[0] && !f.resident_b) continue;
@@ -503,7 +476,7 @@ int wsi_net_finalize(void* net) {
           if (force_res >= 0 && pl[0] != force_res) continue;
           const int sB = pl[0] ? 9 * f.chunks : 4;
           const int nOut = f.tma_epi ? pl[1] : 0;
-          const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(nOut + want_res) * 16384;
+          const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(2 * nOut) * 16384;
           int sA = (int)(budget / ((long long)f.slab_rows * 128));
           if (sA > 4) sA = 4;
           f.stagesA = sA; f.stagesB = sB; f.nOut = nOut; f.nRes = want_res;
@@ -752,15 +725,18 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       }
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];
-      size_t total = (size_t)B * to.H * to.W * (ti.C / 8);
-      int blocks = (int)((total + 255) / 256);
+      const int cv = ti.C / 8;
+      const int bx = cv < 256 ? cv : 256;
+      int by = 256 / bx;
+      if (by > to.W) by = to.W;
+      dim3 block(bx, by);
       if (op.kind == OP_MAXPOOL)
-        k_maxpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, to.H, to.W,
-                                              to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
+        k_pool<true><<<B * to.H, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, 0, to.H, to.W,
+                                                     to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
       else
-        k_avgpool<<<blocks, 256, 0, stream>>>(in_ptr, B, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
-                                              op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.Hp(),
-                                              ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
+        k_pool<false><<<B * to.H, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
+                                                      op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.Hp(),
+                                                      ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
     } else if (op.kind == OP_HEAD) {
       WSI_ARG_CHECK(d_probs, "wsi_net_forward: null probs");
       k_head<<<B, HEAD_THREADS, ti.C * sizeof(float), stream>>>(in_ptr, ti.H * ti.W, ti.C, op.d_fcw, op.d_fcb, op.K,

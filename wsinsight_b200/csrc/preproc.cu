@@ -78,6 +78,7 @@ struct Plan {
   long long plane_stride_px = 0;  // > 0: row-parity plane output layout (conv_stem.cuh)
   int channels = 4;               // 4 | 8 bf16 per output pixel (channels >= 3 are zero)
   int *d_lo, *d_cnt, *d_coef;     // taps (same table for both axes: square patches)
+  uint16_t* d_lut = nullptr;      // [3][256] bf16 bits of ToTensor + Normalize applied to a u8 sample
   size_t smem_bytes;
   CUtensorMap tmap;
 };
@@ -86,13 +87,12 @@ struct PPArgs {
   const int* lo;
   const int* cnt;
   const int* coef;
+  const uint16_t* lut;
   const int32_t* coords;   // (n,2) top-left x,y
   __nv_bfloat16* out;
   uint32_t* out_u8;        // debug/parity: resized RGB0 u8 [n][S][S] (out is ignored when set)
   int ps, S, ksize, TR, G, ngroups, box_w, box_h, max_src_rows;
   int out_H, out_W, pad_top, pad_left;
-  float m0, m1, m2, s0, s1, s2;
-  int has_norm;
   long long plane_stride_px;   // > 0: write two row-parity planes [2][maxB][P][2P] of 4-channel pixels
   int channels;                // 4: 8-byte pixels, 8: 16-byte pixels
 };
@@ -102,35 +102,51 @@ __device__ __forceinline__ uint32_t clip8(int v) {
   return (uint32_t)min(max(v, 0), 255);
 }
 
-// grid: (n_patches, nbands); one CTA = TR output rows x S output columns of one patch
+// grid: (n_patches, nbands); one CTA = TR output rows x S output columns of one patch.
+// One thread owns one output column in both passes: its horizontal taps sit in registers (KS > 0) and the
+// vertical taps of a row are warp-uniform shared-memory broadcasts, so the inner loops are LDS + IMAD only.
+// ToTensor + Normalize + the bf16 rounding are a function of the u8 sample alone: a 3 x 256 table built on the
+// host with the same IEEE fp32 operations torchvision performs (x / 255, (x - mean) / std, one RNE).
+template <int KS>
 __global__ void __launch_bounds__(PP_THREADS)
     k_preprocess(const __grid_constant__ CUtensorMap tmap, PPArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint32_t* s_src = reinterpret_cast<uint32_t*>(smem);                          // box_h x box_w RGBA
   uint32_t* s_int = s_src + (size_t)a.box_h * a.box_w;                          // max_src_rows x S (RGBx u8)
+  int* s_lo = reinterpret_cast<int*>(s_int + (size_t)a.max_src_rows * a.S);     // S
+  int* s_cnt = s_lo + a.S;                                                      // S
+  int* s_coef = s_cnt + a.S;                                                    // S x ksize
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_coef + (size_t)a.S * a.ksize);   // 3 x 256 bf16 bit patterns
   __shared__ __align__(8) uint64_t s_bar;
 
   const int patch = blockIdx.x;
   const int r0 = blockIdx.y * a.TR;
   const int r1 = min(r0 + a.TR, a.S);
   const int px = a.coords[2 * patch + 0], py = a.coords[2 * patch + 1];
-  const int y_lo = a.lo[r0];
-  const int y_hi = a.lo[r1 - 1] + a.cnt[r1 - 1];
-  const int nrows = y_hi - y_lo;
 
   if (threadIdx.x == 0) {
     ptx::mbar_init(&s_bar, 1);
     ptx::fence_barrier_init();
   }
+  for (int i = threadIdx.x; i < a.S; i += PP_THREADS) {
+    s_lo[i] = a.lo[i];
+    s_cnt[i] = a.cnt[i];
+  }
+  for (int i = threadIdx.x; i < a.S * a.ksize; i += PP_THREADS) s_coef[i] = a.coef[i];
+  for (int i = threadIdx.x; i < 768; i += PP_THREADS) s_lut[i] = a.lut[i];
   __syncthreads();
+  const int y_lo = s_lo[r0];
+  const int y_hi = s_lo[r1 - 1] + s_cnt[r1 - 1];
+  const int nrows = y_hi - y_lo;
   uint32_t phase = 0;
+  constexpr int HALF = 1 << (PRECISION_BITS - 1);
 
   // horizontal pass: source rows [y_lo, y_hi) x output columns, chunked by TMA boxes
   for (int yc = 0; yc < nrows; yc += a.box_h) {
     const int rows_here = min(a.box_h, nrows - yc);
     for (int g = 0; g < a.ngroups; ++g) {
       const int xx0 = g * a.G, xx1 = min(xx0 + a.G, a.S);
-      const int xs0 = a.lo[xx0];
+      const int xs0 = s_lo[xx0];
       // TMA needs the box start 16-byte aligned in global memory: align x down to 4 pixels
       const int bx = (px + xs0) & ~3;
       const int shift = (px + xs0) - bx;
@@ -140,69 +156,94 @@ __global__ void __launch_bounds__(PP_THREADS)
       }
       ptx::mbar_wait(&s_bar, phase);
       phase ^= 1;
-      const int ncols = xx1 - xx0;
-      for (int i = threadIdx.x; i < rows_here * ncols; i += PP_THREADS) {
-        const int rr = i / ncols, xx = xx0 + (i - rr * ncols);
-        const int lo = a.lo[xx] - xs0 + shift, n = a.cnt[xx];
-        const int* k = a.coef + (size_t)xx * a.ksize;
-        const uint32_t* src = s_src + rr * a.box_w + lo;
-        int s0 = 1 << (PRECISION_BITS - 1), s1 = s0, s2 = s0;
-        for (int t = 0; t < n; ++t) {
-          const uint32_t p = src[t];
-          const int c = k[t];
-          s0 += (int)(p & 0xff) * c;
-          s1 += (int)((p >> 8) & 0xff) * c;
-          s2 += (int)((p >> 16) & 0xff) * c;
+      for (int xx = xx0 + threadIdx.x; xx < xx1; xx += PP_THREADS) {
+        const uint32_t* src = s_src + (s_lo[xx] - xs0 + shift);
+        uint32_t* dst = s_int + (size_t)yc * a.S + xx;
+        if (KS > 0) {
+          // taps beyond cnt carry zero coefficients (the table is zero padded); the pixels they touch are
+          // inside the shared-memory allocation, whatever they hold
+          int c[KS > 0 ? KS : 1];
+#pragma unroll
+          for (int t = 0; t < KS; ++t) c[t] = s_coef[xx * KS + t];
+#pragma unroll 4
+          for (int rr = 0; rr < rows_here; ++rr) {
+            int s0 = HALF, s1 = HALF, s2 = HALF;
+#pragma unroll
+            for (int t = 0; t < KS; ++t) {
+              const uint32_t p = src[rr * a.box_w + t];
+              s0 += (int)(p & 0xff) * c[t];
+              s1 += (int)((p >> 8) & 0xff) * c[t];
+              s2 += (int)((p >> 16) & 0xff) * c[t];
+            }
+            dst[rr * a.S] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
+          }
+        } else {
+          const int n = s_cnt[xx];
+          const int* k = s_coef + (size_t)xx * a.ksize;
+          for (int rr = 0; rr < rows_here; ++rr) {
+            int s0 = HALF, s1 = HALF, s2 = HALF;
+            for (int t = 0; t < n; ++t) {
+              const uint32_t p = src[rr * a.box_w + t];
+              const int c = k[t];
+              s0 += (int)(p & 0xff) * c;
+              s1 += (int)((p >> 8) & 0xff) * c;
+              s2 += (int)((p >> 16) & 0xff) * c;
+            }
+            dst[rr * a.S] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
+          }
         }
-        s_int[(yc + rr) * a.S + xx] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
       }
       __syncthreads();   // s_src is reused by the next box; s_int rows complete
     }
   }
 
   // vertical pass + ToTensor + Normalize + bf16 NHWC4 store
-  const int nout = (r1 - r0) * a.S;
-  for (int i = threadIdx.x; i < nout; i += PP_THREADS) {
-    const int ry = i / a.S, xx = i - ry * a.S;
-    const int yy = r0 + ry;
-    const int lo = a.lo[yy] - y_lo, n = a.cnt[yy];
-    const int* k = a.coef + (size_t)yy * a.ksize;
-    int s0 = 1 << (PRECISION_BITS - 1), s1 = s0, s2 = s0;
-    for (int t = 0; t < n; ++t) {
-      const uint32_t p = s_int[(lo + t) * a.S + xx];
-      const int c = k[t];
-      s0 += (int)(p & 0xff) * c;
-      s1 += (int)((p >> 8) & 0xff) * c;
-      s2 += (int)((p >> 16) & 0xff) * c;
+  const int P = a.out_H >> 1;
+  for (int xx = threadIdx.x; xx < a.S; xx += PP_THREADS) {
+    for (int yy = r0; yy < r1; ++yy) {
+      const int n = s_cnt[yy];                                   // warp-uniform
+      const uint32_t* col = s_int + (size_t)(s_lo[yy] - y_lo) * a.S + xx;
+      const int* k = s_coef + (size_t)yy * a.ksize;
+      int s0 = HALF, s1 = HALF, s2 = HALF;
+      if (KS > 0) {
+#pragma unroll
+        for (int t = 0; t < KS; ++t)
+          if (t < n) {
+            const uint32_t p = col[t * a.S];
+            const int c = k[t];
+            s0 += (int)(p & 0xff) * c;
+            s1 += (int)((p >> 8) & 0xff) * c;
+            s2 += (int)((p >> 16) & 0xff) * c;
+          }
+      } else {
+        for (int t = 0; t < n; ++t) {
+          const uint32_t p = col[t * a.S];
+          const int c = k[t];
+          s0 += (int)(p & 0xff) * c;
+          s1 += (int)((p >> 8) & 0xff) * c;
+          s2 += (int)((p >> 16) & 0xff) * c;
+        }
+      }
+      const uint32_t u0 = clip8(s0), u1 = clip8(s1), u2 = clip8(s2);
+      if (a.out_u8) {
+        a.out_u8[((size_t)patch * a.S + yy) * a.S + xx] = u0 | (u1 << 8) | (u2 << 16);
+        continue;
+      }
+      uint2 v;
+      v.x = (uint32_t)s_lut[u0] | ((uint32_t)s_lut[256 + u1] << 16);
+      v.y = (uint32_t)s_lut[512 + u2];
+      size_t o;
+      if (a.plane_stride_px > 0) {
+        const int y = a.pad_top + yy;
+        o = (size_t)(y & 1) * (size_t)a.plane_stride_px + ((size_t)patch * P + (y >> 1)) * (size_t)a.out_W + (a.pad_left + xx);
+      } else {
+        o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
+      }
+      if (a.channels == 8)
+        reinterpret_cast<uint4*>(a.out)[o] = make_uint4(v.x, v.y, 0u, 0u);
+      else
+        reinterpret_cast<uint2*>(a.out)[o] = v;
     }
-    if (a.out_u8) {
-      a.out_u8[((size_t)patch * a.S + yy) * a.S + xx] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
-      continue;
-    }
-    float f0 = __fdiv_rn((float)clip8(s0), 255.0f);
-    float f1 = __fdiv_rn((float)clip8(s1), 255.0f);
-    float f2 = __fdiv_rn((float)clip8(s2), 255.0f);
-    if (a.has_norm) {
-      f0 = __fdiv_rn(__fsub_rn(f0, a.m0), a.s0);
-      f1 = __fdiv_rn(__fsub_rn(f1, a.m1), a.s1);
-      f2 = __fdiv_rn(__fsub_rn(f2, a.m2), a.s2);
-    }
-    __nv_bfloat162 lo2 = __floats2bfloat162_rn(f0, f1);
-    __nv_bfloat162 hi2 = __floats2bfloat162_rn(f2, 0.0f);
-    uint2 v;
-    v.x = *reinterpret_cast<uint32_t*>(&lo2);
-    v.y = *reinterpret_cast<uint32_t*>(&hi2);
-    size_t o;
-    if (a.plane_stride_px > 0) {
-      const int y = a.pad_top + yy, P = a.out_H >> 1;
-      o = (size_t)(y & 1) * (size_t)a.plane_stride_px + ((size_t)patch * P + (y >> 1)) * (size_t)a.out_W + (a.pad_left + xx);
-    } else {
-      o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
-    }
-    if (a.channels == 8)
-      reinterpret_cast<uint4*>(a.out)[o] = make_uint4(v.x, v.y, 0u, 0u);
-    else
-      reinterpret_cast<uint2*>(a.out)[o] = v;
   }
 }
 
@@ -280,7 +321,7 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
   if (box_h > 256) box_h = 256;
   if (box_h < 1) box_h = 1;
   p->box_h = box_h;
-  p->smem_bytes = (size_t)box_h * box_w * 4 + (size_t)p->max_src_rows * S * 4;
+  p->smem_bytes = (size_t)box_h * box_w * 4 + (size_t)p->max_src_rows * S * 4 + (size_t)S * 4 * (2 + t.ksize) + 768 * 2;
   if (p->smem_bytes > 200 * 1024) {
     delete p;
     wsi_set_error("wsi_preproc_plan_create: shared memory budget exceeded (%zu)", p->smem_bytes);
@@ -288,7 +329,7 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
   }
   size_t nb = (size_t)S * sizeof(int);
   if (cudaMalloc(&p->d_lo, nb) != cudaSuccess || cudaMalloc(&p->d_cnt, nb) != cudaSuccess ||
-      cudaMalloc(&p->d_coef, nb * t.ksize) != cudaSuccess) {
+      cudaMalloc(&p->d_coef, nb * t.ksize) != cudaSuccess || cudaMalloc(&p->d_lut, 768 * sizeof(uint16_t)) != cudaSuccess) {
     delete p;
     wsi_set_error("wsi_preproc_plan_create: cudaMalloc failed");
     return WSI_ERR_NOMEM;
@@ -296,6 +337,21 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
   cudaMemcpy(p->d_lo, t.lo.data(), nb, cudaMemcpyHostToDevice);
   cudaMemcpy(p->d_cnt, t.cnt.data(), nb, cudaMemcpyHostToDevice);
   cudaMemcpy(p->d_coef, t.coef.data(), nb * t.ksize, cudaMemcpyHostToDevice);
+  {
+    // torchvision: ToTensor = u8 / 255 (fp32), Normalize = (x - mean) / std (fp32); then one RNE to bf16
+    uint16_t lut[768];
+    for (int c = 0; c < 3; ++c)
+      for (int v = 0; v < 256; ++v) {
+        volatile float f = (float)v / 255.0f;
+        if (p->has_norm) {
+          volatile float d = f - p->mean[c];
+          f = d / p->stdv[c];
+        }
+        __nv_bfloat16 b = __float2bfloat16_rn(f);
+        lut[c * 256 + v] = *reinterpret_cast<uint16_t*>(&b);
+      }
+    cudaMemcpy(p->d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice);
+  }
   uint64_t dims[2] = {(uint64_t)slide_w, (uint64_t)slide_h};
   uint64_t strides[1] = {(uint64_t)pitch_bytes};
   uint32_t box[2] = {(uint32_t)box_w, (uint32_t)box_h};
@@ -306,10 +362,13 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
     cudaFree(p->d_lo);
     cudaFree(p->d_cnt);
     cudaFree(p->d_coef);
+    cudaFree(p->d_lut);
     delete p;
     return rc;
   }
-  cudaError_t e = cudaFuncSetAttribute(k_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaError_t e = cudaFuncSetAttribute(k_preprocess<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_preprocess<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_preprocess<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   if (e != cudaSuccess) {
     wsi_set_error("wsi_preproc_plan_create: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return WSI_ERR_CUDA;
@@ -344,13 +403,16 @@ static int preproc_launch(void* plan, const int32_t* d_coords_xy, int n, void* d
   a.out_W = p->out_W;
   a.pad_top = p->pad_top;
   a.pad_left = p->pad_left;
-  a.m0 = p->mean[0]; a.m1 = p->mean[1]; a.m2 = p->mean[2];
-  a.s0 = p->stdv[0]; a.s1 = p->stdv[1]; a.s2 = p->stdv[2];
-  a.has_norm = p->has_norm;
+  a.lut = p->d_lut;
   a.plane_stride_px = p->plane_stride_px;
   a.channels = p->channels;
   dim3 grid(n, p->nbands);
-  k_preprocess<<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
+  if (p->ksize == 3)
+    k_preprocess<3><<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
+  else if (p->ksize == 5)
+    k_preprocess<5><<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
+  else
+    k_preprocess<0><<<grid, PP_THREADS, p->smem_bytes, stream>>>(p->tmap, a);
   wsi_count_launch(1);
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
@@ -397,6 +459,7 @@ void wsi_preproc_plan_destroy(void* plan) {
   cudaFree(p->d_lo);
   cudaFree(p->d_cnt);
   cudaFree(p->d_coef);
+  cudaFree(p->d_lut);
   delete p;
 }
 
