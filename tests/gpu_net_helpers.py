@@ -104,3 +104,29 @@ def emulate_ir(nodes, x_nchw, accum=torch.float64):
             logits = logits.float()
             probs = torch.softmax(logits, 1) if logits.shape[1] > 1 else torch.sigmoid(logits.squeeze(1))
     return acts, probs
+
+
+def run_single_pool(x_nchw, is_max, k, stride, pad, count_include_pad=False, out_channels=None, c_off=0):
+    """One pooling op through the raw C ABI; the output may be a channel slice of a wider (concat) tensor."""
+    lib = _cabi.load()
+    B, Cc, H, W = x_nchw.shape
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    Ct = int(out_channels or Cc)
+    net = C.c_void_p()
+    _cabi.call("wsi_net_create", B, C.byref(net))
+    try:
+        tin, tout = C.c_int(), C.c_int()
+        _cabi.call("wsi_net_add_tensor", net, H, W, Cc, 0, C.byref(tin))
+        _cabi.call("wsi_net_add_tensor", net, Ho, Wo, Ct, 0, C.byref(tout))
+        _cabi.call("wsi_net_add_pool", net, tin.value, tout.value, int(c_off), 1 if is_max else 0, k, stride, pad,
+                   1 if count_include_pad else 0)
+        _cabi.call("wsi_net_finalize", net)
+        xd = x_nchw.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+        _cabi.call("wsi_net_write_tensor", net, tin.value, B, xd.data_ptr(), _cabi.stream_ptr())
+        _cabi.call("wsi_net_forward", net, None, B, None, _cabi.stream_ptr())
+        out = torch.empty((B, Ho, Wo, Ct), dtype=torch.bfloat16, device="cuda")
+        _cabi.call("wsi_net_read_tensor", net, tout.value, B, out.data_ptr(), _cabi.stream_ptr())
+        torch.cuda.synchronize()
+        return out.float().permute(0, 3, 1, 2).cpu()
+    finally:
+        lib.wsi_net_destroy(net)

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from gpu_net_helpers import bf16_round, conv_reference, run_single_conv
+from gpu_net_helpers import bf16_round, conv_reference, run_single_conv, run_single_pool
 
 pytestmark = pytest.mark.gpu
 
@@ -106,6 +106,40 @@ def test_conv_asymmetric_kernels():
         got = run_single_conv(x, w, None, 1, (ph, pw))
         want = conv_reference(x, w, None, 1, (ph, pw))
         _check(got, want, f"conv {kh}x{kw}")
+
+
+# (B, C, H, is_max, k, stride, pad, concat width, channel offset): the pooling shapes of ResNet34 / InceptionV4
+# (3x3 windows take the sliding-window kernel, other windows the generic one) + ragged sizes
+POOL_CASES = [
+    (3, 64, 112, True, 3, 2, 1, None, 0),      # ResNet34 maxpool
+    (2, 64, 147, True, 3, 2, 0, 160, 0),       # InceptionV4 mixed_3a (into a concat buffer)
+    (2, 192, 71, True, 3, 2, 0, 384, 192),     # mixed_5a at a channel offset
+    (3, 384, 35, False, 3, 1, 1, None, 0),     # Inception-A average pool, count_include_pad=False
+    (2, 1024, 17, False, 3, 1, 1, None, 0),    # Inception-B
+    (5, 1536, 8, False, 3, 1, 1, None, 0),     # Inception-C
+    (2, 160, 19, True, 3, 1, 1, None, 0),      # 20 channel vectors (not a power of two), stride 1 max
+    (2, 32, 20, False, 2, 2, 0, None, 0),      # generic kernel: 2x2 window
+    (1, 64, 9, True, 5, 1, 2, None, 0),        # generic kernel: 5x5 window
+]
+
+
+@pytest.mark.parametrize("B,C,H,is_max,k,stride,pad,Ct,c_off", POOL_CASES)
+def test_single_pool_vs_torch(B, C, H, is_max, k, stride, pad, Ct, c_off):
+    g = torch.Generator().manual_seed(B + C + H + k)
+    x = bf16_round(torch.randn((B, C, H, H), generator=g))
+    got = run_single_pool(x, is_max, k, stride, pad, count_include_pad=False, out_channels=Ct, c_off=c_off)
+    if is_max:
+        want = torch.nn.functional.max_pool2d(x, k, stride, pad)
+    else:
+        want = torch.nn.functional.avg_pool2d(x.double(), k, stride, pad, count_include_pad=False).float()
+    got_slice = got[:, c_off:c_off + C]
+    if is_max:
+        assert torch.equal(got_slice, want), "max pooling must be exact"
+    else:
+        assert (got_slice - want).abs().max().item() <= 2.0 ** -8 * max(1.0, want.abs().max().item())
+    if Ct is not None:      # the other channels of the concat buffer are untouched (zero-initialised)
+        rest = torch.cat([got[:, :c_off], got[:, c_off + C:]], 1)
+        assert rest.abs().max().item() == 0.0
 
 
 def _resnet_inputs(B, S, seed):

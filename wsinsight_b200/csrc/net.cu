@@ -123,6 +123,88 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Separable sliding-window pooling for the 3x3 windows of the zoo CNNs (stride 1 or 2).  The generic kernel above
+// re-reads every input vector k*k times through L1/L2 (ncu/bench: 1 TB/s of DRAM traffic, i.e. ~9 TB/s of L2->SM
+// traffic on the Inception-A average pools).  Here a thread owns one (channel vector, output column) and walks
+// DOWN the image: each input row is reduced horizontally once (K loads, neighbours shared through L1) into a
+// K-deep register ring, the vertical reduction is register-only, and consecutive output rows reuse K - S rows.
+template <bool IS_MAX, int K, int S>
+__global__ void __launch_bounds__(256)
+    k_pool_sep(const __nv_bfloat16* __restrict__ in, int H, int W, int C, int pad, int count_include_pad, int Ho, int Wo,
+               __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp,
+               int op, int band, int nbands) {
+  const int cv = C >> 3;
+  const int c8 = blockIdx.z * blockDim.x + threadIdx.x;
+  const int wo = blockIdx.y * blockDim.y + threadIdx.y;
+  if (c8 >= cv || wo >= Wo) return;
+  const int n = blockIdx.x / nbands, b = blockIdx.x - n * nbands;
+  const int ho0 = b * band, ho1 = min(ho0 + band, Ho);
+  const int xb = wo * S - pad;
+  const int ncols = min(xb + K, W) - max(xb, 0);
+  const uint4* img = reinterpret_cast<const uint4*>(in + (size_t)n * iHp * iWp * C) + ((size_t)ip * iWp + ip) * cv + c8;
+  uint4* obase = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + op) * oWp + op) * out_C + out_c_off) + c8;
+  const int ocv = out_C >> 3;
+  float h[K][8];
+  auto hrow = [&](int y, float (&r)[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = IS_MAX ? -INFINITY : 0.f;
+    if (y < 0 || y >= H) return;
+    const uint4* row = img + (size_t)y * iWp * cv;
+#pragma unroll
+    for (int dx = 0; dx < K; ++dx) {
+      const int x = xb + dx;
+      if (x >= 0 && x < W) {
+        const uint4 v = __ldg(row + (size_t)x * cv);
+        if (IS_MAX) {
+          r[0] = fmaxf(r[0], bflo(v.x)); r[1] = fmaxf(r[1], bfhi(v.x));
+          r[2] = fmaxf(r[2], bflo(v.y)); r[3] = fmaxf(r[3], bfhi(v.y));
+          r[4] = fmaxf(r[4], bflo(v.z)); r[5] = fmaxf(r[5], bfhi(v.z));
+          r[6] = fmaxf(r[6], bflo(v.w)); r[7] = fmaxf(r[7], bfhi(v.w));
+        } else {
+          r[0] += bflo(v.x); r[1] += bfhi(v.x); r[2] += bflo(v.y); r[3] += bfhi(v.y);
+          r[4] += bflo(v.z); r[5] += bfhi(v.z); r[6] += bflo(v.w); r[7] += bfhi(v.w);
+        }
+      }
+    }
+  };
+  constexpr int KEEP = K > S ? K - S : 0;      // rows shared by consecutive windows
+  {
+    const int yb = ho0 * S - pad;
+#pragma unroll
+    for (int i = 0; i < KEEP; ++i) hrow(yb + i, h[i + S]);
+  }
+  for (int ho = ho0; ho < ho1; ++ho) {
+    const int yb = ho * S - pad;
+#pragma unroll
+    for (int i = 0; i < KEEP; ++i) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) h[i][e] = h[i + S][e];
+    }
+#pragma unroll
+    for (int i = KEEP; i < K; ++i) hrow(yb + i, h[i]);
+    float m[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float v = h[0][e];
+#pragma unroll
+      for (int i = 1; i < K; ++i) v = IS_MAX ? fmaxf(v, h[i][e]) : v + h[i][e];
+      m[e] = v;
+    }
+    if (!IS_MAX) {
+      const int nrows = min(yb + K, H) - max(yb, 0);
+      const float d = count_include_pad ? (float)(K * K) : (float)(nrows * ncols);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) m[e] = m[e] / d;
+    }
+    uint4 o;
+    o.x = convk::pack_bf16(m[0], m[1]);
+    o.y = convk::pack_bf16(m[2], m[3]);
+    o.z = convk::pack_bf16(m[4], m[5]);
+    o.w = convk::pack_bf16(m[6], m[7]);
+    obase[((size_t)ho * oWp + wo) * ocv] = o;
+  }
+}
+
 // K4d: global average pool + FC + softmax (K>1) / sigmoid (K==1); one CTA per image.
 // run_inference.py:548-551 does the softmax on the CPU; here it is fused into the tail.
 constexpr int HEAD_THREADS = 256;
@@ -726,17 +808,38 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];
       const int cv = ti.C / 8;
-      const int bx = cv < 256 ? cv : 256;
-      int by = 256 / bx;
-      if (by > to.W) by = to.W;
-      dim3 block(bx, by);
-      if (op.kind == OP_MAXPOOL)
-        k_pool<true><<<B * to.H, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, 0, to.H, to.W,
-                                                     to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
-      else
-        k_pool<false><<<B * to.H, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
-                                                      op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.Hp(),
-                                                      ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
+      const bool is_max = op.kind == OP_MAXPOOL;
+      if (op.pk == 3 && (op.pstride == 1 || op.pstride == 2)) {
+        int bx = 32;
+        while (cv % bx) bx >>= 1;
+        int by = 256 / bx;
+        if (by > to.W) by = to.W;
+        const int band = to.H > 24 ? 16 : to.H;
+        const int nbands = (to.H + band - 1) / band;
+        dim3 block(bx, by), grid(B * nbands, (to.W + by - 1) / by, cv / bx);
+#define WSI_POOL_SEP(MAX, S)                                                                                              \
+  k_pool_sep<MAX, 3, S><<<grid, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.ppad, op.count_include_pad, to.H, to.W, \
+                                                    to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(),       \
+                                                    to.Wp(), to.pad, band, nbands)
+        if (is_max) {
+          if (op.pstride == 1) WSI_POOL_SEP(true, 1); else WSI_POOL_SEP(true, 2);
+        } else {
+          if (op.pstride == 1) WSI_POOL_SEP(false, 1); else WSI_POOL_SEP(false, 2);
+        }
+#undef WSI_POOL_SEP
+      } else {
+        const int bx = cv < 256 ? cv : 256;
+        int by = 256 / bx;
+        if (by > to.W) by = to.W;
+        dim3 block(bx, by);
+        if (is_max)
+          k_pool<true><<<B * to.H, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad, 0, to.H, to.W,
+                                                       to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
+        else
+          k_pool<false><<<B * to.H, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.pk, op.pstride, op.ppad,
+                                                        op.count_include_pad, to.H, to.W, to.ptr, to.C, op.out_c_off, ti.Hp(),
+                                                        ti.Wp(), ti.pad, to.Hp(), to.Wp(), to.pad);
+      }
     } else if (op.kind == OP_HEAD) {
       WSI_ARG_CHECK(d_probs, "wsi_net_forward: null probs");
       k_head<<<B, HEAD_THREADS, ti.C * sizeof(float), stream>>>(in_ptr, ti.H * ti.W, ti.C, op.d_fcw, op.d_fcb, op.K,
