@@ -145,7 +145,8 @@ int wsi_net_read_tensor(void* net, int id, int batch, void* d_dense_out, void* s
 int wsi_net_write_tensor(void* net, int id, int batch, const void* d_dense_in, void* stream);
 /* 1 if op `op_index` is a conv that runs on the flat-slab kernel */
 int wsi_net_op_is_flat(void* net, int op_index);
-int wsi_net_num_launches(void* net);
+int wsi_net_num_launches(void* net);   /* kernels one forward launches */
+int wsi_net_num_ops(void* net);        /* ops of the layer graph (>= launches: fused ops launch nothing) */
 /* geometry (H, W, C) of the external input tensor the preprocess kernel must write; K of the head */
 int wsi_net_input_geometry(void* net, int* h_hwc3);
 int wsi_net_num_classes(void* net);

@@ -65,6 +65,7 @@ _PROTOS = {
     "wsi_net_write_tensor": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "wsi_net_op_is_flat": (c_int, [c_void_p, c_int]),
     "wsi_net_num_launches": (c_int, [c_void_p]),
+    "wsi_net_num_ops": (c_int, [c_void_p]),
     "wsi_net_input_geometry": (c_int, [c_void_p, c_int_p]),
     "wsi_net_num_classes": (c_int, [c_void_p]),
     "wsi_net_input_layout": (c_int, [c_void_p, c_int_p]),

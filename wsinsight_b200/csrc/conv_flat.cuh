@@ -28,7 +28,10 @@ namespace convf {
 constexpr int THREADS = 320;   // warp 0 producer, warp 1 MMA, warps 2-5 / 6-9: epilogue group of M-tile 0 / 1
 
 struct Args {
-  int Hp, Wp, H, W, B;          // padded / interior geometry (input == output == residual geometry)
+  int Hp, Wp, H, W, B;          // stored geometry shared by input, output and residual; H x W = OUTPUT interior
+  int pad;                      // border of the OUTPUT interior inside the stored geometry (a 'valid' 3x3 conv is the
+                                // same centred flat conv whose output border is one pixel wider than its input's)
+  int ksteps;                   // K = 16 MMA steps per tap and 64-channel chunk: 4, or 2 when only 32 channels are real
   long long total_rows;         // B * Hp * Wp flat positions
   int num_tiles;                // super-tiles of T*128 positions
   int T;                        // M-tiles per super-tile (1 or 2)
@@ -61,23 +64,27 @@ struct MmaCtx {
   uint64_t *aFull, *aEmpty, *bFull, *bEmpty, *tfull, *tempty;
 };
 
-template <int T>
+template <int T, int KS>
 __device__ __forceinline__ void issue_tap(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
                                           uint32_t accum_first, uint32_t N) {
   ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, accum_first);
   ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
-  ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
-  ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+  if (KS == 4) {
+    ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+    ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+  }
   if (T == 2) {
     const uint32_t d1 = d_tmem + N, a1 = a_lo + 1024u;   // second M-tile: +128 rows of 128 B (>> 4)
     ptx::umma_bf16_lohi(d1, a1 + 0, b_lo + 0, hi, idesc, accum_first);
     ptx::umma_bf16_lohi(d1, a1 + 2, b_lo + 2, hi, idesc, 1u);
-    ptx::umma_bf16_lohi(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
-    ptx::umma_bf16_lohi(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
+    if (KS == 4) {
+      ptx::umma_bf16_lohi(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
+      ptx::umma_bf16_lohi(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
+    }
   }
 }
 
-template <int T, bool RESIDENT>
+template <int T, bool RESIDENT, int KS>
 __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
   int sa = 0, sb = 0, acc = 0;
   uint32_t pa = 0, pb = 0, pacc = 0;
@@ -98,7 +105,7 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
           for (int tap = 0; tap < 9; ++tap) {
             const uint32_t a_lo = slab_lo + (uint32_t)(tap / 3) * m.row_step + (uint32_t)(tap % 3) * 8u;
             const uint32_t b_lo = m.sB_lo + (uint32_t)(tap * m.chunks + c) * m.b_step;
-            issue_tap<T>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
+            issue_tap<T, KS>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
           }
           ptx::umma_commit(&m.aEmpty[sa]);
           if (last_c) ptx::umma_commit(&m.tfull[acc]);
@@ -112,7 +119,7 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
           if (ptx::elect_one()) {
             const uint32_t a_lo = slab_lo + (uint32_t)(tap / 3) * m.row_step + (uint32_t)(tap % 3) * 8u;
             const uint32_t b_lo = m.sB_lo + (uint32_t)sb * m.b_step;
-            issue_tap<T>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
+            issue_tap<T, KS>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
             ptx::umma_commit(&m.bEmpty[sb]);
             if (tap == 8) {
               ptx::umma_commit(&m.aEmpty[sa]);
@@ -241,10 +248,16 @@ __global__ void __launch_bounds__(THREADS, 1)
     m.hi = ptx::sw128_desc_hi();
     m.N = a.N; m.chunks = a.chunks; m.stagesA = a.stagesA; m.stagesB = a.stagesB; m.num_tiles = a.num_tiles;
     m.aFull = aFull; m.aEmpty = aEmpty; m.bFull = bFull; m.bEmpty = bEmpty; m.tfull = tfull; m.tempty = tempty;
-    if (a.T == 2) {
-      if (a.resident_b) mma_loop<2, true>(m); else mma_loop<2, false>(m);
+    if (a.ksteps == 2) {
+      if (a.T == 2) {
+        if (a.resident_b) mma_loop<2, true, 2>(m); else mma_loop<2, false, 2>(m);
+      } else {
+        if (a.resident_b) mma_loop<1, true, 2>(m); else mma_loop<1, false, 2>(m);
+      }
+    } else if (a.T == 2) {
+      if (a.resident_b) mma_loop<2, true, 4>(m); else mma_loop<2, false, 4>(m);
     } else {
-      if (a.resident_b) mma_loop<1, true>(m); else mma_loop<1, false>(m);
+      if (a.resident_b) mma_loop<1, true, 4>(m); else mma_loop<1, false, 4>(m);
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
@@ -269,7 +282,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           const int n = (int)(p / img);
           const int rem = (int)(p - (long long)n * img);
           const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
-          const bool valid = (n < a.B) && (hp >= 1) && (hp <= a.H) && (wp >= 1) && (wp <= a.W);
+          const bool valid = (n < a.B) && (hp >= a.pad) && (hp < a.pad + a.H) && (wp >= a.pad) && (wp < a.pad + a.W);
           const bool do_res = a.has_res && p < a.total_rows;
           const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N);
           uint4 rv[8], rn[8];
@@ -323,7 +336,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         const int n = (int)(p / img);
         const int rem = (int)(p - (long long)n * img);
         const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
-        const bool valid = (n < a.B) && (hp >= 1) && (hp <= a.H) && (wp >= 1) && (wp <= a.W);
+        const bool valid = (n < a.B) && (hp >= a.pad) && (hp < a.pad + a.H) && (wp >= a.pad) && (wp < a.pad + a.W);
         const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + t) * a.N);
         for (int c0 = 0; c0 < a.N; c0 += 32) {
           uint32_t r[32];

@@ -41,6 +41,10 @@ struct Args {
   int slab_pairs;                // pairs per parity slab (multiple of 8)
   int stages;
   int relu;
+  // fused 3x3 / stride 2 / pad 1 max pooling (POOL instantiation): tiles are output-row PAIRS of one image
+  int B, row_pairs, pool_w;      // images, Ho/2 tiles per image, pooled columns
+  __nv_bfloat16* pool_out;       // pooled tensor [B][pool_Hp][pool_Wp][pool_C], interior at (pool_pad, pool_pad)
+  int pool_Hp, pool_Wp, pool_pad, pool_C, pool_c_off;
   const uint8_t* in;             // parity-plane input (bf16 pairs)
   const uint8_t* w;              // weights in canonical no-swizzle blocks [14][8][2][8][8] bf16
   const float* bias;
@@ -66,13 +70,21 @@ __device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint3
       : "memory");
 }
 
+// POOL = false: one super-tile = T*128 consecutive flat outputs, each written to the conv output tensor.
+// POOL = true : ReLU + the 3x3/2 max pooling that follows the stem in every ResNet are fused into the epilogue
+// (the unfused pair wrote and re-read 1.7 GB per 1024 patches: 0.48 + 0.66 ms of an 7.8 ms step).  A CTA walks
+// whole images; tile r of an image is output rows 2r, 2r+1 (2P <= 256 flat positions).  Both epilogue groups
+// stage bias+ReLU'd bf16 rows in one of three 32 KB shared buffers, meet at a named barrier, and then 256 threads
+// reduce pooled row r from rows 2r-1 (second row of the previous tile's buffer), 2r, 2r+1 and store it
+// straight into the (padded) pooled tensor.  Post-ReLU values are >= 0, so a missing neighbour is a 0.
+template <bool POOL>
 __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant__ CUtensorMap tmapO, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
   const int slab_bytes = a.slab_pairs * 16;           // one parity
-  uint8_t* sOut = smem;                               // 4 x 16 KB: [group][buffer], 1024-aligned
-  uint8_t* sW = sOut + 4 * 16384;
+  uint8_t* sOut = smem;                               // 4 x 16 KB: [group][buffer], 1024-aligned (POOL: 3 x 32 KB)
+  uint8_t* sW = sOut + (POOL ? 6 : 4) * 16384;
   uint8_t* sA = sW + W_BYTES;                          // stages x 2 parities x slab_bytes
   float* sBias = reinterpret_cast<float*>(sA + (size_t)a.stages * 2 * slab_bytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 64);
@@ -85,7 +97,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tmapO);
+    if (!POOL) ptx::prefetch_tmap(&tmapO);
     for (int s = 0; s < a.stages; ++s) {
       ptx::mbar_init(&full[s], 1);
       ptx::mbar_init(&empty[s], 1);
@@ -115,10 +127,18 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
     __syncwarp();
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+    const int my_tiles = POOL ? ((a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x) * a.row_pairs
+                              : (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    for (int it = 0; it < my_tiles; ++it) {
       ptx::mbar_wait(&empty[stage], phase ^ 1);
       if (ptx::elect_one()) {
-        const long long q0 = (long long)tile * (T * 128);
+        long long q0;
+        if (POOL) {
+          const int n = (int)blockIdx.x + (it / a.row_pairs) * (int)gridDim.x, r = it % a.row_pairs;
+          q0 = ((long long)n * a.P + 2 * r) * a.P;
+        } else {
+          q0 = (long long)((int)blockIdx.x + it * (int)gridDim.x) * (T * 128);
+        }
         ptx::mbar_arrive_expect_tx(&full[stage], (uint32_t)(2 * slab_bytes));
         uint8_t* dst = sA + (size_t)stage * 2 * slab_bytes;
         bulk_g2s(dst, a.in + q0 * 16, (uint32_t)slab_bytes, &full[stage]);
@@ -142,7 +162,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
     ptx::mbar_wait(wfull, 0);
     int stage = 0, acc = 0;
     uint32_t phase = 0, pacc = 0;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+    const int my_tiles = POOL ? ((a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x) * a.row_pairs
+                              : (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    for (int it = 0; it < my_tiles; ++it) {
       ptx::mbar_wait(&tempty[acc], pacc ^ 1);
       ptx::mbar_wait(&full[stage], phase);
       ptx::tc_fence_after();
@@ -174,6 +196,55 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
     const bool leader = gt == 0;
     if (g == 0 && gt < N) sBias[gt] = a.bias[gt];
     ptx::named_bar_sync(3, 256);                      // bias staged (both groups)
+    if (POOL) {
+      const int et = (int)threadIdx.x - 64;             // 0..255 over both groups
+      const int my_imgs = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+      const int items = a.pool_w * 8;                   // (pooled column, 16-byte channel octet)
+      const uint32_t sbuf0 = ptx::smem_u32(sOut);
+      const uint32_t P = (uint32_t)a.P;
+      auto ldpos = [&](uint32_t buf, uint32_t pos, uint32_t oct) {
+        return ptx::ld_shared_v4(buf + pos * 128u + ((oct ^ (pos & 7u)) << 4));
+      };
+      auto vmax = [](uint4& m, const uint4& x) {
+        __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
+        const __nv_bfloat162* xx = reinterpret_cast<const __nv_bfloat162*>(&x);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) mm[i] = __hmax2(mm[i], xx[i]);
+      };
+      int acc = 0, bsel = 0;
+      uint32_t pacc = 0;
+      for (int im = 0; im < my_imgs; ++im) {
+        const int n = (int)blockIdx.x + im * (int)gridDim.x;
+        __nv_bfloat16* oimg = a.pool_out + (((size_t)n * a.pool_Hp + a.pool_pad) * a.pool_Wp + a.pool_pad) * a.pool_C + a.pool_c_off;
+        for (int r = 0; r < a.row_pairs; ++r) {
+          const uint32_t cur = sbuf0 + (uint32_t)bsel * 32768u;
+          const uint32_t prev = sbuf0 + (uint32_t)(bsel == 0 ? 2 : bsel - 1) * 32768u;
+          ptx::mbar_wait(&tfull[acc], pacc);
+          ptx::tc_fence_after();
+          const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * T + g) * N);
+          convk::epi_chunk64(t_addr, row, true, cur + (uint32_t)g * 16384u, 0u, sBias, 1);
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+          ptx::named_bar_sync(1, 256);                  // rows 2r, 2r+1 staged by both groups
+          for (int i = et; i < items; i += 256) {
+            const uint32_t pc = (uint32_t)i >> 3, oct = (uint32_t)i & 7u;
+            uint4 m = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) {
+              if (dx == 0 && pc == 0) continue;
+              const uint32_t col = 2u * pc + (uint32_t)dx - 1u;
+              if (r > 0) vmax(m, ldpos(prev, P + col, oct));
+              vmax(m, ldpos(cur, col, oct));
+              vmax(m, ldpos(cur, P + col, oct));
+            }
+            *reinterpret_cast<uint4*>(oimg + ((size_t)r * a.pool_Wp + pc) * a.pool_C + oct * 8) = m;
+          }
+          if (++bsel == 3) bsel = 0;
+          if (++acc == 2) { acc = 0; pacc ^= 1; }
+        }
+      }
+    } else {
     uint8_t* myOut = sOut + (size_t)g * 2 * 16384;
     int acc = 0, k = 0;
     uint32_t pacc = 0;
@@ -197,6 +268,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
       if (++acc == 2) { acc = 0; pacc ^= 1; }
     }
     if (leader) ptx::bulk_wait<0>();
+    }
   }
 
   ptx::tc_fence_before();
@@ -208,8 +280,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
   }
 }
 
-static inline size_t smem_bytes(int slab_pairs, int stages) {
-  return 1024 + 4 * 16384 + W_BYTES + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
+static inline size_t smem_bytes(int slab_pairs, int stages, bool pool = false) {
+  return 1024 + (pool ? 6 : 4) * 16384 + W_BYTES + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
 }
 
 }  // namespace convs

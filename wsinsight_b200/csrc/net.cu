@@ -19,6 +19,7 @@ struct Tensor {
   bool external = false;
   int pad = 0;                    // one-pixel zero border (tensors touched by the flat 3x3 conv kernel)
   int xh = 0, xw = 0;             // extra junk rows / columns after the image (output of the flat stem kernel)
+  bool elided = false;            // never materialised: the stem output when the max pooling is fused into the stem
   int Hp() const { return H + 2 * pad + xh; }
   int Wp() const { return W + 2 * pad + xw; }
   size_t interior_offset() const { return ((size_t)pad * Wp() + pad) * C; }   // elements to pixel (0,0)
@@ -34,6 +35,9 @@ struct Op {
   convf::Args fa;
   convs::Args sa;
   bool flat = false;              // 3x3/s1/p1 over padded tensors -> convf::k_conv_flat
+  int fused_pool = -1;            // stem: index of the 3x3/2 max-pool op fused into its epilogue
+  bool skip = false;              // pool op executed by the stem kernel
+  int cin_real = 0;               // input channels that carry a non-zero weight (<= Cin)
   int max_pairs = 0;              // co-resident 2-CTA clusters of the per-tap kernel (queried at first launch)
   CUtensorMap tmA, tmB, tmO, tmR;
   __nv_bfloat16* d_w = nullptr;
@@ -60,6 +64,7 @@ struct Net {
   int num_sms = 148;
   bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
   bool cluster_enabled = true;    // WSI_B200_NO_CLUSTER=1: no CTA pairs / weight multicast in the per-tap kernel
+  bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
   int prof_slots = 0;
@@ -128,6 +133,47 @@ __global__ void __launch_bounds__(256)
 // traffic on the Inception-A average pools).  Here a thread owns one (channel vector, output column) and walks
 // DOWN the image: each input row is reduced horizontally once (K loads, neighbours shared through L1) into a
 // K-deep register ring, the vertical reduction is register-only, and consecutive output rows reuse K - S rows.
+__device__ __forceinline__ uint32_t hmax2_bf16(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// Row accumulator of the sliding-window pool: packed bf16x2 for max (exact, 4 registers per row), fp32 for sums.
+template <bool IS_MAX>
+struct PoolRow;
+template <>
+struct PoolRow<true> {
+  uint4 v;
+  __device__ __forceinline__ void clear() { v = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u); }   // -inf
+  __device__ __forceinline__ void add(const uint4& x) {
+    v.x = hmax2_bf16(v.x, x.x); v.y = hmax2_bf16(v.y, x.y); v.z = hmax2_bf16(v.z, x.z); v.w = hmax2_bf16(v.w, x.w);
+  }
+  __device__ __forceinline__ void merge(const PoolRow& o) { add(o.v); }
+  __device__ __forceinline__ uint4 result(float) const { return v; }
+};
+template <>
+struct PoolRow<false> {
+  float f[8];
+  __device__ __forceinline__ void clear() {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = 0.f;
+  }
+  __device__ __forceinline__ void add(const uint4& x) {
+    f[0] += bflo(x.x); f[1] += bfhi(x.x); f[2] += bflo(x.y); f[3] += bfhi(x.y);
+    f[4] += bflo(x.z); f[5] += bfhi(x.z); f[6] += bflo(x.w); f[7] += bfhi(x.w);
+  }
+  __device__ __forceinline__ void merge(const PoolRow& o) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] += o.f[i];
+  }
+  // one reciprocal per output instead of eight IEEE divisions (ncu: the divisions made the kernel issue-bound,
+  // 76 % issue-slot utilisation at 1.6 TB/s); <= 1 ulp of fp32 before the bf16 rounding
+  __device__ __forceinline__ uint4 result(float rcp) const {
+    return make_uint4(convk::pack_bf16(f[0] * rcp, f[1] * rcp), convk::pack_bf16(f[2] * rcp, f[3] * rcp),
+                      convk::pack_bf16(f[4] * rcp, f[5] * rcp), convk::pack_bf16(f[6] * rcp, f[7] * rcp));
+  }
+};
+
 template <bool IS_MAX, int K, int S>
 __global__ void __launch_bounds__(256)
     k_pool_sep(const __nv_bfloat16* __restrict__ in, int H, int W, int C, int pad, int count_include_pad, int Ho, int Wo,
@@ -144,27 +190,15 @@ __global__ void __launch_bounds__(256)
   const uint4* img = reinterpret_cast<const uint4*>(in + (size_t)n * iHp * iWp * C) + ((size_t)ip * iWp + ip) * cv + c8;
   uint4* obase = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + op) * oWp + op) * out_C + out_c_off) + c8;
   const int ocv = out_C >> 3;
-  float h[K][8];
-  auto hrow = [&](int y, float (&r)[8]) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) r[i] = IS_MAX ? -INFINITY : 0.f;
+  PoolRow<IS_MAX> h[K];
+  auto hrow = [&](int y, PoolRow<IS_MAX>& r) {
+    r.clear();
     if (y < 0 || y >= H) return;
     const uint4* row = img + (size_t)y * iWp * cv;
 #pragma unroll
     for (int dx = 0; dx < K; ++dx) {
       const int x = xb + dx;
-      if (x >= 0 && x < W) {
-        const uint4 v = __ldg(row + (size_t)x * cv);
-        if (IS_MAX) {
-          r[0] = fmaxf(r[0], bflo(v.x)); r[1] = fmaxf(r[1], bfhi(v.x));
-          r[2] = fmaxf(r[2], bflo(v.y)); r[3] = fmaxf(r[3], bfhi(v.y));
-          r[4] = fmaxf(r[4], bflo(v.z)); r[5] = fmaxf(r[5], bfhi(v.z));
-          r[6] = fmaxf(r[6], bflo(v.w)); r[7] = fmaxf(r[7], bfhi(v.w));
-        } else {
-          r[0] += bflo(v.x); r[1] += bfhi(v.x); r[2] += bflo(v.y); r[3] += bfhi(v.y);
-          r[4] += bflo(v.z); r[5] += bfhi(v.z); r[6] += bflo(v.w); r[7] += bfhi(v.w);
-        }
-      }
+      if (x >= 0 && x < W) r.add(__ldg(row + (size_t)x * cv));
     }
   };
   constexpr int KEEP = K > S ? K - S : 0;      // rows shared by consecutive windows
@@ -173,35 +207,22 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int i = 0; i < KEEP; ++i) hrow(yb + i, h[i + S]);
   }
+#pragma unroll 2
   for (int ho = ho0; ho < ho1; ++ho) {
     const int yb = ho * S - pad;
 #pragma unroll
-    for (int i = 0; i < KEEP; ++i) {
-#pragma unroll
-      for (int e = 0; e < 8; ++e) h[i][e] = h[i + S][e];
-    }
+    for (int i = 0; i < KEEP; ++i) h[i] = h[i + S];
 #pragma unroll
     for (int i = KEEP; i < K; ++i) hrow(yb + i, h[i]);
-    float m[8];
+    PoolRow<IS_MAX> m = h[0];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      float v = h[0][e];
-#pragma unroll
-      for (int i = 1; i < K; ++i) v = IS_MAX ? fmaxf(v, h[i][e]) : v + h[i][e];
-      m[e] = v;
-    }
+    for (int i = 1; i < K; ++i) m.merge(h[i]);
+    float rcp = 1.f;
     if (!IS_MAX) {
       const int nrows = min(yb + K, H) - max(yb, 0);
-      const float d = count_include_pad ? (float)(K * K) : (float)(nrows * ncols);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) m[e] = m[e] / d;
+      rcp = 1.0f / (count_include_pad ? (float)(K * K) : (float)(nrows * ncols));
     }
-    uint4 o;
-    o.x = convk::pack_bf16(m[0], m[1]);
-    o.y = convk::pack_bf16(m[2], m[3]);
-    o.z = convk::pack_bf16(m[4], m[5]);
-    o.w = convk::pack_bf16(m[6], m[7]);
-    obase[((size_t)ho * oWp + wo) * ocv] = o;
+    obase[((size_t)ho * oWp + wo) * ocv] = m.result(rcp);
   }
 }
 
@@ -308,6 +329,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->flat_enabled = !(nf && nf[0] == '1');
   const char* nc = getenv("WSI_B200_NO_CLUSTER");
   n->cluster_enabled = !(nc && nc[0] == '1');
+  const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
+  n->stem_pool_enabled = !(nsp && nsp[0] == '1');
   *net_out = n;
   return WSI_OK;
 }
@@ -485,18 +508,40 @@ int wsi_net_finalize(void* net) {
       to.xh = P - to.H;
       to.xw = P - to.W;
     }
+  // stem + ReLU + 3x3/2/pad-1 max pooling (every ResNet): fuse when the stem output has no other reader
+  if (n->stem_pool_enabled)
+    for (size_t i = 0; i < n->ops.size(); ++i) {
+      Op& op = n->ops[i];
+      if (op.kind != OP_CONV || op.is_stem != 2 || !op.relu) continue;
+      int readers = 0, pool_idx = -1;
+      for (size_t j = 0; j < n->ops.size(); ++j) {
+        const Op& o2 = n->ops[j];
+        if (o2.in == op.out || (o2.kind == OP_CONV && o2.res == op.out)) {
+          ++readers;
+          if (o2.kind == OP_MAXPOOL && o2.pk == 3 && o2.pstride == 2 && o2.ppad == 1 && j > i) pool_idx = (int)j;
+        }
+      }
+      const Tensor& ts = n->tensors[op.out];
+      const int P = n->tensors[op.in].H / 2;
+      if (readers == 1 && pool_idx >= 0 && ts.H % 2 == 0 && ts.W % 2 == 0 && 2 * P <= convs::T * 128 &&
+          n->tensors[n->ops[pool_idx].out].C % 8 == 0) {
+        op.fused_pool = pool_idx;
+        n->ops[pool_idx].skip = true;
+        n->tensors[op.out].elided = true;
+      }
+    }
   for (auto& op : n->ops)
     if (op.kind == OP_HEAD && n->tensors[op.in].pad) {
       wsi_set_error("wsi_net_finalize: the head cannot read a padded tensor");
       return WSI_ERR_UNSUPPORTED;
     }
   for (auto& t : n->tensors) {
-    if (t.external) continue;
+    if (t.external || t.elided) continue;
     size_t bytes = (size_t)B * t.Hp() * t.Wp() * t.C * sizeof(__nv_bfloat16);
     WSI_CUDA_CHECK(cudaMalloc(&t.ptr, bytes));
     WSI_CUDA_CHECK(cudaMemset(t.ptr, 0, bytes));
   }
-  int max_smem = 0, max_smem_flat = 0, max_smem_stem = 0;
+  int max_smem = 0, max_smem_flat = 0, max_smem_stem = 0, max_smem_stem_pool = 0;
   for (auto& op : n->ops) {
     if (op.kind == OP_CONV) {
       const Tensor& ti = n->tensors[op.in];
@@ -518,6 +563,19 @@ int wsi_net_finalize(void* net) {
         sa.relu = op.relu;
         sa.w = (const uint8_t*)op.d_w;
         sa.bias = op.d_bias;
+        if (op.fused_pool >= 0) {
+          const Tensor& tp = n->tensors[n->ops[op.fused_pool].out];
+          sa.stages = 3;
+          sa.row_pairs = to.H / 2;
+          sa.pool_w = to.W / 2;
+          sa.pool_out = tp.ptr;
+          sa.pool_Hp = tp.Hp(); sa.pool_Wp = tp.Wp(); sa.pool_pad = tp.pad; sa.pool_C = tp.C;
+          sa.pool_c_off = n->ops[op.fused_pool].out_c_off;
+          int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages, true);
+          WSI_ARG_CHECK(smem <= 227 * 1024, "wsi_net_finalize: fused stem does not fit shared memory (P = %d)", P);
+          if (smem > max_smem_stem_pool) max_smem_stem_pool = smem;
+          continue;
+        }
         int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages);
         WSI_ARG_CHECK(smem <= 227 * 1024, "wsi_net_finalize: stem slab does not fit shared memory (P = %d)", P);
         if (smem > max_smem_stem) max_smem_stem = smem;
@@ -535,6 +593,8 @@ int wsi_net_finalize(void* net) {
         memset(&f, 0, sizeof(f));
         f.Hp = ti.Hp(); f.Wp = ti.Wp(); f.H = ti.H; f.W = ti.W;
         f.N = op.Cout;
+        f.pad = to.pad;
+        f.ksteps = 4;
         f.chunks = op.Cin / 64;
         f.T = 2;
         if (const char* e = getenv("WSI_FLAT_T")) f.T = atoi(e) == 1 ? 1 : 2;      // tuning knobs (bench only)
@@ -683,10 +743,13 @@ int wsi_net_finalize(void* net) {
   if (max_smem > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   if (max_smem_stem > 0)
-    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
+  if (max_smem_stem_pool > 0)
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem_pool));
   if (max_smem_flat > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
-  n->launches_per_forward = (int)n->ops.size();
+  n->launches_per_forward = 0;
+  for (auto& op : n->ops) n->launches_per_forward += op.skip ? 0 : 1;
   n->finalized = true;
   return WSI_OK;
 }
@@ -733,6 +796,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
   for (size_t i = 0; i < n->ops.size(); ++i) {
     Op& op = n->ops[i];
     if (pev) cudaEventRecord(pev[i], stream);
+    if (op.skip) continue;                         // pooling executed inside the stem kernel
     const Tensor& ti = n->tensors[op.in];
     const __nv_bfloat16* in_ptr = ti.external ? (const __nv_bfloat16*)d_input : ti.ptr;
     WSI_ARG_CHECK(in_ptr, "wsi_net_forward: missing input pointer");
@@ -747,8 +811,14 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         sa.in = (const uint8_t*)in_ptr;
         sa.total_q = (long long)B * sa.P * sa.P;
         sa.num_tiles = (int)((sa.total_q + convs::T * 128 - 1) / (convs::T * 128));
+        if (op.fused_pool >= 0) {
+          sa.B = B;
+          int grid = B < n->num_sms ? B : n->num_sms;
+          convs::k_conv_stem<true><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages, true), stream>>>(op.tmB, sa);
+          continue;
+        }
         int grid = sa.num_tiles < n->num_sms ? sa.num_tiles : n->num_sms;
-        convs::k_conv_stem<<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages), stream>>>(op.tmO, sa);
+        convs::k_conv_stem<false><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages), stream>>>(op.tmO, sa);
         continue;
       }
       if (op.flat) {
@@ -850,7 +920,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
     cudaEventRecord(pev[n->ops.size()], stream);
     n->prof_forwards++;
   }
-  wsi_count_launch((int)n->ops.size());
+  wsi_count_launch(n->launches_per_forward);
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
 }
@@ -979,6 +1049,11 @@ int wsi_net_num_classes(void* net) {
     for (auto& op : n->ops)
       if (op.kind == OP_HEAD) return op.K;
   return 0;
+}
+
+int wsi_net_num_ops(void* net) {
+  Net* n = (Net*)net;
+  return n ? (int)n->ops.size() : 0;
 }
 
 int wsi_net_num_launches(void* net) {

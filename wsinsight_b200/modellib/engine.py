@@ -80,6 +80,7 @@ class B200Network:
             self.input_layout.update(kind="nhwc4", plane_stride_px=0)
         self.input_layout["buffer_elems"] = self.input_bytes // 2
         self.num_launches = int(lib.wsi_net_num_launches(self._h))
+        self.num_ops = int(lib.wsi_net_num_ops(self._h))
         self.flops_per_image = float(lib.wsi_net_flops_per_image(self._h))
 
     # -- construction ---------------------------------------------------------
@@ -269,7 +270,7 @@ class B200Network:
         _cabi.call("wsi_net_profile_read", self._h, ms, fl, kd, nmax, C.byref(nf))
         kinds = {0: "conv", 1: "maxpool", 2: "avgpool", 3: "head"}
         ops = [dict(kind=kinds[int(kd[i])], ms_total=float(ms[i]), flops_per_image=float(fl[i]))
-               for i in range(self.num_launches)]
+               for i in range(self.num_ops)]
         return ops, int(nf.value)
 
     def close(self):
