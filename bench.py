@@ -455,9 +455,17 @@ def b200_arm(args, rank, world, local_rank):
     n_conv = sum(1 for o in ops if o["kind"] == "conv")
     other_ms = sum(o["ms_total"] for o in ops if o["kind"] != "conv")
     achieved = conv_fl * B * nfwd / (conv_ms * 1e-3) / 1e12
+    # DRAM bytes per conv launch from the committed `ncu --set full` capture of this same command
+    # (profiles/r01_ncu_conv_traffic.json, made by tools/ncu_traffic.py from the .ncu-rep); None if absent
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_conv_traffic.json")))
+        traffic = tj.get(args.model, {}).get("dram_bytes_per_launch_avg")
+    except Exception:
+        traffic = None
     roofline = {"kernel": f"tcgen05 conv kernels: convs::k_conv_stem + convf::k_conv_flat + convk::k_conv_igemm ({n_conv} launches per step)", "bound": "tensor", "achieved": achieved,
                 "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                "traffic": None, "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
+                "traffic": traffic, "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
                 "flops_per_launch_avg": conv_fl * B / n_conv, "avg_launch_ms": conv_ms / (n_conv * nfwd),
                 "share_of_step": conv_ms / ms}
     pp_bytes = ps * ps * 4 + spec.S * spec.S * 3 * 2     # read ps^2 RGBA + write S^2 x 3 bf16

@@ -129,6 +129,11 @@ int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const floa
                      int pad_w, int relu, int residual_id);
 int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* h_w_oihw,
                         const float* h_bias, int Cout, int relu);
+/* Generalisation: ksize 7 / pad 3 (ResNet) or ksize 3 / pad 0 (InceptionV4 conv2d_1a; input tensor [S'][S'][4] with
+ * S' = S rounded up to even), stride 2.  Replaces the first cuDNN convolution of the TorchScript graph
+ * (modellib/run_inference.py:543). */
+int wsi_net_add_stem_parity(void* net, int in_id, int out_id, const float* w_oihw, const float* bias, int Cout,
+                            int ksize, int pad, int relu);
 int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max, int k, int stride,
                      int pad, int count_include_pad);
 int wsi_net_add_head(void* net, int in_id, const float* h_fc_w, const float* h_fc_b, int K);

@@ -34,6 +34,9 @@ CASES = [
     (3, 64, 56, 64, 3, 1, 1),      # batch not a multiple of the box
     (5, 32, 17, 96, 3, 1, 1),      # Cin < 64, odd spatial size
     (130, 96, 7, 32, 1, 1, 0),     # batch tail beyond one 128-image box
+    (6, 192, 17, 224, 3, 1, 1),    # N tile 224 = 3 x 64 + 32-column tail chunk (Inception-B widths)
+    (4, 64, 20, 160, 1, 1, 0),     # N tile 160 = 2 x 64 + 32
+    (3, 64, 73, 96, 3, 2, 0),      # InceptionV4 mixed_3a conv: stride 2, N = 96
 ]
 
 
@@ -72,6 +75,30 @@ def test_flat_conv_vs_torch(B, Cin, H, Cout, relu_res):
     _check(got, want, f"flat conv {B}x{Cin}x{H} -> {Cout}")
 
 
+# flat kernel beyond ResNet: 'valid' 3x3 (output border one wider than the input's), Cin that is not a multiple of
+# 64 (last chunk zero-filled by TMA), 32 real channels (two K steps per tap), wide rows (one M-tile per slab)
+FLAT_GENERAL_CASES = [
+    (3, 64, 73, 96, 0),     # InceptionV4 mixed_4a 3x3 valid, N = 96
+    (4, 96, 35, 96, 1),     # Inception-A 96 -> 96
+    (2, 32, 61, 32, 0),     # 32 -> 32 valid
+    (2, 32, 59, 64, 1),     # 32 -> 64 same
+    (1, 32, 149, 32, 0),    # InceptionV4 conv2d_2a geometry: 149-pixel rows
+    (2, 32, 147, 64, 1),    # conv2d_2b geometry
+    (3, 160, 30, 64, 0),    # 2.5 chunks, valid
+]
+
+
+@pytest.mark.parametrize("B,Cin,H,Cout,pad", FLAT_GENERAL_CASES)
+def test_flat_conv_general_vs_torch(B, Cin, H, Cout, pad):
+    g = torch.Generator().manual_seed(B * 31 + Cin + H + Cout + pad)
+    x = bf16_round(torch.randn((B, Cin, H, H), generator=g))
+    w = bf16_round(torch.randn((Cout, Cin, 3, 3), generator=g) / (Cin * 9) ** 0.5)
+    b = torch.randn(Cout, generator=g) * 0.1
+    got = run_single_conv(x, w, b, 1, pad, relu=True, expect_flat=True)
+    want = conv_reference(x, w, b, 1, pad, relu=True)
+    _check(got, want, f"flat conv {B}x{Cin}x{H} -> {Cout} pad {pad}")
+
+
 def test_flat_conv_matches_per_tap_kernel(monkeypatch):
     """Same conv through both kernels: the flat-slab path and the per-tap TMA path agree bit for bit
     up to fp32 accumulation order (identical operands, identical rounding point)."""
@@ -96,6 +123,13 @@ def test_conv_residual_relu_epilogue():
     want = conv_reference(x, w, b, 1, 1, relu=True, residual=r)
     _check(got, want, "conv+residual+relu")
     assert got.min().item() >= 0
+    # residual through the 32-column tail chunk (per-tap kernel, N = 96; stride 2 keeps it off the flat kernel)
+    x = bf16_round(torch.randn((5, 64, 30, 30), generator=g))
+    w = bf16_round(torch.randn((96, 64, 3, 3), generator=g) / 24.0)
+    b = torch.randn(96, generator=g) * 0.1
+    r = bf16_round(torch.randn((5, 96, 15, 15), generator=g))
+    got = run_single_conv(x, w, b, 2, 1, relu=True, residual=r, expect_flat=False)
+    _check(got, conv_reference(x, w, b, 2, 1, relu=True, residual=r), "conv s2 N=96 + residual + relu")
 
 
 def test_conv_asymmetric_kernels():

@@ -1,0 +1,59 @@
+"""Summarise an `ncu --set full` capture of the conv kernels into profiles/r01_ncu_conv_traffic.json.
+
+usage: python tools/ncu_traffic.py <model> <report.ncu-rep> [<csv out>]
+Reads dram__bytes_read.sum + dram__bytes_write.sum and gpu__time_duration.sum per launch (ncu --page raw --csv)
+and stores the per-launch average that bench.py reports as roofline.traffic.
+"""
+import csv
+import io
+import json
+import os
+import subprocess
+import sys
+
+UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0,
+        "usecond": 1e-6, "msecond": 1e-3, "nsecond": 1e-9, "second": 1.0}
+
+
+def main():
+    model, rep = sys.argv[1], sys.argv[2]
+    metrics = ("gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,"
+               "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active,"
+               "l1tex__m_xbar2l1tex_read_bytes.sum,sm__throughput.avg.pct_of_peak_sustained_elapsed")
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--metrics", metrics], capture_output=True,
+                         text=True, check=True).stdout
+    if len(sys.argv) > 3:
+        open(sys.argv[3], "w").write(out)
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    col = {h: i for i, h in enumerate(hdr)}
+
+    def val(r, name):
+        return float(r[col[name]]) * UNIT[units[col[name]]]
+
+    per = {}
+    tot_b = tot_t = 0.0
+    for r in data:
+        k = r[col["Kernel Name"]].split("(")[0].replace("void ", "")
+        b = val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum")
+        t = val(r, "gpu__time_duration.sum")
+        d = per.setdefault(k, {"launches": 0, "dram_bytes": 0.0, "time_s": 0.0})
+        d["launches"] += 1
+        d["dram_bytes"] += b
+        d["time_s"] += t
+        tot_b += b
+        tot_t += t
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "profiles", "r01_ncu_conv_traffic.json")
+    try:
+        j = json.load(open(path))
+    except Exception:
+        j = {}
+    j[model] = {"dram_bytes_per_launch_avg": tot_b / len(data), "launches": len(data),
+                "ncu_time_per_launch_avg_us": tot_t / len(data) * 1e6, "per_kernel": per,
+                "source": os.path.basename(rep), "note": "ncu --set full --clock-control none, one forward at batch 1024"}
+    json.dump(j, open(path, "w"), indent=1)
+    print(json.dumps(j[model])[:600])
+
+
+if __name__ == "__main__":
+    main()

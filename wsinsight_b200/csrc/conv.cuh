@@ -130,12 +130,45 @@ __device__ __forceinline__ void epi_chunk64_regs(uint32_t t_addr, int row, uint3
   }
 }
 
+// 32-column tail chunk (N_tile = 64a + 32: Cout 32, 96, 160, 224, 448 of the Inception family): the same
+// epilogue staged as [128 rows][32 ch] = 64-byte rows in the SWIZZLE_64B layout of a {32 ch} TMA store box
+// (16-byte chunk c of row r at r*64 + ((c ^ ((r >> 1) & 3)) << 4); conflict-free for a quarter warp).
+__device__ __forceinline__ void epi_chunk32_regs(uint32_t t_addr, int row, uint32_t s_out, bool has_res,
+                                                 const uint4 (&rv)[8], const float* s_bias, int relu,
+                                                 bool keep = true) {
+  uint32_t r[32];
+  ptx::tmem_ld_32x32b_x32(t_addr, r);
+  ptx::tmem_ld_wait();
+  const uint32_t row_base = (uint32_t)row * 64u;
+  const uint32_t sw = ((uint32_t)row >> 1) & 3u;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
+    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
+    float v0 = __uint_as_float(r[8 * c + 0]) + b0.x, v1 = __uint_as_float(r[8 * c + 1]) + b0.y;
+    float v2 = __uint_as_float(r[8 * c + 2]) + b0.z, v3 = __uint_as_float(r[8 * c + 3]) + b0.w;
+    float v4 = __uint_as_float(r[8 * c + 4]) + b1.x, v5 = __uint_as_float(r[8 * c + 5]) + b1.y;
+    float v6 = __uint_as_float(r[8 * c + 6]) + b1.z, v7 = __uint_as_float(r[8 * c + 7]) + b1.w;
+    if (has_res) {
+      v0 += bf16_lo(rv[c].x); v1 += bf16_hi(rv[c].x); v2 += bf16_lo(rv[c].y); v3 += bf16_hi(rv[c].y);
+      v4 += bf16_lo(rv[c].z); v5 += bf16_hi(rv[c].z); v6 += bf16_lo(rv[c].w); v7 += bf16_hi(rv[c].w);
+    }
+    if (relu) {
+      v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
+      v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
+    }
+    uint32_t o0 = pack_bf16(v0, v1), o1 = pack_bf16(v2, v3), o2 = pack_bf16(v4, v5), o3 = pack_bf16(v6, v7);
+    if (!keep) o0 = o1 = o2 = o3 = 0u;
+    ptx::st_shared_v4(s_out + row_base + (((uint32_t)c ^ sw) << 4), o0, o1, o2, o3);
+  }
+}
+
 // CL = 1: one CTA per tile.  CL = 2: CTA pairs (cta_group::2); a separate instantiation because a kernel that
 // contains cta_group::2 instructions can only be launched as 2-CTA clusters.
 template <int CL>
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_igemm(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                 const __grid_constant__ CUtensorMap tmapO, const Args a) {
+                 const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x A 16KB][stages x B N_tile*128][barriers]
   if (ptx::smem_u32(smem_raw) & 1023u) __trap();
@@ -179,7 +212,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], (uint32_t)(((a.tma_epi && a.N_tile > 64) ? 8 : 4) * CL));
+      ptx::mbar_init(&tempty[s], (uint32_t)(((a.tma_epi && a.N_tile > 64) ? 8 : 4) * CL));   // > 64: two chunks or more
     }
     ptx::fence_barrier_init();
   }
@@ -318,7 +351,8 @@ __global__ void __launch_bounds__(THREADS, 1)
     const bool leader = gt == 0;
     for (int i = (int)threadIdx.x - 64; i < a.Cout; i += 256) sBias[i] = a.bias[i];
     ptx::named_bar_sync(3, 256);
-    const int cn = a.N_tile >> 6;
+    const int cn_full = a.N_tile >> 6;                 // 64-column chunks
+    const int cn = cn_full + ((a.N_tile & 32) ? 1 : 0);  // + one 32-column tail chunk
     const int jstep = cn > 1 ? 2 : 1;
     const uint32_t myOut = ptx::smem_u32(sOut + (size_t)g * 16384);
     const int w_l = row % a.bw;
@@ -342,21 +376,29 @@ __global__ void __launch_bounds__(THREADS, 1)
         int j = cn > 1 ? g : 0;
         uint4 rv[8], rn[8];
         if (do_res) {
+          const int nv = j < cn_full ? 8 : 4;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) rv[i] = __ldg(rbase + 8 * j + i);
+          for (int i = 0; i < 8; ++i)
+            if (i < nv) rv[i] = __ldg(rbase + 8 * j + i);
         }
         ptx::mbar_wait(&tfull[acc], acc_phase);
         ptx::tc_fence_after();
         for (; j < cn; j += jstep) {
           const bool last = j + jstep >= cn;
+          const bool full = j < cn_full;
           if (do_res && !last) {
+            const int nv = (j + jstep) < cn_full ? 8 : 4;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) rn[i] = __ldg(rbase + 8 * (j + jstep) + i);
+            for (int i = 0; i < 8; ++i)
+              if (i < nv) rn[i] = __ldg(rbase + 8 * (j + jstep) + i);
           }
           if (leader) ptx::bulk_wait_read<0>();
           ptx::named_bar_sync(1 + g, 128);              // the group's staging buffer is free again
           const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + 64 * j);
-          epi_chunk64_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, a.relu);
+          if (full)
+            epi_chunk64_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, a.relu);
+          else
+            epi_chunk32_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, a.relu);
           if (last) {
             ptx::tc_fence_before();
             __syncwarp();
@@ -367,8 +409,8 @@ __global__ void __launch_bounds__(THREADS, 1)
           ptx::fence_proxy_async();
           ptx::named_bar_sync(1 + g, 128);              // chunk staged
           if (leader) {
-            ptx::tma_store_4d(&tmapO, sOut + (size_t)g * 16384, a.out_c_off + nt * a.N_tile + 64 * j, tw * a.bw,
-                              th * a.bh, tn * a.bn);
+            ptx::tma_store_4d(full ? &tmapO : &tmapO32, sOut + (size_t)g * 16384, a.out_c_off + nt * a.N_tile + 64 * j,
+                              tw * a.bw, th * a.bh, tn * a.bn);
             ptx::bulk_commit();
           }
           if (!last) {

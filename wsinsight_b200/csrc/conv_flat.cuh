@@ -139,7 +139,7 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
 
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapR, const Args a) {
+                const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -147,8 +147,8 @@ __global__ void __launch_bounds__(THREADS, 1)
   const int b_bytes = a.N * 128;
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)a.stagesA * slab_bytes;
-  uint8_t* sOut = sB + (size_t)a.stagesB * b_bytes;                 // 2 groups x nOut x 16 KB (1024-aligned)
-  float* sBias = reinterpret_cast<float*>(sOut + (size_t)2 * a.nOut * 16384);
+  uint8_t* sOut = sB + (size_t)a.stagesB * b_bytes;                 // T groups x nOut x 16 KB (1024-aligned)
+  float* sBias = reinterpret_cast<float*>(sOut + (size_t)a.T * a.nOut * 16384);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 128);
   uint64_t* aFull = bars;
   uint64_t* aEmpty = aFull + a.stagesA;
@@ -270,7 +270,8 @@ __global__ void __launch_bounds__(THREADS, 1)
       const int g = (warp - 2) >> 2;                    // epilogue group == M-tile of the super-tile
       const int gt = ((warp - 2) & 3) * 32 + lane;      // 0..127 inside the group
       const bool leader = gt == 0;
-      const int cn = a.N >> 6;                          // 64-column chunks per accumulator tile
+      const int cn_full = a.N >> 6;                     // 64-column chunks per accumulator tile
+      const int cn = cn_full + ((a.N & 32) ? 1 : 0);    // + one 32-column tail chunk (N = 32, 96)
       for (int i = (int)threadIdx.x - 64; i < a.N; i += 256) sBias[i] = a.bias[i];
       ptx::named_bar_sync(3, 256);                      // bias staged (both groups)
       if (g < a.T) {
@@ -287,16 +288,21 @@ __global__ void __launch_bounds__(THREADS, 1)
           const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N);
           uint4 rv[8], rn[8];
           if (do_res) {
+            const int nv = cn_full > 0 ? 8 : 4;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) rv[i] = __ldg(rbase + i);
+            for (int i = 0; i < 8; ++i)
+              if (i < nv) rv[i] = __ldg(rbase + i);
           }
           ptx::mbar_wait(&tfull[acc], pacc);
           ptx::tc_fence_after();
           for (int j = 0; j < cn; ++j, ++k) {
             const bool last = j == cn - 1;
+            const bool full = j < cn_full;
             if (do_res && !last) {
+              const int nv = (j + 1) < cn_full ? 8 : 4;
 #pragma unroll
-              for (int i = 0; i < 8; ++i) rn[i] = __ldg(rbase + 8 * (j + 1) + i);
+              for (int i = 0; i < 8; ++i)
+                if (i < nv) rn[i] = __ldg(rbase + 8 * (j + 1) + i);
             }
             const int ob = a.nOut == 2 ? (k & 1) : 0;
             if (leader) {
@@ -304,8 +310,12 @@ __global__ void __launch_bounds__(THREADS, 1)
             }
             ptx::named_bar_sync(1 + g, 128);            // the group's staging buffer ob is free again
             const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + g) * a.N + 64 * j);
-            convk::epi_chunk64_regs(t_addr, row, ptx::smem_u32(myOut + (size_t)ob * 16384), do_res, rv, sBias + 64 * j,
-                                    a.relu, valid);
+            if (full)
+              convk::epi_chunk64_regs(t_addr, row, ptx::smem_u32(myOut + (size_t)ob * 16384), do_res, rv, sBias + 64 * j,
+                                      a.relu, valid);
+            else
+              convk::epi_chunk32_regs(t_addr, row, ptx::smem_u32(myOut + (size_t)ob * 16384), do_res, rv, sBias + 64 * j,
+                                      a.relu, valid);
             if (last) {                                 // this group's accumulator tile fully read: hand it back
               ptx::tc_fence_before();
               __syncwarp();
@@ -314,7 +324,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             ptx::fence_proxy_async();
             ptx::named_bar_sync(1 + g, 128);            // chunk staged
             if (leader) {
-              ptx::tma_store_2d(&tmapO, myOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)q0);
+              ptx::tma_store_2d(full ? &tmapO : &tmapO32, myOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)q0);
               ptx::bulk_commit();
             }
             if (!last) {
@@ -399,7 +409,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
 static inline size_t smem_bytes(const Args& a) {
   return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * a.N * 128 +
-         (size_t)(2 * a.nOut) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
+         (size_t)(a.T * a.nOut) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
 }
 
 }  // namespace convf

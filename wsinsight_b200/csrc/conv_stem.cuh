@@ -29,12 +29,14 @@ namespace convs {
 
 constexpr int THREADS = 320;
 constexpr int T = 2;             // M-tiles per super-tile
-constexpr int KSTEPS = 14;       // 7 tap rows x 2 (pairs {0,1}, {2,3}); K = 16 per step
-constexpr int N = 64;            // Cout
-constexpr int W_BYTES = KSTEPS * N * 16 * 2;   // 28 KB
+// Instantiations: KH = 7, JJ = 2 (7x7/2 pad 3: 7 tap rows x 2 pair-pairs = 14 K steps of 16) and KH = 3, JJ = 1
+// (3x3/2 pad 0, InceptionV4 conv2d_1a: the 3 taps of a row are pixels 2wo..2wo+2 = pairs wo, wo+1 -> one K step
+// per tap row).  Cout (UMMA N) is 64 or 32 at run time.
+constexpr int N_MAX = 64;
 
 struct Args {
   int P;                         // pairs per padded row == padded rows per parity plane
+  int N;                         // Cout: 64 | 32
   long long total_q;             // B * P * P flat outputs
   long long plane_pairs;         // maxB * P * P: distance between the two parity planes (pairs)
   int num_tiles;
@@ -77,17 +79,20 @@ __device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint3
 // stage bias+ReLU'd bf16 rows in one of three 32 KB shared buffers, meet at a named barrier, and then 256 threads
 // reduce pooled row r from rows 2r-1 (second row of the previous tile's buffer), 2r, 2r+1 and store it
 // straight into the (padded) pooled tensor.  Post-ReLU values are >= 0, so a missing neighbour is a 0.
-template <bool POOL>
+template <bool POOL, int KH, int JJ>
 __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant__ CUtensorMap tmapO, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+  constexpr int KSTEPS = KH * JJ;
+  const int N = a.N;
+  const int W_BYTES = KSTEPS * N * 32;
   const int slab_bytes = a.slab_pairs * 16;           // one parity
   uint8_t* sOut = smem;                               // 4 x 16 KB: [group][buffer], 1024-aligned (POOL: 3 x 32 KB)
   uint8_t* sW = sOut + (POOL ? 6 : 4) * 16384;
   uint8_t* sA = sW + W_BYTES;                          // stages x 2 parities x slab_bytes
   float* sBias = reinterpret_cast<float*>(sA + (size_t)a.stages * 2 * slab_bytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 64);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + N_MAX);
   uint64_t* full = bars;
   uint64_t* empty = full + a.stages;
   uint64_t* tfull = empty + a.stages;
@@ -173,7 +178,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
         const uint32_t s_lo = sA_lo + (uint32_t)stage * stage_step;
 #pragma unroll
         for (int ks = 0; ks < KSTEPS; ++ks) {
-          const int kh = ks >> 1, jj = ks & 1;
+          const int kh = ks / JJ, jj = ks % JJ;
           // pair offset inside the parity slab: a*P rows down, 2*jj pairs right (units of 16 B == descriptor units)
           const uint32_t a_lo = s_lo + (uint32_t)(kh & 1) * par_step + (uint32_t)(kh >> 1) * P + (uint32_t)(2 * jj);
           const uint32_t b_lo = w_lo + (uint32_t)ks * (uint32_t)(N * 32 >> 4);
@@ -255,7 +260,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
       ptx::mbar_wait(&tfull[acc], pacc);
       ptx::tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * T + g) * N);
-      convk::epi_chunk64(t_addr, row, true, ptx::smem_u32(myOut + (size_t)ob * 16384), 0u, sBias, a.relu);
+      if (N == 64) {
+        convk::epi_chunk64(t_addr, row, true, ptx::smem_u32(myOut + (size_t)ob * 16384), 0u, sBias, a.relu);
+      } else {
+        const uint4 none[8] = {};
+        convk::epi_chunk32_regs(t_addr, row, ptx::smem_u32(myOut + (size_t)ob * 16384), false, none, sBias, a.relu);
+      }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
@@ -280,8 +290,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
   }
 }
 
-static inline size_t smem_bytes(int slab_pairs, int stages, bool pool = false) {
-  return 1024 + (pool ? 6 : 4) * 16384 + W_BYTES + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
+static inline size_t smem_bytes(int slab_pairs, int stages, bool pool = false, int w_bytes = 14 * 64 * 32) {
+  return 1024 + (pool ? 6 : 4) * 16384 + w_bytes + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
 }
 
 }  // namespace convs

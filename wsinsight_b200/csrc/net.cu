@@ -19,6 +19,7 @@ struct Tensor {
   bool external = false;
   int pad = 0;                    // one-pixel zero border (tensors touched by the flat 3x3 conv kernel)
   int xh = 0, xw = 0;             // extra junk rows / columns after the image (output of the flat stem kernel)
+  bool lock_geom = false;         // border / junk geometry fixed by the producing kernel (parity stem output)
   bool elided = false;            // never materialised: the stem output when the max pooling is fused into the stem
   int Hp() const { return H + 2 * pad + xh; }
   int Wp() const { return W + 2 * pad + xw; }
@@ -39,7 +40,7 @@ struct Op {
   bool skip = false;              // pool op executed by the stem kernel
   int cin_real = 0;               // input channels that carry a non-zero weight (<= Cin)
   int max_pairs = 0;              // co-resident 2-CTA clusters of the per-tap kernel (queried at first launch)
-  CUtensorMap tmA, tmB, tmO, tmR;
+  CUtensorMap tmA, tmB, tmO, tmR, tmO32;
   __nv_bfloat16* d_w = nullptr;
   float* d_bias = nullptr;
   std::vector<__nv_bfloat16> h_w;
@@ -64,6 +65,7 @@ struct Net {
   int num_sms = 148;
   bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
   bool cluster_enabled = true;    // WSI_B200_NO_CLUSTER=1: no CTA pairs / weight multicast in the per-tap kernel
+  bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
@@ -329,6 +331,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->flat_enabled = !(nf && nf[0] == '1');
   const char* nc = getenv("WSI_B200_NO_CLUSTER");
   n->cluster_enabled = !(nc && nc[0] == '1');
+  const char* le = getenv("WSI_B200_LEGACY_EPI");
+  n->legacy_epi = le && le[0] == '1';
   const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
   n->stem_pool_enabled = !(nsp && nsp[0] == '1');
   *net_out = n;
@@ -386,6 +390,14 @@ int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const floa
           size_t k = ((size_t)(y * KW + x) * chunks + c / 64) * 64 + (c % 64);
           op.h_w[(size_t)o * op.Ktot + k] = __float2bfloat16(v);
         }
+  op.cin_real = 0;
+  for (int c = Cin - 1; c >= 0 && !op.cin_real; --c)
+    for (int o = 0; o < Cout && !op.cin_real; ++o)
+      for (int t = 0; t < KH * KW; ++t)
+        if (w_oihw[((size_t)o * Cin + c) * KH * KW + t] != 0.f) {
+          op.cin_real = c + 1;
+          break;
+        }
   op.h_bias.assign(Cout, 0.f);
   if (bias) memcpy(op.h_bias.data(), bias, sizeof(float) * Cout);
   op.flops_per_image = 2.0 * Ho * Wo * (double)Cout * Cin * KH * KW;
@@ -393,41 +405,47 @@ int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const floa
   return WSI_OK;
 }
 
-// ResNet stem: 7x7 stride 2 pad 3 conv on the 3-channel image.  The input tensor is the
-// preprocess kernel's padded NHWC4 layout [B][S+6][Wp][4] (3-pixel zero border, Wp even).
-int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* w_oihw, const float* bias, int Cout,
-                        int relu) {
+// First convolution on the 3-channel image through the parity-plane stem kernel (conv_stem.cuh):
+//   ksize 7, pad 3 (every ResNet): input tensor = the preprocess kernel's padded layout [B][S+6][S+6][4];
+//   ksize 3, pad 0 (InceptionV4 conv2d_1a): input tensor [B][Se][Se][4], Se = S rounded up to even.
+// Stride is 2.  Cout == 64 (or 32 for ksize 3) takes the parity kernel; a 7x7 stem of another width falls back to
+// the per-tap kernel's overlapping-window map.
+int wsi_net_add_stem_parity(void* net, int in_id, int out_id, const float* w_oihw, const float* bias, int Cout,
+                            int ksize, int pad, int relu) {
   Net* n = (Net*)net;
-  WSI_ARG_CHECK(n && !n->finalized && w_oihw, "wsi_net_add_stem7x7: bad state");
+  WSI_ARG_CHECK(n && !n->finalized && w_oihw, "wsi_net_add_stem_parity: bad state");
   WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size() && out_id >= 0 && out_id < (int)n->tensors.size(),
-                "wsi_net_add_stem7x7: bad tensor id");
+                "wsi_net_add_stem_parity: bad tensor id");
+  WSI_ARG_CHECK((ksize == 7 && pad == 3) || (ksize == 3 && pad == 0), "wsi_net_add_stem_parity: 7x7/pad 3 or 3x3/pad 0");
   const Tensor& ti = n->tensors[in_id];
   const Tensor& to = n->tensors[out_id];
-  WSI_ARG_CHECK(ti.C == 4 && (ti.W % 2) == 0, "wsi_net_add_stem7x7: input must be padded NHWC4 with even width");
-  const int S = ti.H - 6;
-  WSI_ARG_CHECK(S > 0 && S % 2 == 0 && ti.W == S + 6, "wsi_net_add_stem7x7: padded geometry must be (S+6)x(S+6)");
-  WSI_ARG_CHECK(to.H == S / 2 && to.W == S / 2 && to.C == Cout, "wsi_net_add_stem7x7: bad output tensor");
-  WSI_ARG_CHECK(pick_ntile(Cout) > 0, "wsi_net_add_stem7x7: Cout must be a multiple of 32");
+  WSI_ARG_CHECK(ti.C == 4 && (ti.W % 2) == 0 && (ti.H % 2) == 0 && ti.H == ti.W,
+                "wsi_net_add_stem_parity: input must be square NHWC4 with an even side");
+  const int Ho = (ti.H - ksize) / 2 + 1;
+  WSI_ARG_CHECK(to.H == Ho && to.W == Ho && to.C == Cout, "wsi_net_add_stem_parity: bad output tensor");
+  WSI_ARG_CHECK(pick_ntile(Cout) > 0, "wsi_net_add_stem_parity: Cout must be a multiple of 32");
+  const bool parity = n->flat_enabled && (Cout == 64 || (ksize == 3 && Cout == 32));
+  WSI_ARG_CHECK(parity || ksize == 7, "wsi_net_add_stem_parity: no kernel for a 3x3 stem with %d filters", Cout);
   Op op;
   op.kind = OP_CONV;
   op.in = in_id; op.out = out_id; op.res = -1;
-  op.Cin = 3; op.Cout = Cout; op.KH = 7; op.KW = 7; op.stride = 2; op.pad_h = 3; op.pad_w = 3;
+  op.Cin = 3; op.Cout = Cout; op.KH = ksize; op.KW = ksize; op.stride = 2; op.pad_h = pad; op.pad_w = pad;
   op.relu = relu; op.out_c_off = 0;
-  // Cout == 64 (every ResNet): the parity-plane stem kernel (conv_stem.cuh); otherwise the per-tap kernel
-  op.is_stem = (Cout == convs::N && n->flat_enabled) ? 2 : 1;
-  op.Ktot = 7 * 32;
+  op.is_stem = parity ? 2 : 1;
+  const int JJ = ksize == 7 ? 2 : 1;
+  op.Ktot = parity ? ksize * JJ * 16 : 7 * 32;
   op.h_w.assign((size_t)Cout * op.Ktot, __float2bfloat16(0.f));
   for (int o = 0; o < Cout; ++o)
     for (int c = 0; c < 3; ++c)
-      for (int y = 0; y < 7; ++y)
-        for (int x = 0; x < 7; ++x) {
-          float v = w_oihw[(((size_t)o * 3 + c) * 7 + y) * 7 + x];
+      for (int y = 0; y < ksize; ++y)
+        for (int x = 0; x < ksize; ++x) {
+          float v = w_oihw[(((size_t)o * 3 + c) * ksize + y) * ksize + x];
           size_t off;
           if (op.is_stem == 2) {
-            // canonical no-swizzle blocks [ks = 2*kh + jj][n/8][k/8][n%8][k%8], k = 16 per block:
+            // canonical no-swizzle blocks [ks = JJ*kh + jj][n/8][k/8][n%8][k%8], k = 16 per block:
             // pixel pair j = x/2 = 2*jj + k/8, element (x%2)*4 + c inside the pair
-            const int j = x >> 1, ks = y * 2 + (j >> 1), k16 = (j & 1) * 8 + (x & 1) * 4 + c;
-            off = (size_t)ks * 1024 + (size_t)(o / 8) * 128 + (size_t)(k16 / 8) * 64 + (size_t)(o % 8) * 8 + (k16 % 8);
+            const int j = x >> 1, ks = y * JJ + (j >> 1), k16 = (j & 1) * 8 + (x & 1) * 4 + c;
+            off = (size_t)ks * Cout * 16 + (size_t)(o / 8) * 128 + (size_t)(k16 / 8) * 64 + (size_t)(o % 8) * 8 + (k16 % 8);
           } else {
             // K layout: chunk kh x [px 0..7][ch 0..3]; px==7 and ch==3 carry zero weights
             off = (size_t)o * op.Ktot + (size_t)y * 32 + x * 4 + c;
@@ -436,9 +454,14 @@ int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* w_oihw, c
         }
   op.h_bias.assign(Cout, 0.f);
   if (bias) memcpy(op.h_bias.data(), bias, sizeof(float) * Cout);
-  op.flops_per_image = 2.0 * to.H * to.W * (double)Cout * 3 * 49;
+  op.flops_per_image = 2.0 * to.H * to.W * (double)Cout * 3 * ksize * ksize;
   n->ops.push_back(std::move(op));
   return WSI_OK;
+}
+
+int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* w_oihw, const float* bias, int Cout,
+                        int relu) {
+  return wsi_net_add_stem_parity(net, in_id, out_id, w_oihw, bias, Cout, 7, 3, relu);
 }
 
 int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max, int k, int stride, int pad,
@@ -484,22 +507,6 @@ int wsi_net_finalize(void* net) {
   Net* n = (Net*)net;
   WSI_ARG_CHECK(n && !n->finalized, "wsi_net_finalize: bad state");
   const int B = n->max_batch;
-  // which convs run on the flat-slab kernel, and which tensors therefore carry a zero border
-  for (auto& op : n->ops) {
-    op.flat = false;
-    if (op.kind != OP_CONV || op.is_stem || !n->flat_enabled) continue;
-    const Tensor& ti = n->tensors[op.in];
-    bool ok = op.KH == 3 && op.KW == 3 && op.stride == 1 && op.pad_h == 1 && op.pad_w == 1 && op.Cin % 64 == 0 &&
-              ti.C == op.Cin && op.Cout % 32 == 0 && op.Cout <= 128 && !ti.external && ti.W >= 24 && ti.H >= 8;
-    if (op.res >= 0 && (n->tensors[op.res].C != op.Cout || n->tensors[op.res].external)) ok = false;
-    op.flat = ok;
-  }
-  for (auto& op : n->ops)
-    if (op.flat) {
-      n->tensors[op.in].pad = 1;
-      n->tensors[op.out].pad = 1;
-      if (op.res >= 0) n->tensors[op.res].pad = 1;
-    }
   for (auto& op : n->ops)
     if (op.kind == OP_CONV && op.is_stem == 2) {
       // the parity-plane stem writes every column / row of its P x P flat grid: P - S/2 junk ones
@@ -507,12 +514,89 @@ int wsi_net_finalize(void* net) {
       const int P = n->tensors[op.in].H / 2;
       to.xh = P - to.H;
       to.xw = P - to.W;
+      to.lock_geom = true;
     }
+  // Which convs run on the flat-slab kernel, and the stored geometry that follows from it.  The kernel computes a
+  // CENTRED 3x3 window at every position of a stored [Hp][Wp] grid shared by input, output and residual:
+  //   pad 1 ('same'):  the input needs a zero border >= 1 and the output keeps the input's border;
+  //   pad 0 ('valid'): no border needed and the (two pixels smaller) output sits one pixel further in,
+  //                    i.e. its border is the input's + 1 -- which is exactly the zero padding a following
+  //                    'same' conv wants.
+  // Borders only grow, so the constraints are propagated to a fixed point; an op whose tensors cannot agree
+  // (a geometry-locked producer, two producers of one concat buffer that disagree) falls back to the per-tap kernel.
+  for (auto& op : n->ops) {
+    op.flat = false;
+    if (op.kind != OP_CONV || op.is_stem || !n->flat_enabled) continue;
+    const Tensor& ti = n->tensors[op.in];
+    bool ok = op.KH == 3 && op.KW == 3 && op.stride == 1 && op.pad_h == op.pad_w && (op.pad_h == 0 || op.pad_h == 1) &&
+              op.Cin % 8 == 0 && ti.C == op.Cin && op.Cout % 32 == 0 && op.Cout <= 128 && !ti.external && ti.W >= 24 &&
+              ti.H >= 8;
+    if (op.pad_h == 0 && getenv("WSI_B200_NO_FLAT_VALID")) ok = false;
+    if (op.res >= 0 && (n->tensors[op.res].C != op.Cout || n->tensors[op.res].external)) ok = false;
+    op.flat = ok;
+  }
+  for (int round = 0; round < 64; ++round) {
+    for (auto& t : n->tensors)
+      if (!t.lock_geom) t.pad = 0;
+    bool conflict = false;
+    for (int iter = 0; iter < 64 && !conflict; ++iter) {
+      bool changed = false;
+      for (auto& op : n->ops) {
+        if (!op.flat) continue;
+        Tensor& ti = n->tensors[op.in];
+        Tensor& to = n->tensors[op.out];
+        const int p = op.pad_h;
+        auto raise = [&](Tensor& t, int want) {
+          if (t.pad >= want) return true;
+          if (t.lock_geom) return false;
+          t.pad = want;
+          changed = true;
+          return true;
+        };
+        bool ok = raise(ti, p) && raise(to, ti.pad + 1 - p) && raise(ti, to.pad - 1 + p);
+        if (ok && op.res >= 0) {
+          Tensor& tr = n->tensors[op.res];
+          ok = raise(tr, to.pad) && raise(to, tr.pad) && raise(ti, to.pad - 1 + p);
+        }
+        if (!ok) {
+          op.flat = false;
+          conflict = true;
+          break;
+        }
+      }
+      if (!changed) break;
+    }
+    if (conflict) continue;
+    // junk rows / columns after the image so that every flat op's tensors share one stored grid
+    for (auto& t : n->tensors)
+      if (!t.lock_geom) t.xh = t.xw = 0;
+    for (auto& op : n->ops) {
+      if (!op.flat) continue;
+      const Tensor& ti = n->tensors[op.in];
+      Tensor& to = n->tensors[op.out];
+      const int xh = ti.Hp() - to.H - 2 * to.pad, xw = ti.Wp() - to.W - 2 * to.pad;
+      bool ok = xh >= 0 && xw >= 0;
+      if (ok && (to.Hp() != ti.Hp() || to.Wp() != ti.Wp())) {
+        if (to.lock_geom || to.xh != 0 || to.xw != 0) ok = false;   // already fixed by another producer
+        else { to.xh = xh; to.xw = xw; }
+      }
+      if (ok && op.res >= 0) {
+        const Tensor& tr = n->tensors[op.res];
+        ok = tr.Hp() == to.Hp() && tr.Wp() == to.Wp();
+      }
+      if (!ok) {
+        op.flat = false;
+        conflict = true;
+        break;
+      }
+    }
+    if (!conflict) break;
+  }
   // stem + ReLU + 3x3/2/pad-1 max pooling (every ResNet): fuse when the stem output has no other reader
   if (n->stem_pool_enabled)
     for (size_t i = 0; i < n->ops.size(); ++i) {
       Op& op = n->ops[i];
-      if (op.kind != OP_CONV || op.is_stem != 2 || !op.relu) continue;
+      if (op.kind != OP_CONV || op.is_stem != 2 || !op.relu || op.KH != 7 || op.Cout != 64) continue;
       int readers = 0, pool_idx = -1;
       for (size_t j = 0; j < n->ops.size(); ++j) {
         const Op& o2 = n->ops[j];
@@ -531,7 +615,7 @@ int wsi_net_finalize(void* net) {
       }
     }
   for (auto& op : n->ops)
-    if (op.kind == OP_HEAD && n->tensors[op.in].pad) {
+    if (op.kind == OP_HEAD && (n->tensors[op.in].pad || n->tensors[op.in].xh || n->tensors[op.in].xw)) {
       wsi_set_error("wsi_net_finalize: the head cannot read a padded tensor");
       return WSI_ERR_UNSUPPORTED;
     }
@@ -556,9 +640,12 @@ int wsi_net_finalize(void* net) {
         const int P = ti.H / 2;
         convs::Args& sa = op.sa;
         memset(&sa, 0, sizeof(sa));
+        const int JJ = op.KH == 7 ? 2 : 1;
+        const int w_bytes = op.KH * JJ * op.Cout * 32;
         sa.P = P;
+        sa.N = op.Cout;
         sa.plane_pairs = (long long)B * P * P;
-        sa.slab_pairs = (convs::T * 128 + 3 * P + 4 + 7) / 8 * 8;
+        sa.slab_pairs = (convs::T * 128 + ((op.KH - 1) / 2) * P + 2 * JJ + 7) / 8 * 8;
         sa.stages = 4;
         sa.relu = op.relu;
         sa.w = (const uint8_t*)op.d_w;
@@ -571,59 +658,61 @@ int wsi_net_finalize(void* net) {
           sa.pool_out = tp.ptr;
           sa.pool_Hp = tp.Hp(); sa.pool_Wp = tp.Wp(); sa.pool_pad = tp.pad; sa.pool_C = tp.C;
           sa.pool_c_off = n->ops[op.fused_pool].out_c_off;
-          int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages, true);
+          int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages, true, w_bytes);
           WSI_ARG_CHECK(smem <= 227 * 1024, "wsi_net_finalize: fused stem does not fit shared memory (P = %d)", P);
           if (smem > max_smem_stem_pool) max_smem_stem_pool = smem;
           continue;
         }
-        int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages);
+        int smem = (int)convs::smem_bytes(sa.slab_pairs, sa.stages, false, w_bytes);
         WSI_ARG_CHECK(smem <= 227 * 1024, "wsi_net_finalize: stem slab does not fit shared memory (P = %d)", P);
         if (smem > max_smem_stem) max_smem_stem = smem;
         uint64_t dims[2] = {(uint64_t)to.C, (uint64_t)B * to.Hp() * to.Wp()};
         uint64_t strides[1] = {(uint64_t)to.C * 2};
-        uint32_t box[2] = {64, 128};
+        uint32_t box[2] = {(uint32_t)op.Cout, 128};
         uint32_t es[2] = {1, 1};
         int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
-                               CU_TENSOR_MAP_SWIZZLE_128B);
+                               op.Cout == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
         if (rc) return rc;
         continue;
       }
       if (op.flat) {
         convf::Args& f = op.fa;
         memset(&f, 0, sizeof(f));
-        f.Hp = ti.Hp(); f.Wp = ti.Wp(); f.H = ti.H; f.W = ti.W;
+        f.Hp = ti.Hp(); f.Wp = ti.Wp(); f.H = to.H; f.W = to.W;
         f.N = op.Cout;
         f.pad = to.pad;
-        f.ksteps = 4;
-        f.chunks = op.Cin / 64;
-        f.T = 2;
-        if (const char* e = getenv("WSI_FLAT_T")) f.T = atoi(e) == 1 ? 1 : 2;      // tuning knobs (bench only)
-        int force_nout = 0, force_res = -1;
+        f.chunks = (op.Cin + 63) / 64;
+        f.ksteps = (f.chunks == 1 && op.cin_real <= 32) ? 2 : 4;
+        int force_T = 0, force_nout = 0, force_res = -1;                              // tuning knobs (bench only)
+        if (const char* e = getenv("WSI_FLAT_T")) force_T = atoi(e) == 1 ? 1 : 2;
         if (const char* e = getenv("WSI_FLAT_NOUT")) force_nout = atoi(e);
         if (const char* e = getenv("WSI_FLAT_RESIDENT")) force_res = atoi(e);
-        f.resident_b = (size_t)9 * f.chunks * f.N * 128 <= 80 * 1024;
-        f.stagesB = f.resident_b ? 9 * f.chunks : 4;
-        const int rows_needed = f.T * 128 + 2 * f.Wp + 2;
-        f.slab_loads = (rows_needed + 255) / 256;
-        f.slab_box_rows = ((rows_needed + f.slab_loads - 1) / f.slab_loads + 7) / 8 * 8;
-        f.slab_rows = f.slab_loads * f.slab_box_rows;
-        f.tma_epi = (op.Cout % 64 == 0) ? 1 : 0;
-        // shared-memory plan: prefer resident weights and double-buffered epilogue staging; give up
-        // the second output staging buffer, then weight residency, before dropping below 2 slabs
-        const int want_res = 0;   // the residual is prefetched into registers (no smem ring)
-        const int plans[4][2] = {{1, 2}, {1, 1}, {0, 2}, {0, 1}};   // {resident weights, nOut}
+        const bool can_reside = (size_t)9 * f.chunks * f.N * 128 <= 80 * 1024;
+        f.tma_epi = (op.Cout % 64 == 0 || (op.Cout % 32 == 0 && !n->legacy_epi)) ? 1 : 0;
+        // shared-memory plan {T, resident weights, staging buffers per group}: prefer two M-tiles per slab (less halo
+        // re-read) with resident weights; wide images (InceptionV4 stem, 150-pixel rows = 300 halo rows per slab) only
+        // fit one M-tile next to resident weights, and streaming 72 KB of weights per 256 pixels costs more L2 traffic
+        // than the extra halo
+        const int plans[7][3] = {{2, 1, 2}, {2, 1, 1}, {1, 1, 2}, {1, 1, 1}, {2, 0, 2}, {2, 0, 1}, {1, 0, 1}};
+        f.stagesA = 0;
         for (auto& pl : plans) {
-          if (pl[0] && !f.resident_b) continue;
-          if (force_nout && pl[1] != force_nout) continue;
-          if (force_res >= 0 && pl[0] != force_res) continue;
-          const int sB = pl[0] ? 9 * f.chunks : 4;
-          const int nOut = f.tma_epi ? pl[1] : 0;
-          const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(2 * nOut) * 16384;
-          int sA = (int)(budget / ((long long)f.slab_rows * 128));
+          if (pl[1] && !can_reside) continue;
+          if (force_T && pl[0] != force_T) continue;
+          if (force_nout && pl[2] != force_nout) continue;
+          if (force_res >= 0 && pl[1] != force_res) continue;
+          const int T = pl[0];
+          const int rows_needed = T * 128 + 2 * f.Wp + 2;
+          const int loads = (rows_needed + 255) / 256;
+          const int box_rows = ((rows_needed + loads - 1) / loads + 7) / 8 * 8;
+          const int slab_rows = loads * box_rows;
+          const int sB = pl[1] ? 9 * f.chunks : 4;
+          const int nOut = f.tma_epi ? pl[2] : 0;
+          const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(T * nOut) * 16384;
+          int sA = (int)(budget / ((long long)slab_rows * 128));
           if (sA > 4) sA = 4;
-          f.stagesA = sA; f.stagesB = sB; f.nOut = nOut; f.nRes = want_res;
-          if (sA >= 2) {
-            f.resident_b = pl[0];
+          if (sA >= 2 && box_rows <= 256) {
+            f.T = T; f.resident_b = pl[1]; f.stagesA = sA; f.stagesB = sB; f.nOut = nOut; f.nRes = 0;
+            f.slab_loads = loads; f.slab_box_rows = box_rows; f.slab_rows = slab_rows;
             break;
           }
         }
@@ -634,20 +723,21 @@ int wsi_net_finalize(void* net) {
         f.out_C = to.C; f.out_c_off = op.out_c_off;
         op.tmO = op.tmB;
         op.tmR = op.tmB;
+        op.tmO32 = op.tmB;
         if (f.tma_epi) {
           uint64_t dims[2] = {(uint64_t)to.C, (uint64_t)B * to.Hp() * to.Wp()};
           uint64_t strides[1] = {(uint64_t)to.C * 2};
           uint32_t box[2] = {64, 128};
           uint32_t es[2] = {1, 1};
-          int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
-                                 CU_TENSOR_MAP_SWIZZLE_128B);
-          if (rc) return rc;
-          if (op.res >= 0) {
-            const Tensor& tr = n->tensors[op.res];
-            uint64_t rdims[2] = {(uint64_t)tr.C, (uint64_t)B * tr.Hp() * tr.Wp()};
-            uint64_t rstrides[1] = {(uint64_t)tr.C * 2};
-            rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr, rdims, rstrides, box, es,
+          int rc = WSI_OK;
+          if (op.Cout >= 64)
+            rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
                                CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+          if (op.Cout & 32) {
+            uint32_t box32[2] = {32, 128};
+            rc = wsi_make_tmap(&op.tmO32, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box32, es,
+                               CU_TENSOR_MAP_SWIZZLE_64B);
             if (rc) return rc;
           }
         }
@@ -684,7 +774,7 @@ int wsi_net_finalize(void* net) {
       a.is_stem = op.is_stem;
       a.N_tile = pick_ntile(op.Cout);
       a.tiles_N = op.Cout / a.N_tile;
-      a.tma_epi = (a.N_tile % 64 == 0) ? 1 : 0;
+      a.tma_epi = (a.N_tile % 64 == 0 || (a.N_tile % 32 == 0 && !n->legacy_epi)) ? 1 : 0;
       a.Cout = op.Cout;
       // CTA pairs (cta_group::2, M = 256): N must be a multiple of 32 there and each CTA's half of the weight
       // block a whole number of 8-row swizzle groups
@@ -705,6 +795,7 @@ int wsi_net_finalize(void* net) {
       int smem = (int)convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout, a.cluster);
       if (smem > max_smem) max_smem = smem;
       op.tmO = op.tmB;
+      op.tmO32 = op.tmB;
       if (a.tma_epi) {
         // destination seen from its interior pixel (0,0) with the stored pitches: partial pixel boxes and
         // the zero border are protected by TMA's bounds clipping
@@ -712,9 +803,17 @@ int wsi_net_finalize(void* net) {
         uint64_t strides[3] = {(uint64_t)to.C * 2, (uint64_t)to.Wp() * to.C * 2, (uint64_t)to.Hp() * to.Wp() * to.C * 2};
         uint32_t box[4] = {64, (uint32_t)a.bw, (uint32_t)a.bh, (uint32_t)a.bn};
         uint32_t es[4] = {1, 1, 1, 1};
-        int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, to.ptr + to.interior_offset(), dims, strides,
-                               box, es, CU_TENSOR_MAP_SWIZZLE_128B);
+        int rc = WSI_OK;
+        if (a.N_tile >= 64)
+          rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, to.ptr + to.interior_offset(), dims, strides,
+                             box, es, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc) return rc;
+        if (a.N_tile & 32) {
+          uint32_t box32[4] = {32, (uint32_t)a.bw, (uint32_t)a.bh, (uint32_t)a.bn};
+          rc = wsi_make_tmap(&op.tmO32, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, to.ptr + to.interior_offset(), dims, strides,
+                             box32, es, CU_TENSOR_MAP_SWIZZLE_64B);
+          if (rc) return rc;
+        }
       }
       // weights: [Cout][Ktot] K-major, box 64 x N_tile, 128B swizzle
       {
@@ -743,9 +842,11 @@ int wsi_net_finalize(void* net) {
   if (max_smem > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convk::k_conv_igemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   if (max_smem_stem > 0)
-    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<false, 7, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
+  if (max_smem_stem > 0)
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<false, 3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
   if (max_smem_stem_pool > 0)
-    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem_pool));
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<true, 7, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem_pool));
   if (max_smem_flat > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
   n->launches_per_forward = 0;
@@ -814,11 +915,15 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         if (op.fused_pool >= 0) {
           sa.B = B;
           int grid = B < n->num_sms ? B : n->num_sms;
-          convs::k_conv_stem<true><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages, true), stream>>>(op.tmB, sa);
+          convs::k_conv_stem<true, 7, 2><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages, true), stream>>>(op.tmB, sa);
           continue;
         }
         int grid = sa.num_tiles < n->num_sms ? sa.num_tiles : n->num_sms;
-        convs::k_conv_stem<false><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages), stream>>>(op.tmO, sa);
+        if (op.KH == 7)
+          convs::k_conv_stem<false, 7, 2><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages), stream>>>(op.tmO, sa);
+        else
+          convs::k_conv_stem<false, 3, 1><<<grid, convs::THREADS,
+                                            convs::smem_bytes(sa.slab_pairs, sa.stages, false, 3 * op.Cout * 32), stream>>>(op.tmO, sa);
         continue;
       }
       if (op.flat) {
@@ -829,7 +934,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         f.out = to.ptr;
         f.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
         int grid = f.num_tiles < n->num_sms ? f.num_tiles : n->num_sms;
-        convf::k_conv_flat<<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmR, f);
+        convf::k_conv_flat<<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, f);
         continue;
       }
       convk::Args a = op.ca;
@@ -871,9 +976,9 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         }
         if (pairs > op.max_pairs) pairs = op.max_pairs;
         cfg.gridDim = dim3((unsigned)(2 * pairs));
-        WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convk::k_conv_igemm<2>, op.tmA, op.tmB, op.tmO, a));
+        WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convk::k_conv_igemm<2>, op.tmA, op.tmB, op.tmO, op.tmO32, a));
       } else {
-        convk::k_conv_igemm<1><<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, a);
+        convk::k_conv_igemm<1><<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, a);
       }
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];

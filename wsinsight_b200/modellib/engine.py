@@ -112,8 +112,17 @@ class B200Network:
                  and S % 2 == 0)
         if stem.residual is not None:
             raise UnknownArchitectureError("the first convolution cannot take a residual")
+        import os
+
+        # InceptionV4 conv2d_1a: 3x3 / stride 2 / no padding, 32 (or 64) filters -> the same parity-plane kernel
+        stem3 = (kh == 3 and kw == 3 and stem.stride == 2 and tuple(stem.pad) == (0, 0)
+                 and int(stem.weight.shape[0]) in (32, 64) and os.environ.get("WSI_B200_NO_FLAT") != "1")
         tensor_of, c_off = {}, {}
-        if stem7:
+        if stem3:
+            se = S + (S & 1)       # stored side rounded up to even; the extra row / column stays zero and is never used
+            self.input_layout = dict(out_H=se, out_W=se, pad_top=0, pad_left=0, channels=4)
+            tensor_of[0] = self._add_tensor(se, se, 4, external=True)
+        elif stem7:
             # ResNet family: the preprocess kernel writes the padded image, patch at (3,3), 4 channels
             # (as row-parity planes when the 64-filter stem kernel is used, see csrc/conv_stem.cuh)
             self.input_layout = dict(out_H=S + 6, out_W=S + 6, pad_top=3, pad_left=3, channels=4)
@@ -156,7 +165,10 @@ class B200Network:
                 w = n.weight.contiguous()
                 b = n.bias.contiguous() if n.bias is not None else None
                 self._keep += [w, b]
-                if n is stem and not stem7:
+                if n is stem and stem3:
+                    _cabi.call("wsi_net_add_stem_parity", self._h, tensor_of[x], tensor_of[i], _fptr(w), _fptr(b), cout,
+                               3, 0, 1 if n.relu else 0)
+                elif n is stem and not stem7:
                     import torch
 
                     w8 = torch.zeros((cout, 8, int(w.shape[2]), int(w.shape[3])), dtype=torch.float32)
