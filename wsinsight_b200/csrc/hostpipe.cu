@@ -67,8 +67,7 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
   int hwc[3] = {0, 0, 0};
   int rc = wsi_net_input_geometry(net, hwc);
   if (rc) return rc;
-  WSI_ARG_CHECK((hwc[2] == 4 || hwc[2] == 8) && hwc[0] >= out_size && hwc[1] >= out_size && ((hwc[0] - out_size) % 2) == 0 &&
-                    hwc[0] == hwc[1],
+  WSI_ARG_CHECK((hwc[2] == 4 || hwc[2] == 8) && hwc[0] >= out_size && hwc[1] >= out_size && hwc[0] == hwc[1],
                 "wsi_hostpipe_create: network input %dx%dx%d does not fit out_size %d", hwc[0], hwc[1], hwc[2],
                 out_size);
   HostPipe* p = new HostPipe();
@@ -81,6 +80,8 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
   p->pitch = patch_pitch_bytes;
   p->in_H = hwc[0];
   p->in_W = hwc[1];
+  // symmetric stem padding (ResNet: 3); an odd difference is the one unused row/column that rounds an odd
+  // input size up to the even side the parity-plane layout needs (InceptionV4: 299 -> 300, pad 0)
   const int pad = (hwc[0] - out_size) / 2;
   auto fail = [&](const char* what, int code) {
     wsi_set_error("wsi_hostpipe_create: %s", what);
