@@ -177,7 +177,7 @@ struct PoolRow<false> {
 };
 
 template <bool IS_MAX, int K, int S>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 6)
     k_pool_sep(const __nv_bfloat16* __restrict__ in, int H, int W, int C, int pad, int count_include_pad, int Ho, int Wo,
                __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp,
                int op, int band, int nbands) {
