@@ -208,6 +208,17 @@ int wsi_synth_slide_host(uint8_t* h_rgba, long long x0, long long y0, int w, int
 int wsi_box_thumbnail(const uint8_t* d_rgba, long long W, long long H, long long pitch_bytes,
                       uint8_t* d_rgb, int Ht, int Wt, void* stream);
 
+/* N1: the thumbnail the reference segments, bit-exact with Pillow.  Replaces
+ * wsinsight/patchlib/pipeline.py:102-105 slide.get_thumbnail(thumbsize) -> tiffslide get_thumbnail ->
+ * Image.thumbnail(size, LANCZOS) (reducing_gap = 2: Reduce.c box reduction + Resample.c Lanczos-3).
+ * wsi_thumbnail_geometry: output size (aspect rule) and the integer reduce factors Pillow picks.
+ * wsi_lanczos_thumbnail: RGBA u8 slide (alpha opaque) -> RGB u8 [out_h][out_w][3]; d_workspace of at least
+ * wsi_thumbnail_workspace_bytes().  A reduce factor of 1 on exactly one axis is WSI_ERR_ARG (unsupported). */
+int wsi_thumbnail_geometry(long long W, long long H, int max_w, int max_h, int* out_w, int* out_h, int* fx, int* fy);
+size_t wsi_thumbnail_workspace_bytes(long long W, long long H, int max_w, int max_h);
+int wsi_lanczos_thumbnail(const uint8_t* d_slide_rgba, long long W, long long H, long long pitch_bytes, int max_w,
+                          int max_h, uint8_t* d_out_rgb, void* d_workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

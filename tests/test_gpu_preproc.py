@@ -82,9 +82,9 @@ def test_synthetic_slide_host_device_identical():
     for (x, y, w, h) in [(0, 0, 64, 64), (2900, 1900, 100, 100), (1234, 777, 333, 50)]:
         assert np.array_equal(synth_window_host(x, y, w, h, 3000, 2000, 5), dev[y:y + h, x:x + w])
     assert (dev[..., 3] == 255).all()
-    th = s.thumbnail_device((256, 256)).cpu().numpy()
+    th = s.thumbnail_device((256, 256), method="box").cpu().numpy()
     assert th.shape == (171, 256, 3)
-    # exact integer box mean
+    # exact integer box mean (the stand-in thumbnail; the Pillow-exact one is covered by tests/test_thumbnail.py)
     j, i = 100, 50
     x0, x1, y0, y1 = j * 3000 // 256, (j + 1) * 3000 // 256, i * 2000 // 171, (i + 1) * 2000 // 171
     box = dev[y0:y1, x0:x1, :3].reshape(-1, 3).astype(np.int64)

@@ -84,20 +84,37 @@ class DeviceSlide:
     def pitch_bytes(self) -> int:
         return int(self.rgba.shape[1]) * 4
 
-    def thumbnail_device(self, size=(2048, 2048)):
-        """Box-average RGB thumbnail on the device: CUDA uint8 (Ht, Wt, 3).
+    def thumbnail_device(self, size=(2048, 2048), method: str = "lanczos"):
+        """RGB thumbnail on the device: CUDA uint8 (Ht, Wt, 3).
 
-        Stand-in for tiffslide's LANCZOS thumbnail (pipeline.py:102-105); PIL-exact thumbnail
-        parity is the "next" row N1 of SURVEY.md section 8(f).
+        ``method="lanczos"`` (default): what the reference segments -- tiffslide ``get_thumbnail`` ->
+        ``Image.thumbnail(size, LANCZOS)`` (pipeline.py:102-105), bit-exact with Pillow (csrc/thumb.cu).
+        ``method="box"``: plain box average (the round-1 stand-in, kept for comparison).
         """
+        import ctypes as C
+
         torch = _cabi.require_cuda()
         wt, ht = _thumb_size(self.dimensions, size)
-        key = (wt, ht)
+        key = (wt, ht, method)
         if key not in self._thumb_cache:
             out = torch.empty((ht, wt, 3), dtype=torch.uint8, device=self.rgba.device)
             with torch.cuda.device(self.rgba.device):
-                _cabi.call("wsi_box_thumbnail", self.rgba.data_ptr(), self.width, self.height, self.pitch_bytes,
-                           out.data_ptr(), ht, wt, _cabi.stream_ptr())
+                if method == "box":
+                    _cabi.call("wsi_box_thumbnail", self.rgba.data_ptr(), self.width, self.height, self.pitch_bytes,
+                               out.data_ptr(), ht, wt, _cabi.stream_ptr())
+                elif method == "lanczos":
+                    ow, oh = C.c_int(), C.c_int()
+                    _cabi.call("wsi_thumbnail_geometry", self.width, self.height, int(size[0]), int(size[1]),
+                               C.byref(ow), C.byref(oh), None, None)
+                    assert (ow.value, oh.value) == (wt, ht), "thumbnail geometry disagrees with the Pillow aspect rule"
+                    nbytes = int(_cabi.load().wsi_thumbnail_workspace_bytes(self.width, self.height, int(size[0]),
+                                                                            int(size[1])))
+                    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=self.rgba.device)
+                    _cabi.call("wsi_lanczos_thumbnail", self.rgba.data_ptr(), self.width, self.height, self.pitch_bytes,
+                               int(size[0]), int(size[1]), out.data_ptr(), ws.data_ptr(), nbytes, _cabi.stream_ptr())
+                    torch.cuda.current_stream().synchronize()      # the workspace is released on return
+                else:
+                    raise ValueError(f"unknown thumbnail method {method!r}")
             self._thumb_cache[key] = out
         return self._thumb_cache[key]
 
