@@ -46,7 +46,21 @@ def _digest() -> str:
 
 
 def build_library(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every .cu under csrc/ for sm_100a and link the shared library."""
+    """Compile every .cu under csrc/ for sm_100a and link the shared library.
+
+    Safe under concurrent callers (one rank per GPU under torchrun): an exclusive file lock serialises the
+    check + build, and the library is linked under a temporary name and renamed into place."""
+    import fcntl
+
+    with open(PKG / ".build.lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            return _build_locked(force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(force: bool, verbose: bool) -> Path:
     dig = _digest()
     if not force and LIB.exists() and STAMP.exists() and STAMP.read_text().strip() == dig:
         return LIB
@@ -72,11 +86,13 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
             failed.append(src)
     if failed:
         raise RuntimeError(f"nvcc failed for {failed}")
-    cmd = [nvcc, "-shared", "-o", str(LIB), *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+    tmp = LIB.with_suffix(f".so.tmp{os.getpid()}")
+    cmd = [nvcc, "-shared", "-o", str(tmp), *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout)
         raise RuntimeError("link of libwsi_b200.so failed")
+    os.replace(tmp, LIB)
     STAMP.write_text(dig)
     return LIB
 
