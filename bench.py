@@ -303,6 +303,10 @@ def b200_arm(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # NCCL prints its version banner on STDOUT when NCCL_DEBUG=VERSION (the image default): keep stdout to the
+        # one JSON line of the contract
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     lib = _cabi.load()
     peaks = load_peaks()
@@ -400,6 +404,28 @@ def b200_arm(args, rank, world, local_rank):
     ms_max = float(tms.item())
     value = world * K * B / (ms_max * 1e-3)
 
+    # ---- density grid of the classified patches: per-rank binning + ONE all-reduce ----
+    from wsinsight_b200.insightlib import allreduce_grids, density_grid_device
+    done = torch.zeros(nb_local * B, dtype=torch.bool, device=dev)
+    for i in range(Wm + K):
+        b = i % nb_local
+        done[b * B:(b + 1) * B] = True
+    cdone = coords[: nb_local * B]
+    xywh = torch.cat([cdone, torch.full_like(cdone, ps)], 1)[done].contiguous()
+    d0, d1 = ev(), ev()
+    barrier()
+    d0.record()
+    dgrid, ddrop = density_grid_device(xywh, probs[done].contiguous(), W, H, 2000)
+    allreduce_grids(dgrid)
+    d1.record()
+    torch.cuda.synchronize()
+    tot = torch.tensor([int(done.sum().item())], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    density = {"bin_px": 2000, "grid": list(dgrid.shape), "ms_bin_plus_allreduce": d0.elapsed_time(d1),
+               "objects": int(tot.item()), "grid_sum": int(dgrid.sum().item()) + 0,
+               "collective": "nccl all_reduce(sum) over ranks" if world > 1 else "none (1 rank)"}
+
     # ---- e2e: host buffers through wsi_hostpipe_* ----
     e2e = None
     if not args.no_e2e:
@@ -488,6 +514,7 @@ def b200_arm(args, rank, world, local_rank):
                       "achieved_gbs": W * H * 4 / (min(thumb_ms) * 1e-3) / 1e9, "peak_gbs": peaks["hbm_gbs"],
                       "frac": W * H * 4 / (min(thumb_ms) * 1e-3) / 1e9 / peaks["hbm_gbs"],
                       "note": "Pillow-exact reduce + Lanczos-3 (csrc/thumb.cu); includes host tap tables + sync"},
+        "density_grid": density,
         "seg_patchify_ms_per_slide": min(seg_ms), "seg_patchify_ms_runs": seg_ms,
         "slide_generation_s": t_gen, "in_tissue_patches": n_total, "patch_size": ps,
     }

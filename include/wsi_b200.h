@@ -219,6 +219,13 @@ size_t wsi_thumbnail_workspace_bytes(long long W, long long H, int max_w, int ma
 int wsi_lanczos_thumbnail(const uint8_t* d_slide_rgba, long long W, long long H, long long pitch_bytes, int max_w,
                           int max_h, uint8_t* d_out_rgb, void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* K5 (BASELINE config 5): per-class density grid.  No upstream implementation exists;
+ * the object centre follows wsinsight/insightlib/insight_helpers.py:26-27 (np.rint(minx + width / 2)), the class is
+ * the first arg-max of the K probabilities.  ACCUMULATES into d_grid int32 [K][Gy][Gx]; objects outside the grid are
+ * counted in *d_dropped.  Grids of several ranks are summed by the caller (one NCCL all-reduce). */
+int wsi_density_accumulate(const int32_t* d_xywh, const float* d_probs, int n, int K, int bin_px, int Gx, int Gy,
+                           int32_t* d_grid, int32_t* d_dropped, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
