@@ -226,6 +226,16 @@ int wsi_lanczos_thumbnail(const uint8_t* d_slide_rgba, long long W, long long H,
 int wsi_density_accumulate(const int32_t* d_xywh, const float* d_probs, int n, int K, int bin_px, int Gx, int Gy,
                            int32_t* d_grid, int32_t* d_dropped, void* stream);
 
+/* N4: the optional /images cache of the patch file.  wsi_extract_patches_rgb replaces
+ * wsinsight/patchlib/io.py:19-48 (read_region + convert("RGB") per patch; zero outside the slide):
+ * d_out_rgb u8 [n][ps][ps][3].  wsi_pack_patches_rgba turns such cached patches back into the RGBA stack
+ * ([n * ps][pitch], A = 255) that wsi_preproc_plan_create accepts as a "slide" of width ps and height n * ps with
+ * patch i at (0, i * ps) -- the device form of wsinsight/modellib/data.py:243-268. */
+int wsi_extract_patches_rgb(const uint8_t* d_slide_rgba, long long W, long long H, long long pitch_bytes,
+                            const int32_t* d_coords_xy, int n, int patch_size, uint8_t* d_out_rgb, void* stream);
+int wsi_pack_patches_rgba(const uint8_t* d_rgb, int n, int patch_size, long long pitch_bytes, uint8_t* d_out_rgba,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

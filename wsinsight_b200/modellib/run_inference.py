@@ -55,6 +55,49 @@ def classify_patches_device(slide, coords_xywh: np.ndarray, net, transform, batc
     return probs
 
 
+def classify_patches_from_images(images, net, transform, batch_size: int, probs_out=None):
+    """Classification from the cached ``/images`` patches instead of the slide (reference ``data.py:243-268,293-300``:
+    ``_get_patch_from_hdf5`` -> transform -> model).  ``images``: uint8 (N, ps, ps, 3), CUDA tensor or numpy array.
+
+    Each batch is packed into an RGBA stack on the device (``wsi_pack_patches_rgba``) that the fused preprocess
+    kernel reads as a slide of width ``ps`` with patch *i* at ``(0, i * ps)``; the result is bit-identical to
+    :func:`classify_patches_device` on the same pixels."""
+    from ..wsi import DeviceSlide
+    from .data import PreprocessPlan
+
+    torch = _cabi.require_cuda()
+    if not hasattr(images, "is_cuda"):
+        images = torch.from_numpy(np.ascontiguousarray(images))
+    images = images.to(net.device).contiguous()
+    if images.dim() != 4 or images.shape[3] != 3 or images.shape[1] != images.shape[2] or images.dtype != torch.uint8:
+        raise ValueError(f"images must be uint8 (N, ps, ps, 3), got {tuple(images.shape)} {images.dtype}")
+    n, ps = int(images.shape[0]), int(images.shape[1])
+    K = net.num_classes
+    probs = probs_out if probs_out is not None else torch.empty((n, K), dtype=torch.float32, device=net.device)
+    if n == 0:
+        return probs
+    B = min(int(batch_size), net.max_batch)
+    wp = (ps + 3) // 4 * 4
+    stack = torch.zeros((B * ps, wp, 4), dtype=torch.uint8, device=net.device)
+    view = DeviceSlide(stack, ps, B * ps, mpp=1.0, name="image-cache")
+    lay = net.input_layout
+    plan = PreprocessPlan(view, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"],
+                          lay.get("plane_stride_px", 0), lay.get("channels", 4))
+    coords = torch.zeros((B, 2), dtype=torch.int32, device=net.device)
+    coords[:, 1] = torch.arange(B, dtype=torch.int32, device=net.device) * ps
+    xin = net.alloc_input()
+    with torch.cuda.device(net.device):
+        for s in range(0, n, B):
+            b = min(B, n - s)
+            _cabi.call("wsi_pack_patches_rgba", images[s:s + b].data_ptr(), b, ps, wp * 4, stack.data_ptr(),
+                       _cabi.stream_ptr())
+            plan.run(coords[:b], xin)
+            net.forward_into(xin, probs[s:s + b])
+    torch.cuda.current_stream().synchronize()      # stack / plan / xin are released on return
+    plan.close()
+    return probs
+
+
 def gather_probs(probs_local, n_total: int, rank: int, world: int):
     """Gather per-rank (N_r, K) probability shards on rank 0 (NCCL on GPUs, gloo on CPU).
 

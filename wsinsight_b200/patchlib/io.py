@@ -23,6 +23,27 @@ except Exception:  # noqa: BLE001
     h5py = None
 
 
+def extract_patches_from_slide(slide, coords, patch_size: int, as_numpy: bool = False):
+    """RGB patches ``(N, ps, ps, 3)`` uint8 for top-left ``coords`` (N, 2) at level 0 -- the optional ``/images``
+    cache of the patch file (reference ``patchlib/io.py:19-48``: ``read_region`` + ``convert("RGB")`` per patch,
+    zero outside the slide).  One gather kernel over the device-resident slide; returns a CUDA tensor, or a numpy
+    array with ``as_numpy=True`` (what ``save_hdf5(images=...)`` stores)."""
+    from .. import _cabi
+
+    torch = _cabi.require_cuda()
+    c = np.asarray(coords.cpu().numpy() if hasattr(coords, "cpu") else coords, dtype=np.int32)
+    if c.ndim != 2 or c.shape[1] != 2:
+        raise ValueError(f"coords must be (N, 2), got {c.shape}")
+    dev = slide.rgba.device
+    dc = torch.from_numpy(np.ascontiguousarray(c)).to(dev)
+    out = torch.empty((len(c), int(patch_size), int(patch_size), 3), dtype=torch.uint8, device=dev)
+    if len(c):
+        with torch.cuda.device(dev):
+            _cabi.call("wsi_extract_patches_rgb", slide.rgba.data_ptr(), slide.width, slide.height, slide.pitch_bytes,
+                       dc.data_ptr(), len(c), int(patch_size), out.data_ptr(), _cabi.stream_ptr())
+    return out.cpu().numpy() if as_numpy else out
+
+
 def square_polygons(coords: np.ndarray, patch_size: int) -> np.ndarray:
     """Per-patch closed 5-vertex squares, vectorised (reference loop: pipeline.py:386-400).
 
