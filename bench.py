@@ -29,6 +29,17 @@ import threading
 import time
 from pathlib import Path
 
+_JSON_FD = None        # original stdout when fd 1 had to be pointed at stderr (see b200_arm)
+
+
+def emit_json(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
 ROOT = Path(__file__).resolve().parent
 if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
@@ -303,10 +314,12 @@ def b200_arm(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # NCCL prints its version banner on STDOUT when NCCL_DEBUG=VERSION (the image default): keep stdout to the
-        # one JSON line of the contract
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL writes its version banner to file descriptor 1 from C code: point fd 1 at stderr for the rest of the
+        # run and keep the original stdout for the one JSON line of the contract
+        global _JSON_FD
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     lib = _cabi.load()
     peaks = load_peaks()
@@ -535,7 +548,7 @@ def b200_arm(args, rank, world, local_rank):
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args, coords_all, ps, W, H, thumb, res, spec)
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     if world > 1:
         dist.destroy_process_group()
 

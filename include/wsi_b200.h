@@ -236,6 +236,17 @@ int wsi_extract_patches_rgb(const uint8_t* d_slide_rgba, long long W, long long 
 int wsi_pack_patches_rgba(const uint8_t* d_rgb, int n, int patch_size, long long pitch_bytes, uint8_t* d_out_rgba,
                           void* stream);
 
+/* a13 / N3: batch step of the cell-model tile stitcher, fused.  Replaces
+ * wsinsight/modellib/tilefuse.py:219-278 TileRemapStitcher.accumulate_batch_torch (softmax, bilinear
+ * align_corners=False resize h -> S, hv * alpha, tp renormalisation, D2H and the Python paste loop) with one kernel
+ * writing into device canvases np_map f32 [H][W], hv_map f32 [H][W][2], tp_map f32 [H][W][K].
+ * Inputs are the model outputs, f32 NCHW: np_logits [B][2][h][h], hv [B][2][h][h], tp_logits [B][K][h][h];
+ * d_coords int32 [B][coord_stride] holds (minx, miny, ...) of each tile; its S x S interior lands at
+ * (minx + halo, miny + halo), clipped to the canvas.  Tiles of one call must not overlap. */
+int wsi_tilefuse_accumulate(const float* d_np_logits, const float* d_hv, const float* d_tp_logits,
+                            const int32_t* d_coords, int coord_stride, int B, int K, int h, int S, int halo, float alpha,
+                            int canvas_W, int canvas_H, float* d_np_map, float* d_hv_map, float* d_tp_map, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -93,6 +93,8 @@ _PROTOS = {
     "wsi_density_accumulate": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "wsi_extract_patches_rgb": (c_int, [c_void_p, c_ll, c_ll, c_ll, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "wsi_pack_patches_rgba": (c_int, [c_void_p, c_int, c_int, c_ll, c_void_p, c_void_p]),
+    "wsi_tilefuse_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                        C.c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "wsi_thumbnail_geometry": (c_int, [c_ll, c_ll, c_int, c_int, c_int_p, c_int_p, c_int_p, c_int_p]),
     "wsi_thumbnail_workspace_bytes": (C.c_size_t, [c_ll, c_ll, c_int, c_int]),
     "wsi_lanczos_thumbnail": (c_int, [c_void_p, c_ll, c_ll, c_ll, c_int, c_int, c_void_p, c_void_p, C.c_size_t, c_void_p]),
