@@ -19,6 +19,10 @@ def _inputs(B, K, h, seed, W, H, S, halo):
     ys = (idx // (cols + 1) - 1) * S - halo + 5
     coords = torch.stack([xs, ys, torch.full_like(xs, S + 2 * halo), torch.full_like(xs, S + 2 * halo)], 1)
     coords[0, 0], coords[0, 1] = W + 50, 0                      # entirely outside: skipped
+    coords[1, 0], coords[1, 1] = (W // S // 2) * S - halo + 3, -halo + 5     # at least one tile inside the canvas (same grid)
+    for i in range(2, B):                                       # keep the interiors disjoint (the reference's never overlap)
+        if coords[i, 0] == coords[1, 0] and coords[i, 1] == coords[1, 1]:
+            coords[i, 0] = W + 50
     return np_l, hv, tp_l, coords
 
 
