@@ -20,16 +20,33 @@ def main():
     metrics = ("gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,"
                "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active,"
                "l1tex__m_xbar2l1tex_read_bytes.sum,sm__throughput.avg.pct_of_peak_sustained_elapsed")
-    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--metrics", metrics], capture_output=True,
-                         text=True, check=True).stdout
-    if len(sys.argv) > 3:
-        open(sys.argv[3], "w").write(out)
+    if rep.endswith(".csv"):      # exported on the GPU box: `--page raw --csv` (wide) or a `--metrics ... --csv` log (long)
+        out = open(rep).read()
+        out = out[out.index('"ID"'):]
+    else:
+        out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--metrics", metrics], capture_output=True,
+                             text=True, check=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
+    if "Metric Name" in rows[0]:  # long format -> wide
+        c = {h: i for i, h in enumerate(rows[0])}
+        wide, unit_of = {}, {}
+        for r in rows[1:]:
+            if len(r) < len(rows[0]):
+                continue
+            w = wide.setdefault(r[c["ID"]], {"Kernel Name": r[c["Kernel Name"]]})
+            w[r[c["Metric Name"]]] = r[c["Metric Value"]].replace(",", "")
+            unit_of[r[c["Metric Name"]]] = r[c["Metric Unit"]]
+        names = ["Kernel Name"] + sorted(unit_of)
+        rows = [names, [""] + [unit_of[n] for n in names[1:]]] + [[w.get(n, "0") for n in names] for w in wide.values()]
+    if len(sys.argv) > 3:
+        keep = [i for i, h in enumerate(rows[0]) if h in ("ID", "Kernel Name", "Grid Size", "Block Size") or h in metrics.split(",")]
+        with open(sys.argv[3], "w", newline="") as f:
+            csv.writer(f).writerows([[r[i] for i in keep] for r in rows])
     hdr, units, data = rows[0], rows[1], rows[2:]
     col = {h: i for i, h in enumerate(hdr)}
 
     def val(r, name):
-        return float(r[col[name]]) * UNIT[units[col[name]]]
+        return float(r[col[name]].replace(",", "")) * UNIT.get(units[col[name]], 1.0)
 
     per = {}
     tot_b = tot_t = 0.0

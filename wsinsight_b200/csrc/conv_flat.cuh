@@ -31,6 +31,7 @@ struct Args {
   int Hp, Wp, H, W, B;          // stored geometry shared by input, output and residual; H x W = OUTPUT interior
   int pad;                      // border of the OUTPUT interior inside the stored geometry (a 'valid' 3x3 conv is the
                                 // same centred flat conv whose output border is one pixel wider than its input's)
+  int cluster;                  // 1, or 2: CTA pairs (k_conv_flat<2>, launched as 2-CTA clusters)
   int ksteps;                   // K = 16 MMA steps per tap and 64-channel chunk: 4, or 2 when only 32 channels are real
   long long total_rows;         // B * Hp * Wp flat positions
   int num_tiles;                // super-tiles of T*128 positions
@@ -61,35 +62,46 @@ struct MmaCtx {
   uint32_t row_step;              // Wp * 8: one image row of the padded layout in descriptor units
   uint32_t tmem_base, idesc, hi;
   int N, chunks, stagesA, stagesB, num_tiles;
+  int first_unit, unit_step, num_units;   // work units of this CTA (pair mode: one unit = two consecutive super-tiles)
   uint64_t *aFull, *aEmpty, *bFull, *bEmpty, *tfull, *tempty;
 };
 
-template <int T, int KS>
+template <bool PAIR>
+__device__ __forceinline__ void umma1(uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc) {
+  if (PAIR) ptx::umma_bf16_lohi_2sm(d, a_lo, b_lo, hi, idesc, acc); else ptx::umma_bf16_lohi(d, a_lo, b_lo, hi, idesc, acc);
+}
+
+template <int T, int KS, bool PAIR>
 __device__ __forceinline__ void issue_tap(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
                                           uint32_t accum_first, uint32_t N) {
-  ptx::umma_bf16_lohi(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, accum_first);
-  ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+  umma1<PAIR>(d_tmem, a_lo + 0, b_lo + 0, hi, idesc, accum_first);
+  umma1<PAIR>(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
   if (KS == 4) {
-    ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
-    ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+    umma1<PAIR>(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+    umma1<PAIR>(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
   }
   if (T == 2) {
     const uint32_t d1 = d_tmem + N, a1 = a_lo + 1024u;   // second M-tile: +128 rows of 128 B (>> 4)
-    ptx::umma_bf16_lohi(d1, a1 + 0, b_lo + 0, hi, idesc, accum_first);
-    ptx::umma_bf16_lohi(d1, a1 + 2, b_lo + 2, hi, idesc, 1u);
+    umma1<PAIR>(d1, a1 + 0, b_lo + 0, hi, idesc, accum_first);
+    umma1<PAIR>(d1, a1 + 2, b_lo + 2, hi, idesc, 1u);
     if (KS == 4) {
-      ptx::umma_bf16_lohi(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
-      ptx::umma_bf16_lohi(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
+      umma1<PAIR>(d1, a1 + 4, b_lo + 4, hi, idesc, 1u);
+      umma1<PAIR>(d1, a1 + 6, b_lo + 6, hi, idesc, 1u);
     }
   }
 }
 
-template <int T, bool RESIDENT, int KS>
+template <bool PAIR>
+__device__ __forceinline__ void commit1(uint64_t* bar) {
+  if (PAIR) ptx::umma_commit_2sm(bar, (uint16_t)3); else ptx::umma_commit(bar);   // pair: arrives in both CTAs
+}
+
+template <int T, bool RESIDENT, int KS, bool PAIR>
 __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
   int sa = 0, sb = 0, acc = 0;
   uint32_t pa = 0, pb = 0, pacc = 0;
   bool first_tile = true;
-  for (int tile = blockIdx.x; tile < m.num_tiles; tile += gridDim.x) {
+  for (int u = m.first_unit; u < m.num_units; u += m.unit_step) {
     ptx::mbar_wait(&m.tempty[acc], pacc ^ 1);
     const uint32_t d_tmem = m.tmem_base + (uint32_t)(acc * T) * (uint32_t)m.N;
     for (int c = 0; c < m.chunks; ++c) {
@@ -105,10 +117,10 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
           for (int tap = 0; tap < 9; ++tap) {
             const uint32_t a_lo = slab_lo + (uint32_t)(tap / 3) * m.row_step + (uint32_t)(tap % 3) * 8u;
             const uint32_t b_lo = m.sB_lo + (uint32_t)(tap * m.chunks + c) * m.b_step;
-            issue_tap<T, KS>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
+            issue_tap<T, KS, PAIR>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
           }
-          ptx::umma_commit(&m.aEmpty[sa]);
-          if (last_c) ptx::umma_commit(&m.tfull[acc]);
+          commit1<PAIR>(&m.aEmpty[sa]);
+          if (last_c) commit1<PAIR>(&m.tfull[acc]);
         }
         __syncwarp();
       } else {
@@ -119,11 +131,11 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
           if (ptx::elect_one()) {
             const uint32_t a_lo = slab_lo + (uint32_t)(tap / 3) * m.row_step + (uint32_t)(tap % 3) * 8u;
             const uint32_t b_lo = m.sB_lo + (uint32_t)sb * m.b_step;
-            issue_tap<T, KS>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
-            ptx::umma_commit(&m.bEmpty[sb]);
+            issue_tap<T, KS, PAIR>(d_tmem, a_lo, b_lo, m.hi, m.idesc, tap == 0 ? (uint32_t)(c != 0) : 1u, (uint32_t)m.N);
+            commit1<PAIR>(&m.bEmpty[sb]);
             if (tap == 8) {
-              ptx::umma_commit(&m.aEmpty[sa]);
-              if (last_c) ptx::umma_commit(&m.tfull[acc]);
+              commit1<PAIR>(&m.aEmpty[sa]);
+              if (last_c) commit1<PAIR>(&m.tfull[acc]);
             }
           }
           __syncwarp();
@@ -137,6 +149,11 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
   }
 }
 
+// CL = 1: one CTA per super-tile.  CL = 2: CTA PAIRS (cta_group::2): the leader's tcgen05.mma spans both SMs
+// (M = 256: M-tile t of BOTH CTAs' slabs against the weight k-block whose N/2-row halves sit in the two CTAs), so each
+// SM reads 4 KB of A + N*16 B of B per K step instead of 4 KB + N*32 B: with N = 64 / 128 the single-CTA kernel is
+// bound by shared-memory operand bandwidth (128 B/clk: 67 % / 100 % of the tensor rate before any other smem traffic).
+template <int CL>
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                 const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32, const Args a) {
@@ -144,7 +161,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
   const int slab_bytes = a.slab_rows * 128;
-  const int b_bytes = a.N * 128;
+  const int b_bytes = (CL == 2 ? a.N / 2 : a.N) * 128;      // per-CTA bytes of one weight k-block
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)a.stagesA * slab_bytes;
   uint8_t* sOut = sB + (size_t)a.stagesB * b_bytes;                 // T groups x nOut x 16 KB (1024-aligned)
@@ -161,6 +178,14 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int TM = a.T * 128;
+  // work units: one super-tile per CTA and iteration; in pair mode unit u of the PAIR is super-tiles 2u, 2u + 1 and
+  // CTA `crank` takes 2u + crank, clamped to the last one (an odd count makes the last pair compute it twice:
+  // identical stores)
+  const uint32_t crank = CL == 2 ? ptx::cluster_ctarank() : 0u;
+  const int num_units = CL == 2 ? (a.num_tiles + 1) / 2 : a.num_tiles;
+  const int first_unit = CL == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int unit_step = CL == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  auto tile_of = [&](int u) { return CL == 2 ? min(2 * u + (int)crank, a.num_tiles - 1) : u; };
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmapA);
@@ -175,17 +200,27 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], a.tma_epi ? 4 * a.T : 4);
+      ptx::mbar_init(&tempty[s], (uint32_t)((a.tma_epi ? 4 * a.T : 4) * CL));
       ptx::mbar_init(&resFull[s], 1);
     }
     ptx::fence_barrier_init();
   }
+  if (CL == 2) {
+    __syncthreads();
+    ptx::cluster_sync();                      // both CTAs' barriers exist before the pair-wide TMEM allocation
+  }
   if (warp == 1) {
-    ptx::tmem_alloc(tmem_slot, 512);
-    ptx::tmem_relinquish();
+    if (CL == 2) {
+      ptx::tmem_alloc_2sm(tmem_slot, 512);
+      ptx::tmem_relinquish_2sm();
+    } else {
+      ptx::tmem_alloc(tmem_slot, 512);
+      ptx::tmem_relinquish();
+    }
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (CL == 2) ptx::cluster_sync();           // the peer's barriers are initialised before anything remote happens
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -195,16 +230,28 @@ __global__ void __launch_bounds__(THREADS, 1)
       int sa = 0, sb = 0;
       uint32_t pa = 0, pb = 0;
       bool first = true;
-      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        const long long q0 = (long long)tile * TM;
+      const bool arm = CL == 1 || crank == 0;     // pair mode: only the leader arms, for the bytes of BOTH CTAs
+      for (int u = first_unit; u < num_units; u += unit_step) {
+        const long long q0 = (long long)tile_of(u) * TM;
         const int row0 = (int)(q0 - a.Wp - 1);
+        if (a.has_res && q0 < a.total_rows && ptx::elect_one()) {
+          // the epilogue reads this super-tile's residual rows stagesA slabs from now: have them in L2 by then
+          // (HBM latency under load exceeds the one-tile lead of the register prefetch)
+          const long long rows = a.total_rows - q0 < TM ? a.total_rows - q0 : TM;
+          ptx::bulk_prefetch_l2(a.residual + (size_t)q0 * a.N, (uint32_t)(rows * a.N * 2));
+        }
+        __syncwarp();
         for (int c = 0; c < a.chunks; ++c) {
           ptx::mbar_wait(&aEmpty[sa], pa ^ 1);
           if (ptx::elect_one()) {
-            ptx::mbar_arrive_expect_tx(&aFull[sa], (uint32_t)slab_bytes);
-            for (int i = 0; i < a.slab_loads; ++i)
-              ptx::tma_load_2d(sA + (size_t)sa * slab_bytes + (size_t)i * a.slab_box_rows * 128, &tmapA, &aFull[sa],
-                               c * 64, row0 + i * a.slab_box_rows);
+            if (arm) ptx::mbar_arrive_expect_tx(&aFull[sa], (uint32_t)(slab_bytes * CL));
+            for (int i = 0; i < a.slab_loads; ++i) {
+              void* dst = sA + (size_t)sa * slab_bytes + (size_t)i * a.slab_box_rows * 128;
+              if (CL == 2)
+                ptx::tma_load_2d_2sm(dst, &tmapA, ptx::leader_bar_addr(&aFull[sa]), c * 64, row0 + i * a.slab_box_rows);
+              else
+                ptx::tma_load_2d(dst, &tmapA, &aFull[sa], c * 64, row0 + i * a.slab_box_rows);
+            }
           }
           __syncwarp();
           if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
@@ -212,8 +259,12 @@ __global__ void __launch_bounds__(THREADS, 1)
             if (first && ptx::elect_one())
               for (int tap = 0; tap < 9; ++tap) {
                 const int kb = tap * a.chunks + c;
-                ptx::mbar_arrive_expect_tx(&bFull[kb], (uint32_t)b_bytes);
-                ptx::tma_load_2d(sB + (size_t)kb * b_bytes, &tmapB, &bFull[kb], kb * 64, 0);
+                if (arm) ptx::mbar_arrive_expect_tx(&bFull[kb], (uint32_t)(b_bytes * CL));
+                if (CL == 2)
+                  ptx::tma_load_2d_2sm(sB + (size_t)kb * b_bytes, &tmapB, ptx::leader_bar_addr(&bFull[kb]), kb * 64,
+                                       (int)crank * (a.N >> 1));
+                else
+                  ptx::tma_load_2d(sB + (size_t)kb * b_bytes, &tmapB, &bFull[kb], kb * 64, 0);
               }
             __syncwarp();
           } else {
@@ -221,8 +272,12 @@ __global__ void __launch_bounds__(THREADS, 1)
               const int kb = tap * a.chunks + c;
               ptx::mbar_wait(&bEmpty[sb], pb ^ 1);
               if (ptx::elect_one()) {
-                ptx::mbar_arrive_expect_tx(&bFull[sb], (uint32_t)b_bytes);
-                ptx::tma_load_2d(sB + (size_t)sb * b_bytes, &tmapB, &bFull[sb], kb * 64, 0);
+                if (arm) ptx::mbar_arrive_expect_tx(&bFull[sb], (uint32_t)(b_bytes * CL));
+                if (CL == 2)
+                  ptx::tma_load_2d_2sm(sB + (size_t)sb * b_bytes, &tmapB, ptx::leader_bar_addr(&bFull[sb]), kb * 64,
+                                       (int)crank * (a.N >> 1));
+                else
+                  ptx::tma_load_2d(sB + (size_t)sb * b_bytes, &tmapB, &bFull[sb], kb * 64, 0);
               }
               __syncwarp();
               if (++sb == a.stagesB) { sb = 0; pb ^= 1; }
@@ -244,20 +299,24 @@ __global__ void __launch_bounds__(THREADS, 1)
     m.b_step = (uint32_t)b_bytes >> 4;
     m.row_step = (uint32_t)a.Wp * 8u;
     m.tmem_base = tmem_base;
-    m.idesc = ptx::make_idesc_bf16(128, a.N);
+    m.idesc = ptx::make_idesc_bf16(CL == 2 ? 256 : 128, a.N);
     m.hi = ptx::sw128_desc_hi();
     m.N = a.N; m.chunks = a.chunks; m.stagesA = a.stagesA; m.stagesB = a.stagesB; m.num_tiles = a.num_tiles;
+    m.first_unit = first_unit; m.unit_step = unit_step; m.num_units = num_units;
     m.aFull = aFull; m.aEmpty = aEmpty; m.bFull = bFull; m.bEmpty = bEmpty; m.tfull = tfull; m.tempty = tempty;
-    if (a.ksteps == 2) {
-      if (a.T == 2) {
-        if (a.resident_b) mma_loop<2, true, 2>(m); else mma_loop<2, false, 2>(m);
+    constexpr bool PAIR = CL == 2;
+    if (!PAIR || crank == 0) {                      // pair mode: only the leader CTA issues
+      if (a.ksteps == 2) {
+        if (a.T == 2) {
+          if (a.resident_b) mma_loop<2, true, 2, PAIR>(m); else mma_loop<2, false, 2, PAIR>(m);
+        } else {
+          if (a.resident_b) mma_loop<1, true, 2, PAIR>(m); else mma_loop<1, false, 2, PAIR>(m);
+        }
+      } else if (a.T == 2) {
+        if (a.resident_b) mma_loop<2, true, 4, PAIR>(m); else mma_loop<2, false, 4, PAIR>(m);
       } else {
-        if (a.resident_b) mma_loop<1, true, 2>(m); else mma_loop<1, false, 2>(m);
+        if (a.resident_b) mma_loop<1, true, 4, PAIR>(m); else mma_loop<1, false, 4, PAIR>(m);
       }
-    } else if (a.T == 2) {
-      if (a.resident_b) mma_loop<2, true, 4>(m); else mma_loop<2, false, 4>(m);
-    } else {
-      if (a.resident_b) mma_loop<1, true, 4>(m); else mma_loop<1, false, 4>(m);
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
@@ -277,8 +336,8 @@ __global__ void __launch_bounds__(THREADS, 1)
       if (g < a.T) {
         uint8_t* myOut = sOut + (size_t)g * a.nOut * 16384;
         int k = 0;
-        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-          const long long q0 = (long long)tile * TM + g * 128;
+        for (int u = first_unit; u < num_units; u += unit_step) {
+          const long long q0 = (long long)tile_of(u) * TM + g * 128;
           const long long p = q0 + row;
           const int n = (int)(p / img);
           const int rem = (int)(p - (long long)n * img);
@@ -319,7 +378,9 @@ __global__ void __launch_bounds__(THREADS, 1)
             if (last) {                                 // this group's accumulator tile fully read: hand it back
               ptx::tc_fence_before();
               __syncwarp();
-              if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+              if (lane == 0) {
+                if (CL == 2) ptx::mbar_arrive_cluster(&tempty[acc], 0u); else ptx::mbar_arrive(&tempty[acc]);
+              }
             }
             ptx::fence_proxy_async();
             ptx::named_bar_sync(1 + g, 128);            // chunk staged
@@ -337,8 +398,8 @@ __global__ void __launch_bounds__(THREADS, 1)
         if (leader) ptx::bulk_wait<0>();
       }
     } else if (warp < 6)
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-      const long long q0 = (long long)tile * TM;
+    for (int u = first_unit; u < num_units; u += unit_step) {
+      const long long q0 = (long long)tile_of(u) * TM;
       ptx::mbar_wait(&tfull[acc], pacc);
       ptx::tc_fence_after();
       for (int t = 0; t < a.T; ++t) {
@@ -393,22 +454,25 @@ __global__ void __launch_bounds__(THREADS, 1)
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if (CL == 2) ptx::mbar_arrive_cluster(&tempty[acc], 0u); else ptx::mbar_arrive(&tempty[acc]);
+      }
       if (++acc == 2) { acc = 0; pacc ^= 1; }
     }
   }
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (CL == 2) ptx::cluster_sync();   // nobody leaves while the peer may still arrive here
   if (warp == 1) {
     __syncwarp();
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, 512);
+    if (CL == 2) ptx::tmem_dealloc_2sm(tmem_base, 512); else ptx::tmem_dealloc(tmem_base, 512);
   }
 }
 
 static inline size_t smem_bytes(const Args& a) {
-  return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * a.N * 128 +
+  return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * (a.cluster == 2 ? a.N / 2 : a.N) * 128 +
          (size_t)(a.T * a.nOut) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
 }
 

@@ -65,6 +65,7 @@ struct Net {
   int num_sms = 148;
   bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
   bool cluster_enabled = true;    // WSI_B200_NO_CLUSTER=1: no CTA pairs / weight multicast in the per-tap kernel
+  bool no_flat_pair = false;      // WSI_B200_NO_FLAT_PAIR=1: the flat kernel stays single-CTA
   bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
   int launches_per_forward = 0;
@@ -331,6 +332,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->flat_enabled = !(nf && nf[0] == '1');
   const char* nc = getenv("WSI_B200_NO_CLUSTER");
   n->cluster_enabled = !(nc && nc[0] == '1');
+  const char* nfp = getenv("WSI_B200_NO_FLAT_PAIR");
+  n->no_flat_pair = nfp && nfp[0] == '1';
   const char* le = getenv("WSI_B200_LEGACY_EPI");
   n->legacy_epi = le && le[0] == '1';
   const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
@@ -687,7 +690,10 @@ int wsi_net_finalize(void* net) {
         if (const char* e = getenv("WSI_FLAT_T")) force_T = atoi(e) == 1 ? 1 : 2;
         if (const char* e = getenv("WSI_FLAT_NOUT")) force_nout = atoi(e);
         if (const char* e = getenv("WSI_FLAT_RESIDENT")) force_res = atoi(e);
-        const bool can_reside = (size_t)9 * f.chunks * f.N * 128 <= 80 * 1024;
+        // CTA pairs: each CTA keeps half of every weight k-block (N/2 rows, a whole number of 8-row swizzle groups)
+        f.cluster = (n->cluster_enabled && !n->no_flat_pair && f.N % 16 == 0) ? 2 : 1;
+        const int nB = f.cluster == 2 ? f.N / 2 : f.N;           // weight rows per CTA
+        const bool can_reside = (size_t)9 * f.chunks * nB * 128 <= 80 * 1024;
         f.tma_epi = (op.Cout % 64 == 0 || (op.Cout % 32 == 0 && !n->legacy_epi)) ? 1 : 0;
         // shared-memory plan {T, resident weights, staging buffers per group}: prefer two M-tiles per slab (less halo
         // re-read) with resident weights; wide images (InceptionV4 stem, 150-pixel rows = 300 halo rows per slab) only
@@ -707,7 +713,7 @@ int wsi_net_finalize(void* net) {
           const int slab_rows = loads * box_rows;
           const int sB = pl[1] ? 9 * f.chunks : 4;
           const int nOut = f.tma_epi ? pl[2] : 0;
-          const long long budget = 224 * 1024 - 2048 - (long long)sB * f.N * 128 - (long long)(T * nOut) * 16384;
+          const long long budget = 224 * 1024 - 2048 - (long long)sB * nB * 128 - (long long)(T * nOut) * 16384;
           int sA = (int)(budget / ((long long)slab_rows * 128));
           if (sA > 4) sA = 4;
           if (sA >= 2 && box_rows <= 256) {
@@ -746,7 +752,7 @@ int wsi_net_finalize(void* net) {
         {
           uint64_t dims[2] = {(uint64_t)op.Ktot, (uint64_t)op.Cout};
           uint64_t strides[1] = {(uint64_t)op.Ktot * 2};
-          uint32_t box[2] = {64, (uint32_t)f.N};
+          uint32_t box[2] = {64, (uint32_t)(f.cluster == 2 ? f.N / 2 : f.N)};
           uint32_t es[2] = {1, 1};
           int rc = wsi_make_tmap(&op.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op.d_w, dims, strides, box, es,
                                  CU_TENSOR_MAP_SWIZZLE_128B);
@@ -847,8 +853,10 @@ int wsi_net_finalize(void* net) {
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<false, 3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem));
   if (max_smem_stem_pool > 0)
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convs::k_conv_stem<true, 7, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_stem_pool));
-  if (max_smem_flat > 0)
-    WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
+  if (max_smem_flat > 0) {
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
+  }
   n->launches_per_forward = 0;
   for (auto& op : n->ops) n->launches_per_forward += op.skip ? 0 : 1;
   n->finalized = true;
@@ -933,8 +941,38 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         f.num_tiles = (int)((f.total_rows + f.T * 128 - 1) / (f.T * 128));
         f.out = to.ptr;
         f.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
+        if (f.cluster == 2) {
+          const long long units = (f.num_tiles + 1) / 2;
+          long long pairs = units < n->num_sms / 2 ? units : n->num_sms / 2;
+          cudaLaunchConfig_t cfg;
+          memset(&cfg, 0, sizeof(cfg));
+          cfg.blockDim = dim3(convf::THREADS);
+          cfg.dynamicSmemBytes = convf::smem_bytes(f);
+          cfg.stream = stream;
+          cudaLaunchAttribute attr[1];
+          attr[0].id = cudaLaunchAttributeClusterDimension;
+          attr[0].val.clusterDim.x = 2;
+          attr[0].val.clusterDim.y = 1;
+          attr[0].val.clusterDim.z = 1;
+          cfg.attrs = attr;
+          cfg.numAttrs = 1;
+          if (op.max_pairs == 0) {
+            // GPCs with an odd SM count cannot host a pair on every SM: size the persistent grid to what is co-resident
+            int nclusters = 0;
+            cfg.gridDim = dim3((unsigned)(n->num_sms / 2 * 2));
+            if (cudaOccupancyMaxActiveClusters(&nclusters, convf::k_conv_flat<2>, &cfg) != cudaSuccess || nclusters <= 0) {
+              cudaGetLastError();
+              nclusters = n->num_sms / 2;
+            }
+            op.max_pairs = nclusters;
+          }
+          if (pairs > op.max_pairs) pairs = op.max_pairs;
+          cfg.gridDim = dim3((unsigned)(2 * pairs));
+          WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convf::k_conv_flat<2>, op.tmA, op.tmB, op.tmO, op.tmO32, f));
+          continue;
+        }
         int grid = f.num_tiles < n->num_sms ? f.num_tiles : n->num_sms;
-        convf::k_conv_flat<<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, f);
+        convf::k_conv_flat<1><<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, f);
         continue;
       }
       convk::Args a = op.ca;
