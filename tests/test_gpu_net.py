@@ -152,13 +152,23 @@ POOL_CASES = [
     (2, 1024, 17, False, 3, 1, 1, None, 0),    # Inception-B
     (5, 1536, 8, False, 3, 1, 1, None, 0),     # Inception-C
     (2, 160, 19, True, 3, 1, 1, None, 0),      # 20 channel vectors (not a power of two), stride 1 max
+    (2, 96, 35, False, 3, 2, 1, None, 0),      # 12 channel vectors -> 4-vector tiles, stride-2 average
+    (1, 24, 13, True, 3, 1, 1, None, 0),       # 3 channel vectors -> 1-vector tiles
+    (2, 64, 150, False, 3, 1, 1, None, 0),     # several column tiles per row
     (2, 32, 20, False, 2, 2, 0, None, 0),      # generic kernel: 2x2 window
     (1, 64, 9, True, 5, 1, 2, None, 0),        # generic kernel: 5x5 window
 ]
 
 
+@pytest.mark.parametrize("tma_ring", [True, False])
 @pytest.mark.parametrize("B,C,H,is_max,k,stride,pad,Ct,c_off", POOL_CASES)
-def test_single_pool_vs_torch(B, C, H, is_max, k, stride, pad, Ct, c_off):
+def test_single_pool_vs_torch(B, C, H, is_max, k, stride, pad, Ct, c_off, tma_ring, monkeypatch):
+    # 3x3 pools run through the TMA-ring kernel by default; WSI_B200_NO_POOL_RING=1 (read at net creation) selects
+    # the direct-load kernel, kept as the fallback for shapes the ring plan rejects
+    if not tma_ring:
+        if k != 3:
+            pytest.skip("the generic kernel has one path")
+        monkeypatch.setenv("WSI_B200_NO_POOL_RING", "1")
     g = torch.Generator().manual_seed(B + C + H + k)
     x = bf16_round(torch.randn((B, C, H, H), generator=g))
     got = run_single_pool(x, is_max, k, stride, pad, count_include_pad=False, out_channels=Ct, c_off=c_off)

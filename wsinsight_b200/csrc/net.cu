@@ -40,6 +40,7 @@ struct Op {
   bool skip = false;              // pool op executed by the stem kernel
   int cin_real = 0;               // input channels that carry a non-zero weight (<= Cin)
   int max_pairs = 0;              // co-resident 2-CTA clusters of the per-tap kernel (queried at first launch)
+  int pt_ct = 0, pt_wt = 0, pt_cols = 0, pt_R = 0;   // 3x3 pool through the TMA ring: tile (channel vectors, output columns), box columns, depth
   CUtensorMap tmA, tmB, tmO, tmR, tmO32;
   __nv_bfloat16* d_w = nullptr;
   float* d_bias = nullptr;
@@ -66,6 +67,7 @@ struct Net {
   bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
   bool cluster_enabled = true;    // WSI_B200_NO_CLUSTER=1: no CTA pairs / weight multicast in the per-tap kernel
   bool no_flat_pair = false;      // WSI_B200_NO_FLAT_PAIR=1: the flat kernel stays single-CTA
+  bool pool_ring = true;          // WSI_B200_NO_POOL_RING=1: 3x3 pools by the register-ring kernel (direct global loads)
   bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
   int launches_per_forward = 0;
@@ -182,10 +184,13 @@ __global__ void __launch_bounds__(256, 6)
     k_pool_sep(const __nv_bfloat16* __restrict__ in, int H, int W, int C, int pad, int count_include_pad, int Ho, int Wo,
                __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp,
                int op, int band, int nbands) {
+  // threads walk the (output column, 16-byte channel vector) plane of a row in flat order: no idle lanes whatever
+  // Wo and C are (the 2-D mapping left 27 % of the threads idle at 35 x 48 vectors), and consecutive threads read
+  // consecutive 16 bytes of the input row
   const int cv = C >> 3;
-  const int c8 = blockIdx.z * blockDim.x + threadIdx.x;
-  const int wo = blockIdx.y * blockDim.y + threadIdx.y;
-  if (c8 >= cv || wo >= Wo) return;
+  const int flat = blockIdx.y * blockDim.x + threadIdx.x;
+  if (flat >= Wo * cv) return;
+  const int wo = flat / cv, c8 = flat - wo * cv;
   const int n = blockIdx.x / nbands, b = blockIdx.x - n * nbands;
   const int ho0 = b * band, ho1 = min(ho0 + band, Ho);
   const int xb = wo * S - pad;
@@ -226,6 +231,92 @@ __global__ void __launch_bounds__(256, 6)
       rcp = 1.0f / (count_include_pad ? (float)(K * K) : (float)(nrows * ncols));
     }
     obase[((size_t)ho * oWp + wo) * ocv] = m.result(rcp);
+  }
+}
+
+// 3x3 pools, input rows staged through shared memory by TMA.  The register-ring kernel above keeps only the loads
+// of one row iteration in flight and two of its three loads per row hit lines a neighbour already requested, so the
+// unique bytes in flight per SM (~24 KB) cover about half of the HBM latency-bandwidth product (2.7-3.0 TB/s
+// measured).  Here a CTA owns a (wt output columns) x (ct 16-byte channel vectors) tile of one image and walks down
+// all its rows; one elected thread streams the matching input box of every row ((wt-1)*S+3 columns x ct vectors,
+// one 3-D TMA box, out-of-bounds columns zero-filled and masked by the window bounds) into an R-deep ring with
+// mbarrier completion: R - 1 rows per CTA are always in flight, tiles span the whole image width where they can
+// (no halo columns re-read), and the threads keep the K-row register ring of the kernel above.
+template <bool IS_MAX, int S>
+__global__ void __launch_bounds__(288)
+    k_pool3_tma(const __grid_constant__ CUtensorMap tmI, int H, int W, int pad, int count_include_pad, int Ho, int Wo,
+                __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int ip, int oHp, int oWp, int op,
+                int ct, int wt, int row_bytes, int row_stride, int R) {
+  constexpr int K = 3;
+  extern __shared__ __align__(128) uint8_t pool_smem[];
+  const uint32_t base = (ptx::smem_u32(pool_smem) + 127u) & ~127u;
+  uint8_t* sm = pool_smem + (base - ptx::smem_u32(pool_smem));
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm);                  // R <= 16 barriers
+  uint8_t* ring = sm + 128;                                          // R rows of row_stride bytes (128-aligned)
+  const int n = blockIdx.x, wo0 = blockIdx.y * wt, c0 = blockIdx.z * ct;
+  const int wl = (int)threadIdx.x / ct, cl = (int)threadIdx.x - wl * ct;
+  const int wo = wo0 + wl;
+  const bool active = wl < wt && wo < Wo;
+  const int x0 = wo0 * S - pad;                                      // image column of box column 0 (may be -1)
+  const int y_begin = max(-pad, 0), y_end = min((Ho - 1) * S - pad + K, H);     // valid input rows [y_begin, y_end)
+  const int nrows = y_end - y_begin;
+  auto issue = [&](int k) {                   // k-th valid row -> ring slot k % R (thread 0 only)
+    const int st = k % R;
+    ptx::mbar_arrive_expect_tx(&full[st], (uint32_t)row_bytes);
+    ptx::tma_load_3d(ring + (size_t)st * row_stride, &tmI, &full[st], c0 * 8, ip + x0, n * iHp + ip + y_begin + k);
+  };
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmI);
+    for (int i = 0; i < R; ++i) ptx::mbar_init(&full[i], 1);
+    ptx::fence_barrier_init();
+    for (int k = 0; k < R && k < nrows; ++k) issue(k);
+  }
+  __syncthreads();
+  const int xb = wo * S - pad;
+  const int ncols = min(xb + K, W) - max(xb, 0);
+  uint4* obase = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + op) * oWp + op) * out_C + out_c_off) + c0 + cl;
+  const int ocv = out_C >> 3;
+  int kk = 0, st = 0;
+  uint32_t par = 0;
+  PoolRow<IS_MAX> h[K];
+  auto hrow = [&](int y, PoolRow<IS_MAX>& r) {     // rows are consumed in increasing y: the next one is ring slot `st`
+    r.clear();
+    if (y < 0 || y >= H) return;
+    ptx::mbar_wait(&full[st], par);
+    const uint4* row = reinterpret_cast<const uint4*>(ring + (size_t)st * row_stride) + (wl * S) * ct + cl;
+    if (active) {
+#pragma unroll
+      for (int dx = 0; dx < K; ++dx) {
+        const int x = xb + dx;
+        if (x >= 0 && x < W) r.add(row[dx * ct]);
+      }
+    }
+    __syncthreads();                               // slot read by everyone: refill it with row kk + R
+    if (threadIdx.x == 0 && kk + R < nrows) issue(kk + R);
+    ++kk;
+    if (++st == R) { st = 0; par ^= 1; }
+  };
+  constexpr int KEEP = K - S;
+  {
+    const int yb = -pad;
+#pragma unroll
+    for (int i = 0; i < KEEP; ++i) hrow(yb + i, h[i + S]);
+  }
+  for (int ho = 0; ho < Ho; ++ho) {
+    const int yb = ho * S - pad;
+#pragma unroll
+    for (int i = 0; i < KEEP; ++i) h[i] = h[i + S];
+#pragma unroll
+    for (int i = KEEP; i < K; ++i) hrow(yb + i, h[i]);
+    PoolRow<IS_MAX> m = h[0];
+#pragma unroll
+    for (int i = 1; i < K; ++i) m.merge(h[i]);
+    float rcp = 1.f;
+    if (!IS_MAX) {
+      const int nr = min(yb + K, H) - max(yb, 0);
+      rcp = 1.0f / (count_include_pad ? (float)(K * K) : (float)(nr * ncols));
+    }
+    if (active) obase[((size_t)ho * oWp + wo) * ocv] = m.result(rcp);
   }
 }
 
@@ -334,6 +425,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->cluster_enabled = !(nc && nc[0] == '1');
   const char* nfp = getenv("WSI_B200_NO_FLAT_PAIR");
   n->no_flat_pair = nfp && nfp[0] == '1';
+  const char* npr = getenv("WSI_B200_NO_POOL_RING");
+  n->pool_ring = !(npr && npr[0] == '1');
   const char* le = getenv("WSI_B200_LEGACY_EPI");
   n->legacy_epi = le && le[0] == '1';
   const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
@@ -504,6 +597,17 @@ int wsi_net_add_head(void* net, int in_id, const float* fc_w, const float* fc_b,
   op.flops_per_image = 2.0 * K * ti.C;
   n->ops.push_back(std::move(op));
   return WSI_OK;
+}
+
+// input tensor map of the TMA-ring pool kernel: (C, Wp, B*Hp) bf16, box = (ct vectors, box columns, one row)
+static int encode_pool_map(Net* n, Op& op, const void* base) {
+  const Tensor& ti = n->tensors[op.in];
+  uint64_t dims[3] = {(uint64_t)ti.C, (uint64_t)ti.Wp(), (uint64_t)n->max_batch * ti.Hp()};
+  uint64_t strides[2] = {(uint64_t)ti.C * 2, (uint64_t)ti.Wp() * ti.C * 2};
+  uint32_t box[3] = {(uint32_t)op.pt_ct * 8, (uint32_t)op.pt_cols, 1};
+  uint32_t es[3] = {1, 1, 1};
+  return wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, strides, box, es,
+                       CU_TENSOR_MAP_SWIZZLE_NONE);
 }
 
 int wsi_net_finalize(void* net) {
@@ -836,6 +940,34 @@ int wsi_net_finalize(void* net) {
         int rc = wsi_net_encode_input_map(net, (int)(&op - &n->ops[0]), ti.ptr);
         if (rc) return rc;
       }
+    } else if ((op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) && !op.skip) {
+      // 3x3 pools over internal tensors: tile plan + input tensor map of the TMA-ring kernel
+      const Tensor& ti = n->tensors[op.in];
+      const Tensor& to = n->tensors[op.out];
+      const int cv = ti.C / 8;
+      op.pt_ct = 0;
+      if (op.pk == 3 && (op.pstride == 1 || op.pstride == 2) && ti.C % 8 == 0) {
+        int ct = 0, wt = 0;
+        for (int c : {32, 16, 8})                       // whole image width per CTA when <= 288 slots
+          if (cv % c == 0 && c * to.W <= 288 && c * to.W > ct * wt) { ct = c; wt = to.W; }
+        if (!ct) {
+          ct = cv % 8 == 0 ? 8 : (cv % 4 == 0 ? 4 : (cv % 2 == 0 ? 2 : 1));
+          const int per = 288 / ct;
+          const int ntiles = (to.W + per - 1) / per;
+          wt = (to.W + ntiles - 1) / ntiles;
+        }
+        const int cols = (wt - 1) * op.pstride + 3;
+        const int row_stride = (cols * ct * 16 + 127) / 128 * 128;
+        int R = (40 * 1024) / row_stride;
+        if (R > 12) R = 12;
+        if (cols <= 256 && R >= 3) {
+          op.pt_ct = ct; op.pt_wt = wt; op.pt_cols = cols; op.pt_R = R;
+          if (!ti.external) {                           // an external input is mapped at every forward
+            int rc = encode_pool_map(n, op, ti.ptr);
+            if (rc) return rc;
+          }
+        }
+      }
     } else if (op.kind == OP_HEAD) {
       WSI_CUDA_CHECK(cudaMalloc(&op.d_fcw, op.h_fcw.size() * sizeof(float)));
       WSI_CUDA_CHECK(cudaMemcpy(op.d_fcw, op.h_fcw.data(), op.h_fcw.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -857,6 +989,10 @@ int wsi_net_finalize(void* net) {
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
   }
+  WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   n->launches_per_forward = 0;
   for (auto& op : n->ops) n->launches_per_forward += op.skip ? 0 : 1;
   n->finalized = true;
@@ -1023,13 +1159,30 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       const int cv = ti.C / 8;
       const bool is_max = op.kind == OP_MAXPOOL;
       if (op.pk == 3 && (op.pstride == 1 || op.pstride == 2)) {
-        int bx = 32;
-        while (cv % bx) bx >>= 1;
-        int by = 256 / bx;
-        if (by > to.W) by = to.W;
-        const int band = to.H > 24 ? 16 : to.H;
-        const int nbands = (to.H + band - 1) / band;
-        dim3 block(bx, by), grid(B * nbands, (to.W + by - 1) / by, cv / bx);
+        if (n->pool_ring && op.pt_ct > 0) {
+          if (ti.external) {
+            int rc = encode_pool_map(n, op, in_ptr);
+            if (rc) return rc;
+          }
+          const int row_bytes = op.pt_cols * op.pt_ct * 16, row_stride = (row_bytes + 127) / 128 * 128;
+          const size_t smem = 256 + (size_t)op.pt_R * row_stride;
+          dim3 grid(B, (to.W + op.pt_wt - 1) / op.pt_wt, cv / op.pt_ct);
+          const int threads = (op.pt_wt * op.pt_ct + 31) / 32 * 32;
+#define WSI_POOL_TMA(MAX, S)                                                                                             \
+  k_pool3_tma<MAX, S><<<grid, threads, smem, stream>>>(op.tmA, ti.H, ti.W, op.ppad, op.count_include_pad, to.H, to.W,    \
+                                                       to.ptr, to.C, op.out_c_off, ti.Hp(), ti.pad, to.Hp(), to.Wp(),    \
+                                                       to.pad, op.pt_ct, op.pt_wt, row_bytes, row_stride, op.pt_R)
+          if (is_max) {
+            if (op.pstride == 1) WSI_POOL_TMA(true, 1); else WSI_POOL_TMA(true, 2);
+          } else {
+            if (op.pstride == 1) WSI_POOL_TMA(false, 1); else WSI_POOL_TMA(false, 2);
+          }
+#undef WSI_POOL_TMA
+          continue;
+        }
+        const int nbands = to.H > 24 ? (to.H + 15) / 16 : 1;     // <= 16 output rows per CTA, bands of equal height
+        const int band = (to.H + nbands - 1) / nbands;
+        dim3 block(256), grid(B * nbands, (to.W * cv + 255) / 256);
 #define WSI_POOL_SEP(MAX, S)                                                                                              \
   k_pool_sep<MAX, 3, S><<<grid, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.ppad, op.count_include_pad, to.H, to.W, \
                                                     to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(),       \
