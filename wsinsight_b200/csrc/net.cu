@@ -40,7 +40,7 @@ struct Op {
   bool skip = false;              // pool op executed by the stem kernel
   int cin_real = 0;               // input channels that carry a non-zero weight (<= Cin)
   int max_pairs = 0;              // co-resident 2-CTA clusters of the per-tap kernel (queried at first launch)
-  int pt_ct = 0, pt_wt = 0, pt_cols = 0, pt_R = 0;   // 3x3 pool through the TMA ring: tile (channel vectors, output columns), box columns, depth
+  int pt_ct = 0, pt_wt = 0, pt_cols = 0, pt_R = 0, pt_per = 1;   // 3x3 pool through the TMA ring: tile (channel vectors, output columns), box columns, depth
   CUtensorMap tmA, tmB, tmO, tmR, tmO32;
   __nv_bfloat16* d_w = nullptr;
   float* d_bias = nullptr;
@@ -154,6 +154,8 @@ struct PoolRow<true> {
     v.x = hmax2_bf16(v.x, x.x); v.y = hmax2_bf16(v.y, x.y); v.z = hmax2_bf16(v.z, x.z); v.w = hmax2_bf16(v.w, x.w);
   }
   __device__ __forceinline__ void merge(const PoolRow& o) { add(o.v); }
+  __device__ __forceinline__ void set(const uint4& x) { v = x; }
+  static __device__ __forceinline__ uint4 neutral() { return make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u); }
   __device__ __forceinline__ uint4 result(float) const { return v; }
 };
 template <>
@@ -171,6 +173,11 @@ struct PoolRow<false> {
 #pragma unroll
     for (int i = 0; i < 8; ++i) f[i] += o.f[i];
   }
+  __device__ __forceinline__ void set(const uint4& x) {
+    f[0] = bflo(x.x); f[1] = bfhi(x.x); f[2] = bflo(x.y); f[3] = bfhi(x.y);
+    f[4] = bflo(x.z); f[5] = bfhi(x.z); f[6] = bflo(x.w); f[7] = bfhi(x.w);
+  }
+  static __device__ __forceinline__ uint4 neutral() { return make_uint4(0u, 0u, 0u, 0u); }
   // one reciprocal per output instead of eight IEEE divisions (ncu: the divisions made the kernel issue-bound,
   // 76 % issue-slot utilisation at 1.6 TB/s); <= 1 ulp of fp32 before the bf16 rounding
   __device__ __forceinline__ uint4 result(float rcp) const {
@@ -317,6 +324,110 @@ __global__ void __launch_bounds__(288)
       rcp = 1.0f / (count_include_pad ? (float)(K * K) : (float)(nr * ncols));
     }
     if (active) obase[((size_t)ho * oWp + wo) * ocv] = m.result(rcp);
+  }
+}
+
+// Stride-1 3x3 pools (every Inception average pool): the kernel above is ISSUE-bound there (ncu: 90 % issue-slot
+// utilisation at 4.1 TB/s, ~220 instructions per output vector: three loads + unpacks per output, register-ring
+// moves, one IEEE division).  Same TMA ring, but a thread owns TWO adjacent output columns (four input columns per
+// row, the middle pair summed once), the three-row ring is addressed statically (row loop unrolled by 3, no moves)
+// and the 1/count factors come from a three-entry per-thread table.
+template <bool IS_MAX>
+__global__ void __launch_bounds__(288, 2)
+    k_pool3s1_tma(const __grid_constant__ CUtensorMap tmI, int H, int W, int pad, int count_include_pad, int Ho, int Wo,
+                  __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int ip, int oHp, int oWp, int op,
+                  int ct, int wt, int row_bytes, int row_stride, int R) {
+  constexpr int K = 3;
+  extern __shared__ __align__(128) uint8_t pool_smem[];
+  const uint32_t base = (ptx::smem_u32(pool_smem) + 127u) & ~127u;
+  uint8_t* sm = pool_smem + (base - ptx::smem_u32(pool_smem));
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm);
+  uint8_t* ring = sm + 128;
+  const int n = blockIdx.x, wo0 = blockIdx.y * wt, c0 = blockIdx.z * ct;
+  const int wl = (int)threadIdx.x / ct, cl = (int)threadIdx.x - wl * ct;       // wl: PAIR of output columns
+  const int wo_end = min(wo0 + wt, Wo);
+  const int wa = wo0 + 2 * wl;                                                 // first output column of the thread
+  const bool act_a = wa < wo_end, act_b = wa + 1 < wo_end;
+  const int x0 = wo0 - pad;                                                    // image column of box column 0
+  const int y_begin = max(-pad, 0), y_end = min(Ho - 1 - pad + K, H);
+  const int nrows = y_end - y_begin;
+  auto issue = [&](int k) {
+    const int st = k % R;
+    ptx::mbar_arrive_expect_tx(&full[st], (uint32_t)row_bytes);
+    ptx::tma_load_3d(ring + (size_t)st * row_stride, &tmI, &full[st], c0 * 8, ip + x0, n * iHp + ip + y_begin + k);
+  };
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmI);
+    for (int i = 0; i < R; ++i) ptx::mbar_init(&full[i], 1);
+    ptx::fence_barrier_init();
+    for (int k = 0; k < R && k < nrows; ++k) issue(k);
+  }
+  __syncthreads();
+  const int xa = wa - pad;                                                     // leftmost input column of output a
+  bool okc[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) okc[i] = act_a && xa + i >= 0 && xa + i < W;
+  float rcp_a[4], rcp_b[4];                                                    // index = valid rows of the window
+  {
+    const int nca = min(xa + K, W) - max(xa, 0), ncb = min(xa + 1 + K, W) - max(xa + 1, 0);
+#pragma unroll
+    for (int r = 1; r <= 3; ++r) {
+      rcp_a[r] = 1.0f / (count_include_pad ? 9.0f : (float)(r * max(nca, 1)));
+      rcp_b[r] = 1.0f / (count_include_pad ? 9.0f : (float)(r * max(ncb, 1)));
+    }
+    rcp_a[0] = rcp_b[0] = 0.f;
+  }
+  uint4* obase = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + op) * oWp + op) * out_C + out_c_off) + c0 + cl;
+  const int ocv = out_C >> 3;
+  int kk = 0, st = 0;
+  uint32_t par = 0;
+  PoolRow<IS_MAX> ha[K], hb[K];
+  // horizontal pass of input row y for both outputs: a = c0+c1+c2, b = c1+c2+c3 (masked columns are neutral)
+  auto hrow = [&](int y, PoolRow<IS_MAX>& ra, PoolRow<IS_MAX>& rb) {
+    ra.clear();
+    rb.clear();
+    if (y < 0 || y >= H) return;
+    ptx::mbar_wait(&full[st], par);
+    const uint4* row = reinterpret_cast<const uint4*>(ring + (size_t)st * row_stride) + (2 * wl) * ct + cl;
+    if (act_a) {
+      const uint4 nt = PoolRow<IS_MAX>::neutral();
+      const uint4 v0 = okc[0] ? row[0] : nt, v1 = okc[1] ? row[1 * ct] : nt;
+      const uint4 v2 = okc[2] ? row[2 * ct] : nt, v3 = okc[3] ? row[3 * ct] : nt;
+      PoolRow<IS_MAX> mid;
+      mid.set(v1);
+      mid.add(v2);
+      ra.set(v0);
+      ra.merge(mid);
+      rb.set(v3);
+      rb.merge(mid);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && kk + R < nrows) issue(kk + R);
+    ++kk;
+    if (++st == R) { st = 0; par ^= 1; }
+  };
+  hrow(-pad + 0, ha[0], hb[0]);
+  hrow(-pad + 1, ha[1], hb[1]);
+  for (int hb0 = 0; hb0 < Ho; hb0 += 3) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int ho = hb0 + j;
+      if (ho < Ho) {                                      // uniform across the CTA
+        const int yb = ho - pad;
+        hrow(yb + 2, ha[(j + 2) % 3], hb[(j + 2) % 3]);   // input row ho + 2 (relative) lives in ring slot (ho + 2) % 3
+        PoolRow<IS_MAX> ma = ha[j % 3], mb = hb[j % 3];
+        ma.merge(ha[(j + 1) % 3]);
+        ma.merge(ha[(j + 2) % 3]);
+        mb.merge(hb[(j + 1) % 3]);
+        mb.merge(hb[(j + 2) % 3]);
+        const int nr = min(yb + K, H) - max(yb, 0);
+        const float fa = nr >= 3 ? rcp_a[3] : (nr == 2 ? rcp_a[2] : rcp_a[1]);
+        const float fb = nr >= 3 ? rcp_b[3] : (nr == 2 ? rcp_b[2] : rcp_b[1]);
+        uint4* o = obase + ((size_t)ho * oWp + wa) * ocv;
+        if (act_a) o[0] = ma.result(fa);
+        if (act_b) o[ocv] = mb.result(fb);
+      }
+    }
   }
 }
 
@@ -947,21 +1058,25 @@ int wsi_net_finalize(void* net) {
       const int cv = ti.C / 8;
       op.pt_ct = 0;
       if (op.pk == 3 && (op.pstride == 1 || op.pstride == 2) && ti.C % 8 == 0) {
+        // stride 1: a thread owns two adjacent output columns (k_pool3s1_tma), so a slot is a column PAIR
+        const int per = op.pstride == 1 ? 2 : 1;
+        const int units_w = (to.W + per - 1) / per;
         int ct = 0, wt = 0;
         for (int c : {32, 16, 8})                       // whole image width per CTA when <= 288 slots
-          if (cv % c == 0 && c * to.W <= 288 && c * to.W > ct * wt) { ct = c; wt = to.W; }
+          if (cv % c == 0 && c * units_w <= 288 && c * units_w > ct * ((wt + per - 1) / per)) { ct = c; wt = to.W; }
         if (!ct) {
           ct = cv % 8 == 0 ? 8 : (cv % 4 == 0 ? 4 : (cv % 2 == 0 ? 2 : 1));
-          const int per = 288 / ct;
-          const int ntiles = (to.W + per - 1) / per;
+          const int cap = 288 / ct * per;               // output columns per CTA
+          const int ntiles = (to.W + cap - 1) / cap;
           wt = (to.W + ntiles - 1) / ntiles;
+          wt = (wt + per - 1) / per * per;
         }
-        const int cols = (wt - 1) * op.pstride + 3;
+        const int cols = per == 2 ? (wt + 1) / 2 * 2 + 2 : (wt - 1) * op.pstride + 3;
         const int row_stride = (cols * ct * 16 + 127) / 128 * 128;
         int R = (40 * 1024) / row_stride;
         if (R > 12) R = 12;
         if (cols <= 256 && R >= 3) {
-          op.pt_ct = ct; op.pt_wt = wt; op.pt_cols = cols; op.pt_R = R;
+          op.pt_ct = ct; op.pt_wt = wt; op.pt_cols = cols; op.pt_R = R; op.pt_per = per;
           if (!ti.external) {                           // an external input is mapped at every forward
             int rc = encode_pool_map(n, op, ti.ptr);
             if (rc) return rc;
@@ -989,6 +1104,8 @@ int wsi_net_finalize(void* net) {
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
   }
+  WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3s1_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3s1_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
@@ -1167,7 +1284,20 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
           const int row_bytes = op.pt_cols * op.pt_ct * 16, row_stride = (row_bytes + 127) / 128 * 128;
           const size_t smem = 256 + (size_t)op.pt_R * row_stride;
           dim3 grid(B, (to.W + op.pt_wt - 1) / op.pt_wt, cv / op.pt_ct);
-          const int threads = (op.pt_wt * op.pt_ct + 31) / 32 * 32;
+          const int threads = ((op.pt_wt + op.pt_per - 1) / op.pt_per * op.pt_ct + 31) / 32 * 32;
+          if (op.pt_per == 2) {
+            if (is_max)
+              k_pool3s1_tma<true><<<grid, threads, smem, stream>>>(op.tmA, ti.H, ti.W, op.ppad, op.count_include_pad, to.H,
+                                                                   to.W, to.ptr, to.C, op.out_c_off, ti.Hp(), ti.pad,
+                                                                   to.Hp(), to.Wp(), to.pad, op.pt_ct, op.pt_wt, row_bytes,
+                                                                   row_stride, op.pt_R);
+            else
+              k_pool3s1_tma<false><<<grid, threads, smem, stream>>>(op.tmA, ti.H, ti.W, op.ppad, op.count_include_pad, to.H,
+                                                                    to.W, to.ptr, to.C, op.out_c_off, ti.Hp(), ti.pad,
+                                                                    to.Hp(), to.Wp(), to.pad, op.pt_ct, op.pt_wt, row_bytes,
+                                                                    row_stride, op.pt_R);
+            continue;
+          }
 #define WSI_POOL_TMA(MAX, S)                                                                                             \
   k_pool3_tma<MAX, S><<<grid, threads, smem, stream>>>(op.tmA, ti.H, ti.W, op.ppad, op.count_include_pad, to.H, to.W,    \
                                                        to.ptr, to.C, op.out_c_off, ti.Hp(), ti.pad, to.Hp(), to.Wp(),    \
