@@ -127,6 +127,12 @@ int wsi_net_add_tensor(void* net, int H, int W, int C, int external, int* id_out
 int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const float* h_w_oihw,
                      const float* h_bias, int Cin, int Cout, int KH, int KW, int stride, int pad_h,
                      int pad_w, int relu, int residual_id);
+/* Same, reading input channels [in_c_off, in_c_off + Cin) of a wider internal tensor: the engine merges sibling 1x1
+ * convolutions of an Inception block (same input: `torch.cat` branches of the TorchScript graph the reference runs,
+ * run_inference.py:541) into one launch writing one tensor, and the branch convolutions that follow read slices. */
+int wsi_net_add_conv_slice(void* net, int in_id, int in_c_off, int out_id, int out_c_off, const float* h_w_oihw,
+                           const float* h_bias, int Cin, int Cout, int KH, int KW, int stride, int pad_h, int pad_w,
+                           int relu, int residual_id);
 int wsi_net_add_stem7x7(void* net, int in_id, int out_id, const float* h_w_oihw,
                         const float* h_bias, int Cout, int relu);
 /* Generalisation: ksize 7 / pad 3 (ResNet) or ksize 3 / pad 0 (InceptionV4 conv2d_1a; input tensor [S'][S'][4] with

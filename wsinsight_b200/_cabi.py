@@ -54,6 +54,8 @@ _PROTOS = {
     "wsi_net_add_tensor": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int_p]),
     "wsi_net_add_conv": (c_int, [c_void_p, c_int, c_int, c_int, c_float_p, c_float_p, c_int, c_int, c_int,
                                  c_int, c_int, c_int, c_int, c_int, c_int]),
+    "wsi_net_add_conv_slice": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_float_p, c_float_p, c_int, c_int, c_int,
+                                       c_int, c_int, c_int, c_int, c_int, c_int]),
     "wsi_net_add_stem7x7": (c_int, [c_void_p, c_int, c_int, c_float_p, c_float_p, c_int, c_int]),
     "wsi_net_add_stem_parity": (c_int, [c_void_p, c_int, c_int, c_float_p, c_float_p, c_int, c_int, c_int, c_int]),
     "wsi_net_add_pool": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int]),

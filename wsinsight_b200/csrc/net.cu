@@ -47,6 +47,7 @@ struct Op {
   std::vector<__nv_bfloat16> h_w;
   std::vector<float> h_bias;
   int Cin, Cout, KH, KW, stride, pad_h, pad_w, relu, out_c_off, is_stem;
+  int in_c_off = 0;               // first input channel read (slice of a wider tensor)
   int Ktot;
   // pool
   int pk, pstride, ppad, count_include_pad;
@@ -561,13 +562,25 @@ int wsi_net_add_tensor(void* net, int H, int W, int C, int external, int* id_out
 int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const float* w_oihw, const float* bias,
                      int Cin, int Cout, int KH, int KW, int stride, int pad_h, int pad_w, int relu,
                      int residual_id) {
+  return wsi_net_add_conv_slice(net, in_id, 0, out_id, out_c_off, w_oihw, bias, Cin, Cout, KH, KW, stride, pad_h, pad_w,
+                                relu, residual_id);
+}
+
+// Convolution over channels [in_c_off, in_c_off + Cin) of the input tensor (sibling 1x1 convs merged into one launch
+// write one wide tensor; their consumers read slices of it).  The A-operand tensor maps start at the slice and
+// declare Cin channels, so TMA's zero fill past the slice works as for a whole tensor.
+int wsi_net_add_conv_slice(void* net, int in_id, int in_c_off, int out_id, int out_c_off, const float* w_oihw,
+                           const float* bias, int Cin, int Cout, int KH, int KW, int stride, int pad_h, int pad_w,
+                           int relu, int residual_id) {
   Net* n = (Net*)net;
   WSI_ARG_CHECK(n && !n->finalized && w_oihw, "wsi_net_add_conv: bad state");
   WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size() && out_id >= 0 && out_id < (int)n->tensors.size(),
                 "wsi_net_add_conv: bad tensor id");
   const Tensor& ti = n->tensors[in_id];
   const Tensor& to = n->tensors[out_id];
-  WSI_ARG_CHECK(ti.C == Cin, "wsi_net_add_conv: Cin %d != tensor C %d", Cin, ti.C);
+  WSI_ARG_CHECK(in_c_off >= 0 && in_c_off % 8 == 0 && in_c_off + Cin <= ti.C && (in_c_off == 0 || !ti.external),
+                "wsi_net_add_conv: channels [%d, %d) outside tensor C %d", in_c_off, in_c_off + Cin, ti.C);
+  WSI_ARG_CHECK(ti.C == Cin || !ti.external, "wsi_net_add_conv: Cin %d != external tensor C %d", Cin, ti.C);
   WSI_ARG_CHECK(Cin % 8 == 0, "wsi_net_add_conv: Cin must be a multiple of 8 (got %d)", Cin);
   const int Ho = (ti.H + 2 * pad_h - KH) / stride + 1, Wo = (ti.W + 2 * pad_w - KW) / stride + 1;
   WSI_ARG_CHECK(Ho == to.H && Wo == to.W, "wsi_net_add_conv: output shape %dx%d != tensor %dx%d", Ho, Wo, to.H,
@@ -585,7 +598,7 @@ int wsi_net_add_conv(void* net, int in_id, int out_id, int out_c_off, const floa
   op.kind = OP_CONV;
   op.in = in_id; op.out = out_id; op.res = residual_id;
   op.Cin = Cin; op.Cout = Cout; op.KH = KH; op.KW = KW; op.stride = stride; op.pad_h = pad_h; op.pad_w = pad_w;
-  op.relu = relu; op.out_c_off = out_c_off; op.is_stem = 0;
+  op.relu = relu; op.out_c_off = out_c_off; op.is_stem = 0; op.in_c_off = in_c_off;
   const int chunks = (Cin + 63) / 64;
   op.Ktot = KH * KW * chunks * 64;
   op.h_w.assign((size_t)Cout * op.Ktot, __float2bfloat16(0.f));
@@ -747,7 +760,7 @@ int wsi_net_finalize(void* net) {
     if (op.kind != OP_CONV || op.is_stem || !n->flat_enabled) continue;
     const Tensor& ti = n->tensors[op.in];
     bool ok = op.KH == 3 && op.KW == 3 && op.stride == 1 && op.pad_h == op.pad_w && (op.pad_h == 0 || op.pad_h == 1) &&
-              op.Cin % 8 == 0 && ti.C == op.Cin && op.Cout % 32 == 0 && op.Cout <= 128 && !ti.external && ti.W >= 24 &&
+              op.Cin % 8 == 0 && op.Cout % 32 == 0 && op.Cout <= 128 && !ti.external && ti.W >= 24 &&
               ti.H >= 8;
     if (op.pad_h == 0 && getenv("WSI_B200_NO_FLAT_VALID")) ok = false;
     if (op.res >= 0 && (n->tensors[op.res].C != op.Cout || n->tensors[op.res].external)) ok = false;
@@ -974,11 +987,11 @@ int wsi_net_finalize(void* net) {
           if (rc) return rc;
         }
         {
-          uint64_t dims[2] = {(uint64_t)ti.C, (uint64_t)B * ti.Hp() * ti.Wp()};
+          uint64_t dims[2] = {(uint64_t)op.Cin, (uint64_t)B * ti.Hp() * ti.Wp()};
           uint64_t strides[1] = {(uint64_t)ti.C * 2};
           uint32_t box[2] = {64, (uint32_t)f.slab_box_rows};
           uint32_t es[2] = {1, 1};
-          int rc = wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ti.ptr, dims, strides, box, es,
+          int rc = wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ti.ptr + op.in_c_off, dims, strides, box, es,
                                  CU_TENSOR_MAP_SWIZZLE_128B);
           if (rc) return rc;
         }
@@ -1138,8 +1151,8 @@ int wsi_net_encode_input_map(void* net, int op_index, const void* base) {
   }
   // a padded tensor is addressed from its interior pixel (0,0) with the padded pitches; TMA's
   // out-of-bounds zero fill then stands in for the border exactly as for a dense tensor
-  base = (const __nv_bfloat16*)base + ti.interior_offset();
-  uint64_t dims[4] = {(uint64_t)ti.C, (uint64_t)ti.W, (uint64_t)ti.H, B};
+  base = (const __nv_bfloat16*)base + ti.interior_offset() + op.in_c_off;
+  uint64_t dims[4] = {(uint64_t)op.Cin, (uint64_t)ti.W, (uint64_t)ti.H, B};
   uint64_t strides[3] = {(uint64_t)ti.C * 2, (uint64_t)ti.Wp() * ti.C * 2, (uint64_t)ti.Hp() * ti.Wp() * ti.C * 2};
   uint32_t box[4] = {64, (uint32_t)(a.bw * a.stride), (uint32_t)(a.bh * a.stride), (uint32_t)a.bn};
   uint32_t es[4] = {1, (uint32_t)a.stride, (uint32_t)a.stride, 1};
