@@ -130,6 +130,42 @@ __device__ __forceinline__ void epi_chunk64_regs(uint32_t t_addr, int row, uint3
   }
 }
 
+// Same, with the residual tile already IN the staging buffer (TMA-loaded in the swizzled layout the output uses):
+// every thread reads its own 8 x 16 B, adds, and writes the result back to the same addresses.  A thread's row is a
+// TMEM lane, so residual loads from global memory touch 32 different 128-byte lines per warp instruction; through
+// TMA + conflict-free LDS the same bytes cost 1/8 of the L1/shared wavefronts (layer1 of ResNet34: 0.30 -> see
+// DESIGN.md 4.1).
+__device__ __forceinline__ void epi_chunk64_smemres(uint32_t t_addr, int row, uint32_t s_buf, const float* s_bias,
+                                                    int relu, bool keep = true) {
+  uint32_t r[64];
+  ptx::tmem_ld_32x32b_x32(t_addr, r);
+  ptx::tmem_ld_32x32b_x32(t_addr + 32u, r + 32);
+  const uint32_t row_base = s_buf + (uint32_t)row * 128u;
+  const uint32_t sw = (uint32_t)row & 7u;
+  uint4 rv[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) rv[c] = ptx::ld_shared_v4(row_base + (((uint32_t)c ^ sw) << 4));
+  ptx::tmem_ld_wait();
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
+    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
+    float v0 = __uint_as_float(r[8 * c + 0]) + b0.x, v1 = __uint_as_float(r[8 * c + 1]) + b0.y;
+    float v2 = __uint_as_float(r[8 * c + 2]) + b0.z, v3 = __uint_as_float(r[8 * c + 3]) + b0.w;
+    float v4 = __uint_as_float(r[8 * c + 4]) + b1.x, v5 = __uint_as_float(r[8 * c + 5]) + b1.y;
+    float v6 = __uint_as_float(r[8 * c + 6]) + b1.z, v7 = __uint_as_float(r[8 * c + 7]) + b1.w;
+    v0 += bf16_lo(rv[c].x); v1 += bf16_hi(rv[c].x); v2 += bf16_lo(rv[c].y); v3 += bf16_hi(rv[c].y);
+    v4 += bf16_lo(rv[c].z); v5 += bf16_hi(rv[c].z); v6 += bf16_lo(rv[c].w); v7 += bf16_hi(rv[c].w);
+    if (relu) {
+      v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
+      v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
+    }
+    uint32_t o0 = pack_bf16(v0, v1), o1 = pack_bf16(v2, v3), o2 = pack_bf16(v4, v5), o3 = pack_bf16(v6, v7);
+    if (!keep) o0 = o1 = o2 = o3 = 0u;   // border rows of the padded flat layout stay zero
+    ptx::st_shared_v4(row_base + (((uint32_t)c ^ sw) << 4), o0, o1, o2, o3);
+  }
+}
+
 // 32-column tail chunk (N_tile = 64a + 32: Cout 32, 96, 160, 224, 448 of the Inception family): the same
 // epilogue staged as [128 rows][32 ch] = 64-byte rows in the SWIZZLE_64B layout of a {32 ch} TMA store box
 // (16-byte chunk c of row r at r*64 + ((c ^ ((r >> 1) & 3)) << 4); conflict-free for a quarter warp).

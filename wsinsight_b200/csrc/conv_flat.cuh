@@ -45,6 +45,7 @@ struct Args {
   int relu, has_res;
   int out_C, out_c_off;         // channels of the destination tensor / concat offset
   int tma_epi;                  // N % 64 == 0: epilogue staged in smem and written by TMA stores
+  int res_smem;                 // residual tiles are TMA-loaded into the output staging buffers (needs nOut == 2)
   int nOut, nRes;               // output staging buffers (16 KB each) PER epilogue group; nRes unused (residual
                                 // chunks are prefetched from global memory into registers one chunk ahead)
   const __nv_bfloat16* residual;
@@ -156,7 +157,8 @@ __device__ __forceinline__ void mma_loop(const MmaCtx& m) {
 template <int CL>
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_flat(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32, const Args a) {
+                const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32,
+                const __grid_constant__ CUtensorMap tmapR, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   uint64_t* tfull = bEmpty + a.stagesB;
   uint64_t* tempty = tfull + 2;
   uint64_t* resFull = tempty + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resFull + 2);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resFull + 4);     // resFull[group * 2 + buffer]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int TM = a.T * 128;
@@ -202,6 +204,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       ptx::mbar_init(&tfull[s], 1);
       ptx::mbar_init(&tempty[s], (uint32_t)((a.tma_epi ? 4 * a.T : 4) * CL));
       ptx::mbar_init(&resFull[s], 1);
+      ptx::mbar_init(&resFull[2 + s], 1);
     }
     ptx::fence_barrier_init();
   }
@@ -336,6 +339,72 @@ __global__ void __launch_bounds__(THREADS, 1)
       if (g < a.T) {
         uint8_t* myOut = sOut + (size_t)g * a.nOut * 16384;
         int k = 0;
+        if (a.res_smem) {
+          // Residual through shared memory: the group leader TMA-loads the residual tile of chunk k + 1 into the OTHER
+          // staging buffer (after the store issued from it has finished reading), every thread adds its own row in
+          // place, and the same buffer is then TMA-stored as the output.
+          uint64_t* rf = resFull + g * 2;
+          if (leader && first_unit < num_units) {
+            ptx::mbar_arrive_expect_tx(&rf[0], 16384u);
+            ptx::tma_load_2d(myOut, &tmapR, &rf[0], 0, (int)((long long)tile_of(first_unit) * TM + g * 128));
+          }
+          for (int u = first_unit; u < num_units; u += unit_step) {
+            const long long q0 = (long long)tile_of(u) * TM + g * 128;
+            const long long p = q0 + row;
+            const int n = (int)(p / img);
+            const int rem = (int)(p - (long long)n * img);
+            const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
+            const bool valid = (n < a.B) && (hp >= a.pad) && (hp < a.pad + a.H) && (wp >= a.pad) && (wp < a.pad + a.W);
+            const int un = u + unit_step;
+            const long long q0n = un < num_units ? (long long)tile_of(un) * TM + g * 128 : -1;
+            ptx::mbar_wait(&tfull[acc], pacc);
+            ptx::tc_fence_after();
+            for (int j = 0; j < cn_full; ++j, ++k) {
+              const bool last = j == cn_full - 1;
+              const int ob = k & 1;
+              if (leader && (!last || q0n >= 0)) {
+                ptx::bulk_wait_read<0>();               // the store issued from the other buffer has read it
+                ptx::mbar_arrive_expect_tx(&rf[ob ^ 1], 16384u);
+                ptx::tma_load_2d(myOut + (size_t)(ob ^ 1) * 16384, &tmapR, &rf[ob ^ 1], last ? 0 : 64 * (j + 1),
+                                 (int)(last ? q0n : q0));
+              }
+              ptx::mbar_wait(&rf[ob], (uint32_t)((k >> 1) & 1));
+              const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * a.T + g) * a.N + 64 * j);
+              convk::epi_chunk64_smemres(t_addr, row, ptx::smem_u32(myOut + (size_t)ob * 16384), sBias + 64 * j, a.relu,
+                                         valid);
+              if (last) {
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                  if (CL == 2) ptx::mbar_arrive_cluster(&tempty[acc], 0u); else ptx::mbar_arrive(&tempty[acc]);
+                }
+              }
+              ptx::fence_proxy_async();
+              ptx::named_bar_sync(1 + g, 128);          // chunk staged
+              if (leader) {
+                ptx::tma_store_2d(&tmapO, myOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)q0);
+                ptx::bulk_commit();
+              }
+            }
+            if (++acc == 2) { acc = 0; pacc ^= 1; }
+          }
+          if (leader) ptx::bulk_wait<0>();
+        } else {
+        // Residual rows are prefetched into registers one CHUNK ahead, across tiles: the first chunk of the next
+        // super-tile is requested while the last chunk of this one is processed.  (Requesting it only at the top of
+        // the next iteration put the whole HBM/L2 latency, ~1.5x the MMA time of an N = 64 tile, on the epilogue's
+        // critical path: ncu long-scoreboard stalls, 0.30 ms against 0.215 ms without a residual.)
+        uint4 rv[8], rn[8];
+        const int nv0 = cn_full > 0 ? 8 : 4;
+        if (a.has_res && first_unit < num_units) {
+          const long long p0 = (long long)tile_of(first_unit) * TM + g * 128 + row;
+          if (p0 < a.total_rows) {
+            const uint4* rb = reinterpret_cast<const uint4*>(a.residual + (size_t)p0 * a.N);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              if (i < nv0) rv[i] = __ldg(rb + i);
+          }
+        }
         for (int u = first_unit; u < num_units; u += unit_step) {
           const long long q0 = (long long)tile_of(u) * TM + g * 128;
           const long long p = q0 + row;
@@ -345,13 +414,9 @@ __global__ void __launch_bounds__(THREADS, 1)
           const bool valid = (n < a.B) && (hp >= a.pad) && (hp < a.pad + a.H) && (wp >= a.pad) && (wp < a.pad + a.W);
           const bool do_res = a.has_res && p < a.total_rows;
           const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N);
-          uint4 rv[8], rn[8];
-          if (do_res) {
-            const int nv = cn_full > 0 ? 8 : 4;
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-              if (i < nv) rv[i] = __ldg(rbase + i);
-          }
+          const int un = u + unit_step;
+          const long long pn = un < num_units ? (long long)tile_of(un) * TM + g * 128 + row : a.total_rows;
+          const uint4* rnext = reinterpret_cast<const uint4*>(a.residual + (size_t)pn * a.N);
           ptx::mbar_wait(&tfull[acc], pacc);
           ptx::tc_fence_after();
           for (int j = 0; j < cn; ++j, ++k) {
@@ -362,6 +427,11 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll
               for (int i = 0; i < 8; ++i)
                 if (i < nv) rn[i] = __ldg(rbase + 8 * (j + 1) + i);
+            }
+            if (a.has_res && last && pn < a.total_rows) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                if (i < nv0) rn[i] = __ldg(rnext + i);
             }
             const int ob = a.nOut == 2 ? (k & 1) : 0;
             if (leader) {
@@ -388,7 +458,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               ptx::tma_store_2d(full ? &tmapO : &tmapO32, myOut + (size_t)ob * 16384, a.out_c_off + 64 * j, (int)q0);
               ptx::bulk_commit();
             }
-            if (!last) {
+            if (a.has_res) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) rv[i] = rn[i];
             }
@@ -396,6 +466,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           if (++acc == 2) { acc = 0; pacc ^= 1; }
         }
         if (leader) ptx::bulk_wait<0>();
+        }
       }
     } else if (warp < 6)
     for (int u = first_unit; u < num_units; u += unit_step) {
@@ -473,7 +544,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
 static inline size_t smem_bytes(const Args& a) {
   return 1024 + (size_t)a.stagesA * a.slab_rows * 128 + (size_t)a.stagesB * (a.cluster == 2 ? a.N / 2 : a.N) * 128 +
-         (size_t)(a.T * a.nOut) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 6) * 8 + 16;
+         (size_t)(a.T * a.nOut) * 16384 + 512 + (size_t)(2 * a.stagesA + 2 * a.stagesB + 8) * 8 + 16;
 }
 
 }  // namespace convf

@@ -68,6 +68,7 @@ struct Net {
   bool flat_enabled = true;       // WSI_B200_NO_FLAT=1 forces every conv onto the per-tap TMA kernel
   bool cluster_enabled = true;    // WSI_B200_NO_CLUSTER=1: no CTA pairs / weight multicast in the per-tap kernel
   bool no_flat_pair = false;      // WSI_B200_NO_FLAT_PAIR=1: the flat kernel stays single-CTA
+  bool res_smem_enabled = true;   // WSI_B200_NO_RES_SMEM=1: flat-kernel residual through registers (scattered loads)
   bool pool_ring = true;          // WSI_B200_NO_POOL_RING=1: 3x3 pools by the register-ring kernel (direct global loads)
   bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
@@ -537,6 +538,7 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->cluster_enabled = !(nc && nc[0] == '1');
   const char* nfp = getenv("WSI_B200_NO_FLAT_PAIR");
   n->no_flat_pair = nfp && nfp[0] == '1';
+  n->res_smem_enabled = getenv("WSI_B200_NO_RES_SMEM") == nullptr;
   const char* npr = getenv("WSI_B200_NO_POOL_RING");
   n->pool_ring = !(npr && npr[0] == '1');
   const char* le = getenv("WSI_B200_LEGACY_EPI");
@@ -958,6 +960,18 @@ int wsi_net_finalize(void* net) {
         op.tmO = op.tmB;
         op.tmR = op.tmB;
         op.tmO32 = op.tmB;
+        f.res_smem = 0;
+        if (f.has_res && f.tma_epi && f.nOut == 2 && op.Cout % 64 == 0 && n->res_smem_enabled) {
+          const Tensor& tr = n->tensors[op.res];
+          uint64_t dims[2] = {(uint64_t)tr.C, (uint64_t)B * tr.Hp() * tr.Wp()};
+          uint64_t strides[1] = {(uint64_t)tr.C * 2};
+          uint32_t box[2] = {64, 128};
+          uint32_t es[2] = {1, 1};
+          int rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+          f.res_smem = 1;
+        }
         if (f.tma_epi) {
           uint64_t dims[2] = {(uint64_t)to.C, (uint64_t)B * to.Hp() * to.Wp()};
           uint64_t strides[1] = {(uint64_t)to.C * 2};
@@ -1234,11 +1248,11 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
           }
           if (pairs > op.max_pairs) pairs = op.max_pairs;
           cfg.gridDim = dim3((unsigned)(2 * pairs));
-          WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convf::k_conv_flat<2>, op.tmA, op.tmB, op.tmO, op.tmO32, f));
+          WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convf::k_conv_flat<2>, op.tmA, op.tmB, op.tmO, op.tmO32, op.tmR, f));
           continue;
         }
         int grid = f.num_tiles < n->num_sms ? f.num_tiles : n->num_sms;
-        convf::k_conv_flat<1><<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, f);
+        convf::k_conv_flat<1><<<grid, convf::THREADS, convf::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, op.tmR, f);
         continue;
       }
       convk::Args a = op.ca;
