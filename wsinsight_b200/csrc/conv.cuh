@@ -37,6 +37,7 @@ struct Args {
   int stages;
   int out_C, out_c_off;                      // channels of the destination tensor / concat offset
   int res_C;                                 // channels of the residual tensor (0 = none)
+  int res_smem;                              // residual boxes are TMA-loaded into the staging buffers (tmapR)
   int out_pad, res_pad;                      // one-pixel zero border of the destination / residual tensor (0|1)
   int out_Hp, out_Wp, res_Hp, res_Wp;        // stored rows / columns of the destination / residual tensor
   int tma_epi;                               // N_tile % 64 == 0: smem-staged epilogue + TMA stores, two warp groups
@@ -142,20 +143,18 @@ __device__ __forceinline__ void epi_chunk64_smemres(uint32_t t_addr, int row, ui
   ptx::tmem_ld_32x32b_x32(t_addr + 32u, r + 32);
   const uint32_t row_base = s_buf + (uint32_t)row * 128u;
   const uint32_t sw = (uint32_t)row & 7u;
-  uint4 rv[8];
-#pragma unroll
-  for (int c = 0; c < 8; ++c) rv[c] = ptx::ld_shared_v4(row_base + (((uint32_t)c ^ sw) << 4));
   ptx::tmem_ld_wait();
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
+    const uint4 rv = ptx::ld_shared_v4(row_base + (((uint32_t)c ^ sw) << 4));
     const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
     const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
     float v0 = __uint_as_float(r[8 * c + 0]) + b0.x, v1 = __uint_as_float(r[8 * c + 1]) + b0.y;
     float v2 = __uint_as_float(r[8 * c + 2]) + b0.z, v3 = __uint_as_float(r[8 * c + 3]) + b0.w;
     float v4 = __uint_as_float(r[8 * c + 4]) + b1.x, v5 = __uint_as_float(r[8 * c + 5]) + b1.y;
     float v6 = __uint_as_float(r[8 * c + 6]) + b1.z, v7 = __uint_as_float(r[8 * c + 7]) + b1.w;
-    v0 += bf16_lo(rv[c].x); v1 += bf16_hi(rv[c].x); v2 += bf16_lo(rv[c].y); v3 += bf16_hi(rv[c].y);
-    v4 += bf16_lo(rv[c].z); v5 += bf16_hi(rv[c].z); v6 += bf16_lo(rv[c].w); v7 += bf16_hi(rv[c].w);
+    v0 += bf16_lo(rv.x); v1 += bf16_hi(rv.x); v2 += bf16_lo(rv.y); v3 += bf16_hi(rv.y);
+    v4 += bf16_lo(rv.z); v5 += bf16_hi(rv.z); v6 += bf16_lo(rv.w); v7 += bf16_hi(rv.w);
     if (relu) {
       v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
       v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
@@ -204,7 +203,8 @@ __device__ __forceinline__ void epi_chunk32_regs(uint32_t t_addr, int row, uint3
 template <int CL>
 __global__ void __launch_bounds__(THREADS, 1)
     k_conv_igemm(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                 const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32, const Args a) {
+                 const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapO32,
+                 const __grid_constant__ CUtensorMap tmapR, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x A 16KB][stages x B N_tile*128][barriers]
   if (ptx::smem_u32(smem_raw) & 1023u) __trap();
@@ -220,7 +220,8 @@ __global__ void __launch_bounds__(THREADS, 1)
   uint64_t* empty = bars + a.stages;
   uint64_t* tfull = bars + 2 * a.stages;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* resFull = tempty + 2;                  // residual tile landed in the staging buffer of group g
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resFull + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = a.tiles_w * a.tiles_h * a.tiles_n;
@@ -249,6 +250,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
       ptx::mbar_init(&tempty[s], (uint32_t)(((a.tma_epi && a.N_tile > 64) ? 8 : 4) * CL));   // > 64: two chunks or more
+      ptx::mbar_init(&resFull[s], 1);
     }
     ptx::fence_barrier_init();
   }
@@ -395,7 +397,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int h_l = (row / a.bw) % a.bh;
     const int n_l = row / (a.bw * a.bh);
     int acc = 0, k = 0;
-    uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0, res_phase = 0;
     for (int u = first_unit; u < total_units; u += unit_step, ++k) {
       const bool part = cn > 1 ? (g < cn) : ((k & 1) == g);
       if (part) {
@@ -410,6 +412,49 @@ __global__ void __launch_bounds__(THREADS, 1)
         const size_t rpix = ((size_t)n * a.res_Hp + ho + a.res_pad) * a.res_Wp + wo + a.res_pad;
         const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + rpix * a.res_C + nt * a.N_tile);
         int j = cn > 1 ? g : 0;
+        if (a.res_smem) {
+          // Residual through shared memory (long-K convs, where the exposed TMA latency per chunk hides under the
+          // tile's MMA time): the leader loads the residual box of the chunk into the staging buffer as soon as the
+          // previous store has read it, every thread adds its own row in place (see epi_chunk64_smemres).
+          auto issue_res = [&](int jj) {
+            if (leader) {
+              ptx::bulk_wait_read<0>();
+              ptx::mbar_arrive_expect_tx(&resFull[g], 16384u);
+              ptx::tma_load_4d(sOut + (size_t)g * 16384, &tmapR, &resFull[g], nt * a.N_tile + 64 * jj, tw * a.bw,
+                               th * a.bh, tn * a.bn);
+            }
+          };
+          issue_res(j);                                   // before the wait on the accumulator
+          ptx::mbar_wait(&tfull[acc], acc_phase);
+          ptx::tc_fence_after();
+          for (; j < cn; j += jstep) {
+            const bool last = j + jstep >= cn;
+            ptx::mbar_wait(&resFull[g], res_phase);
+            res_phase ^= 1;
+            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + 64 * j);
+            epi_chunk64_smemres(t_addr, row, myOut, sBias + nt * a.N_tile + 64 * j, a.relu);
+            if (last) {
+              ptx::tc_fence_before();
+              __syncwarp();
+              if (lane == 0) {
+                if (CL == 2) ptx::mbar_arrive_cluster(&tempty[acc], 0u); else ptx::mbar_arrive(&tempty[acc]);
+              }
+            }
+            ptx::fence_proxy_async();
+            ptx::named_bar_sync(1 + g, 128);              // chunk staged
+            if (leader) {
+              ptx::tma_store_4d(&tmapO, sOut + (size_t)g * 16384, a.out_c_off + nt * a.N_tile + 64 * j, tw * a.bw,
+                                th * a.bh, tn * a.bn);
+              ptx::bulk_commit();
+            }
+            if (!last) issue_res(j + jstep);
+          }
+          if (++acc == 2) {
+            acc = 0;
+            acc_phase ^= 1;
+          }
+          continue;
+        }
         uint4 rv[8], rn[8];
         if (do_res) {
           const int nv = j < cn_full ? 8 : 4;

@@ -1056,6 +1056,17 @@ int wsi_net_finalize(void* net) {
           rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, to.ptr + to.interior_offset(), dims, strides,
                              box, es, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc) return rc;
+        op.tmR = op.tmO;
+        a.res_smem = 0;
+        if (op.res >= 0 && a.N_tile % 64 == 0 && n->res_smem_enabled && op.KH * op.KW * a.cin_chunks >= 16) {
+          const Tensor& tr = n->tensors[op.res];
+          uint64_t rdims[4] = {(uint64_t)tr.C, (uint64_t)tr.W, (uint64_t)tr.H, (uint64_t)B};
+          uint64_t rstrides[3] = {(uint64_t)tr.C * 2, (uint64_t)tr.Wp() * tr.C * 2, (uint64_t)tr.Hp() * tr.Wp() * tr.C * 2};
+          rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, tr.ptr + tr.interior_offset(), rdims, rstrides,
+                             box, es, CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+          a.res_smem = 1;
+        }
         if (a.N_tile & 32) {
           uint32_t box32[4] = {32, (uint32_t)a.bw, (uint32_t)a.bh, (uint32_t)a.bn};
           rc = wsi_make_tmap(&op.tmO32, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, to.ptr + to.interior_offset(), dims, strides,
@@ -1294,9 +1305,9 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         }
         if (pairs > op.max_pairs) pairs = op.max_pairs;
         cfg.gridDim = dim3((unsigned)(2 * pairs));
-        WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convk::k_conv_igemm<2>, op.tmA, op.tmB, op.tmO, op.tmO32, a));
+        WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convk::k_conv_igemm<2>, op.tmA, op.tmB, op.tmO, op.tmO32, op.tmR, a));
       } else {
-        convk::k_conv_igemm<1><<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, a);
+        convk::k_conv_igemm<1><<<grid, convk::THREADS, smem, stream>>>(op.tmA, op.tmB, op.tmO, op.tmO32, op.tmR, a);
       }
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];
