@@ -12,7 +12,7 @@ ncu -i /tmp/conv_full_r34.ncu-rep --page details --csv > gpurun_out/conv_full_r3
 for k in k_conv_flat k_conv_igemm k_conv_stem; do
   ncu -i /tmp/conv_full_r34.ncu-rep --page source --csv -k regex:$k -c 1 > gpurun_out/conv_full_r34_source_$k.csv 2>> gpurun_out/export.err; echo "export source $k rc=$?"
 done
-timeout 900 ncu --metrics $M --clock-control none -k regex:k_conv -s 149 -c 149 --csv --log-file gpurun_out/conv_metrics_iv4.csv python bench.py --model inceptionv4 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_iv4.log 2>&1; echo "ncu iv4 rc=$?"
+timeout 900 ncu --metrics $M --clock-control none -k regex:k_conv -s 133 -c 133 --csv --log-file gpurun_out/conv_metrics_iv4.csv python bench.py --model inceptionv4 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_iv4.log 2>&1; echo "ncu iv4 rc=$?"
 timeout 600 ncu --set full --clock-control none -k regex:"k_reduce|k_preprocess|k_pool3_tma|k_head" -c 8 -o /tmp/aux_full python bench.py --model inceptionv4 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_aux.log 2>&1; echo "ncu aux rc=$?"
 ncu -i /tmp/aux_full.ncu-rep --page raw --csv > gpurun_out/aux_full_raw.csv 2>> gpurun_out/export.err
 cp /tmp/aux_full.ncu-rep gpurun_out/ 2>/dev/null
