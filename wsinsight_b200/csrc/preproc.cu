@@ -97,10 +97,15 @@ struct PPArgs {
   int channels;                // 4: 8-byte pixels, 8: 16-byte pixels
 };
 
-__device__ __forceinline__ uint32_t clip8(int v) {
-  v >>= PRECISION_BITS;
-  return (uint32_t)min(max(v, 0), 255);
-}
+// Pillow clips (sum >> PRECISION_BITS) to [0, 255].  For the triangle filter every coefficient is >= 0 and a row sums
+// to 2^22 + at most ksize/2 rounding units, so HALF + sum(c * p) lies in [2^21, 255 * 2^22 + 255 * ksize/2 + 2^21]
+// < 256 * 2^22 for any ksize < 16384 (checked when the plan is built): the clip can never fire and is left out
+// (six min/max instructions per pixel in an issue-bound kernel).
+__device__ __forceinline__ uint32_t clip8(int v) { return (uint32_t)v >> PRECISION_BITS; }
+// bytes 0..2 of an RGBx word, zero extended (one PRMT each instead of shift + mask)
+__device__ __forceinline__ int byte0(uint32_t p) { return (int)(p & 0xffu); }
+__device__ __forceinline__ int byte1(uint32_t p) { return (int)__byte_perm(p, 0u, 0x4441u); }
+__device__ __forceinline__ int byte2(uint32_t p) { return (int)__byte_perm(p, 0u, 0x4442u); }
 
 // grid: (n_patches, nbands); one CTA = TR output rows x S output columns of one patch.
 // One thread owns one output column in both passes: its horizontal taps sit in registers (KS > 0) and the
@@ -171,9 +176,9 @@ __global__ void __launch_bounds__(PP_THREADS)
 #pragma unroll
             for (int t = 0; t < KS; ++t) {
               const uint32_t p = src[rr * a.box_w + t];
-              s0 += (int)(p & 0xff) * c[t];
-              s1 += (int)((p >> 8) & 0xff) * c[t];
-              s2 += (int)((p >> 16) & 0xff) * c[t];
+              s0 += byte0(p) * c[t];
+              s1 += byte1(p) * c[t];
+              s2 += byte2(p) * c[t];
             }
             dst[rr * a.S] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
           }
@@ -185,9 +190,9 @@ __global__ void __launch_bounds__(PP_THREADS)
             for (int t = 0; t < n; ++t) {
               const uint32_t p = src[rr * a.box_w + t];
               const int c = k[t];
-              s0 += (int)(p & 0xff) * c;
-              s1 += (int)((p >> 8) & 0xff) * c;
-              s2 += (int)((p >> 16) & 0xff) * c;
+              s0 += byte0(p) * c;
+              s1 += byte1(p) * c;
+              s2 += byte2(p) * c;
             }
             dst[rr * a.S] = clip8(s0) | (clip8(s1) << 8) | (clip8(s2) << 16);
           }
@@ -200,28 +205,42 @@ __global__ void __launch_bounds__(PP_THREADS)
   // vertical pass + ToTensor + Normalize + bf16 NHWC4 store
   const int P = a.out_H >> 1;
   for (int xx = threadIdx.x; xx < a.S; xx += PP_THREADS) {
-    for (int yy = r0; yy < r1; ++yy) {
+    // destination index of (row r0, column xx), then advanced row by row: in the row-parity-plane layout an even
+    // stored row y is followed by y + 1 one plane further, an odd one by the next row of plane 0
+    long long o;
+    {
+      const int y = a.pad_top + r0;
+      if (a.plane_stride_px > 0)
+        o = (long long)(y & 1) * a.plane_stride_px + ((long long)patch * P + (y >> 1)) * a.out_W + (a.pad_left + xx);
+      else
+        o = ((long long)patch * a.out_H + y) * a.out_W + (a.pad_left + xx);
+    }
+    const long long step_even = a.plane_stride_px > 0 ? (long long)a.plane_stride_px : (long long)a.out_W;
+    const long long step_odd = a.plane_stride_px > 0 ? (long long)a.out_W - a.plane_stride_px : (long long)a.out_W;
+    int ypar = (a.pad_top + r0) & 1;
+    for (int yy = r0; yy < r1; ++yy, o += ypar ? step_odd : step_even, ypar ^= 1) {
       const int n = s_cnt[yy];                                   // warp-uniform
       const uint32_t* col = s_int + (size_t)(s_lo[yy] - y_lo) * a.S + xx;
       const int* k = s_coef + (size_t)yy * a.ksize;
       int s0 = HALF, s1 = HALF, s2 = HALF;
       if (KS > 0) {
+        // as in the horizontal pass: taps beyond cnt carry zero coefficients and the rows they touch lie inside the
+        // shared-memory allocation (at most KS - 1 rows past the staged ones, into the tables that follow s_int)
 #pragma unroll
-        for (int t = 0; t < KS; ++t)
-          if (t < n) {
-            const uint32_t p = col[t * a.S];
-            const int c = k[t];
-            s0 += (int)(p & 0xff) * c;
-            s1 += (int)((p >> 8) & 0xff) * c;
-            s2 += (int)((p >> 16) & 0xff) * c;
-          }
+        for (int t = 0; t < KS; ++t) {
+          const uint32_t p = col[t * a.S];
+          const int c = k[t];
+          s0 += byte0(p) * c;
+          s1 += byte1(p) * c;
+          s2 += byte2(p) * c;
+        }
       } else {
         for (int t = 0; t < n; ++t) {
           const uint32_t p = col[t * a.S];
           const int c = k[t];
-          s0 += (int)(p & 0xff) * c;
-          s1 += (int)((p >> 8) & 0xff) * c;
-          s2 += (int)((p >> 16) & 0xff) * c;
+          s0 += byte0(p) * c;
+          s1 += byte1(p) * c;
+          s2 += byte2(p) * c;
         }
       }
       const uint32_t u0 = clip8(s0), u1 = clip8(s1), u2 = clip8(s2);
@@ -232,13 +251,6 @@ __global__ void __launch_bounds__(PP_THREADS)
       uint2 v;
       v.x = (uint32_t)s_lut[u0] | ((uint32_t)s_lut[256 + u1] << 16);
       v.y = (uint32_t)s_lut[512 + u2];
-      size_t o;
-      if (a.plane_stride_px > 0) {
-        const int y = a.pad_top + yy;
-        o = (size_t)(y & 1) * (size_t)a.plane_stride_px + ((size_t)patch * P + (y >> 1)) * (size_t)a.out_W + (a.pad_left + xx);
-      } else {
-        o = (((size_t)patch * a.out_H + (a.pad_top + yy)) * a.out_W + (a.pad_left + xx));
-      }
       if (a.channels == 8)
         reinterpret_cast<uint4*>(a.out)[o] = make_uint4(v.x, v.y, 0u, 0u);
       else
@@ -275,6 +287,24 @@ int wsi_preproc_plan_create(const uint8_t* d_slide_rgba, long long slide_w, long
   }
   Taps t = make_taps(patch_size, out_size);
   p->ksize = t.ksize;
+  // the kernels rely on the clip to [0, 255] being a no-op (see clip8): non-negative taps, row sums ~ 2^22
+  for (int i = 0; i < out_size; ++i) {
+    long long sum = 0;
+    for (int k = 0; k < t.ksize; ++k) {
+      const int c = t.coef[(size_t)i * t.ksize + k];
+      if (c < 0) {
+        delete p;
+        wsi_set_error("wsi_preproc_plan_create: negative resampling coefficient");
+        return WSI_ERR_UNSUPPORTED;
+      }
+      sum += c;
+    }
+    if (sum > (1LL << PRECISION_BITS) + 8192) {
+      delete p;
+      wsi_set_error("wsi_preproc_plan_create: resampling coefficients of output %d sum to %lld", i, sum);
+      return WSI_ERR_UNSUPPORTED;
+    }
+  }
   const int S = out_size;
   // rows per band so that the u8 intermediate stays <= PP_MAX_INTER_ROWS source rows
   int TR = 16;
