@@ -51,6 +51,9 @@ struct Op {
   int Ktot;
   // pool
   int pk, pstride, ppad, count_include_pad;
+  int prelu = 0;                  // average pool followed by + bias, ReLU (a 1x1 conv commuted in front of the pool)
+  float* d_pbias = nullptr;
+  std::vector<float> h_pbias;
   // head
   int K;
   float* d_fcw = nullptr;
@@ -159,6 +162,7 @@ struct PoolRow<true> {
   __device__ __forceinline__ void set(const uint4& x) { v = x; }
   static __device__ __forceinline__ uint4 neutral() { return make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u); }
   __device__ __forceinline__ uint4 result(float) const { return v; }
+  __device__ __forceinline__ uint4 result_bias(float, const float (&)[8], int) const { return v; }   // max: no bias
 };
 template <>
 struct PoolRow<false> {
@@ -186,13 +190,24 @@ struct PoolRow<false> {
     return make_uint4(convk::pack_bf16(f[0] * rcp, f[1] * rcp), convk::pack_bf16(f[2] * rcp, f[3] * rcp),
                       convk::pack_bf16(f[4] * rcp, f[5] * rcp), convk::pack_bf16(f[6] * rcp, f[7] * rcp));
   }
+  // average, then + bias and optional ReLU (the epilogue of a 1x1 conv that was moved in front of the pool)
+  __device__ __forceinline__ uint4 result_bias(float rcp, const float (&b)[8], int relu) const {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      v[i] = fmaf(f[i], rcp, b[i]);
+      if (relu) v[i] = fmaxf(v[i], 0.f);
+    }
+    return make_uint4(convk::pack_bf16(v[0], v[1]), convk::pack_bf16(v[2], v[3]), convk::pack_bf16(v[4], v[5]),
+                      convk::pack_bf16(v[6], v[7]));
+  }
 };
 
 template <bool IS_MAX, int K, int S>
 __global__ void __launch_bounds__(256, 6)
     k_pool_sep(const __nv_bfloat16* __restrict__ in, int H, int W, int C, int pad, int count_include_pad, int Ho, int Wo,
                __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int iWp, int ip, int oHp, int oWp,
-               int op, int band, int nbands) {
+               int op, int band, int nbands, const float* __restrict__ pbias, int prelu) {
   // threads walk the (output column, 16-byte channel vector) plane of a row in flat order: no idle lanes whatever
   // Wo and C are (the 2-D mapping left 27 % of the threads idle at 35 x 48 vectors), and consecutive threads read
   // consecutive 16 bytes of the input row
@@ -207,6 +222,9 @@ __global__ void __launch_bounds__(256, 6)
   const uint4* img = reinterpret_cast<const uint4*>(in + (size_t)n * iHp * iWp * C) + ((size_t)ip * iWp + ip) * cv + c8;
   uint4* obase = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + op) * oWp + op) * out_C + out_c_off) + c8;
   const int ocv = out_C >> 3;
+  float bz[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) bz[i] = pbias ? __ldg(pbias + c8 * 8 + i) : 0.f;
   PoolRow<IS_MAX> h[K];
   auto hrow = [&](int y, PoolRow<IS_MAX>& r) {
     r.clear();
@@ -239,7 +257,7 @@ __global__ void __launch_bounds__(256, 6)
       const int nrows = min(yb + K, H) - max(yb, 0);
       rcp = 1.0f / (count_include_pad ? (float)(K * K) : (float)(nrows * ncols));
     }
-    obase[((size_t)ho * oWp + wo) * ocv] = m.result(rcp);
+    obase[((size_t)ho * oWp + wo) * ocv] = pbias ? m.result_bias(rcp, bz, prelu) : m.result(rcp);
   }
 }
 
@@ -338,7 +356,7 @@ template <bool IS_MAX>
 __global__ void __launch_bounds__(288, 2)
     k_pool3s1_tma(const __grid_constant__ CUtensorMap tmI, int H, int W, int pad, int count_include_pad, int Ho, int Wo,
                   __nv_bfloat16* __restrict__ out, int out_C, int out_c_off, int iHp, int ip, int oHp, int oWp, int op,
-                  int ct, int wt, int row_bytes, int row_stride, int R) {
+                  int ct, int wt, int row_bytes, int row_stride, int R, const float* __restrict__ pbias, int prelu) {
   constexpr int K = 3;
   extern __shared__ __align__(128) uint8_t pool_smem[];
   const uint32_t base = (ptx::smem_u32(pool_smem) + 127u) & ~127u;
@@ -381,6 +399,9 @@ __global__ void __launch_bounds__(288, 2)
   }
   uint4* obase = reinterpret_cast<uint4*>(out + (((size_t)n * oHp + op) * oWp + op) * out_C + out_c_off) + c0 + cl;
   const int ocv = out_C >> 3;
+  float bz[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) bz[i] = pbias ? __ldg(pbias + (c0 + cl) * 8 + i) : 0.f;
   int kk = 0, st = 0;
   uint32_t par = 0;
   PoolRow<IS_MAX> ha[K], hb[K];
@@ -426,8 +447,8 @@ __global__ void __launch_bounds__(288, 2)
         const float fa = nr >= 3 ? rcp_a[3] : (nr == 2 ? rcp_a[2] : rcp_a[1]);
         const float fb = nr >= 3 ? rcp_b[3] : (nr == 2 ? rcp_b[2] : rcp_b[1]);
         uint4* o = obase + ((size_t)ho * oWp + wa) * ocv;
-        if (act_a) o[0] = ma.result(fa);
-        if (act_b) o[ocv] = mb.result(fb);
+        if (act_a) o[0] = pbias ? ma.result_bias(fa, bz, prelu) : ma.result(fa);
+        if (act_b) o[ocv] = pbias ? mb.result_bias(fb, bz, prelu) : mb.result(fb);
       }
     }
   }
@@ -704,6 +725,22 @@ int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max
   op.pk = k; op.pstride = stride; op.ppad = pad; op.count_include_pad = count_include_pad;
   op.out_c_off = out_c_off;
   n->ops.push_back(std::move(op));
+  return WSI_OK;
+}
+
+// 3x3 / stride 1 AVERAGE pool followed by + bias[c] and optional ReLU.  conv1x1(avgpool(x)) == avgpool(conv1x1(x))
+// (both linear, the divisor depends on the position only), so the engine runs the 1x1 conv of an Inception pool branch
+// FIRST (without bias / ReLU) and pools its 4-8x narrower output here: the wide block input is no longer read and
+// re-written by a pooling pass.
+int wsi_net_add_pool_bias(void* net, int in_id, int out_id, int out_c_off, int k, int stride, int pad,
+                          int count_include_pad, const float* bias, int relu) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && k == 3 && stride == 1 && bias, "wsi_net_add_pool_bias: only 3x3 / stride 1 average pools");
+  int rc = wsi_net_add_pool(net, in_id, out_id, out_c_off, 0, k, stride, pad, count_include_pad);
+  if (rc) return rc;
+  Op& op = n->ops.back();
+  op.h_pbias.assign(bias, bias + n->tensors[in_id].C);
+  op.prelu = relu ? 1 : 0;
   return WSI_OK;
 }
 
@@ -1090,6 +1127,11 @@ int wsi_net_finalize(void* net) {
         if (rc) return rc;
       }
     } else if ((op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) && !op.skip) {
+      if (!op.h_pbias.empty()) {
+        WSI_CUDA_CHECK(cudaMalloc(&op.d_pbias, op.h_pbias.size() * sizeof(float)));
+        WSI_CUDA_CHECK(cudaMemcpy(op.d_pbias, op.h_pbias.data(), op.h_pbias.size() * sizeof(float),
+                                  cudaMemcpyHostToDevice));
+      }
       // 3x3 pools over internal tensors: tile plan + input tensor map of the TMA-ring kernel
       const Tensor& ti = n->tensors[op.in];
       const Tensor& to = n->tensors[op.out];
@@ -1100,8 +1142,8 @@ int wsi_net_finalize(void* net) {
         const int per = op.pstride == 1 ? 2 : 1;
         const int units_w = (to.W + per - 1) / per;
         int ct = 0, wt = 0;
-        for (int c : {32, 16, 8})                       // whole image width per CTA when <= 288 slots
-          if (cv % c == 0 && c * units_w <= 288 && c * units_w > ct * ((wt + per - 1) / per)) { ct = c; wt = to.W; }
+        for (int c = 32; c >= 4; --c)                   // whole image width per CTA when <= 288 slots; inner TMA
+          if (cv % c == 0 && c * units_w <= 288 && c * units_w > ct * ((wt + per - 1) / per)) { ct = c; wt = to.W; }   // rows >= 64 B
         if (!ct) {
           ct = cv % 8 == 0 ? 8 : (cv % 4 == 0 ? 4 : (cv % 2 == 0 ? 2 : 1));
           const int cap = 288 / ct * per;               // output columns per CTA
@@ -1328,12 +1370,12 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
               k_pool3s1_tma<true><<<grid, threads, smem, stream>>>(op.tmA, ti.H, ti.W, op.ppad, op.count_include_pad, to.H,
                                                                    to.W, to.ptr, to.C, op.out_c_off, ti.Hp(), ti.pad,
                                                                    to.Hp(), to.Wp(), to.pad, op.pt_ct, op.pt_wt, row_bytes,
-                                                                   row_stride, op.pt_R);
+                                                                   row_stride, op.pt_R, nullptr, 0);
             else
               k_pool3s1_tma<false><<<grid, threads, smem, stream>>>(op.tmA, ti.H, ti.W, op.ppad, op.count_include_pad, to.H,
                                                                     to.W, to.ptr, to.C, op.out_c_off, ti.Hp(), ti.pad,
                                                                     to.Hp(), to.Wp(), to.pad, op.pt_ct, op.pt_wt, row_bytes,
-                                                                    row_stride, op.pt_R);
+                                                                    row_stride, op.pt_R, op.d_pbias, op.prelu);
             continue;
           }
 #define WSI_POOL_TMA(MAX, S)                                                                                             \
@@ -1354,7 +1396,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
 #define WSI_POOL_SEP(MAX, S)                                                                                              \
   k_pool_sep<MAX, 3, S><<<grid, block, 0, stream>>>(in_ptr, ti.H, ti.W, ti.C, op.ppad, op.count_include_pad, to.H, to.W, \
                                                     to.ptr, to.C, op.out_c_off, ti.Hp(), ti.Wp(), ti.pad, to.Hp(),       \
-                                                    to.Wp(), to.pad, band, nbands)
+                                                    to.Wp(), to.pad, band, nbands, op.d_pbias, op.prelu)
         if (is_max) {
           if (op.pstride == 1) WSI_POOL_SEP(true, 1); else WSI_POOL_SEP(true, 2);
         } else {
@@ -1543,6 +1585,7 @@ void wsi_net_destroy(void* net) {
     if (op.d_w) cudaFree(op.d_w);
     if (op.d_bias) cudaFree(op.d_bias);
     if (op.d_fcw) cudaFree(op.d_fcw);
+    if (op.d_pbias) cudaFree(op.d_pbias);
     if (op.d_fcb) cudaFree(op.d_fcb);
   }
   delete n;

@@ -146,6 +146,25 @@ class B200Network:
                         raise UnknownArchitectureError("cat channel offsets must be multiples of 8")
                     tensor_of[p], c_off[p] = tid, off
                     off += nodes[p].shape[0]
+        # Pool branch of an Inception block: avg_pool2d(3, 1, 1) -> 1x1 conv.  Both are linear and the pool divisor
+        # depends on the position only, so conv1x1(avgpool(x)) == avgpool(conv1x1(x)): run the conv FIRST (no bias, no
+        # ReLU; it reads x like its sibling branches) and pool its 4-8x narrower output with bias + ReLU fused into the
+        # pooling kernel (wsi_net_add_pool_bias).  The wide block input is then no longer read and re-written by a
+        # pooling pass.  Pool node i keeps its index but now holds conv1x1_nobias(x) (self.commuted_pools).
+        commute = {}
+        if os.environ.get("WSI_B200_NO_POOL_COMMUTE") != "1":
+            for j, m in enumerate(nodes):
+                if (m.kind == "conv" and m is not stem and m.residual is None and tuple(m.weight.shape[2:]) == (1, 1)
+                        and int(m.stride) == 1 and tuple(m.pad) == (0, 0) and int(m.weight.shape[0]) % 32 == 0):
+                    i = m.inputs[0]
+                    p = nodes[i]
+                    if (p.kind == "pool" and not p.pool_max and int(p.k) == 3 and int(p.pstride) == 1
+                            and int(p.ppad) == 1 and p.n_uses == 1 and i not in tensor_of
+                            and int(m.weight.shape[0]) < int(p.shape[0])):
+                        commute[i] = j
+        self.commuted_pools = sorted(commute)
+        conv_of_pool = dict(commute)
+        pool_of_conv = {j: i for i, j in commute.items()}
         # Sibling 1x1 convolutions (same input, stride 1, no padding, same activation -- the branch heads of an
         # Inception block) whose outputs feed only convolutions: ONE launch with the filters stacked writes one wide
         # tensor and the consumers read channel slices of it, so the block input is read from HBM once per group
@@ -180,6 +199,8 @@ class B200Network:
         for i, n in enumerate(nodes):
             if n.kind in ("conv", "pool") and i not in tensor_of:
                 c, h, w = n.shape
+                if i in conv_of_pool:
+                    c = int(nodes[conv_of_pool[i]].weight.shape[0])
                 tensor_of[i], c_off[i] = self._add_tensor(h, w, c), 0
         self.num_classes = None
         self._keep = []
@@ -195,6 +216,21 @@ class B200Network:
             elif c_off.get(x, 0) != 0 or (nodes[x].kind in ("conv", "pool") and
                                           nodes[x].shape[0] != self._tensor_channels(nodes, tensor_of, x)):
                 raise UnknownArchitectureError("reading a channel slice of a concat buffer is not supported")
+            if n.kind == "conv" and i in pool_of_conv:
+                b = (n.bias if n.bias is not None else __import__("torch").zeros(int(n.weight.shape[0]))).contiguous()
+                self._keep.append(b)
+                pn = nodes[pool_of_conv[i]]
+                _cabi.call("wsi_net_add_pool_bias", self._h, tensor_of[x], tensor_of[i], c_off[i], int(pn.k),
+                           int(pn.pstride), int(pn.ppad), 1 if pn.count_include_pad else 0, _fptr(b),
+                           1 if n.relu else 0)
+                continue
+            if n.kind == "pool" and i in conv_of_pool:
+                cn = nodes[conv_of_pool[i]]
+                w = cn.weight.contiguous()
+                self._keep.append(w)
+                _cabi.call("wsi_net_add_conv_slice", self._h, tensor_of[x], int(in_off), tensor_of[i], 0, _fptr(w), None,
+                           int(w.shape[1]), int(w.shape[0]), 1, 1, 1, 0, 0, 0, -1)
+                continue
             if n.kind == "conv":
                 if i in merged_into and merged_into[i] in emitted_groups:
                     continue                       # already emitted with the first visited member of its group
