@@ -146,8 +146,11 @@ int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max
  * (avg_pool2d -> 1x1 BasicConv2d in the TorchScript graph, executed by run_inference.py:541) is run as
  * 1x1 conv (no bias, no ReLU) -> this op, which is the same linear map with the pooling pass over 4-8x fewer
  * channels. */
-int wsi_net_add_pool_bias(void* net, int in_id, int out_id, int out_c_off, int k, int stride, int pad,
-                          int count_include_pad, const float* h_bias, int relu);
+int wsi_net_add_pool_bias(void* net, int in_id, int in_c_off, int C, int out_id, int out_c_off, int k, int stride,
+                          int pad, int count_include_pad, const float* h_bias, int relu);
+/* ReLU of the convolution added last only on its first `cols` output channels (multiple of 64): lets the bias-free,
+ * ReLU-free 1x1 conv of a commuted pool branch ride in the same launch as its sibling 1x1 branch convs. */
+int wsi_net_set_conv_relu_cols(void* net, int cols);
 int wsi_net_add_head(void* net, int in_id, const float* h_fc_w, const float* h_fc_b, int K);
 int wsi_net_finalize(void* net);
 /* d_input: the external input tensor (bf16 NHWC, layout of wsi_preproc_run); d_probs: f32 [B][K]

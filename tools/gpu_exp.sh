@@ -9,3 +9,4 @@ run() {
 }
 MODEL=inceptionv4 run iv4_commute X=1
 MODEL=inceptionv4 run iv4_nocommute WSI_B200_NO_POOL_COMMUTE=1
+MODEL=inceptionv4 run iv4_nosib WSI_B200_NO_SIBLING_MERGE=1

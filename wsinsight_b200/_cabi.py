@@ -59,7 +59,9 @@ _PROTOS = {
     "wsi_net_add_stem7x7": (c_int, [c_void_p, c_int, c_int, c_float_p, c_float_p, c_int, c_int]),
     "wsi_net_add_stem_parity": (c_int, [c_void_p, c_int, c_int, c_float_p, c_float_p, c_int, c_int, c_int, c_int]),
     "wsi_net_add_pool": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int]),
-    "wsi_net_add_pool_bias": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_float_p, c_int]),
+    "wsi_net_add_pool_bias": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                      c_float_p, c_int]),
+    "wsi_net_set_conv_relu_cols": (c_int, [c_void_p, c_int]),
     "wsi_net_add_head": (c_int, [c_void_p, c_int, c_float_p, c_float_p, c_int]),
     "wsi_net_finalize": (c_int, [c_void_p]),
     "wsi_net_forward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),

@@ -48,6 +48,8 @@ struct Args {
                                              // stage is 16 KB + N_tile*64 B and the ring is 1.5x deeper (the single-CTA
                                              // ring starved: ncu showed the MMA warp waiting on TMA data 26 % of the time)
   int relu;
+  int relu_cols;                             // TMA epilogue: ReLU on output channels < relu_cols (merged sibling convs
+                                             // may end with a slice that has none); Cout or 0 for ordinary convs
   const __nv_bfloat16* residual;
   const float* bias;                         // [tiles_N * N_tile]
   __nv_bfloat16* out;
@@ -432,7 +434,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             ptx::mbar_wait(&resFull[g], res_phase);
             res_phase ^= 1;
             const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + 64 * j);
-            epi_chunk64_smemres(t_addr, row, myOut, sBias + nt * a.N_tile + 64 * j, a.relu);
+            epi_chunk64_smemres(t_addr, row, myOut, sBias + nt * a.N_tile + 64 * j, (nt * a.N_tile + 64 * j) < a.relu_cols);
             if (last) {
               ptx::tc_fence_before();
               __syncwarp();
@@ -477,9 +479,9 @@ __global__ void __launch_bounds__(THREADS, 1)
           ptx::named_bar_sync(1 + g, 128);              // the group's staging buffer is free again
           const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + 64 * j);
           if (full)
-            epi_chunk64_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, a.relu);
+            epi_chunk64_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, (nt * a.N_tile + 64 * j) < a.relu_cols);
           else
-            epi_chunk32_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, a.relu);
+            epi_chunk32_regs(t_addr, row, myOut, do_res, rv, sBias + nt * a.N_tile + 64 * j, (nt * a.N_tile + 64 * j) < a.relu_cols);
           if (last) {
             ptx::tc_fence_before();
             __syncwarp();

@@ -48,6 +48,8 @@ struct Op {
   std::vector<float> h_bias;
   int Cin, Cout, KH, KW, stride, pad_h, pad_w, relu, out_c_off, is_stem;
   int in_c_off = 0;               // first input channel read (slice of a wider tensor)
+  int relu_cols = -1;             // conv: ReLU only on output channels < relu_cols (-1: all, when relu is set)
+  int pC = 0;                     // pool: channels pooled (slice [in_c_off, in_c_off + pC) of the input tensor)
   int Ktot;
   // pool
   int pk, pstride, ppad, count_include_pad;
@@ -728,19 +730,45 @@ int wsi_net_add_pool(void* net, int in_id, int out_id, int out_c_off, int is_max
   return WSI_OK;
 }
 
+// ReLU of the conv added last only on its first `cols` output channels (multiple of 64).
+int wsi_net_set_conv_relu_cols(void* net, int cols) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized && !n->ops.empty() && n->ops.back().kind == OP_CONV, "wsi_net_set_conv_relu_cols: no conv");
+  Op& op = n->ops.back();
+  WSI_ARG_CHECK(op.relu && cols > 0 && cols <= op.Cout && cols % 64 == 0,
+                "wsi_net_set_conv_relu_cols: bad column count %d", cols);
+  op.relu_cols = cols;
+  return WSI_OK;
+}
+
 // 3x3 / stride 1 AVERAGE pool followed by + bias[c] and optional ReLU.  conv1x1(avgpool(x)) == avgpool(conv1x1(x))
 // (both linear, the divisor depends on the position only), so the engine runs the 1x1 conv of an Inception pool branch
 // FIRST (without bias / ReLU) and pools its 4-8x narrower output here: the wide block input is no longer read and
 // re-written by a pooling pass.
-int wsi_net_add_pool_bias(void* net, int in_id, int out_id, int out_c_off, int k, int stride, int pad,
+int wsi_net_add_pool_bias(void* net, int in_id, int in_c_off, int C, int out_id, int out_c_off, int k, int stride, int pad,
                           int count_include_pad, const float* bias, int relu) {
   Net* n = (Net*)net;
-  WSI_ARG_CHECK(n && k == 3 && stride == 1 && bias, "wsi_net_add_pool_bias: only 3x3 / stride 1 average pools");
-  int rc = wsi_net_add_pool(net, in_id, out_id, out_c_off, 0, k, stride, pad, count_include_pad);
-  if (rc) return rc;
-  Op& op = n->ops.back();
-  op.h_pbias.assign(bias, bias + n->tensors[in_id].C);
+  WSI_ARG_CHECK(n && !n->finalized && k == 3 && stride == 1 && bias,
+                "wsi_net_add_pool_bias: only 3x3 / stride 1 average pools");
+  WSI_ARG_CHECK(in_id >= 0 && in_id < (int)n->tensors.size() && out_id >= 0 && out_id < (int)n->tensors.size(),
+                "wsi_net_add_pool_bias: bad tensor id");
+  const Tensor& ti = n->tensors[in_id];
+  const Tensor& to = n->tensors[out_id];
+  const int Ho = ti.H + 2 * pad - k + 1, Wo = ti.W + 2 * pad - k + 1;
+  WSI_ARG_CHECK(Ho == to.H && Wo == to.W, "wsi_net_add_pool_bias: output shape mismatch");
+  WSI_ARG_CHECK(C > 0 && C % 8 == 0 && in_c_off >= 0 && in_c_off % 8 == 0 && in_c_off + C <= ti.C && !ti.external &&
+                    to.C % 8 == 0 && out_c_off % 8 == 0 && out_c_off + C <= to.C,
+                "wsi_net_add_pool_bias: channel layout");
+  Op op;
+  op.kind = OP_AVGPOOL;
+  op.in = in_id; op.out = out_id; op.res = -1;
+  op.pk = k; op.pstride = stride; op.ppad = pad; op.count_include_pad = count_include_pad;
+  op.out_c_off = out_c_off;
+  op.in_c_off = in_c_off;
+  op.pC = C;
+  op.h_pbias.assign(bias, bias + C);
   op.prelu = relu ? 1 : 0;
+  n->ops.push_back(std::move(op));
   return WSI_OK;
 }
 
@@ -765,10 +793,11 @@ int wsi_net_add_head(void* net, int in_id, const float* fc_w, const float* fc_b,
 // input tensor map of the TMA-ring pool kernel: (C, Wp, B*Hp) bf16, box = (ct vectors, box columns, one row)
 static int encode_pool_map(Net* n, Op& op, const void* base) {
   const Tensor& ti = n->tensors[op.in];
-  uint64_t dims[3] = {(uint64_t)ti.C, (uint64_t)ti.Wp(), (uint64_t)n->max_batch * ti.Hp()};
+  uint64_t dims[3] = {(uint64_t)(op.pC ? op.pC : ti.C), (uint64_t)ti.Wp(), (uint64_t)n->max_batch * ti.Hp()};
   uint64_t strides[2] = {(uint64_t)ti.C * 2, (uint64_t)ti.Wp() * ti.C * 2};
   uint32_t box[3] = {(uint32_t)op.pt_ct * 8, (uint32_t)op.pt_cols, 1};
   uint32_t es[3] = {1, 1, 1};
+  base = (const __nv_bfloat16*)base + op.in_c_off;
   return wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, strides, box, es,
                        CU_TENSOR_MAP_SWIZZLE_NONE);
 }
@@ -1076,6 +1105,9 @@ int wsi_net_finalize(void* net) {
       a.res_Hp = op.res >= 0 ? n->tensors[op.res].Hp() : 0;
       a.res_Wp = op.res >= 0 ? n->tensors[op.res].Wp() : 0;
       a.relu = op.relu;
+      a.relu_cols = op.relu ? (op.relu_cols >= 0 ? op.relu_cols : op.Cout) : 0;
+      WSI_ARG_CHECK(a.relu_cols == 0 || a.relu_cols == op.Cout || (a.tma_epi && a.relu_cols % 64 == 0),
+                    "wsi_net_finalize: partial ReLU needs the TMA epilogue and a 64-channel boundary");
       a.bias = op.d_bias;
       int smem = (int)convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout, a.cluster);
       if (smem > max_smem) max_smem = smem;
@@ -1135,7 +1167,7 @@ int wsi_net_finalize(void* net) {
       // 3x3 pools over internal tensors: tile plan + input tensor map of the TMA-ring kernel
       const Tensor& ti = n->tensors[op.in];
       const Tensor& to = n->tensors[op.out];
-      const int cv = ti.C / 8;
+      const int cv = (op.pC ? op.pC : ti.C) / 8;
       op.pt_ct = 0;
       if (op.pk == 3 && (op.pstride == 1 || op.pstride == 2) && ti.C % 8 == 0) {
         // stride 1: a thread owns two adjacent output columns (k_pool3s1_tma), so a slot is a column PAIR
@@ -1353,10 +1385,12 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       }
     } else if (op.kind == OP_MAXPOOL || op.kind == OP_AVGPOOL) {
       const Tensor& to = n->tensors[op.out];
-      const int cv = ti.C / 8;
+      const bool sliced = op.in_c_off != 0 || (op.pC != 0 && op.pC != ti.C);
+      const int cv = (op.pC ? op.pC : ti.C) / 8;
       const bool is_max = op.kind == OP_MAXPOOL;
+      WSI_ARG_CHECK(!sliced || op.pt_ct > 0, "wsi_net_forward: a pool over a channel slice needs the TMA-ring plan");
       if (op.pk == 3 && (op.pstride == 1 || op.pstride == 2)) {
-        if (n->pool_ring && op.pt_ct > 0) {
+        if ((n->pool_ring || sliced) && op.pt_ct > 0) {
           if (ti.external) {
             int rc = encode_pool_map(n, op, in_ptr);
             if (rc) return rc;

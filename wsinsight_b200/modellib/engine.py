@@ -184,15 +184,28 @@ class B200Network:
                         and int(n.weight.shape[0]) % 8 == 0
                         and all(nodes[j].kind == "conv" and how == "in" for j, how in users.get(i, []))):
                     sibs.setdefault((n.inputs[0], bool(n.relu)), []).append(i)
+            # the bias-free, ReLU-free 1x1 conv of a commuted pool branch reads the same input: it rides in the same
+            # launch as the LAST slice (ReLU only on the channels before it: wsi_net_set_conv_relu_cols)
+            for pi in sorted(conv_of_pool):
+                key = (nodes[pi].inputs[0], True)
+                if key in sibs:
+                    sibs[key].append(pi)
+
+            def mcout(m):
+                return int(nodes[conv_of_pool[m]].weight.shape[0]) if nodes[m].kind == "pool" else int(nodes[m].weight.shape[0])
+
             for (x, _), members in sibs.items():
-                if len(members) < 2 or sum(int(nodes[i].weight.shape[0]) for i in members) % 32:
+                relu_c = sum(mcout(m) for m in members if nodes[m].kind == "conv")
+                if any(nodes[m].kind == "pool" for m in members) and relu_c % 64:
+                    members = [m for m in members if nodes[m].kind == "conv"]
+                if len(members) < 2 or sum(mcout(m) for m in members) % 32:
                     continue
                 c, h, w = nodes[members[0]].shape
-                tid = self._add_tensor(h, w, sum(nodes[i].shape[0] for i in members))
+                tid = self._add_tensor(h, w, sum(mcout(m) for m in members))
                 off = 0
                 for i in members:
                     tensor_of[i], c_off[i] = tid, off
-                    off += nodes[i].shape[0]
+                    off += mcout(i)
                     merged_into[i] = members[0]
                 group_of[members[0]] = members
         self.merged_groups = list(group_of.values())
@@ -220,9 +233,34 @@ class B200Network:
                 b = (n.bias if n.bias is not None else __import__("torch").zeros(int(n.weight.shape[0]))).contiguous()
                 self._keep.append(b)
                 pn = nodes[pool_of_conv[i]]
-                _cabi.call("wsi_net_add_pool_bias", self._h, tensor_of[x], tensor_of[i], c_off[i], int(pn.k),
-                           int(pn.pstride), int(pn.ppad), 1 if pn.count_include_pad else 0, _fptr(b),
-                           1 if n.relu else 0)
+                _cabi.call("wsi_net_add_pool_bias", self._h, tensor_of[x], int(in_off), int(n.weight.shape[0]),
+                           tensor_of[i], c_off[i], int(pn.k), int(pn.pstride), int(pn.ppad),
+                           1 if pn.count_include_pad else 0, _fptr(b), 1 if n.relu else 0)
+                continue
+            if i in merged_into:
+                # one launch for the whole sibling group, emitted with its first visited member
+                import torch
+
+                if merged_into[i] in emitted_groups:
+                    continue
+                emitted_groups.add(merged_into[i])
+                ws, bs, relu_c, has_pool = [], [], 0, False
+                for m in group_of[merged_into[i]]:
+                    mn = nodes[conv_of_pool[m]] if nodes[m].kind == "pool" else nodes[m]
+                    ws.append(mn.weight)
+                    if nodes[m].kind == "pool":
+                        has_pool = True
+                        bs.append(torch.zeros(int(mn.weight.shape[0])))
+                    else:
+                        relu_c += int(mn.weight.shape[0])
+                        bs.append(mn.bias if mn.bias is not None else torch.zeros(int(mn.weight.shape[0])))
+                w, b = torch.cat(ws, 0).contiguous(), torch.cat(bs, 0).contiguous()
+                self._keep += [w, b]
+                first = nodes[group_of[merged_into[i]][0]]
+                _cabi.call("wsi_net_add_conv_slice", self._h, tensor_of[x], int(in_off), tensor_of[i], 0, _fptr(w),
+                           _fptr(b), int(w.shape[1]), int(w.shape[0]), 1, 1, 1, 0, 0, 1 if first.relu else 0, -1)
+                if has_pool:
+                    _cabi.call("wsi_net_set_conv_relu_cols", self._h, relu_c)
                 continue
             if n.kind == "pool" and i in conv_of_pool:
                 cn = nodes[conv_of_pool[i]]
@@ -232,22 +270,10 @@ class B200Network:
                            int(w.shape[1]), int(w.shape[0]), 1, 1, 1, 0, 0, 0, -1)
                 continue
             if n.kind == "conv":
-                if i in merged_into and merged_into[i] in emitted_groups:
-                    continue                       # already emitted with the first visited member of its group
                 cout, cin = int(n.weight.shape[0]), int(n.weight.shape[1])
                 w = n.weight.contiguous()
                 b = n.bias.contiguous() if n.bias is not None else None
                 out_off = c_off[i]
-                if i in merged_into:
-                    import torch
-
-                    emitted_groups.add(merged_into[i])
-                    out_off = 0
-                    ms = [nodes[j] for j in group_of[merged_into[i]]]
-                    w = torch.cat([m.weight for m in ms], 0).contiguous()
-                    b = torch.cat([m.bias if m.bias is not None else torch.zeros(int(m.weight.shape[0]))
-                                   for m in ms], 0).contiguous()
-                    cout = int(w.shape[0])
                 self._keep += [w, b]
                 if n is stem and stem3:
                     _cabi.call("wsi_net_add_stem_parity", self._h, tensor_of[x], tensor_of[i], _fptr(w), _fptr(b), cout,
