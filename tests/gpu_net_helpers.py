@@ -130,3 +130,29 @@ def run_single_pool(x_nchw, is_max, k, stride, pad, count_include_pad=False, out
         return out.float().permute(0, 3, 1, 2).cpu()
     finally:
         lib.wsi_net_destroy(net)
+
+
+def run_pool_bias(x_nchw, in_c_off, Cs, bias, relu, count_include_pad=False, out_channels=None, c_off=0):
+    """3x3/1/1 average pool + bias + ReLU over channels [in_c_off, in_c_off + Cs) of the input (wsi_net_add_pool_bias)."""
+    lib = _cabi.load()
+    B, Cc, H, W = x_nchw.shape
+    Ct = int(out_channels or Cs)
+    net = C.c_void_p()
+    _cabi.call("wsi_net_create", B, C.byref(net))
+    try:
+        tin, tout = C.c_int(), C.c_int()
+        _cabi.call("wsi_net_add_tensor", net, H, W, Cc, 0, C.byref(tin))
+        _cabi.call("wsi_net_add_tensor", net, H, W, Ct, 0, C.byref(tout))
+        b = bias.contiguous().float()
+        _cabi.call("wsi_net_add_pool_bias", net, tin.value, int(in_c_off), int(Cs), tout.value, int(c_off), 3, 1, 1,
+                   1 if count_include_pad else 0, C.cast(b.data_ptr(), _cabi.c_float_p), 1 if relu else 0)
+        _cabi.call("wsi_net_finalize", net)
+        xd = x_nchw.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+        _cabi.call("wsi_net_write_tensor", net, tin.value, B, xd.data_ptr(), _cabi.stream_ptr())
+        _cabi.call("wsi_net_forward", net, None, B, None, _cabi.stream_ptr())
+        out = torch.empty((B, H, W, Ct), dtype=torch.bfloat16, device="cuda")
+        _cabi.call("wsi_net_read_tensor", net, tout.value, B, out.data_ptr(), _cabi.stream_ptr())
+        torch.cuda.synchronize()
+        return out.float().permute(0, 3, 1, 2).cpu()
+    finally:
+        lib.wsi_net_destroy(net)

@@ -186,6 +186,27 @@ def test_single_pool_vs_torch(B, C, H, is_max, k, stride, pad, Ct, c_off, tma_ri
         assert rest.abs().max().item() == 0.0
 
 
+@pytest.mark.parametrize("B,Ctot,off,Cs,H,relu,cip", [
+    (2, 224, 128, 96, 35, True, False),     # Inception-A pool branch after the commute: slice of the sibling tensor
+    (2, 512, 384, 128, 17, True, False),    # Inception-B
+    (3, 1024, 768, 256, 8, True, False),    # Inception-C
+    (2, 64, 0, 64, 20, False, True),        # whole tensor, no ReLU, count_include_pad
+])
+def test_pool_bias_slice_vs_torch(B, Ctot, off, Cs, H, relu, cip):
+    """avg_pool2d(3,1,1) + bias + ReLU over a channel slice (wsi_net_add_pool_bias) vs torch in double."""
+    from gpu_net_helpers import run_pool_bias
+
+    g = torch.Generator().manual_seed(B + Ctot + H)
+    x = bf16_round(torch.randn((B, Ctot, H, H), generator=g))
+    bias = torch.randn((Cs,), generator=g)
+    got = run_pool_bias(x, off, Cs, bias, relu, count_include_pad=cip)
+    want = torch.nn.functional.avg_pool2d(x[:, off:off + Cs].double(), 3, 1, 1, count_include_pad=cip)
+    want = want + bias.double().view(1, -1, 1, 1)
+    if relu:
+        want = want.clamp_min(0)
+    assert (got.double() - want).abs().max().item() <= 2.0 ** -8 * max(1.0, want.abs().max().item())
+
+
 def _resnet_inputs(B, S, seed):
     g = torch.Generator().manual_seed(seed)
     # normalised-image-like values, exactly bf16 representable (what the preprocess kernel emits)
