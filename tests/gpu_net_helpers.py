@@ -156,3 +156,36 @@ def run_pool_bias(x_nchw, in_c_off, Cs, bias, relu, count_include_pad=False, out
         return out.float().permute(0, 3, 1, 2).cpu()
     finally:
         lib.wsi_net_destroy(net)
+
+
+def run_conv_slice(x_nchw, in_c_off, w, b, stride, pad, relu_cols=None, expect_flat=None):
+    """Conv over channels [in_c_off, in_c_off + Cin) of a wider tensor (wsi_net_add_conv_slice) with ReLU on the first
+    ``relu_cols`` output channels only (wsi_net_set_conv_relu_cols; None = plain ReLU on all)."""
+    lib = _cabi.load()
+    B, Ctot, H, W = x_nchw.shape
+    Cout, Cin, KH, KW = w.shape
+    Ho, Wo = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+    net = C.c_void_p()
+    _cabi.call("wsi_net_create", B, C.byref(net))
+    try:
+        tin, tout = C.c_int(), C.c_int()
+        _cabi.call("wsi_net_add_tensor", net, H, W, Ctot, 0, C.byref(tin))
+        _cabi.call("wsi_net_add_tensor", net, Ho, Wo, Cout, 0, C.byref(tout))
+        wc, bc = w.contiguous().float().cpu(), b.contiguous().float().cpu()
+        _cabi.call("wsi_net_add_conv_slice", net, tin.value, int(in_c_off), tout.value, 0,
+                   C.cast(wc.data_ptr(), _cabi.c_float_p), C.cast(bc.data_ptr(), _cabi.c_float_p), Cin, Cout, KH, KW,
+                   stride, pad, pad, 1, -1)
+        if relu_cols is not None:
+            _cabi.call("wsi_net_set_conv_relu_cols", net, int(relu_cols))
+        _cabi.call("wsi_net_finalize", net)
+        xd = x_nchw.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+        _cabi.call("wsi_net_write_tensor", net, tin.value, B, xd.data_ptr(), _cabi.stream_ptr())
+        _cabi.call("wsi_net_forward", net, None, B, None, _cabi.stream_ptr())
+        out = torch.empty((B, Ho, Wo, Cout), dtype=torch.bfloat16, device="cuda")
+        _cabi.call("wsi_net_read_tensor", net, tout.value, B, out.data_ptr(), _cabi.stream_ptr())
+        if expect_flat is not None:
+            assert bool(lib.wsi_net_op_is_flat(net, 0)) == expect_flat
+        torch.cuda.synchronize()
+        return out.float().permute(0, 3, 1, 2).cpu()
+    finally:
+        lib.wsi_net_destroy(net)

@@ -207,6 +207,28 @@ def test_pool_bias_slice_vs_torch(B, Ctot, off, Cs, H, relu, cip):
     assert (got.double() - want).abs().max().item() <= 2.0 ** -8 * max(1.0, want.abs().max().item())
 
 
+@pytest.mark.parametrize("B,Ctot,off,Cin,H,Cout,k,pad,relu_cols,flat", [
+    (2, 384, 0, 384, 35, 224, 1, 0, 128, False),    # Inception-A sibling launch: ReLU on the first two slices only
+    (2, 1024, 0, 1024, 17, 512, 1, 0, 384, False),  # Inception-B (two N tiles)
+    (2, 224, 64, 64, 35, 96, 3, 1, None, True),     # branch 3x3 reading slice [64, 128) of the sibling tensor (flat kernel)
+    (2, 512, 192, 192, 17, 224, 1, 0, None, False), # per-tap kernel over a slice in the middle of the tensor
+    (1, 160, 96, 40, 20, 64, 1, 0, None, False),    # slice at the end, Cin % 64 != 0 (TMA zero fill past the slice)
+])
+def test_conv_slice_partial_relu_vs_torch(B, Ctot, off, Cin, H, Cout, k, pad, relu_cols, flat):
+    """wsi_net_add_conv_slice / wsi_net_set_conv_relu_cols (what the merged Inception branch convs use) vs torch."""
+    from gpu_net_helpers import run_conv_slice
+
+    g = torch.Generator().manual_seed(B + Ctot + off + Cout)
+    x = bf16_round(torch.randn((B, Ctot, H, H), generator=g))
+    w = bf16_round(torch.randn((Cout, Cin, k, k), generator=g) / (Cin * k * k) ** 0.5)
+    b = torch.randn(Cout, generator=g) * 0.1
+    got = run_conv_slice(x, off, w, b, 1, pad, relu_cols=relu_cols, expect_flat=flat)
+    want = conv_reference(x[:, off:off + Cin], w, b, 1, pad)
+    rc = Cout if relu_cols is None else relu_cols
+    want = torch.cat([want[:, :rc].clamp_min(0), want[:, rc:]], 1)
+    _check(got, want, f"conv slice {Ctot}[{off}:{off + Cin}] -> {Cout} relu_cols {relu_cols}")
+
+
 def _resnet_inputs(B, S, seed):
     g = torch.Generator().manual_seed(seed)
     # normalised-image-like values, exactly bf16 representable (what the preprocess kernel emits)
