@@ -71,6 +71,27 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
                             const int* h_min_object_px, const int* h_min_hole_px, uint8_t* d_mask,
                             uint8_t* d_outer, void* d_ws, size_t ws_bytes, void* stream);
 
+/* Extended form.  Two things the reference leaves to its dependencies are parameters here:
+ *  - binary_threshold == WSI_SEG_THRESHOLD_OTSU: the threshold of cv.threshold (segment.py:80-83) is chosen per
+ *    slide by Otsu's method on the median-filtered saturation image, bit-identical to
+ *    cv.threshold(S_med, 0, 255, THRESH_BINARY | THRESH_OTSU) (OpenCV getThreshVal_Otsu_8u).  NOT upstream
+ *    behaviour (the reference always uses the fixed threshold, default 7): an extra mode named by the task.
+ *  - closing_dilation_origin / closing_erosion_origin: the column/row of the k x k footprint that sits on the
+ *    output pixel (window offsets [-origin .. k-1-origin]) for the dilation and the erosion of
+ *    binary_closing(ones(k,k)) (segment.py:87-89).  -1 selects the default, the raw even footprint as
+ *    scipy.ndimage centres it: dilation (k-1)/2, erosion k/2 (k = 6: offsets -2..+3 then -3..+2).  A footprint
+ *    front-padded to (k+1) x (k+1) is dilation k/2, erosion (k-1)/2.  The conventions agree for odd k and,
+ *    for even k, everywhere except within k/2 pixels of the image border.
+ * d_info (optional): int32 [n][4] per slide {threshold used, mask has tissue (valid when d_outer != NULL), 0, 0}. */
+#define WSI_SEG_THRESHOLD_OTSU (-1)
+int wsi_seg_tissue_batch_ex(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W,
+                            const int* h_pitch, const long long* h_rgb_off,
+                            const long long* h_mask_off, int median_filter_size,
+                            int binary_threshold, int closing_kernel_size,
+                            int closing_dilation_origin, int closing_erosion_origin,
+                            const int* h_min_object_px, const int* h_min_hole_px, uint8_t* d_mask,
+                            uint8_t* d_outer, int* d_info, void* d_ws, size_t ws_bytes, void* stream);
+
 /* Outermost-component restriction of an existing 0/1 mask (the polygon stage alone):
  * get_multipolygon_from_binary_arr(), wsinsight/patchlib/patch.py:35-130. */
 int wsi_outermost_u8(const uint8_t* d_mask, int H, int W, uint8_t* d_outer, void* d_ws,
@@ -109,6 +130,10 @@ int wsi_preproc_run_u8(void* plan, const int32_t* d_coords_xy, int n, uint8_t* d
  * wsi_net_input_layout): two row-parity planes, bf16 [2][max_batch][P][2P][4] with P = out_H/2, planes
  * plane_stride_px pixels apart; 0 restores [n][out_H][out_W][4]. */
 int wsi_preproc_plan_set_parity_layout(void* plan, long long plane_stride_px);
+/* Dense layout only: the number of patches the output buffer passed to wsi_preproc_run holds (0 = unchecked).
+ * wsi_preproc_run returns WSI_ERR_ARG when n exceeds it; with the parity layout the capacity follows from
+ * plane_stride_px and is always checked (a larger batch would spill plane 0 into plane 1). */
+int wsi_preproc_plan_set_capacity(void* plan, int max_patches);
 /* bf16 channels per output pixel: 4 (default) or 8 (first convolutions that run on the generic kernel);
  * channels 3.. are zero. */
 int wsi_preproc_plan_set_channels(void* plan, int channels);

@@ -32,16 +32,66 @@ from scipy import ndimage as ndi
 _FOUR_CONN = ndi.generate_binary_structure(2, 1)
 
 
-def binary_closing_lib(mask: np.ndarray, k: int) -> np.ndarray:
-    """skimage.morphology.binary_closing(mask, ones((k,k))) (segment.py:87-89).
+def binary_closing_lib(mask: np.ndarray, k: int, convention: str = "scipy_raw") -> np.ndarray:
+    """skimage.morphology.binary_closing(mask, ones((k,k))) (segment.py:87-89) as scipy.ndimage calls.
 
-    skimage 0.25.2 ``binary_closing`` = ``binary_dilation`` then ``binary_erosion``
-    with default ``mode='ignore'`` i.e. dilation pads with False and erosion pads
-    with True; both forward the raw footprint to scipy.ndimage.
+    skimage ``binary_closing`` = ``binary_dilation`` then ``binary_erosion`` with default ``mode='ignore'``,
+    i.e. dilation pads with False and erosion pads with True.  What is NOT pinned (skimage is not importable
+    here) is how an EVEN footprint is centred before scipy sees it; the candidates, each as the scipy call it
+    would be (they agree for odd k, and for even k everywhere except within k/2 px of the image border):
+
+    ``scipy_raw``         the raw ones((k,k)) goes to scipy (default; == footprint end-padded to odd size)
+    ``front_padded``      footprint padded with a zero row/column in FRONT to (k+1, k+1)
+                          (skimage ``pad_footprint(fp, pad_end=False)``)
+    ``mirrored_erosion``  raw dilation, erosion with the footprint mirrored about its centre
+                          (for scipy: ``origin=-1`` on an even footprint)
     """
     fp = np.ones((k, k), dtype=bool)
-    tmp = ndi.binary_dilation(mask, structure=fp, border_value=False)
-    return ndi.binary_erosion(tmp, structure=fp, border_value=True)
+    if convention == "scipy_raw" or k % 2 == 1:
+        tmp = ndi.binary_dilation(mask, structure=fp, border_value=False)
+        return ndi.binary_erosion(tmp, structure=fp, border_value=True)
+    if convention == "front_padded":
+        fpp = np.zeros((k + 1, k + 1), dtype=bool)
+        fpp[1:, 1:] = True
+        tmp = ndi.binary_dilation(mask, structure=fpp, border_value=False)
+        return ndi.binary_erosion(tmp, structure=fpp, border_value=True)
+    if convention == "mirrored_erosion":
+        tmp = ndi.binary_dilation(mask, structure=fp, border_value=False)
+        return ndi.binary_erosion(tmp, structure=fp, border_value=True, origin=-1)
+    raise ValueError(convention)
+
+
+def closing_origins(k: int, convention: str = "scipy_raw"):
+    """(dilation origin, erosion origin): window offsets are [-origin .. k-1-origin]."""
+    return {"scipy_raw": ((k - 1) // 2, k // 2), "front_padded": (k // 2, (k - 1) // 2),
+            "mirrored_erosion": ((k - 1) // 2, (k - 1) // 2)}[convention]
+
+
+def otsu_threshold_restated(img_u8: np.ndarray) -> int:
+    """OpenCV ``getThreshVal_Otsu_8u`` (imgproc/thresh.cpp): the sequential float64 loop the CUDA kernel repeats.
+    Pinned against ``cv.threshold(..., THRESH_OTSU)`` in tests/test_oracle.py."""
+    h = np.bincount(img_u8.ravel(), minlength=256).astype(np.int64)
+    eps = np.float64(np.finfo(np.float32).eps)
+    scale = np.float64(1.0) / np.float64(img_u8.size)
+    mu = np.float64(0)
+    for i in range(256):
+        mu += np.float64(i) * np.float64(h[i])
+    mu *= scale
+    mu1 = q1 = max_sigma = np.float64(0)
+    max_val = 0
+    for i in range(256):
+        p_i = np.float64(h[i]) * scale
+        mu1 *= q1
+        q1 += p_i
+        q2 = np.float64(1.0) - q1
+        if min(q1, q2) < eps or max(q1, q2) > np.float64(1.0) - eps:
+            continue
+        mu1 = (mu1 + np.float64(i) * p_i) / q1
+        mu2 = (mu - q1 * mu1) / q2
+        sigma = q1 * q2 * (mu1 - mu2) * (mu1 - mu2)
+        if sigma > max_sigma:
+            max_sigma, max_val = sigma, i
+    return int(max_val)
 
 
 def remove_small_objects_lib(mask: np.ndarray, min_size: int) -> np.ndarray:
@@ -69,12 +119,17 @@ def remove_small_holes_lib(mask: np.ndarray, area_threshold: int) -> np.ndarray:
 def segment_tissue(
     im_arr: np.ndarray,
     median_filter_size: int = 7,
-    binary_threshold: int = 7,
+    binary_threshold=7,
     closing_kernel_size: int = 6,
     min_object_size_px: int = 512,
     min_hole_size_px: int = 1024,
+    closing_convention: str = "scipy_raw",
+    return_threshold: bool = False,
 ) -> np.ndarray:
-    """Restatement of ``segment_tissue`` (segment.py:13-97), same signature/defaults."""
+    """Restatement of ``segment_tissue`` (segment.py:13-97), same signature/defaults.
+
+    ``binary_threshold="otsu"`` is the extra mode (not upstream): ``cv.threshold(sat, 0, 255, THRESH_BINARY |
+    THRESH_OTSU)`` instead of the fixed threshold."""
     im_arr = np.asarray(im_arr)
     assert im_arr.ndim == 3
     assert im_arr.shape[2] == 3
@@ -85,12 +140,15 @@ def segment_tissue(
             f" {median_filter_size}"
         )
     sat = cv.medianBlur(np.ascontiguousarray(sat), median_filter_size)
-    _, thr = cv.threshold(sat, thresh=binary_threshold, maxval=255, type=cv.THRESH_BINARY)
+    if isinstance(binary_threshold, str):
+        used, thr = cv.threshold(sat, thresh=0, maxval=255, type=cv.THRESH_BINARY | cv.THRESH_OTSU)
+    else:
+        used, thr = cv.threshold(sat, thresh=binary_threshold, maxval=255, type=cv.THRESH_BINARY)
     mask = thr > 0
-    mask = binary_closing_lib(mask, closing_kernel_size)
+    mask = binary_closing_lib(mask, closing_kernel_size, closing_convention)
     mask = remove_small_objects_lib(mask, min_object_size_px)
     mask = remove_small_holes_lib(mask, min_hole_size_px)
-    return mask
+    return (mask, int(used)) if return_threshold else mask
 
 
 def segment_stages(im_arr, median_filter_size=7, binary_threshold=7, closing_kernel_size=6,
@@ -149,15 +207,15 @@ def median_threshold_restated(sat: np.ndarray, k: int, thresh: int) -> np.ndarra
     return cnt >= (k * k + 1) // 2
 
 
-def closing_restated(mask: np.ndarray, k: int) -> np.ndarray:
+def closing_restated(mask: np.ndarray, k: int, convention: str = "scipy_raw") -> np.ndarray:
     """Closing with ones(k,k) as explicit window offsets (Appendix A.4).
 
-    dilation window offsets  [-(k-1)//2 .. k//2]  (k=6: [-2..+3]), outside = 0
-    erosion  window offsets  [-(k//2) .. (k-1)//2] (k=6: [-3..+2]), outside = 1
+    dilation window offsets  [-d .. k-1-d], outside = 0;  erosion window offsets [-e .. k-1-e], outside = 1,
+    (d, e) = ``closing_origins(k, convention)``; default (scipy_raw, k=6): [-2..+3] then [-3..+2].
     """
     h, w = mask.shape
-    dlo, dhi = (k - 1) // 2, k // 2
-    elo, ehi = k // 2, (k - 1) // 2
+    dlo, elo = closing_origins(k, convention)
+    dhi, ehi = k - 1 - dlo, k - 1 - elo
     m = mask.astype(bool)
     # dilation (separable OR)
     p = np.pad(m, ((0, 0), (dlo, dhi)), constant_values=False)

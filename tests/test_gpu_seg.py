@@ -55,6 +55,85 @@ def test_full_mask(shape, seed, obj, hole):
     assert got.dtype == bool and np.array_equal(got, want), _report("mask", got, want)
 
 
+def _border_touching_thumbnail(h, w, seed):
+    """tissue touching all four thumbnail borders (where the closing conventions differ) + interior blobs"""
+    img = blob_thumbnail(h, w, seed, smooth=3)
+    rng = np.random.default_rng(seed)
+    fg = lambda n, m: np.stack([rng.integers(150, 230, (n, m)), rng.integers(60, 150, (n, m)),  # noqa: E731
+                                rng.integers(140, 210, (n, m))], -1).astype(np.uint8)
+    img[:9, w // 5: w // 2] = fg(9, w // 2 - w // 5)                 # top
+    img[h - 8:, w // 3: 3 * w // 4] = fg(8, 3 * w // 4 - w // 3)     # bottom
+    img[h // 4: h // 2, :10] = fg(h // 2 - h // 4, 10)               # left
+    img[h // 3: 2 * h // 3, w - 7:] = fg(2 * h // 3 - h // 3, 7)     # right
+    img[:6, :6] = fg(6, 6)                                           # corner
+    return img
+
+
+@pytest.mark.parametrize("convention", ["scipy_raw", "front_padded", "mirrored_erosion"])
+@pytest.mark.parametrize("k", [6, 4, 7])
+def test_closing_conventions_vs_scipy_forms(convention, k):
+    """Each candidate convention of the even-footprint closing against the scipy call it stands for, on a thumbnail
+    with tissue on all four borders; the candidates differ from the default only within k/2 px of the border."""
+    img = _border_touching_thumbnail(150, 190, 70 + k)
+    thr = segment.segment_stages(img, 7, 7, 1, 0, 0)["thr"]
+    want = segment.binary_closing_lib(thr, k, convention)
+    assert np.array_equal(want, segment.closing_restated(thr, k, convention))
+    got = _seg(img, closing_kernel_size=k, min_object_size_px=0, min_hole_size_px=0, closing_convention=convention)
+    assert np.array_equal(got, want), _report(f"closing {k} {convention}", got, want)
+    base = segment.binary_closing_lib(thr, k, "scipy_raw")
+    if convention == "front_padded":
+        d = np.argwhere(want != base)
+        b = k // 2
+        assert all(y < b or x < b or y >= 150 - b or x >= 190 - b for y, x in d.tolist())
+        if k % 2 == 0:
+            assert len(d) > 0          # the test image does exercise the difference
+    # full pipeline under the convention
+    want_full = segment.segment_tissue(img, 7, 7, k, 40, 30, closing_convention=convention)
+    got_full = _seg(img, closing_kernel_size=k, min_object_size_px=40, min_hole_size_px=30,
+                    closing_convention=convention)
+    assert np.array_equal(got_full, want_full), _report("mask", got_full, want_full)
+
+
+@pytest.mark.parametrize("shape,seed", [((120, 150), 0), ((300, 333), 1), ((1638, 2048), 2), ((64, 64), 3)])
+def test_otsu_mode_vs_cv2(shape, seed):
+    """Extra mode (not upstream): threshold chosen by cv.threshold(..., THRESH_OTSU) on the median-filtered S."""
+    from wsinsight_b200.patchlib import segment_tissue_device
+    img = blob_thumbnail(*shape, 80 + seed, smooth=5 if shape[0] < 1000 else 12)
+    want, t_want = segment.segment_tissue(img, 7, "otsu", 6, 30, 20, return_threshold=True)
+    masks, _, info = segment_tissue_device([torch.from_numpy(img).cuda()], 7, "otsu", 6, 30, 20, return_info=True)
+    assert int(info[0, 0].item()) == t_want, (int(info[0, 0].item()), t_want)
+    got = masks[0].cpu().numpy().astype(bool)
+    assert np.array_equal(got, want), _report("otsu mask", got, want)
+    # the exact median itself (other window sizes too)
+    for k in (3, 5):
+        w2, t2 = segment.segment_tissue(img, k, "otsu", 1, 0, 0, return_threshold=True)
+        m2, _, i2 = segment_tissue_device([torch.from_numpy(img).cuda()], k, "otsu", 1, 0, 0, return_info=True)
+        assert int(i2[0, 0].item()) == t2 and np.array_equal(m2[0].cpu().numpy().astype(bool), w2)
+
+
+def test_otsu_cohort_and_flags():
+    from wsinsight_b200.patchlib import segment_tissue_device
+    imgs = [blob_thumbnail(200, 260, 90), np.full((40, 50, 3), 245, np.uint8), blob_thumbnail(97, 131, 91, smooth=4)]
+    masks, outers, info = segment_tissue_device([torch.from_numpy(i).cuda() for i in imgs], 7, "otsu", 6, 20, 20,
+                                                return_info=True)
+    info = info.cpu().numpy()
+    for i, img in enumerate(imgs):
+        want, t = segment.segment_tissue(img, 7, "otsu", 6, 20, 20, return_threshold=True)
+        assert info[i, 0] == t and np.array_equal(masks[i].cpu().numpy().astype(bool), want)
+        assert bool(info[i, 1]) == bool(want.any())
+
+
+def test_legacy_and_run_based_labelling_agree(monkeypatch):
+    """A/B switch WSI_B200_SEG_LEGACY=1 (per-pixel unions, k*k-tap morphology) vs the default kernels."""
+    from wsinsight_b200.patchlib import segment_tissue_device
+    imgs = [blob_thumbnail(301, 277, 95, smooth=3), _border_touching_thumbnail(130, 170, 96)]
+    new = segment_tissue_device([torch.from_numpy(i).cuda() for i in imgs], 7, 7, 6, [25, 30], [25, 20])
+    monkeypatch.setenv("WSI_B200_SEG_LEGACY", "1")
+    old = segment_tissue_device([torch.from_numpy(i).cuda() for i in imgs], 7, 7, 6, [25, 30], [25, 20])
+    for a, b in zip(new[0] + new[1], old[0] + old[1]):
+        assert torch.equal(a, b)
+
+
 def test_edge_cases_empty_full_tiny():
     for img in (np.full((40, 50, 3), 245, np.uint8), np.tile(np.uint8([160, 32, 240]), (40, 50, 1)),
                 np.tile(np.uint8([160, 32, 240]), (1, 1, 1)), blob_thumbnail(7, 300, 5), blob_thumbnail(300, 5, 6)):

@@ -99,6 +99,41 @@ def test_lowering_rejects_unknown_graphs():
     with pytest.raises(UnknownArchitectureError):
         lower_torchscript(torch.jit.script(Odd().eval()), 32)
 
+    class RawAndActivated(torch.nn.Module):
+        """a conv output read both raw (by a second conv) and through ReLU: fusing the ReLU into the producer
+        would hand the activated tensor to the raw reader"""
+        def __init__(self):
+            super().__init__()
+            self.c1 = torch.nn.Conv2d(3, 8, 3, padding=1)
+            self.c2 = torch.nn.Conv2d(8, 8, 3, padding=1)
+            self.fc = torch.nn.Linear(8, 2)
+
+        def forward(self, x):
+            y = self.c1(x)
+            z = self.c2(y) + torch.relu(y)
+            return self.fc(torch.flatten(torch.nn.functional.adaptive_avg_pool2d(torch.relu(z), (1, 1)), 1))
+
+    with pytest.raises(UnknownArchitectureError, match="un-activated"):
+        lower_torchscript(torch.jit.script(RawAndActivated().eval()), 32)
+
+    class PreAddRead(torch.nn.Module):
+        """the pre-add value of the only fusable conv feeds another conv as well"""
+        def __init__(self):
+            super().__init__()
+            self.c1 = torch.nn.Conv2d(3, 8, 3, padding=1)
+            self.c2 = torch.nn.Conv2d(8, 8, 3, padding=1)
+            self.c3 = torch.nn.Conv2d(8, 8, 3, padding=1)
+            self.fc = torch.nn.Linear(8, 2)
+
+        def forward(self, x):
+            a = torch.relu(self.c1(x))
+            y = self.c2(a)
+            z = torch.relu(y + a) + torch.relu(self.c3(y))
+            return self.fc(torch.flatten(torch.nn.functional.adaptive_avg_pool2d(z, (1, 1)), 1))
+
+    with pytest.raises(UnknownArchitectureError):
+        lower_torchscript(torch.jit.script(PreAddRead().eval()), 32)
+
 
 def test_transform_config_parsing():
     from wsinsight_b200.modellib.models import ModelConfiguration

@@ -153,3 +153,41 @@ def test_preprocess_lib_normalize_and_padding():
     u8 = preprocess.resize_restated_u8(crop[..., :3], 64, 64)
     want = preprocess.normalize_restated(u8, mean, std).transpose(2, 0, 1)
     assert np.array_equal(t, want)
+
+
+def test_otsu_restatement_vs_cv2():
+    """The float64 loop the CUDA kernel repeats (oracle.segment.otsu_threshold_restated) against cv.threshold(OTSU)."""
+    import cv2
+    from oracle import segment
+    rng = np.random.default_rng(0)
+    for t in range(60):
+        h, w = rng.integers(5, 200, 2)
+        kind = t % 4
+        if kind == 0:
+            img = rng.integers(0, 256, (h, w)).astype(np.uint8)
+        elif kind == 1:
+            img = np.clip(rng.normal(rng.integers(0, 255), rng.integers(1, 60), (h, w)), 0, 255).astype(np.uint8)
+        elif kind == 2:
+            img = np.where(rng.random((h, w)) < rng.random(), np.clip(rng.normal(30, 10, (h, w)), 0, 255),
+                           np.clip(rng.normal(180, 30, (h, w)), 0, 255)).astype(np.uint8)
+        else:
+            img = np.full((h, w), rng.integers(0, 256), np.uint8)
+        t_cv, _ = cv2.threshold(img, 0, 255, cv2.THRESH_BINARY | cv2.THRESH_OTSU)
+        assert int(t_cv) == segment.otsu_threshold_restated(img)
+
+
+def test_closing_conventions_restated_vs_scipy():
+    """Every candidate footprint-origin convention: explicit window offsets == the scipy call it stands for; the
+    front-padded candidate differs from the default only within k/2 px of the border (VERDICT r1 weak #2)."""
+    from conftest import blob_mask
+    from oracle import segment
+    for conv in ("scipy_raw", "front_padded", "mirrored_erosion"):
+        for k in (2, 3, 4, 6, 7, 8):
+            for t in range(3):
+                m = blob_mask(80, 90, t + k, density=0.5, smooth=2.0)
+                m[0:5, 10:30] = True
+                m[:, 0] |= (t % 2 == 1)
+                assert np.array_equal(segment.binary_closing_lib(m, k, conv), segment.closing_restated(m, k, conv))
+    m = blob_mask(80, 90, 3, density=0.5, smooth=2.0)
+    d = np.argwhere(segment.binary_closing_lib(m, 6, "scipy_raw") != segment.binary_closing_lib(m, 6, "front_padded"))
+    assert len(d) > 0 and all(y < 3 or x < 3 or y >= 77 or x >= 87 for y, x in d.tolist())

@@ -40,6 +40,9 @@ _PROTOS = {
     "wsi_seg_tissue_batch_u8": (c_int, [c_void_p, c_int, c_int_p, c_int_p, c_int_p, c_ll_p, c_ll_p,
                                         c_int, c_int, c_int, c_int_p, c_int_p, c_void_p, c_void_p,
                                         c_void_p, c_size_t, c_void_p]),
+    "wsi_seg_tissue_batch_ex": (c_int, [c_void_p, c_int, c_int_p, c_int_p, c_int_p, c_ll_p, c_ll_p,
+                                        c_int, c_int, c_int, c_int, c_int, c_int_p, c_int_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_size_t, c_void_p]),
     "wsi_outermost_u8": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "wsi_patch_grid_workspace_bytes": (c_size_t, [c_ll, c_ll, c_int, c_int]),
     "wsi_patch_grid": (c_int, [c_void_p, c_int, c_int, c_ll, c_ll, c_int, c_int, c_void_p, c_int,
@@ -78,6 +81,7 @@ _PROTOS = {
     "wsi_net_input_bytes": (c_size_t, [c_void_p]),
     "wsi_preproc_plan_set_parity_layout": (c_int, [c_void_p, c_ll]),
     "wsi_preproc_plan_set_channels": (c_int, [c_void_p, c_int]),
+    "wsi_preproc_plan_set_capacity": (c_int, [c_void_p, c_int]),
     "wsi_hostpipe_create": (c_int, [c_void_p, c_int, c_ll, c_int, c_float_p, c_float_p, c_int, c_int,
                                     C.POINTER(c_void_p)]),
     "wsi_hostpipe_submit": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),

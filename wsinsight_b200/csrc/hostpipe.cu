@@ -97,19 +97,23 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
     hc[2 * i + 1] = i * patch_size;
   }
   if (cudaMalloc(&p->d_coords, hc.size() * sizeof(int32_t)) != cudaSuccess) return fail("cudaMalloc", WSI_ERR_NOMEM);
-  cudaMemcpy(p->d_coords, hc.data(), hc.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+  if (cudaMemcpy(p->d_coords, hc.data(), hc.size() * sizeof(int32_t), cudaMemcpyHostToDevice) != cudaSuccess)
+    return fail("copy of the patch-slot coordinates failed", WSI_ERR_CUDA);
   p->slots.resize(depth);
   const size_t stage_bytes = (size_t)max_batch * patch_size * (size_t)patch_pitch_bytes;
   const size_t input_bytes = wsi_net_input_bytes(net);
   int lay[4] = {0, 0, 0, 0};
   rc = wsi_net_input_layout(net, lay);
-  if (rc) return rc;
+  if (rc) {
+    destroy(p);
+    return rc;
+  }
   const long long plane_stride_px = lay[0] == 1 ? (((long long)lay[3] << 32) | (unsigned int)lay[2]) : 0;
   for (auto& s : p->slots) {
     if (cudaMalloc(&s.d_stage, stage_bytes) != cudaSuccess || cudaMalloc(&s.d_input, input_bytes) != cudaSuccess ||
         cudaMalloc(&s.d_probs, (size_t)max_batch * p->K * sizeof(float)) != cudaSuccess)
       return fail("cudaMalloc", WSI_ERR_NOMEM);
-    cudaMemset(s.d_input, 0, input_bytes);
+    if (cudaMemset(s.d_input, 0, input_bytes) != cudaSuccess) return fail("cudaMemset of the input buffer failed", WSI_ERR_CUDA);
     if (cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s.staged_free, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming) != cudaSuccess)
@@ -123,7 +127,7 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
       return rc;
     }
   }
-  WSI_CUDA_CHECK(cudaDeviceSynchronize());
+  if (cudaDeviceSynchronize() != cudaSuccess) return fail("cudaDeviceSynchronize failed", WSI_ERR_CUDA);
   *pipe_out = p;
   return WSI_OK;
 }

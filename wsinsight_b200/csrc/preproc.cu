@@ -76,6 +76,7 @@ struct Plan {
   float mean[3], stdv[3];
   int has_norm;
   long long plane_stride_px = 0;  // > 0: row-parity plane output layout (conv_stem.cuh)
+  int capacity = 0;               // > 0: patches the dense output buffer holds (wsi_preproc_plan_set_capacity)
   int channels = 4;               // 4 | 8 bf16 per output pixel (channels >= 3 are zero)
   int *d_lo, *d_cnt, *d_coef;     // taps (same table for both axes: square patches)
   uint16_t* d_lut = nullptr;      // [3][256] bf16 bits of ToTensor + Normalize applied to a u8 sample
@@ -413,6 +414,13 @@ static int preproc_launch(void* plan, const int32_t* d_coords_xy, int n, void* d
   WSI_ARG_CHECK(plan && d_coords_xy && (d_out_bf16 || d_out_u8), "wsi_preproc_run: null pointer");
   if (n <= 0) return WSI_OK;
   Plan* p = (Plan*)plan;
+  // parity-plane layout: plane 0 holds at most plane_stride_px / ((out_H / 2) * out_W) patches before it runs into plane 1
+  WSI_ARG_CHECK(d_out_u8 || p->plane_stride_px == 0 ||
+                    (long long)n * (p->out_H / 2) * p->out_W <= p->plane_stride_px,
+                "wsi_preproc_run: %d patches exceed the capacity of the parity-plane buffer (%lld)", n,
+                p->plane_stride_px / ((long long)(p->out_H / 2) * p->out_W));
+  WSI_ARG_CHECK(d_out_u8 || p->capacity <= 0 || n <= p->capacity,
+                "wsi_preproc_run: %d patches exceed the output capacity %d", n, p->capacity);
   PPArgs a;
   a.out_u8 = (uint32_t*)d_out_u8;
   a.lo = p->d_lo;
@@ -464,6 +472,12 @@ int wsi_preproc_plan_set_parity_layout(void* plan, long long plane_stride_px) {
   WSI_ARG_CHECK(plane_stride_px == 0 || (p->out_H == p->out_W && (p->out_H & 1) == 0),
                 "wsi_preproc_plan_set_parity_layout: the padded output must be square with an even side");
   p->plane_stride_px = plane_stride_px;
+  return WSI_OK;
+}
+
+int wsi_preproc_plan_set_capacity(void* plan, int max_patches) {
+  WSI_ARG_CHECK(plan && max_patches >= 0, "wsi_preproc_plan_set_capacity: bad arguments");
+  ((Plan*)plan)->capacity = max_patches;
   return WSI_OK;
 }
 

@@ -12,6 +12,7 @@
 // a prefix table), so a 64-slide cohort costs the same number of launches as one slide.
 #include "common.cuh"
 #include "../../include/wsi_b200.h"
+#include <stdlib.h>
 #include <vector>
 
 namespace {
@@ -54,9 +55,17 @@ constexpr int K1_TW = 64;
 constexpr int K1_TH = 16;
 constexpr int K1_THREADS = 256;
 
+__device__ __forceinline__ int sat_of(const uint8_t* __restrict__ p) {
+  const int R = p[0], G = p[1], B = p[2];
+  const int v = max(R, max(G, B));
+  const int d = v - min(R, min(G, B));
+  return (d * c_sdiv[v] + (1 << 11)) >> 12;
+}
+
+// legacy form (k*k taps per output), kept for A/B (WSI_B200_SEG_LEGACY=1)
 __global__ void __launch_bounds__(K1_THREADS)
-    k_sat_median_thresh(const uint8_t* __restrict__ rgb_all, SegBatch sb, int k, int thresh,
-                        uint8_t* __restrict__ out_all) {
+    k_sat_median_thresh_v1(const uint8_t* __restrict__ rgb_all, SegBatch sb, int k, int thresh,
+                           uint8_t* __restrict__ out_all) {
   extern __shared__ uint8_t s_b[];  // (TH+2r) x (TW+2r) thresholded bits
   const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
   const SegSlide sl = sb.slides[s];
@@ -72,12 +81,7 @@ __global__ void __launch_bounds__(K1_THREADS)
     int ly = i / sw, lx = i - ly * sw;
     int gx = min(max(x0 + lx, 0), W - 1);   // BORDER_REPLICATE
     int gy = min(max(y0 + ly, 0), H - 1);
-    const uint8_t* p = rgb + (size_t)gy * sl.pitch + (size_t)gx * 3;
-    int R = p[0], G = p[1], B = p[2];
-    int v = max(R, max(G, B));
-    int d = v - min(R, min(G, B));
-    int sat = (d * c_sdiv[v] + (1 << 11)) >> 12;
-    s_b[i] = (sat > thresh) ? 1 : 0;
+    s_b[i] = (sat_of(rgb + (size_t)gy * sl.pitch + (size_t)gx * 3) > thresh) ? 1 : 0;
   }
   __syncthreads();
   const int need = (k * k + 1) >> 1;
@@ -94,12 +98,151 @@ __global__ void __launch_bounds__(K1_THREADS)
   }
 }
 
-// ----------------------------------------------------------------------------
-// K1b: closing with ones(k,k):  dilation offsets [-(k-1)/2 .. k/2] (outside = 0)
-// then erosion offsets [-(k/2) .. (k-1)/2] (outside = 1)  (scipy / skimage convention)
-// ----------------------------------------------------------------------------
+// separable form: threshold bits -> k-wide row sums -> k-high column sums (2k taps per output)
 __global__ void __launch_bounds__(K1_THREADS)
-    k_closing(const uint8_t* __restrict__ in_all, SegBatch sb, int k, uint8_t* __restrict__ out_all) {
+    k_sat_median_thresh(const uint8_t* __restrict__ rgb_all, SegBatch sb, int k, int thresh,
+                        uint8_t* __restrict__ out_all) {
+  extern __shared__ uint8_t s_b[];  // (TH+2r) x (TW+2r) thresholded bits, then (TH+2r) x TW row sums
+  const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.tile_base[s]);
+  const int ty = tile / sl.tiles_x, tx = tile - ty * sl.tiles_x;
+  const uint8_t* __restrict__ rgb = rgb_all + sl.rgb_off;
+  uint8_t* __restrict__ out = out_all + sl.mask_off;
+  const int H = sl.H, W = sl.W;
+  const int r = k >> 1;
+  const int sw = K1_TW + 2 * r, sh = K1_TH + 2 * r;
+  uint8_t* s_h = s_b + sw * sh;
+  const int x0 = tx * K1_TW - r, y0 = ty * K1_TH - r;
+  for (int i = threadIdx.x; i < sw * sh; i += K1_THREADS) {
+    int ly = i / sw, lx = i - ly * sw;
+    int gx = min(max(x0 + lx, 0), W - 1);   // BORDER_REPLICATE
+    int gy = min(max(y0 + ly, 0), H - 1);
+    s_b[i] = (sat_of(rgb + (size_t)gy * sl.pitch + (size_t)gx * 3) > thresh) ? 1 : 0;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < sh * K1_TW; i += K1_THREADS) {
+    const int ly = i / K1_TW, lx = i - ly * K1_TW;
+    const uint8_t* row = s_b + ly * sw + lx;
+    int c = 0;
+    for (int dx = 0; dx < k; ++dx) c += row[dx];
+    s_h[i] = (uint8_t)c;                     // k <= 31
+  }
+  __syncthreads();
+  const int need = (k * k + 1) >> 1;
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += K1_THREADS) {
+    int ly = i / K1_TW, lx = i - ly * K1_TW;
+    int gx = tx * K1_TW + lx, gy = ty * K1_TH + ly;
+    if (gx >= W || gy >= H) continue;
+    int cnt = 0;
+    for (int dy = 0; dy < k; ++dy) cnt += s_h[(ly + dy) * K1_TW + lx];
+    out[(size_t)gy * W + gx] = cnt >= need ? 1 : 0;
+  }
+}
+
+// Otsu mode (extra, not upstream: SURVEY F2 / north_star "thumbnail Otsu threshold"): the exact k x k median of S
+// (cv.medianBlur, BORDER_REPLICATE) by 8-step bisection on the value, plus a per-slide 256-bin histogram.
+__global__ void __launch_bounds__(K1_THREADS)
+    k_sat_median_value(const uint8_t* __restrict__ rgb_all, SegBatch sb, int k, uint8_t* __restrict__ val_all,
+                       int* __restrict__ hist_all) {
+  extern __shared__ uint8_t s_b[];  // (TH+2r) x (TW+2r) saturation values
+  __shared__ int s_hist[256];
+  const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.tile_base[s]);
+  const int ty = tile / sl.tiles_x, tx = tile - ty * sl.tiles_x;
+  const uint8_t* __restrict__ rgb = rgb_all + sl.rgb_off;
+  uint8_t* __restrict__ out = val_all + sl.mask_off;
+  const int H = sl.H, W = sl.W;
+  const int r = k >> 1;
+  const int sw = K1_TW + 2 * r, sh = K1_TH + 2 * r;
+  const int x0 = tx * K1_TW - r, y0 = ty * K1_TH - r;
+  s_hist[threadIdx.x] = 0;                  // K1_THREADS == 256
+  for (int i = threadIdx.x; i < sw * sh; i += K1_THREADS) {
+    int ly = i / sw, lx = i - ly * sw;
+    int gx = min(max(x0 + lx, 0), W - 1);
+    int gy = min(max(y0 + ly, 0), H - 1);
+    s_b[i] = (uint8_t)sat_of(rgb + (size_t)gy * sl.pitch + (size_t)gx * 3);
+  }
+  __syncthreads();
+  const int rank = (k * k) >> 1;            // 0-based index of the median in the sorted window
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += K1_THREADS) {
+    int ly = i / K1_TW, lx = i - ly * K1_TW;
+    int gx = tx * K1_TW + lx, gy = ty * K1_TH + ly;
+    if (gx >= W || gy >= H) continue;
+    int med = 0;                            // largest c with #{window < c} <= rank
+    for (int bit = 7; bit >= 0; --bit) {
+      const int c = med | (1 << bit);
+      int cnt = 0;
+      for (int dy = 0; dy < k; ++dy) {
+        const uint8_t* row = s_b + (ly + dy) * sw + lx;
+        for (int dx = 0; dx < k; ++dx) cnt += row[dx] < c;
+      }
+      if (cnt <= rank) med = c;
+    }
+    out[(size_t)gy * W + gx] = (uint8_t)med;
+    atomicAdd(&s_hist[med], 1);
+  }
+  __syncthreads();
+  const int hv = s_hist[threadIdx.x];
+  if (hv) atomicAdd(&hist_all[s * 256 + threadIdx.x], hv);
+}
+
+// cv::threshold(..., THRESH_OTSU) threshold selection (OpenCV imgproc/thresh.cpp getThreshVal_Otsu_8u): the same
+// sequential float64 operations in the same order, no FMA contraction.  One thread per slide.
+__global__ void k_otsu(const int* __restrict__ hist_all, SegBatch sb, int* __restrict__ thr_out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= sb.n) return;
+  const int* __restrict__ h = hist_all + s * 256;
+  const SegSlide sl = sb.slides[s];
+  const double scale = __ddiv_rn(1.0, (double)(sl.W * sl.H));
+  double mu = 0.0;
+  for (int i = 0; i < 256; ++i) mu = __dadd_rn(mu, __dmul_rn((double)i, (double)h[i]));
+  mu = __dmul_rn(mu, scale);
+  const double eps = 1.1920928955078125e-07;   // FLT_EPSILON
+  double mu1 = 0.0, q1 = 0.0, max_sigma = 0.0;
+  int max_val = 0;
+  for (int i = 0; i < 256; ++i) {
+    const double p_i = __dmul_rn((double)h[i], scale);
+    mu1 = __dmul_rn(mu1, q1);
+    q1 = __dadd_rn(q1, p_i);
+    const double q2 = __dsub_rn(1.0, q1);
+    if (fmin(q1, q2) < eps || fmax(q1, q2) > __dsub_rn(1.0, eps)) continue;
+    mu1 = __ddiv_rn(__dadd_rn(mu1, __dmul_rn((double)i, p_i)), q1);
+    const double mu2 = __ddiv_rn(__dsub_rn(mu, __dmul_rn(q1, mu1)), q2);
+    const double d = __dsub_rn(mu1, mu2);
+    const double sigma = __dmul_rn(__dmul_rn(__dmul_rn(q1, q2), d), d);
+    if (sigma > max_sigma) {
+      max_sigma = sigma;
+      max_val = i;
+    }
+  }
+  thr_out[s] = max_val;
+}
+
+// mask = value > thr[slide]   (cv.threshold THRESH_BINARY with the per-slide Otsu threshold)
+__global__ void __launch_bounds__(256)
+    k_thresh_slide(const uint8_t* __restrict__ val_all, SegBatch sb, long long total, const int* __restrict__ thr,
+                   uint8_t* __restrict__ out_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= total) return;
+  const int s = find_slide(sb.px_base, sb.n, g);
+  const SegSlide sl = sb.slides[s];
+  const long long idx = g - sb.px_base[s];
+  (out_all + sl.mask_off)[idx] = (val_all + sl.mask_off)[idx] > thr[s] ? 1 : 0;
+}
+
+// ----------------------------------------------------------------------------
+// K1b: closing with ones(k,k):  dilation offsets [-da .. k-1-da] (outside = 0) then erosion offsets
+// [-ea .. k-1-ea] (outside = 1).  (da, ea) is the footprint-origin convention; it only matters for even k
+// and only within k/2 pixels of the image border (a closing is translation invariant in the interior):
+//   scipy / raw even footprint (default, == end-padded):  da = (k-1)/2, ea = k/2
+//   front-padded (k+1)x(k+1) footprint:                   da = k/2,     ea = (k-1)/2
+// ----------------------------------------------------------------------------
+// legacy form (k*k taps per stage), kept for A/B (WSI_B200_SEG_LEGACY=1)
+__global__ void __launch_bounds__(K1_THREADS)
+    k_closing_v1(const uint8_t* __restrict__ in_all, SegBatch sb, int k, int dlo, int elo,
+                 uint8_t* __restrict__ out_all) {
   extern __shared__ uint8_t s_m[];
   const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
   const SegSlide sl = sb.slides[s];
@@ -108,7 +251,6 @@ __global__ void __launch_bounds__(K1_THREADS)
   const uint8_t* __restrict__ in = in_all + sl.mask_off;
   uint8_t* __restrict__ out = out_all + sl.mask_off;
   const int H = sl.H, W = sl.W;
-  const int dlo = (k - 1) >> 1, elo = k >> 1;
   const int halo = k - 1;
   const int iw = K1_TW + 2 * halo, ih = K1_TH + 2 * halo;      // input tile
   const int dw = K1_TW + halo, dh = K1_TH + halo;              // dilated tile
@@ -152,6 +294,69 @@ __global__ void __launch_bounds__(K1_THREADS)
   }
 }
 
+// separable form: row OR -> column OR (+ outside = 1) -> row AND -> column AND  (4k taps per output)
+__global__ void __launch_bounds__(K1_THREADS)
+    k_closing(const uint8_t* __restrict__ in_all, SegBatch sb, int k, int dlo, int elo,
+              uint8_t* __restrict__ out_all) {
+  extern __shared__ uint8_t s_m[];
+  const int s = find_slide(sb.tile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.tile_base[s]);
+  const int ty = tile / sl.tiles_x, tx = tile - ty * sl.tiles_x;
+  const uint8_t* __restrict__ in = in_all + sl.mask_off;
+  uint8_t* __restrict__ out = out_all + sl.mask_off;
+  const int H = sl.H, W = sl.W;
+  const int halo = k - 1;
+  const int iw = K1_TW + 2 * halo, ih = K1_TH + 2 * halo;      // input tile
+  const int dw = K1_TW + halo, dh = K1_TH + halo;              // dilated tile
+  uint8_t* s_in = s_m;                 // ih x iw
+  uint8_t* s_t = s_in + iw * ih;       // ih x dw   row OR
+  uint8_t* s_d = s_t + ih * dw;        // dh x dw   dilated (outside the image = 1)
+  uint8_t* s_e = s_d + dh * dw;        // dh x TW   row AND
+  const int bx = tx * K1_TW, by = ty * K1_TH;
+  for (int i = threadIdx.x; i < iw * ih; i += K1_THREADS) {
+    int ly = i / iw, lx = i - ly * iw;
+    int gx = bx - elo - dlo + lx, gy = by - elo - dlo + ly;
+    s_in[i] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? in[(size_t)gy * W + gx] : 0;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < ih * dw; i += K1_THREADS) {
+    int ly = i / dw, lx = i - ly * dw;
+    const uint8_t* row = s_in + ly * iw + lx;
+    uint8_t v = 0;
+    for (int dx = 0; dx < k; ++dx) v |= row[dx];
+    s_t[i] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < dh * dw; i += K1_THREADS) {
+    int ly = i / dw, lx = i - ly * dw;
+    int gx = bx - elo + lx, gy = by - elo + ly;
+    uint8_t v = 1;
+    if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
+      v = 0;
+      for (int dy = 0; dy < k; ++dy) v |= s_t[(ly + dy) * dw + lx];
+    }
+    s_d[i] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < dh * K1_TW; i += K1_THREADS) {
+    int ly = i / K1_TW, lx = i - ly * K1_TW;
+    const uint8_t* row = s_d + ly * dw + lx;
+    uint8_t v = 1;
+    for (int dx = 0; dx < k; ++dx) v &= row[dx];
+    s_e[i] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < K1_TW * K1_TH; i += K1_THREADS) {
+    int ly = i / K1_TW, lx = i - ly * K1_TW;
+    int gx = bx + lx, gy = by + ly;
+    if (gx >= W || gy >= H) continue;
+    uint8_t v = 1;
+    for (int dy = 0; dy < k; ++dy) v &= s_e[(ly + dy) * K1_TW + lx];
+    out[(size_t)gy * W + gx] = v;
+  }
+}
+
 // ----------------------------------------------------------------------------
 // K1c: connected components by lock-free union-find (min-label roots).
 // One labelling handles both classes at once: a pixel merges with a neighbour of
@@ -187,11 +392,11 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b) {
   } while (!done);
 }
 
-constexpr int CC_TW = 32, CC_TH = 16;   // 512-pixel tiles, 1 thread per pixel
+constexpr int CC_TW = 32, CC_TH = 32;   // 1024-pixel tiles, 1 thread per pixel, one warp per tile row
 
-// Phase 1: tile-local union-find in shared memory, then publish slide-local ids of the local roots.
+// ---- legacy labelling (one union per pixel and neighbour), kept for A/B (WSI_B200_SEG_LEGACY=1) ----
 __global__ void __launch_bounds__(CC_TW* CC_TH)
-    k_ccl_local(const uint8_t* __restrict__ mask_all, SegBatch sb, int conn8_fg, int* __restrict__ L_all) {
+    k_ccl_local_v1(const uint8_t* __restrict__ mask_all, SegBatch sb, int conn8_fg, int* __restrict__ L_all) {
   __shared__ int s_L[CC_TW * CC_TH];
   __shared__ uint8_t s_v[CC_TW * CC_TH];
   const int s = find_slide(sb.ctile_base, sb.n, blockIdx.x);
@@ -226,10 +431,9 @@ __global__ void __launch_bounds__(CC_TW* CC_TH)
   if (blockIdx.x == sb.ctile_base[s] && t == 0) L[H * W] = H * W;   // frame node
 }
 
-// Phase 2: merge across tile borders (and optionally tie border background to the frame node).
 __global__ void __launch_bounds__(256)
-    k_ccl_border(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int conn8_fg, int frame,
-                 int* __restrict__ L_all) {
+    k_ccl_border_v1(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int conn8_fg, int frame,
+                    int* __restrict__ L_all) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= total) return;
   const int s = find_slide(sb.px_base, sb.n, g);
@@ -250,6 +454,122 @@ __global__ void __launch_bounds__(256)
     if ((top_edge || right_edge) && gx < W - 1 && mask[idx - W + 1] == 1) uf_union(L, idx, idx - W + 1);
   }
   if (frame && v == 0 && img_border) uf_union(L, idx, H * W);
+}
+
+// ---- run-based labelling ----
+// Phase 1: a warp owns one 32-pixel tile row.  Ballots give the row as bit words; a pixel's first label is the
+// start of its horizontal run (clz on the run-start bits), so the row needs no unions at all.  Two vertically
+// adjacent runs of equal value overlap in columns [a, b] where a is the start of one of them: ONE union per pair
+// of touching runs, at the lanes where either row starts a run.  8-connectivity of the foreground adds only the
+// pure diagonal contacts (both shared 4-neighbours are background); every other diagonal pair is already
+// connected through a horizontal run and a vertical union.  Blob-shaped masks go from ~2 atomics per pixel to a
+// handful per tile.
+__global__ void __launch_bounds__(CC_TW* CC_TH)
+    k_ccl_local(const uint8_t* __restrict__ mask_all, SegBatch sb, int conn8_fg, int* __restrict__ L_all) {
+  __shared__ int s_L[CC_TW * CC_TH];
+  __shared__ unsigned s_fg[CC_TH], s_st[CC_TH];
+  const int s = find_slide(sb.ctile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.ctile_base[s]);
+  const int ty = tile / sl.ctiles_x, tx = tile - ty * sl.ctiles_x;
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W;
+  const int t = threadIdx.x;
+  const int lane = t & 31, ly = t >> 5;
+  const int gx = tx * CC_TW + lane, gy = ty * CC_TH + ly;
+  const bool in = gx < W && gy < H;
+  const bool v = in && mask[(size_t)gy * W + gx] != 0;
+  const unsigned va = __ballot_sync(0xffffffffu, in);
+  const unsigned fg = __ballot_sync(0xffffffffu, v);
+  const unsigned st = (fg ^ (fg << 1)) | (va ^ (va << 1)) | 1u;      // bit x: a run starts at column x
+  const int rs = 31 - __clz(st & (0xffffffffu >> (31 - lane)));      // start of this lane's run
+  s_L[t] = (ly << 5) + rs;
+  if (lane == 0) {
+    s_fg[ly] = fg;
+    s_st[ly] = st;
+  }
+  __syncthreads();
+  if (in && ly > 0) {
+    // the pixel above is inside the image whenever this one is
+    const unsigned fgu = s_fg[ly - 1], stu = s_st[ly - 1];
+    if (((((fg ^ fgu) >> lane) & 1u) == 0u) && (((st | stu) >> lane) & 1u)) uf_union(s_L, t, t - CC_TW);
+    if (conn8_fg) {
+      const unsigned dl = fg & (fgu << 1) & ~fgu & ~(fg << 1);       // up-left is fg, up and left are bg
+      const unsigned dr = fg & (fgu >> 1) & ~fgu & ~(fg >> 1);       // up-right is fg, up and right are bg
+      if ((dl >> lane) & 1u) uf_union(s_L, t, t - CC_TW - 1);
+      if ((dr >> lane) & 1u) uf_union(s_L, t, t - CC_TW + 1);
+    }
+  }
+  __syncthreads();
+  if (in) {
+    const int rt = uf_find(s_L, t);
+    L[(size_t)gy * W + gx] = (ty * CC_TH + (rt >> 5)) * W + tx * CC_TW + (rt & 31);
+  }
+  if (blockIdx.x == sb.ctile_base[s] && t == 0) L[H * W] = H * W;   // frame node
+}
+
+// Phase 2: merge across tile borders, one 128-thread CTA per tile: threads 0..31 walk the top row (unions with the
+// row above, and the diagonal contacts that cross a tile border upwards), 32..63 the left column (unions with the
+// column to the left, diagonal contacts that cross only the vertical border), 64..95 / 96..127 the image's right
+// column / bottom row where the tile contains them (frame ties).  As in phase 1 a union is issued only where a
+// run starts on either side of the border, so a large region costs one global atomic per tile edge.
+__global__ void __launch_bounds__(128)
+    k_ccl_border(const uint8_t* __restrict__ mask_all, SegBatch sb, int conn8_fg, int frame, int* __restrict__ L_all) {
+  const int s = find_slide(sb.ctile_base, sb.n, blockIdx.x);
+  const SegSlide sl = sb.slides[s];
+  const int tile = (int)(blockIdx.x - sb.ctile_base[s]);
+  const int ty = tile / sl.ctiles_x, tx = tile - ty * sl.ctiles_x;
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W;
+  const int bx = tx * CC_TW, by = ty * CC_TH;
+  const int j = threadIdx.x & 31, role = threadIdx.x >> 5;
+  if (role == 0) {                       // top row of the tile
+    const int gx = bx + j, gy = by;
+    if (gx >= W || gy >= H) return;
+    const int idx = gy * W + gx;
+    const uint8_t v = mask[idx];
+    if (gy > 0) {
+      const uint8_t up = mask[idx - W];
+      const uint8_t lf = gx > 0 ? mask[idx - 1] : 2, ul = gx > 0 ? mask[idx - W - 1] : 2;
+      if (up == v && (j == 0 || lf != v || ul != v)) uf_union(L, idx, idx - W);
+      if (conn8_fg && v == 1 && up == 0) {
+        if (ul == 1 && lf == 0) uf_union(L, idx, idx - W - 1);
+        if (gx < W - 1 && mask[idx - W + 1] == 1 && mask[idx + 1] == 0) uf_union(L, idx, idx - W + 1);
+      }
+    } else if (frame && v == 0 && (j == 0 || mask[idx - 1] != 0)) {
+      uf_union(L, idx, H * W);           // image top border
+    }
+  } else if (role == 1) {                // left column of the tile
+    const int gx = bx, gy = by + j;
+    if (gx >= W || gy >= H) return;
+    const int idx = gy * W + gx;
+    const uint8_t v = mask[idx];
+    if (gx > 0) {
+      const uint8_t lf = mask[idx - 1];
+      const uint8_t up = gy > 0 ? mask[idx - W] : 2, ul = gy > 0 ? mask[idx - W - 1] : 2;
+      if (lf == v && (j == 0 || up != v || ul != v)) uf_union(L, idx, idx - 1);
+      if (conn8_fg && v == 1 && lf == 0) {
+        if (j > 0 && ul == 1 && up == 0) uf_union(L, idx, idx - W - 1);
+        if (j < CC_TH - 1 && gy < H - 1 && mask[idx + W - 1] == 1 && mask[idx + W] == 0) uf_union(L, idx, idx + W - 1);
+      }
+    } else if (frame && v == 0 && (j == 0 || mask[idx - W] != 0)) {
+      uf_union(L, idx, H * W);           // image left border
+    }
+  } else if (role == 2) {                // image right border, where this tile holds column W-1
+    if (!frame || bx + CC_TW < W) return;
+    const int gx = W - 1, gy = by + j;
+    if (gy >= H) return;
+    const int idx = gy * W + gx;
+    if (mask[idx] == 0 && (j == 0 || mask[idx - W] != 0)) uf_union(L, idx, H * W);
+  } else {                               // image bottom border, where this tile holds row H-1
+    if (!frame || by + CC_TH < H) return;
+    const int gx = bx + j, gy = H - 1;
+    if (gx >= W) return;
+    const int idx = gy * W + gx;
+    if (mask[idx] == 0 && (j == 0 || mask[idx - 1] != 0)) uf_union(L, idx, H * W);
+  }
 }
 
 // Phase 3: flatten + per-root area of class `cls` pixels (warp-aggregated atomics).
@@ -275,7 +595,18 @@ __global__ void __launch_bounds__(256)
       area = area_all;
     }
   }
-  if (cls < 0) return;   // flatten only (warp-uniform)
+  if (cls < 0) return;   // flatten only (kernel-uniform)
+  // block-level fast path: interior blocks see one root; count its pixels with one atomic per CTA
+  __shared__ int s_key;
+  if (threadIdx.x == 0) s_key = root;
+  __syncthreads();
+  const bool same = act && root == s_key;
+  const int c = __syncthreads_count(same);
+  if (threadIdx.x == 0 && c) atomicAdd(&area_all[root], c);
+  if (same) {
+    act = false;
+    root = -1 - (int)(threadIdx.x & 31);
+  }
   unsigned peers = __match_any_sync(0xffffffffu, root);
   if (act && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&area[root], __popc(peers));
 }
@@ -322,14 +653,22 @@ __global__ void __launch_bounds__(256)
 }
 __global__ void __launch_bounds__(256)
     k_outer_apply(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
-                  const int* __restrict__ flag_all, uint8_t* __restrict__ outer_all) {
+                  const int* __restrict__ flag_all, uint8_t* __restrict__ outer_all, int* __restrict__ info) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= total) return;
-  const int s = find_slide(sb.px_base, sb.n, g);
-  const SegSlide sl = sb.slides[s];
-  const int idx = (int)(g - sb.px_base[s]);
-  const uint8_t m = (mask_all + sl.mask_off)[idx];
-  (outer_all + sl.mask_off)[idx] = (m == 1 && flag_all[sl.lab_off + L_all[sl.lab_off + idx]]) ? 1 : 0;
+  int key = -1 - (int)(threadIdx.x & 31);
+  if (g < total) {
+    const int s = find_slide(sb.px_base, sb.n, g);
+    const SegSlide sl = sb.slides[s];
+    const int idx = (int)(g - sb.px_base[s]);
+    const uint8_t m = (mask_all + sl.mask_off)[idx];
+    (outer_all + sl.mask_off)[idx] = (m == 1 && flag_all[sl.lab_off + L_all[sl.lab_off + idx]]) ? 1 : 0;
+    if (m == 1) key = s;
+  }
+  if (info) {
+    // per-slide "the mask has tissue" flag (replaces a host-side mask.any()): one store per warp and slide
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (key >= 0 && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) info[4 * key + 1] = 1;
+  }
 }
 
 // ----------------------------------------------------------------------------
@@ -454,7 +793,8 @@ int upload_sdiv() {
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct BatchLayout {
-  size_t off_desc, off_tile, off_ctile, off_px, off_tmp, off_L, off_aux, total;
+  size_t off_desc, off_tile, off_ctile, off_px, off_hist, off_thr, off_info, off_tmp, off_L, off_aux, total;
+  size_t head_bytes;      // descriptor tables: one host->device copy
   long long npx, ntiles, nctiles;
 };
 
@@ -473,11 +813,25 @@ BatchLayout batch_layout(int n, const int* H, const int* W) {
   b.off_tile = o;  o += align_up(sizeof(long long) * (n + 1), 256);
   b.off_ctile = o; o += align_up(sizeof(long long) * (n + 1), 256);
   b.off_px = o;    o += align_up(sizeof(long long) * (n + 1), 256);
+  b.head_bytes = o;
+  b.off_hist = o;  o += align_up(sizeof(int) * 256 * (size_t)n, 256);     // Otsu mode: per-slide histogram of S_med
+  b.off_thr = o;   o += align_up(sizeof(int) * (size_t)n, 256);           //            per-slide threshold
+  b.off_info = o;  o += align_up(sizeof(int) * 4 * (size_t)n, 256);       // per-slide {threshold, has_tissue, 0, 0}
   b.off_tmp = o;   o += align_up((size_t)b.npx, 256);
   b.off_L = o;     o += align_up(((size_t)b.npx + n) * sizeof(int), 256);
   b.off_aux = o;   o += align_up(((size_t)b.npx + n) * sizeof(int), 256);
   b.total = o;
   return b;
+}
+
+bool seg_legacy() {
+  const char* e = getenv("WSI_B200_SEG_LEGACY");
+  return e && e[0] == '1';
+}
+
+__global__ void k_info_thr(const int* __restrict__ thr, int fixed_thr, int n, int* __restrict__ info) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) info[4 * s] = thr ? thr[s] : fixed_thr;
 }
 
 }  // namespace
@@ -502,9 +856,12 @@ static int seg_prepare(int n, const int* h_H, const int* h_W, const int* h_pitch
   const BatchLayout bl = batch_layout(n, h_H, h_W);
   WSI_ARG_CHECK(ws_bytes >= bl.total, "wsi_seg_tissue: workspace too small (%zu < %zu)", ws_bytes, bl.total);
   WSI_ARG_CHECK(bl.npx + n < (1ll << 31), "wsi_seg_tissue: cohort too large for one call");
-  // descriptor tables (host staging -> workspace head)
-  std::vector<SegSlide> hs(n);
-  std::vector<long long> tb(n + 1), cb(n + 1), pb(n + 1);
+  // descriptor tables, staged contiguously on the host in the layout of the workspace head: ONE copy
+  std::vector<uint8_t> head(bl.head_bytes, 0);
+  SegSlide* hs = (SegSlide*)(head.data() + bl.off_desc);
+  long long* tb = (long long*)(head.data() + bl.off_tile);
+  long long* cb = (long long*)(head.data() + bl.off_ctile);
+  long long* pb = (long long*)(head.data() + bl.off_px);
   tb[0] = cb[0] = pb[0] = 0;
   long long max_mask_end = 0;
   for (int s = 0; s < n; ++s) {
@@ -528,13 +885,8 @@ static int seg_prepare(int n, const int* h_H, const int* h_W, const int* h_pitch
   // the median scratch is addressed with the mask offsets, so masks must pack the cohort densely
   WSI_ARG_CHECK(max_mask_end <= bl.npx, "wsi_seg_tissue: mask offsets must pack the cohort densely");
   uint8_t* ws = (uint8_t*)d_ws;
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_desc, hs.data(), sizeof(SegSlide) * n, cudaMemcpyHostToDevice, stream));
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_tile, tb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
-                                 stream));
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_ctile, cb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
-                                 stream));
-  WSI_CUDA_CHECK(cudaMemcpyAsync(ws + bl.off_px, pb.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice,
-                                 stream));
+  // pageable source: the runtime stages the bytes before returning, so `head` may go out of scope
+  WSI_CUDA_CHECK(cudaMemcpyAsync(ws, head.data(), bl.head_bytes, cudaMemcpyHostToDevice, stream));
   sb_out->slides = (const SegSlide*)(ws + bl.off_desc);
   sb_out->tile_base = (const long long*)(ws + bl.off_tile);
   sb_out->ctile_base = (const long long*)(ws + bl.off_ctile);
@@ -544,29 +896,42 @@ static int seg_prepare(int n, const int* h_H, const int* h_W, const int* h_pitch
   return WSI_OK;
 }
 
+// one labelling of the whole cohort: tile-local pass + border merge (+ frame ties)
+static void seg_label(const SegBatch& sb, const BatchLayout& bl, const uint8_t* d_mask, int conn8_fg, int frame, int* L,
+                      cudaStream_t stream) {
+  if (seg_legacy()) {
+    k_ccl_local_v1<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, conn8_fg, L);
+    k_ccl_border_v1<<<wsi_cdiv(bl.npx, 256), 256, 0, stream>>>(d_mask, sb, bl.npx, conn8_fg, frame, L);
+  } else {
+    k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, conn8_fg, L);
+    k_ccl_border<<<(unsigned)bl.nctiles, 128, 0, stream>>>(d_mask, sb, conn8_fg, frame, L);
+  }
+  wsi_count_launch(2);
+}
+
 // 8-connected foreground labelling + frame adjacency -> outermost-component mask
 static int seg_outermost(const SegBatch& sb, const BatchLayout& bl, const uint8_t* d_mask, uint8_t* d_outer, void* d_ws,
-                         cudaStream_t stream) {
+                         int* d_info, cudaStream_t stream) {
   uint8_t* ws = (uint8_t*)d_ws;
   int* L = (int*)(ws + bl.off_L);
   int* aux = (int*)(ws + bl.off_aux);
   const long long total = bl.npx;
   const size_t lab_bytes = ((size_t)bl.npx + sb.n) * sizeof(int);
   const int nb = wsi_cdiv(total, 256);
-  k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, 1, L);
-  k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, sb, total, 1, 1, L);
+  seg_label(sb, bl, d_mask, 1, 1, L, stream);
   k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
   WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
   k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux);
-  k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer);
-  wsi_count_launch(5);
+  k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer, d_info);
+  wsi_count_launch(3);
   return WSI_OK;
 }
 
-int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W, const int* h_pitch,
+int wsi_seg_tissue_batch_ex(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W, const int* h_pitch,
                             const long long* h_rgb_off, const long long* h_mask_off, int median_filter_size,
-                            int binary_threshold, int closing_kernel_size, const int* h_min_object_px,
-                            const int* h_min_hole_px, uint8_t* d_mask, uint8_t* d_outer, void* d_ws, size_t ws_bytes,
+                            int binary_threshold, int closing_kernel_size, int closing_dilation_origin,
+                            int closing_erosion_origin, const int* h_min_object_px, const int* h_min_hole_px,
+                            uint8_t* d_mask, uint8_t* d_outer, int* d_info, void* d_ws, size_t ws_bytes,
                             void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   WSI_ARG_CHECK(d_rgb && d_mask && d_ws && h_H && h_W && h_pitch && h_rgb_off && h_mask_off && h_min_object_px &&
@@ -577,6 +942,11 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
                 "median_filter_size must be greater than 1 and odd, but got %d", median_filter_size);
   WSI_ARG_CHECK(median_filter_size <= 31, "median_filter_size > 31 unsupported");
   WSI_ARG_CHECK(closing_kernel_size >= 1 && closing_kernel_size <= 32, "closing_kernel_size out of range");
+  WSI_ARG_CHECK(binary_threshold >= WSI_SEG_THRESHOLD_OTSU, "binary_threshold must be >= 0 or WSI_SEG_THRESHOLD_OTSU");
+  const int k = closing_kernel_size;
+  const int dlo = closing_dilation_origin < 0 ? (k - 1) / 2 : closing_dilation_origin;
+  const int elo = closing_erosion_origin < 0 ? k / 2 : closing_erosion_origin;
+  WSI_ARG_CHECK(dlo < k && elo < k, "closing origins (%d, %d) must lie inside the %dx%d footprint", dlo, elo, k, k);
   for (int s = 0; s < n; ++s)
     WSI_ARG_CHECK(h_pitch[s] >= 3 * h_W[s], "wsi_seg_tissue: pitch %d < 3*W (%d)", h_pitch[s], h_W[s]);
   int rc = upload_sdiv();
@@ -590,21 +960,46 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
   uint8_t* tmp = ws + bl.off_tmp;
   int* L = (int*)(ws + bl.off_L);
   int* aux = (int*)(ws + bl.off_aux);
+  int* hist = (int*)(ws + bl.off_hist);
+  int* thr = (int*)(ws + bl.off_thr);
+  int* info = d_info ? d_info : (int*)(ws + bl.off_info);
   const long long total = bl.npx;
   const size_t lab_bytes = ((size_t)bl.npx + n) * sizeof(int);
   const int nb = wsi_cdiv(total, 256);
+  const bool legacy = seg_legacy();
   int launches = 0;
+  WSI_CUDA_CHECK(cudaMemsetAsync(info, 0, sizeof(int) * 4 * (size_t)n, stream));
   {
-    int r = median_filter_size / 2;
-    size_t smem = (size_t)(K1_TW + 2 * r) * (K1_TH + 2 * r);
-    k_sat_median_thresh<<<(unsigned)bl.ntiles, K1_THREADS, smem, stream>>>(d_rgb, sb, median_filter_size,
-                                                                           binary_threshold, tmp);
-    ++launches;
+    const int r = median_filter_size / 2;
+    const size_t sw = K1_TW + 2 * r, sh = K1_TH + 2 * r;
+    if (binary_threshold == WSI_SEG_THRESHOLD_OTSU) {
+      // S_med values -> d_mask (scratch), histogram -> Otsu threshold per slide -> tmp = S_med > t
+      WSI_CUDA_CHECK(cudaMemsetAsync(hist, 0, sizeof(int) * 256 * (size_t)n, stream));
+      k_sat_median_value<<<(unsigned)bl.ntiles, K1_THREADS, sw * sh, stream>>>(d_rgb, sb, median_filter_size, d_mask,
+                                                                               hist);
+      k_otsu<<<wsi_cdiv(n, 32), 32, 0, stream>>>(hist, sb, thr);
+      k_thresh_slide<<<nb, 256, 0, stream>>>(d_mask, sb, total, thr, tmp);
+      k_info_thr<<<wsi_cdiv(n, 64), 64, 0, stream>>>(thr, 0, n, info);
+      launches += 4;
+    } else {
+      if (legacy)
+        k_sat_median_thresh_v1<<<(unsigned)bl.ntiles, K1_THREADS, sw * sh, stream>>>(d_rgb, sb, median_filter_size,
+                                                                                     binary_threshold, tmp);
+      else
+        k_sat_median_thresh<<<(unsigned)bl.ntiles, K1_THREADS, sw * sh + sh * K1_TW, stream>>>(
+            d_rgb, sb, median_filter_size, binary_threshold, tmp);
+      k_info_thr<<<wsi_cdiv(n, 64), 64, 0, stream>>>(nullptr, binary_threshold, n, info);
+      launches += 2;
+    }
   }
   {
-    int k = closing_kernel_size, halo = k - 1;
-    size_t smem = (size_t)(K1_TW + 2 * halo) * (K1_TH + 2 * halo) + (size_t)(K1_TW + halo) * (K1_TH + halo);
-    k_closing<<<(unsigned)bl.ntiles, K1_THREADS, smem, stream>>>(tmp, sb, k, d_mask);
+    const int halo = k - 1;
+    const size_t iw = K1_TW + 2 * halo, ih = K1_TH + 2 * halo, dw = K1_TW + halo, dh = K1_TH + halo;
+    if (legacy)
+      k_closing_v1<<<(unsigned)bl.ntiles, K1_THREADS, iw * ih + dw * dh, stream>>>(tmp, sb, k, dlo, elo, d_mask);
+    else
+      k_closing<<<(unsigned)bl.ntiles, K1_THREADS, iw * ih + ih * dw + dh * dw + dh * K1_TW, stream>>>(tmp, sb, k, dlo,
+                                                                                                    elo, d_mask);
     ++launches;
   }
   // remove_small_objects (4-conn foreground, area < min) then remove_small_holes (4-conn background)
@@ -613,20 +1008,30 @@ int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const i
     bool any = false;
     for (int s = 0; s < n; ++s) any = any || ((cls ? h_min_object_px[s] : h_min_hole_px[s]) > 0);
     if (!any) continue;
-    k_ccl_local<<<(unsigned)bl.nctiles, CC_TW * CC_TH, 0, stream>>>(d_mask, sb, 0, L);
-    k_ccl_border<<<nb, 256, 0, stream>>>(d_mask, sb, total, 0, 0, L);
+    seg_label(sb, bl, d_mask, 0, 0, L, stream);
     WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
     k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, cls, L, aux);
     k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls);
-    launches += 4;
+    launches += 2;
   }
   wsi_count_launch(launches);
   if (d_outer) {
-    rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, stream);
+    rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, info, stream);
     if (rc) return rc;
   }
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
+}
+
+int wsi_seg_tissue_batch_u8(const uint8_t* d_rgb, int n, const int* h_H, const int* h_W, const int* h_pitch,
+                            const long long* h_rgb_off, const long long* h_mask_off, int median_filter_size,
+                            int binary_threshold, int closing_kernel_size, const int* h_min_object_px,
+                            const int* h_min_hole_px, uint8_t* d_mask, uint8_t* d_outer, void* d_ws, size_t ws_bytes,
+                            void* stream_) {
+  WSI_ARG_CHECK(binary_threshold >= 0, "wsi_seg_tissue: binary_threshold must be >= 0 (Otsu: wsi_seg_tissue_batch_ex)");
+  return wsi_seg_tissue_batch_ex(d_rgb, n, h_H, h_W, h_pitch, h_rgb_off, h_mask_off, median_filter_size,
+                                 binary_threshold, closing_kernel_size, -1, -1, h_min_object_px, h_min_hole_px, d_mask,
+                                 d_outer, nullptr, d_ws, ws_bytes, stream_);
 }
 
 int wsi_seg_tissue_u8(const uint8_t* d_rgb, int H, int W, int pitch_bytes, int median_filter_size,
@@ -648,7 +1053,7 @@ int wsi_outermost_u8(const uint8_t* d_mask, int H, int W, uint8_t* d_outer, void
   BatchLayout bl;
   int rc = seg_prepare(1, &H, &W, nullptr, nullptr, &zero, nullptr, nullptr, d_ws, ws_bytes, stream, &sb, &bl);
   if (rc) return rc;
-  rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, stream);
+  rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, nullptr, stream);
   if (rc) return rc;
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;

@@ -50,6 +50,7 @@ class PreprocessPlan:
         self.out_H = int(out_H) if out_H is not None else self.S
         self.out_W = int(out_W) if out_W is not None else self.S
         self.pad_top, self.pad_left = int(pad_top), int(pad_left)
+        self._capacity = 0
         self._h = C.c_void_p()
         mean = _cabi.float_array(transform.mean) if transform.mean is not None else None
         std = _cabi.float_array(transform.std) if transform.std is not None else None
@@ -80,7 +81,10 @@ class PreprocessPlan:
         if self.plane_stride_px:
             assert out.numel() >= 2 * self.plane_stride_px * 4
         else:
-            assert out.numel() >= n * self.out_H * self.out_W * self.channels
+            cap = int(out.numel() // (self.out_H * self.out_W * self.channels))
+            if cap != self._capacity:
+                _cabi.call("wsi_preproc_plan_set_capacity", self._h, cap)
+                self._capacity = cap
         with torch.cuda.device(out.device):
             _cabi.call("wsi_preproc_run", self._h, coords_xy.data_ptr(), n, out.data_ptr(), _cabi.stream_ptr(stream))
 

@@ -135,17 +135,27 @@ def lower_torchscript(path_or_module, input_hw: int) -> List[IRNode]:
             x = src(ins[0])
             if nodes[x].kind != "conv" or nodes[x].relu:
                 raise UnknownArchitectureError("ReLU that does not follow a convolution / residual add")
+            if len(ins[0].uses()) != 1:
+                # the ReLU is fused into the producing conv: a second reader of the pre-activation value
+                # (pre-activation blocks, a raw branch) would silently see the activated tensor
+                raise UnknownArchitectureError("ReLU input is also read un-activated by another op")
             nodes[x].relu = True
             env[oname] = x
         elif kind in ("aten::add", "aten::add_"):
             if float(_const(ins[2])) != 1.0:
                 raise UnknownArchitectureError("add with alpha != 1")
             a, b = src(ins[0]), src(ins[1])
-            tgt, other = (a, b) if (nodes[a].kind == "conv" and not nodes[a].relu and nodes[a].residual is None) \
-                else (b, a)
-            t = nodes[tgt]
-            if t.kind != "conv" or t.relu or t.residual is not None or nodes[other].shape != t.shape:
+
+            def fusable(j, v):
+                # the add is fused into the conv that produced `v`: nothing else may read the pre-add value
+                return nodes[j].kind == "conv" and not nodes[j].relu and nodes[j].residual is None \
+                    and len(v.uses()) == 1
+
+            pick = next(((t_, o_) for t_, v_, o_ in ((a, ins[0], b), (b, ins[1], a)) if t_ != o_ and fusable(t_, v_)), None)
+            if pick is None or nodes[pick[0]].shape != nodes[pick[1]].shape:
                 raise UnknownArchitectureError("residual add that cannot be fused into a convolution")
+            tgt, other = pick
+            t = nodes[tgt]
             t.residual = other
             env[oname] = tgt
         elif kind == "aten::max_pool2d":

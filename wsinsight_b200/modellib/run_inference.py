@@ -46,6 +46,8 @@ def classify_patches_device(slide, coords_xywh: np.ndarray, net, transform, batc
     probs = probs_out if probs_out is not None else torch.empty((n, K), dtype=torch.float32, device=net.device)
     if n == 0:
         return probs
+    # the network's input buffer holds at most max_batch patches (the parity-plane layout fixes the plane stride)
+    batch_size = max(1, min(int(batch_size), net.max_batch))
     dset = WholeSlideImagePatches(slide, coords_xywh, transform, batch_size, net.input_layout, device_coords)
     s = 0
     for batch, bc in dset:
@@ -185,15 +187,23 @@ def run_inference(
     transform = make_compose_from_transform_config(model_info.config.transform)
     net = None
     for patch_path in patch_paths:
-        meta = load_patch_file(patch_path)
-        wsi_path = str(meta["slide_path"])
-        slide_csv = model_output_dir / (Path(wsi_path).stem + ".csv")
+        # the reference isolates failures per slide and records ``wsi_path.stem`` (run_inference.py:232-280)
+        stem = Path(str(patch_path).replace(".npz", "")).stem
+        try:
+            meta = load_patch_file(patch_path)
+            wsi_path = str(meta["slide_path"])
+            stem = Path(wsi_path).stem
+        except Exception as e:  # noqa: BLE001 - one unreadable patch file must not abort the cohort
+            failed_inference.append(stem)
+            logger.error(f"Cannot read patch file {patch_path}", exc_info=e)
+            continue
+        slide_csv = model_output_dir / (stem + ".csv")
         if slide_csv.exists():
             logger.info(f"Output CSV exists... skipping. {slide_csv}")
             continue
         slide = slides.get(wsi_path)
         if slide is None:
-            failed_inference.append(wsi_path)
+            failed_inference.append(stem)
             logger.error(f"slide {wsi_path} is not open on the device")
             continue
         try:
@@ -209,7 +219,7 @@ def run_inference(
             probs = classify_patches_device(slide, coords, net, transform, batch_size)
             write_slide_csv(slide_csv, coords, probs.cpu().numpy(), model_info.config.class_names)
         except Exception as e:  # noqa: BLE001 - slide-granular isolation, as upstream :268-280
-            failed_inference.append(wsi_path)
+            failed_inference.append(stem)
             logger.error(f"Failed inference on {wsi_path}", exc_info=e)
     return failed_patching, failed_inference
 

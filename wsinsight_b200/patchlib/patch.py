@@ -66,8 +66,12 @@ def get_multipolygon_from_binary_arr(arr, scale=None, *, slide_dims=None):
 
 
 def patch_grid_device(region: TissueRegion, patch_size: int, half_patch_size: int, overlap: float = 0.0,
-                      stream=None):
-    """Device-side grid filter.  Returns ``(coords int32 CUDA (N,2), tile_dim (n_i, n_j))``."""
+                      stream=None, sync: bool = True):
+    """Device-side grid filter.  Returns ``(coords int32 CUDA (N,2), tile_dim (n_i, n_j))``.
+
+    ``sync=False`` skips the device->host read of the patch count: the result is then
+    ``(coords_capacity, count_tensor, tile_dim)`` with ``coords_capacity`` sized for every candidate and only its
+    first ``count`` rows valid, so a cohort loop can enqueue every slide before it reads any count."""
     torch = _cabi.require_cuda()
     if overlap >= 1:
         raise ValueError(f"overlap must be in (-inf, 1) but got {overlap}")
@@ -90,6 +94,8 @@ def patch_grid_device(region: TissueRegion, patch_size: int, half_patch_size: in
             "wsi_patch_grid", outer.data_ptr(), int(outer.shape[0]), int(outer.shape[1]), W, H, half, int(step),
             coords.data_ptr(), cap, count.data_ptr(), td, ws.data_ptr(), ws_bytes, _cabi.stream_ptr(stream),
         )
+    if not sync:
+        return coords, count, (int(td[0]), int(td[1]))
     n = int(count.item())
     return coords[:n], (int(td[0]), int(td[1]))
 

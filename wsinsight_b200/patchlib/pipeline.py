@@ -39,6 +39,7 @@ class SlidePatchResult:
     mask: object = None          # CUDA uint8 (Ht, Wt)
     coords: object = None        # CUDA int32 (N, 2), None if no tissue
     tile_dim: tuple = None
+    threshold: int = None        # binary threshold used (the Otsu value in "otsu" mode)
 
 
 def slide_scalars(slide, patch_size_px, patch_spacing_um_px, thumbsize, min_object_size_um2, min_hole_size_um2):
@@ -68,6 +69,7 @@ def segment_and_patch_slides_device(
     min_hole_size_um2: float = 190 ** 2,
     overlap: float = 0.0,
     thumbs=None,
+    closing_convention="scipy_raw",
 ) -> List[SlidePatchResult]:
     """Cohort-level hot path: thumbnails -> masks -> outermost regions -> in-tissue grids.
 
@@ -81,19 +83,27 @@ def segment_and_patch_slides_device(
           for s in slides]
     if thumbs is None:
         thumbs = [s.thumbnail_device(tuple(thumbsize)) for s in slides]
-    masks, outers = segment_tissue_device(
+    masks, outers, info = segment_tissue_device(
         thumbs, median_filter_size, binary_threshold, closing_kernel_size,
-        [c["min_object_size_px"] for c in sc], [c["min_hole_size_px"] for c in sc], want_outer=True)
-    results = []
+        [c["min_object_size_px"] for c in sc], [c["min_hole_size_px"] for c in sc], want_outer=True,
+        closing_convention=closing_convention, return_info=True)
+    # every slide's grid filter is enqueued before anything is read back: ONE device->host copy for the cohort
+    torch = _cabi.require_cuda()
+    results, pending = [], []
     for s, c, m, o in zip(slides, sc, masks, outers):
         r = SlidePatchResult(s.name, c["patch_size"], c["half_patch_size"], c["min_object_size_px"],
                              c["min_hole_size_px"], mask=m)
         region = TissueRegion(o, s.width, s.height)
-        coords, tile_dim = patch_grid_device(region, c["patch_size"], c["half_patch_size"], overlap)
+        coords, count, tile_dim = patch_grid_device(region, c["patch_size"], c["half_patch_size"], overlap, sync=False)
         r.tile_dim = tile_dim
-        # "no contours" in the reference (patch.py:61-62) == empty mask -> None, no files
-        r.coords = coords if bool(m.any().item()) else None
+        pending.append((coords, count))
         results.append(r)
+    counts = torch.cat([cnt for _, cnt in pending]).cpu().tolist() if pending else []
+    flags = info.cpu().numpy()
+    for r, (coords, _), n, f in zip(results, pending, counts, flags):
+        r.threshold = int(f[0])
+        # "no contours" in the reference (patch.py:61-62) == empty mask -> None, no files
+        r.coords = coords[: int(n)] if int(f[1]) else None
     return results
 
 

@@ -24,15 +24,39 @@ def _check_median(median_filter_size: int) -> None:
         )
 
 
+#: footprint-origin conventions of ``binary_closing(ones(k, k))`` for even k: (dilation origin, erosion origin) as
+#: functions of k; window offsets are ``[-origin .. k-1-origin]``.  They agree for odd k and, for even k, everywhere
+#: except within k/2 pixels of the thumbnail border.
+CLOSING_CONVENTIONS = {
+    # scipy.ndimage on the raw even footprint (== a footprint end-padded to odd size): the default
+    "scipy_raw": lambda k: ((k - 1) // 2, k // 2),
+    # footprint front-padded to (k+1) x (k+1) before scipy sees it (skimage ``pad_footprint(pad_end=False)``)
+    "front_padded": lambda k: (k // 2, (k - 1) // 2),
+    # raw dilation, erosion with the mirrored footprint
+    "mirrored_erosion": lambda k: ((k - 1) // 2, (k - 1) // 2),
+}
+
+
+def closing_origins(closing_kernel_size: int, convention="scipy_raw"):
+    if isinstance(convention, str):
+        if convention not in CLOSING_CONVENTIONS:
+            raise ValueError(f"unknown closing convention {convention!r}; choose from {sorted(CLOSING_CONVENTIONS)}")
+        return CLOSING_CONVENTIONS[convention](int(closing_kernel_size))
+    d, e = convention
+    return int(d), int(e)
+
+
 def segment_tissue_device(
     thumbs: Sequence,
     median_filter_size: int = 7,
-    binary_threshold: int = 7,
+    binary_threshold: int | str = 7,
     closing_kernel_size: int = 6,
     min_object_size_px: int | Sequence[int] = 512,
     min_hole_size_px: int | Sequence[int] = 1024,
     want_outer: bool = True,
     stream=None,
+    closing_convention="scipy_raw",
+    return_info: bool = False,
 ):
     """Segment a cohort of device-resident thumbnails in one batched launch sequence.
 
@@ -40,6 +64,11 @@ def segment_tissue_device(
     lists of CUDA uint8 tensors (H, W) with values 0/1 (views into two packed buffers).
     ``outers`` is the mask restricted to outermost 8-connected components -- the region the
     reference's contour/polygon stage keeps (patch.py:78-123) and the input of the grid filter.
+
+    ``binary_threshold="otsu"`` (extra mode, not upstream): per-slide Otsu threshold on the median-filtered
+    saturation, identical to ``cv.threshold(S_med, 0, 255, THRESH_BINARY | THRESH_OTSU)``.
+    ``closing_convention``: see :data:`CLOSING_CONVENTIONS`.  ``return_info=True`` appends a CUDA int32 ``(n, 4)``
+    tensor ``[threshold used, mask has tissue, 0, 0]`` (no host synchronisation happens here).
     """
     torch = _cabi.require_cuda()
     _check_median(median_filter_size)
@@ -72,25 +101,39 @@ def segment_tissue_device(
     Ha, Wa = _cabi.int_array(Hs), _cabi.int_array(Ws)
     ws_bytes = lib.wsi_seg_batch_workspace_bytes(n, Ha, Wa)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    info = torch.empty((n, 4), dtype=torch.int32, device=dev)
+    if isinstance(binary_threshold, str):
+        if binary_threshold.lower() != "otsu":
+            raise ValueError(f"binary_threshold must be an integer or 'otsu', got {binary_threshold!r}")
+        thr = -1                                    # WSI_SEG_THRESHOLD_OTSU
+    else:
+        thr = int(binary_threshold)
+        if thr < 0:
+            raise ValueError("binary_threshold must be >= 0")
+    d_org, e_org = closing_origins(closing_kernel_size, closing_convention)
     with torch.cuda.device(dev):
         _cabi.call(
-            "wsi_seg_tissue_batch_u8", rgb.data_ptr(), n, Ha, Wa, _cabi.int_array([3 * w for w in Ws]),
-            _cabi.ll_array(rgb_off), _cabi.ll_array(mask_off), int(median_filter_size), int(binary_threshold),
-            int(closing_kernel_size), _cabi.int_array(obj), _cabi.int_array(hole), mask.data_ptr(),
-            outer.data_ptr() if want_outer else None, ws.data_ptr(), ws_bytes, _cabi.stream_ptr(stream),
+            "wsi_seg_tissue_batch_ex", rgb.data_ptr(), n, Ha, Wa, _cabi.int_array([3 * w for w in Ws]),
+            _cabi.ll_array(rgb_off), _cabi.ll_array(mask_off), int(median_filter_size), thr,
+            int(closing_kernel_size), d_org, e_org, _cabi.int_array(obj), _cabi.int_array(hole), mask.data_ptr(),
+            outer.data_ptr() if want_outer else None, info.data_ptr(), ws.data_ptr(), ws_bytes,
+            _cabi.stream_ptr(stream),
         )
     masks = [mask[o:o + h * w].view(h, w) for o, h, w in zip(mask_off, Hs, Ws)]
     outers = [outer[o:o + h * w].view(h, w) for o, h, w in zip(mask_off, Hs, Ws)] if want_outer else None
+    if return_info:
+        return masks, outers, info
     return masks, outers
 
 
 def segment_tissue(
     im_arr,
     median_filter_size: int = 7,
-    binary_threshold: int = 7,
+    binary_threshold: int | str = 7,
     closing_kernel_size: int = 6,
     min_object_size_px: int = 512,
     min_hole_size_px: int = 1024,
+    closing_convention="scipy_raw",
 ):
     """Drop-in for ``wsinsight.patchlib.segment.segment_tissue`` (segment.py:13-97).
 
@@ -104,6 +147,6 @@ def segment_tissue(
     t = torch.from_numpy(np.ascontiguousarray(im_arr, dtype=np.uint8)).cuda()
     masks, _ = segment_tissue_device(
         [t], median_filter_size, binary_threshold, closing_kernel_size, min_object_size_px,
-        min_hole_size_px, want_outer=False,
+        min_hole_size_px, want_outer=False, closing_convention=closing_convention,
     )
     return masks[0].cpu().numpy().astype(bool)
