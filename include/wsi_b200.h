@@ -209,6 +209,9 @@ int wsi_net_set_profiling(void* net, int slots);
 int wsi_net_profile_read(void* net, double* h_op_ms, double* h_op_flops, int* h_op_kind, int max_ops,
                          int* h_forwards);
 double wsi_net_flops_per_image(void* net);
+/* Algorithmic HBM bytes per image of the convolution launches (input slice + residual read once, output written
+ * once; what roofline.traffic from ncu is compared with). */
+double wsi_net_conv_bytes_per_image(void* net);
 void wsi_net_destroy(void* net);
 
 /* ---- host-buffer entry of the classification loop ------------------------------------------ */

@@ -95,6 +95,7 @@ _PROTOS = {
     "wsi_net_profile_read": (c_int, [c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), c_int_p, c_int,
                                      c_int_p]),
     "wsi_net_flops_per_image": (C.c_double, [c_void_p]),
+    "wsi_net_conv_bytes_per_image": (C.c_double, [c_void_p]),
     "wsi_net_destroy": (None, [c_void_p]),
     "wsi_synth_slide": (c_int, [c_void_p, c_ll, c_ll, c_ll, C.c_uint, c_void_p]),
     "wsi_synth_slide_host": (c_int, [c_void_p, c_ll, c_ll, c_int, c_int, c_ll, c_ll, C.c_uint]),

@@ -1609,6 +1609,25 @@ double wsi_net_flops_per_image(void* net) {
   return f;
 }
 
+// Algorithmic HBM bytes of the convolution launches per image: every conv reads its (slice of the) input once,
+// its residual once, its weights once per forward (amortised over the batch: not counted) and writes its output
+// once; a stem with the max-pooling fused writes the pooled tensor instead of the conv output.
+double wsi_net_conv_bytes_per_image(void* net) {
+  Net* n = (Net*)net;
+  double b = 0;
+  if (!n) return 0;
+  for (auto& op : n->ops) {
+    if (op.kind != OP_CONV) continue;
+    const Tensor& ti = n->tensors[op.in];
+    const Tensor* to = &n->tensors[op.out];
+    if (op.fused_pool >= 0) to = &n->tensors[n->ops[op.fused_pool].out];
+    const double cin = op.is_stem ? (double)ti.C : (double)op.Cin;
+    b += 2.0 * ti.H * ti.W * cin + 2.0 * to->H * to->W * op.Cout;
+    if (op.res >= 0) b += 2.0 * to->H * to->W * op.Cout;
+  }
+  return b;
+}
+
 void wsi_net_destroy(void* net) {
   Net* n = (Net*)net;
   if (!n) return;

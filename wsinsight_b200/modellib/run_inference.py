@@ -123,6 +123,54 @@ def gather_probs(probs_local, n_total: int, rank: int, world: int):
     return torch.cat([bufs[r][: hi - lo] for r, (lo, hi) in enumerate(sizes)], dim=0)
 
 
+def dist_rank_world():
+    """(rank, world) of the running ``torch.distributed`` job, (0, 1) outside one."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def classify_coords_sharded(slide, coords_xywh: np.ndarray, net, transform, batch_size: int, rank=None, world=None):
+    """ONE slide on all ranks of a ``torch.distributed`` job (replaces ``nn.DataParallel``, reference
+    run_inference.py:173-174): rank r classifies ``shard_range(N, r, R)`` of the x-major patch list -- an x-band of
+    the slide, no data-path collective -- and the ``(N_r, K)`` shards are gathered on rank 0 with one collective.
+
+    Returns the (N, K) float32 NumPy array on rank 0, ``None`` on the other ranks."""
+    if rank is None or world is None:
+        rank, world = dist_rank_world()
+    n = len(coords_xywh)
+    lo, hi = shard_range(n, rank, world)
+    local = classify_patches_device(slide, coords_xywh[lo:hi], net, transform, batch_size)
+    full = gather_probs(local, n, rank, world)
+    return full.cpu().numpy() if full is not None else None
+
+
+def classify_slide_sharded(slide, patch_size_px: int, patch_spacing_um_px: float, net, transform, batch_size: int,
+                           rank=None, world=None, thumb=None, **seg_kwargs):
+    """Whole-slide form: tissue segmentation + patchify run redundantly on every rank (about a millisecond; the
+    coordinates then need no broadcast), then :func:`classify_coords_sharded`.
+
+    Returns ``(coords_xywh (N, 4) int64, probs (N, K) float32)`` on rank 0, ``(coords_xywh, None)`` elsewhere."""
+    from ..patchlib import segment_and_patch_slides_device
+
+    res = segment_and_patch_slides_device([slide], patch_size_px, patch_spacing_um_px,
+                                          thumbs=None if thumb is None else [thumb], **seg_kwargs)[0]
+    if res.coords is None:
+        return np.zeros((0, 4), np.int64), (np.zeros((0, net.num_classes), np.float32) if (rank or 0) == 0 else None)
+    if rank is None or world is None:
+        rank, world = dist_rank_world()
+    n = int(res.coords.shape[0])
+    lo, hi = shard_range(n, rank, world)
+    cxy = res.coords.cpu().numpy().astype(np.int64)
+    xywh = np.concatenate([cxy, np.full_like(cxy, res.patch_size)], 1)
+    local = classify_patches_device(slide, xywh[lo:hi], net, transform, batch_size,
+                                    device_coords=res.coords[lo:hi].contiguous())
+    full = gather_probs(local, n, rank, world)
+    return xywh, (full.cpu().numpy() if full is not None else None)
+
+
 def write_slide_csv(path, coords_xywh: np.ndarray, probs: np.ndarray, class_names: List[str]) -> None:
     """CSV assembly of run_inference.py:568-607,732-733: minx,miny,width,height,prob_<class>..."""
     import pandas as pd
@@ -163,6 +211,11 @@ def run_inference(
     :class:`~wsinsight_b200.wsi.DeviceSlide` (decoders are out of scope).  ``num_workers`` is
     accepted and ignored: there are no DataLoader workers on this path.
 
+    Under ``torch.distributed`` (one process per GPU, NCCL) every rank calls this function with the same arguments
+    and its own ``slides`` (each slide open on the rank's device): each slide's patch list is sharded across the
+    ranks (:func:`classify_coords_sharded`) and rank 0 writes the CSV -- the reference's ``nn.DataParallel``
+    (:173-174) without the scatter/gather of image batches.
+
     Returns ``(failed_patching, failed_inference)`` like the reference.
     """
     if references_dir or qupath_detection_dir or qupath_geojson_detection_dir or qupath_geojson_annotation_dir \
@@ -179,6 +232,7 @@ def run_inference(
         raise PatchDirectoryNotFound("Results dir must include 'patches' dir")
     model_output_dir = results_dir / "model-outputs-csv"
     model_output_dir.mkdir(exist_ok=True)
+    rank, world = dist_rank_world()
     slides = slides or {}
     patch_paths = sorted(list(patch_dir.glob("*.h5")) + list(patch_dir.glob("*.h5.npz")))
     failed_patching = [str(p) for p in (slide_paths or [])
@@ -216,8 +270,12 @@ def run_inference(
 
                 net = B200Network.from_torchscript(model_info.model_path, model_info.config.num_classes,
                                                    input_size=S, max_batch=batch_size, device=slide.rgba.device)
-            probs = classify_patches_device(slide, coords, net, transform, batch_size)
-            write_slide_csv(slide_csv, coords, probs.cpu().numpy(), model_info.config.class_names)
+            if world > 1:
+                probs = classify_coords_sharded(slide, coords, net, transform, batch_size, rank, world)
+            else:
+                probs = classify_patches_device(slide, coords, net, transform, batch_size).cpu().numpy()
+            if rank == 0:
+                write_slide_csv(slide_csv, coords, probs, model_info.config.class_names)
         except Exception as e:  # noqa: BLE001 - slide-granular isolation, as upstream :268-280
             failed_inference.append(stem)
             logger.error(f"Failed inference on {wsi_path}", exc_info=e)

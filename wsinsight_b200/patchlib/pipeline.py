@@ -107,19 +107,35 @@ def segment_and_patch_slides_device(
     return results
 
 
+def draw_contours_on_thumbnail(thumb_rgb: np.ndarray, mask: np.ndarray) -> np.ndarray:
+    """Overlay of the reference's mask JPEG (io.py:146-166 + patch.py:57-60): the tissue mask's
+    ``cv.findContours(RETR_CCOMP, CHAIN_APPROX_SIMPLE)`` contours drawn 7 px wide on the thumbnail, outer
+    boundaries (no parent in the hierarchy) in (0, 255, 255), hole boundaries in (255, 255, 0).
+    An exporter, not part of the parity surface of the kernels: host OpenCV on the device-produced mask."""
+    import cv2 as cv
+
+    img = np.ascontiguousarray(thumb_rgb).copy()
+    contours, hierarchy = cv.findContours(np.ascontiguousarray(mask, dtype=np.uint8) * 255, cv.RETR_CCOMP,
+                                          cv.CHAIN_APPROX_SIMPLE)
+    if hierarchy is None:
+        return img
+    parent = hierarchy[0, :, 3]
+    outer = [c for c, p in zip(contours, parent) if p < 0]
+    holes = [c for c, p in zip(contours, parent) if p >= 0]
+    cv.drawContours(img, outer, -1, (0, 255, 255), 7)
+    cv.drawContours(img, holes, -1, (255, 255, 0), 7)
+    return img
+
+
 def _write_mask_jpeg(mask_path: Path, thumb_dev, mask_dev) -> None:
-    """Tissue overlay for humans (reference: io.py:146-166 draws cv2 contours; here the mask edge
-    is tinted).  Not part of the parity surface ("next" row N2)."""
+    """``masks/<stem>.jpg``: contour overlay, then ``thumbnail((1024, 1024), LANCZOS)`` (pipeline.py:439-444)."""
     from PIL import Image
 
-    thumb = thumb_dev.cpu().numpy().copy()
-    m = mask_dev.cpu().numpy().astype(bool)
-    edge = m & ~(np.roll(m, 1, 0) & np.roll(m, -1, 0) & np.roll(m, 1, 1) & np.roll(m, -1, 1))
-    thumb[edge] = (0, 255, 0)
-    img = Image.fromarray(thumb, mode="RGB")
+    img = Image.fromarray(draw_contours_on_thumbnail(thumb_dev.cpu().numpy(), mask_dev.cpu().numpy())).convert("RGB")
     img.thumbnail((1024, 1024), resample=Image.Resampling.LANCZOS)
     mask_path.parent.mkdir(exist_ok=True, parents=True)
-    img.save(mask_path)
+    with mask_path.open("wb") as fh:
+        img.save(fh)
 
 
 def segment_and_patch_one_slide(
@@ -145,6 +161,7 @@ def segment_and_patch_one_slide(
     stardist_normalization_pmax: float = 99.8,
     cache_image_patches: bool = False,
     slide=None,
+    closing_convention="scipy_raw",
 ) -> None:
     """Reference signature (pipeline.py:45-67).  ``slide`` is the opened
     :class:`~wsinsight_b200.wsi.DeviceSlide`; ``slide_path`` names it (stem = slide id)."""
@@ -163,7 +180,8 @@ def segment_and_patch_one_slide(
         return None
     res = segment_and_patch_slides_device(
         [slide], patch_size_px, patch_spacing_um_px, thumbsize, median_filter_size, binary_threshold,
-        closing_kernel_size, min_object_size_um2, min_hole_size_um2, overlap)[0]
+        closing_kernel_size, min_object_size_um2, min_hole_size_um2, overlap,
+        closing_convention=closing_convention)[0]
     if res.coords is None:
         logger.warning(f"No tissue was found in slide {slide_path}")
         return None
