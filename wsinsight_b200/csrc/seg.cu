@@ -1059,6 +1059,33 @@ int wsi_outermost_u8(const uint8_t* d_mask, int H, int W, uint8_t* d_outer, void
   return WSI_OK;
 }
 
+// Generic labelling of ONE 0/1 image for other modules (csrc/cellpost.cu): min-index union-find labels of both classes
+// (4-connected; conn8_fg adds the diagonals for the foreground; frame ties border background to the node H*W) and,
+// for area_cls in {0, 1}, the pixel count of every component of that class at its root.  *d_L_out / *d_area_out
+// point INTO the workspace (H*W + 1 ints each) and stay valid until the workspace is reused.
+int wsi_ccl_label_u8(const uint8_t* d_mask, int H, int W, int conn8_fg, int frame, int area_cls, int** d_L_out,
+                     int** d_area_out, void* d_ws, size_t ws_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_mask && d_ws && d_L_out, "wsi_ccl_label_u8: null pointer");
+  WSI_ARG_CHECK(area_cls >= -1 && area_cls <= 1, "wsi_ccl_label_u8: area_cls must be -1, 0 or 1");
+  const long long zero = 0;
+  SegBatch sb;
+  BatchLayout bl;
+  int rc = seg_prepare(1, &H, &W, nullptr, nullptr, &zero, nullptr, nullptr, d_ws, ws_bytes, stream, &sb, &bl);
+  if (rc) return rc;
+  uint8_t* ws = (uint8_t*)d_ws;
+  int* L = (int*)(ws + bl.off_L);
+  int* aux = (int*)(ws + bl.off_aux);
+  seg_label(sb, bl, d_mask, conn8_fg, frame, L, stream);
+  if (area_cls >= 0) WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, ((size_t)bl.npx + 1) * sizeof(int), stream));
+  k_ccl_flatten_area<<<wsi_cdiv(bl.npx, 256), 256, 0, stream>>>(d_mask, sb, bl.npx, area_cls, L, aux);
+  wsi_count_launch(1);
+  *d_L_out = L;
+  if (d_area_out) *d_area_out = aux;
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
+
 size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int half, int step) {
   if (step <= 0) return 0;
   long long ni = slide_w > half ? (slide_w - half + step - 1) / step : 0;
