@@ -290,6 +290,35 @@ int wsi_tilefuse_accumulate(const float* d_np_logits, const float* d_hv, const f
                             const int32_t* d_coords, int coord_stride, int B, int K, int h, int S, int halo, float alpha,
                             int canvas_W, int canvas_H, float* d_np_map, float* d_hv_map, float* d_tp_map, void* stream);
 
+/* N3 / a13: one padded tile of TileRemapStitcher.finalize (wsinsight/modellib/tilefuse.py:280-415): _proc_np_hv
+ * (:39-103: np >= 0.5, label + remove_small_objects, min-max normalised HV maps, Sobel ksize 21, ridge / marker,
+ * binary_fill_holes, 5x5 elliptical opening, label + remove_small_objects, GaussianBlur 3x3, marker-controlled
+ * watershed) and _stitching_worker (:109-174: interior crop, bounding box, class-probability means, outer contour)
+ * entirely on the device.
+ *   d_np / d_hv / d_tp point at the first pixel of the PADDED tile inside the canvases (f32; hv 2 and tp K interleaved
+ *   values per pixel), *_pitch = elements per canvas row.  [iy0, iy1) x [ix0, ix1) is the interior slice inside the
+ *   padded H x W tile, (gx0, gy0) its slide coordinates.
+ * Outputs (device): d_counts int32[4] = {instances, polygon points, error (1: > max_instances, 2: > max_poly_points),
+ * markers}; d_bbox int32 [max_instances][4] (x, y, w, h in slide pixels, instances in label order == the order of
+ * ndi.label); d_cls_mean f32 [max_instances][K]; d_poly_npts / d_poly_off int32 [max_instances] (0 points: the
+ * reference drops polygons with < 3 vertices); d_poly_xy int32 [max_poly_points][2]; d_inst_map (optional) int32
+ * [H][W] instance labels of the padded tile.  Differences to the reference are confined to exact floating-point ties
+ * of the flooding order and to instances that the interior crop splits into several 8-connected pieces (the piece
+ * holding the first raster pixel is traced; the reference takes the piece with the largest contour area). */
+size_t wsi_cellpost_workspace_bytes(int H, int W, int K, int max_instances);
+int wsi_cellpost_tile(const float* d_np, long long np_pitch, const float* d_hv, long long hv_pitch, const float* d_tp,
+                      long long tp_pitch, int K, int H, int W, int iy0, int iy1, int ix0, int ix1, int gx0, int gy0,
+                      int min_object_size, int max_instances, int max_poly_points, int* d_counts, int* d_bbox,
+                      float* d_cls_mean, int* d_poly_npts, int* d_poly_off, int* d_poly_xy, int* d_inst_map, void* d_ws,
+                      size_t ws_bytes, void* stream);
+
+/* Connected-component labelling of one 0/1 image (the labelling stage of K1, exported for the cell path): min-index
+ * union-find roots of both classes, 4-connected (conn8_fg: 8-connected foreground; frame: border background tied to
+ * node H*W); area_cls in {0, 1}: pixel count of that class at every root (-1: none).  *d_L_out / *d_area_out point
+ * into d_ws (wsi_seg_workspace_bytes(H, W) bytes). */
+int wsi_ccl_label_u8(const uint8_t* d_mask, int H, int W, int conn8_fg, int frame, int area_cls, int** d_L_out,
+                     int** d_area_out, void* d_ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

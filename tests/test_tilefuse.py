@@ -37,11 +37,13 @@ def test_oracle_shapes_and_sums():
 @pytest.mark.gpu
 @pytest.mark.parametrize("B,K,h,S,halo,W,H,alpha", [(9, 6, 164, 256, 46, 700, 600, 256 / 164), (5, 2, 40, 40, 0, 150, 170, 1.0),
                                                    (7, 5, 64, 37, 5, 120, 90, 0.37), (3, 16, 10, 64, 8, 100, 100, 2.0)])
-def test_stitcher_matches_reference_ops(B, K, h, S, halo, W, H, alpha):
+@pytest.mark.parametrize("canvas_tile", [2048, 64])
+def test_stitcher_matches_reference_ops(B, K, h, S, halo, W, H, alpha, canvas_tile):
     from wsinsight_b200.modellib.tilefuse import TileRemapStitcher
 
     np_l, hv, tp_l, coords = _inputs(B, K, h, B + K + h, W, H, S, halo)
-    st = TileRemapStitcher(K, W, H, S, halo, slide_mpp=1.0, model_mpp=alpha)
+    # canvas_tile = 64: the sparse canvases are many small tiles, every paste straddles several of them
+    st = TileRemapStitcher(K, W, H, S, halo, slide_mpp=1.0, model_mpp=alpha, canvas_tile=canvas_tile)
     st.accumulate_batch_torch({"np": np_l.cuda(), "hv": hv.cuda(), "tp": tp_l.cuda()}, coords)
     a, b, c = otf.accumulate(np_l, hv, tp_l, coords, S, halo, alpha, W, H)
     for got, want, name in ((st.np_map, a, "np"), (st.hv_map, b, "hv"), (st.tp_map, c, "tp")):
@@ -53,7 +55,26 @@ def test_stitcher_matches_reference_ops(B, K, h, S, halo, W, H, alpha):
     st.accumulate_batch_torch({"nuclei_binary_map": np2.cuda(), "hv_map": hv2.cuda(), "nuclei_type_map": tp2.cuda()}, coords2)
     a, b, c = otf.accumulate(np2, hv2, tp2, coords2, S, halo, alpha, W, H, a, b, c)
     assert np.abs(st.tp_map.cpu().numpy() - c).max() <= 2e-6
-    with pytest.raises(NotImplementedError):
-        st.finalize()
+    assert st.allocated_tiles() <= st.tiles_x * st.tiles_y
     with pytest.raises(ValueError):
         st.accumulate_batch_torch({"np": np_l.cuda(), "hv": hv.cuda(), "tp": tp_l[:, :1].cuda()}, coords)
+
+
+@pytest.mark.gpu
+def test_overlapping_tiles_of_one_batch_paste_in_order():
+    """The reference pastes tile after tile (tilefuse.py:262-278): where interiors of one batch overlap, the later tile
+    wins.  The device path detects the overlap and pastes in order instead of racing."""
+    from wsinsight_b200.modellib.tilefuse import TileRemapStitcher
+
+    B, K, h, S, halo, W, H = 6, 3, 24, 48, 4, 200, 160
+    g = torch.Generator().manual_seed(7)
+    np_l, hv, tp_l = torch.randn((B, 2, h, h), generator=g), torch.randn((B, 2, h, h), generator=g), torch.randn((B, K, h, h), generator=g)
+    xs = torch.tensor([0, 20, 40, 100, 110, 30])
+    ys = torch.tensor([0, 10, 30, 60, 70, 20])
+    coords = torch.stack([xs - halo, ys - halo, torch.full_like(xs, S + 2 * halo), torch.full_like(xs, S + 2 * halo)], 1)
+    st = TileRemapStitcher(K, W, H, S, halo, slide_mpp=1.0, model_mpp=1.0, canvas_tile=64)
+    st.accumulate_batch_torch({"np": np_l.cuda(), "hv": hv.cuda(), "tp": tp_l.cuda()}, coords)
+    a, b, c = otf.accumulate(np_l, hv, tp_l, coords, S, halo, 1.0, W, H)
+    assert np.abs(st.np_map.cpu().numpy() - a).max() <= 2e-6
+    assert np.abs(st.hv_map.cpu().numpy() - b).max() <= 2e-5
+    assert np.abs(st.tp_map.cpu().numpy() - c).max() <= 2e-6

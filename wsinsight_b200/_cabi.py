@@ -105,6 +105,12 @@ _PROTOS = {
     "wsi_pack_patches_rgba": (c_int, [c_void_p, c_int, c_int, c_ll, c_void_p, c_void_p]),
     "wsi_tilefuse_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                         C.c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "wsi_cellpost_workspace_bytes": (C.c_size_t, [c_int, c_int, c_int, c_int]),
+    "wsi_cellpost_tile": (c_int, [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_int, c_int, c_int, c_int, c_int, c_int,
+                                  c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "wsi_ccl_label_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, C.POINTER(c_void_p), C.POINTER(c_void_p),
+                                 c_void_p, c_size_t, c_void_p]),
     "wsi_thumbnail_geometry": (c_int, [c_ll, c_ll, c_int, c_int, c_int_p, c_int_p, c_int_p, c_int_p]),
     "wsi_thumbnail_workspace_bytes": (C.c_size_t, [c_ll, c_ll, c_int, c_int]),
     "wsi_lanczos_thumbnail": (c_int, [c_void_p, c_ll, c_ll, c_ll, c_int, c_int, c_void_p, c_void_p, C.c_size_t, c_void_p]),

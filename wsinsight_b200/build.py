@@ -18,7 +18,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libwsi_b200.so"
 STAMP = PKG / ".libwsi_b200.stamp"
-SOURCES = ["common.cu", "seg.cu", "preproc.cu", "net.cu", "synth.cu", "hostpipe.cu", "thumb.cu", "density.cu", "patchio.cu", "tilefuse.cu"]
+SOURCES = ["common.cu", "seg.cu", "preproc.cu", "net.cu", "synth.cu", "hostpipe.cu", "thumb.cu", "density.cu", "patchio.cu", "tilefuse.cu", "cellpost.cu"]
 HEADERS = ["common.cuh", "conv.cuh", "../../include/wsi_b200.h"]
 
 NVCC_FLAGS = [
