@@ -45,6 +45,18 @@ __device__ __forceinline__ int find_slide(const long long* __restrict__ base, in
   return lo;
 }
 
+// Per-pixel kernels: the slide of a CTA's first pixel is searched once (thread 0) and broadcast; a pixel past the end
+// of that slide steps forward linearly (a CTA straddles at most a couple of slides).  The binary search per thread
+// was a chain of log2(n) dependent loads in front of every pixel of a cohort.  Must be called by ALL threads of the CTA.
+__device__ __forceinline__ int find_slide_cta(const long long* __restrict__ base, int n, long long g) {
+  __shared__ int s_first;
+  if (threadIdx.x == 0) s_first = find_slide(base, n, (long long)blockIdx.x * blockDim.x);
+  __syncthreads();
+  int s = s_first;
+  while (s + 1 < n && base[s + 1] <= g) ++s;
+  return s;
+}
+
 // ----------------------------------------------------------------------------
 // K1a: RGB -> HSV saturation (OpenCV 8-bit formula) -> (S > thresh) -> k x k box
 // count with replicate border >= (k*k+1)/2   [== medianBlur(S,k) > thresh]
@@ -225,8 +237,8 @@ __global__ void __launch_bounds__(256)
     k_thresh_slide(const uint8_t* __restrict__ val_all, SegBatch sb, long long total, const int* __restrict__ thr,
                    uint8_t* __restrict__ out_all) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
   if (g >= total) return;
-  const int s = find_slide(sb.px_base, sb.n, g);
   const SegSlide sl = sb.slides[s];
   const long long idx = g - sb.px_base[s];
   (out_all + sl.mask_off)[idx] = (val_all + sl.mask_off)[idx] > thr[s] ? 1 : 0;
@@ -435,8 +447,8 @@ __global__ void __launch_bounds__(256)
     k_ccl_border_v1(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int conn8_fg, int frame,
                     int* __restrict__ L_all) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
   if (g >= total) return;
-  const int s = find_slide(sb.px_base, sb.n, g);
   const SegSlide sl = sb.slides[s];
   const int idx = (int)(g - sb.px_base[s]);
   const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
@@ -574,21 +586,27 @@ __global__ void __launch_bounds__(128)
 
 // Phase 3: flatten + per-root area of class `cls` pixels (warp-aggregated atomics).
 __global__ void __launch_bounds__(256)
-    k_ccl_flatten_area(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int cls,
+    k_ccl_flatten_area(const uint8_t* mask_all_c, SegBatch sb, long long total, int cls,
                        int* __restrict__ L_all, int* __restrict__ area_all) {
+  uint8_t* mask_all = const_cast<uint8_t*>(mask_all_c);   // transient marks 2 (fg -> bg) / 3 (bg -> fg) are folded to 0 / 1
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = g < total;
   int root = -1 - (int)(threadIdx.x & 31);
   bool act = false;
   int* area = nullptr;
+  const int s = find_slide_cta(sb.px_base, sb.n, live ? g : total - 1);
   if (live) {
-    const int s = find_slide(sb.px_base, sb.n, g);
     const SegSlide sl = sb.slides[s];
     const int idx = (int)(g - sb.px_base[s]);
     int* L = L_all + sl.lab_off;
     const int r = uf_find(L, idx);
     L[idx] = r;
-    act = (mask_all + sl.mask_off)[idx] == cls;
+    uint8_t m = (mask_all + sl.mask_off)[idx];
+    if (m > 1) {
+      m &= 1;
+      (mask_all + sl.mask_off)[idx] = m;
+    }
+    act = m == cls;
     if (act) {
       // key must be unique across slides inside one warp: use the global label slot
       root = (int)(sl.lab_off + r);
@@ -614,10 +632,10 @@ __global__ void __launch_bounds__(256)
 // cls==1: remove foreground components with area < thr; cls==0: fill background components with area < thr
 __global__ void __launch_bounds__(256)
     k_ccl_apply(uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
-                const int* __restrict__ area_all, int cls) {
+                const int* __restrict__ area_all, int cls, int mark) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
   if (g >= total) return;
-  const int s = find_slide(sb.px_base, sb.n, g);
   const SegSlide sl = sb.slides[s];
   const int idx = (int)(g - sb.px_base[s]);
   uint8_t* mask = mask_all + sl.mask_off;
@@ -625,7 +643,76 @@ __global__ void __launch_bounds__(256)
   if (thr <= 0) return;
   // L may not be fully flattened for pixels processed by other blocks of the fused flatten/area pass
   // when this kernel runs (it is: separate launch), so one lookup suffices.
-  if (mask[idx] == cls && area_all[sl.lab_off + L_all[sl.lab_off + idx]] < thr) mask[idx] = 1 - cls;
+  // mark == 0: write the new class; else write the transient mark (2: fg -> bg, 3: bg -> fg; value & 1 is the class)
+  // that the incremental merge kernels look for
+  if (mask[idx] == cls && area_all[sl.lab_off + L_all[sl.lab_off + idx]] < thr) mask[idx] = mark ? mark : 1 - cls;
+}
+
+// Incremental relabelling: pixels that just changed class (value == mark) join the neighbouring components of their new
+// class -- a handful of unions on the existing forest instead of a second labelling of the whole cohort.  Pixels
+// carrying the same mark belonged to one old component and already share a root.
+__global__ void __launch_bounds__(256)
+    k_ccl_merge_flipped(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int mark,
+                        int* __restrict__ L_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
+  if (g >= total) return;
+  const SegSlide sl = sb.slides[s];
+  const int idx = (int)(g - sb.px_base[s]);
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  if (mask[idx] != mark) return;
+  int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W, cls = mark & 1;
+  const int gy = idx / W, gx = idx - gy * W;
+  auto link = [&](int q) {
+    const uint8_t m = mask[q];
+    if (m != mark && (m & 1) == cls) uf_union(L, idx, q);
+  };
+  if (gx > 0) link(idx - 1);
+  if (gx < W - 1) link(idx + 1);
+  if (gy > 0) link(idx - W);
+  if (gy < H - 1) link(idx + W);
+}
+
+// From the 4-connected labelling of both classes to the one the outermost test needs: filled holes (mark 3) join the
+// foreground around them, foreground pixels gain their pure diagonal contacts (8-connectivity), border background is
+// tied to the frame node (one union per run of border background).
+__global__ void __launch_bounds__(256)
+    k_ccl_outer_links(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int* __restrict__ L_all) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
+  if (g >= total) return;
+  const SegSlide sl = sb.slides[s];
+  const int idx = (int)(g - sb.px_base[s]);
+  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+  int* __restrict__ L = L_all + sl.lab_off;
+  const int H = sl.H, W = sl.W;
+  const int gy = idx / W, gx = idx - gy * W;
+  const uint8_t m = mask[idx];
+  auto fg = [&](int q) { return (mask[q] & 1) != 0; };
+  if (m & 1) {
+    if (m == 3) {
+      if (gx > 0 && mask[idx - 1] == 1) uf_union(L, idx, idx - 1);
+      if (gx < W - 1 && mask[idx + 1] == 1) uf_union(L, idx, idx + 1);
+      if (gy > 0 && mask[idx - W] == 1) uf_union(L, idx, idx - W);
+      if (gy < H - 1 && mask[idx + W] == 1) uf_union(L, idx, idx + W);
+    }
+    if (gy > 0 && !fg(idx - W)) {
+      if (gx > 0 && fg(idx - W - 1) && !fg(idx - 1)) uf_union(L, idx, idx - W - 1);
+      if (gx < W - 1 && fg(idx - W + 1) && !fg(idx + 1)) uf_union(L, idx, idx - W + 1);
+    }
+  } else {
+    bool tie = false;
+    if (gy == 0 || gy == H - 1) tie = gx == 0 || fg(idx - 1);
+    if (!tie && (gx == 0 || gx == W - 1)) tie = gy == 0 || fg(idx - W);
+    if (tie) uf_union(L, idx, H * W);
+  }
+}
+
+// fold the transient marks when no later kernel does it
+__global__ void __launch_bounds__(256) k_mask_norm(uint8_t* __restrict__ mask, long long nbytes) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < nbytes && mask[g] > 1) mask[g] &= 1;
 }
 
 // outermost: a foreground component is outermost iff one of its pixels is on the image border or
@@ -634,8 +721,8 @@ __global__ void __launch_bounds__(256)
     k_outer_flag(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
                  int* __restrict__ flag_all) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
   if (g >= total) return;
-  const int s = find_slide(sb.px_base, sb.n, g);
   const SegSlide sl = sb.slides[s];
   const int idx = (int)(g - sb.px_base[s]);
   const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
@@ -656,8 +743,8 @@ __global__ void __launch_bounds__(256)
                   const int* __restrict__ flag_all, uint8_t* __restrict__ outer_all, int* __restrict__ info) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   int key = -1 - (int)(threadIdx.x & 31);
+  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
   if (g < total) {
-    const int s = find_slide(sb.px_base, sb.n, g);
     const SegSlide sl = sb.slides[s];
     const int idx = (int)(g - sb.px_base[s]);
     const uint8_t m = (mask_all + sl.mask_off)[idx];
@@ -665,9 +752,18 @@ __global__ void __launch_bounds__(256)
     if (m == 1) key = s;
   }
   if (info) {
-    // per-slide "the mask has tissue" flag (replaces a host-side mask.any()): one store per warp and slide
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (key >= 0 && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) info[4 * key + 1] = 1;
+    // per-slide "the mask has tissue" flag (replaces a host-side mask.any()): one store per warp in the common case
+    // of a warp inside one slide, one per lane otherwise
+    const unsigned live = __ballot_sync(0xffffffffu, key >= 0);
+    if (live) {
+      const int k0 = __shfl_sync(0xffffffffu, key, __ffs(live) - 1);
+      const bool uniform = __all_sync(0xffffffffu, key < 0 || key == k0);
+      if (uniform) {
+        if ((int)(threadIdx.x & 31) == __ffs(live) - 1) info[4 * k0 + 1] = 1;
+      } else if (key >= 0) {
+        info[4 * key + 1] = 1;
+      }
+    }
   }
 }
 
@@ -909,16 +1005,24 @@ static void seg_label(const SegBatch& sb, const BatchLayout& bl, const uint8_t* 
   wsi_count_launch(2);
 }
 
-// 8-connected foreground labelling + frame adjacency -> outermost-component mask
-static int seg_outermost(const SegBatch& sb, const BatchLayout& bl, const uint8_t* d_mask, uint8_t* d_outer, void* d_ws,
-                         int* d_info, cudaStream_t stream) {
+// 8-connected foreground labelling + frame adjacency -> outermost-component mask.
+// have_base: L already holds the 4-connected labelling of both classes of the mask as it was before the pixels now
+// carrying the marks 2 / 3 changed class (those with mark 2 are already merged): add the missing links instead of
+// labelling again.
+static int seg_outermost(const SegBatch& sb, const BatchLayout& bl, uint8_t* d_mask, uint8_t* d_outer, void* d_ws,
+                         int* d_info, bool have_base, cudaStream_t stream) {
   uint8_t* ws = (uint8_t*)d_ws;
   int* L = (int*)(ws + bl.off_L);
   int* aux = (int*)(ws + bl.off_aux);
   const long long total = bl.npx;
   const size_t lab_bytes = ((size_t)bl.npx + sb.n) * sizeof(int);
   const int nb = wsi_cdiv(total, 256);
-  seg_label(sb, bl, d_mask, 1, 1, L, stream);
+  if (have_base) {
+    k_ccl_outer_links<<<nb, 256, 0, stream>>>(d_mask, sb, total, L);
+    wsi_count_launch(1);
+  } else {
+    seg_label(sb, bl, d_mask, 1, 1, L, stream);
+  }
   k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
   WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
   k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux);
@@ -1003,20 +1107,50 @@ int wsi_seg_tissue_batch_ex(const uint8_t* d_rgb, int n, const int* h_H, const i
     ++launches;
   }
   // remove_small_objects (4-conn foreground, area < min) then remove_small_holes (4-conn background)
-  for (int pass = 0; pass < 2; ++pass) {
-    const int cls = pass == 0 ? 1 : 0;
-    bool any = false;
-    for (int s = 0; s < n; ++s) any = any || ((cls ? h_min_object_px[s] : h_min_hole_px[s]) > 0);
-    if (!any) continue;
+  bool any_obj = false, any_hole = false;
+  for (int s = 0; s < n; ++s) {
+    any_obj = any_obj || h_min_object_px[s] > 0;
+    any_hole = any_hole || h_min_hole_px[s] > 0;
+  }
+  bool have_base = false;
+  if (legacy) {
+    for (int pass = 0; pass < 2; ++pass) {
+      const int cls = pass == 0 ? 1 : 0;
+      if (!(cls ? any_obj : any_hole)) continue;
+      seg_label(sb, bl, d_mask, 0, 0, L, stream);
+      WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
+      k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, cls, L, aux);
+      k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls, 0);
+      launches += 2;
+    }
+  } else if (any_obj || any_hole || d_outer) {
+    // ONE labelling of both classes; every later stage adds the few unions its class changes call for
     seg_label(sb, bl, d_mask, 0, 0, L, stream);
-    WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
-    k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, cls, L, aux);
-    k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls);
-    launches += 2;
+    have_base = true;
+    bool marks = false;
+    if (any_obj) {
+      WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
+      k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, 1, L, aux);
+      k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, 1, 2);
+      k_ccl_merge_flipped<<<nb, 256, 0, stream>>>(d_mask, sb, total, 2, L);
+      launches += 3;
+      marks = true;
+    }
+    if (any_hole) {
+      WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
+      k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, 0, L, aux);     // folds the marks 2 -> 0
+      k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, 0, 3);
+      launches += 2;
+      marks = true;
+    }
+    if (!d_outer && marks) {
+      k_mask_norm<<<wsi_cdiv(total, 256), 256, 0, stream>>>(d_mask, total);
+      ++launches;
+    }
   }
   wsi_count_launch(launches);
   if (d_outer) {
-    rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, info, stream);
+    rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, info, have_base, stream);
     if (rc) return rc;
   }
   WSI_CUDA_CHECK(cudaGetLastError());
@@ -1053,7 +1187,7 @@ int wsi_outermost_u8(const uint8_t* d_mask, int H, int W, uint8_t* d_outer, void
   BatchLayout bl;
   int rc = seg_prepare(1, &H, &W, nullptr, nullptr, &zero, nullptr, nullptr, d_ws, ws_bytes, stream, &sb, &bl);
   if (rc) return rc;
-  rc = seg_outermost(sb, bl, d_mask, d_outer, d_ws, nullptr, stream);
+  rc = seg_outermost(sb, bl, const_cast<uint8_t*>(d_mask), d_outer, d_ws, nullptr, false, stream);
   if (rc) return rc;
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
