@@ -219,6 +219,30 @@ def test_grid_vs_contour_oracle(seed):
     assert got.dtype == np.int64 and got.tolist() == sorted(got.tolist())
 
 
+def test_grid_self_touching_necks_vs_contour_oracle():
+    """Contours that touch themselves (1-px necks, diagonal contacts, a hole reaching a neck): the shapes for which the
+    reference repairs polygons with Shapely's buffer(0) (patch.py:95-97).  Oracle: live cv2 contours + even-odd
+    point-in-polygon in the reference's add / subtract order; GEOS' own repair is NOT pinned (shapely is absent)."""
+    m = np.zeros((60, 80), bool)
+    m[5:25, 5:25] = True
+    m[14, 25:40] = True                      # 1-px horizontal neck
+    m[5:25, 40:60] = True
+    m[25:40, 50] = True                      # 1-px vertical neck
+    m[40:55, 40:70] = True
+    m[45:50, 45:50] = False                  # hole
+    m[30:38, 10:18] = True
+    m[38:46, 18:26] = True                   # diagonal contact of two squares (8-connected, one contour)
+    m[12:16, 12:16] = False
+    m[16:20, 16:20] = False                  # two holes touching diagonally
+    W, H, ps = 80 * 23 + 3, 60 * 19 + 1, 17
+    got = _grid(m, W, H, ps)
+    want, ties = patchgrid.patch_coordinates(m, W, H, ps, round(ps / 2), 0.0, return_ties=True)
+    tie = {tuple(t) for t in ties.tolist()}
+    a = [t for t in map(tuple, want.tolist()) if t not in tie]
+    b = [t for t in map(tuple, got.tolist()) if t not in tie]
+    assert a == b and len(a) > 100, f"{len(a)} vs {len(b)}; ties {len(tie)}"
+
+
 def test_grid_errors_and_empty():
     from wsinsight_b200.patchlib import get_multipolygon_from_binary_arr, get_patch_coordinates_within_polygon
     assert get_multipolygon_from_binary_arr(np.zeros((32, 32), np.uint8), slide_dims=(320, 320)) is None

@@ -584,68 +584,88 @@ __global__ void __launch_bounds__(128)
   }
 }
 
-// Phase 3: flatten + per-root area of class `cls` pixels (warp-aggregated atomics).
+// ---- per-pixel passes: PXT pixels per thread (iteration it of a CTA handles pixel first + it * 256 + tid, coalesced) ----
+constexpr int PXT = 4;
+constexpr int PX_CTA = 256 * PXT;
+
+// slide of the CTA's first pixel: one binary search per CTA (thread 0) + broadcast.  Called by ALL threads, once.
+__device__ __forceinline__ int cta_slide(const long long* __restrict__ base, int n, long long first) {
+  __shared__ int s_first;
+  if (threadIdx.x == 0) s_first = find_slide(base, n, first);
+  __syncthreads();
+  return s_first;
+}
+__device__ __forceinline__ int advance_slide(const long long* __restrict__ base, int n, int s, long long g) {
+  while (s + 1 < n && base[s + 1] <= g) ++s;
+  return s;
+}
+
+// Phase 3: flatten + per-root area of class `cls` pixels (one atomic per CTA pass when all its pixels share a root,
+// warp-aggregated atomics otherwise).  Transient marks 2 (fg -> bg) / 3 (bg -> fg) are folded to 0 / 1 here.
 __global__ void __launch_bounds__(256)
     k_ccl_flatten_area(const uint8_t* mask_all_c, SegBatch sb, long long total, int cls,
                        int* __restrict__ L_all, int* __restrict__ area_all) {
-  uint8_t* mask_all = const_cast<uint8_t*>(mask_all_c);   // transient marks 2 (fg -> bg) / 3 (bg -> fg) are folded to 0 / 1
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = g < total;
-  int root = -1 - (int)(threadIdx.x & 31);
-  bool act = false;
-  int* area = nullptr;
-  const int s = find_slide_cta(sb.px_base, sb.n, live ? g : total - 1);
-  if (live) {
-    const SegSlide sl = sb.slides[s];
-    const int idx = (int)(g - sb.px_base[s]);
-    int* L = L_all + sl.lab_off;
-    const int r = uf_find(L, idx);
-    L[idx] = r;
-    uint8_t m = (mask_all + sl.mask_off)[idx];
-    if (m > 1) {
-      m &= 1;
-      (mask_all + sl.mask_off)[idx] = m;
-    }
-    act = m == cls;
-    if (act) {
-      // key must be unique across slides inside one warp: use the global label slot
-      root = (int)(sl.lab_off + r);
-      area = area_all;
-    }
-  }
-  if (cls < 0) return;   // flatten only (kernel-uniform)
-  // block-level fast path: interior blocks see one root; count its pixels with one atomic per CTA
+  uint8_t* mask_all = const_cast<uint8_t*>(mask_all_c);
+  const long long first = (long long)blockIdx.x * PX_CTA;
+  const int s0 = cta_slide(sb.px_base, sb.n, first);
   __shared__ int s_key;
-  if (threadIdx.x == 0) s_key = root;
-  __syncthreads();
-  const bool same = act && root == s_key;
-  const int c = __syncthreads_count(same);
-  if (threadIdx.x == 0 && c) atomicAdd(&area_all[root], c);
-  if (same) {
-    act = false;
-    root = -1 - (int)(threadIdx.x & 31);
+#pragma unroll 1
+  for (int it = 0; it < PXT; ++it) {
+    const long long g = first + it * 256 + threadIdx.x;
+    const bool live = g < total;
+    int root = -1 - (int)(threadIdx.x & 31);
+    bool act = false;
+    if (live) {
+      const int s = advance_slide(sb.px_base, sb.n, s0, g);
+      const SegSlide sl = sb.slides[s];
+      const int idx = (int)(g - sb.px_base[s]);
+      int* L = L_all + sl.lab_off;
+      const int r = uf_find(L, idx);
+      L[idx] = r;
+      uint8_t m = (mask_all + sl.mask_off)[idx];
+      if (m > 1) {
+        m &= 1;
+        (mask_all + sl.mask_off)[idx] = m;
+      }
+      act = m == cls;
+      if (act) root = (int)(sl.lab_off + r);   // unique across slides inside one warp: the global label slot
+    }
+    if (cls < 0) continue;   // flatten only (kernel-uniform)
+    __syncthreads();
+    if (threadIdx.x == 0) s_key = root;
+    __syncthreads();
+    const bool same = act && root == s_key;
+    const int c = __syncthreads_count(same);
+    if (threadIdx.x == 0 && c) atomicAdd(&area_all[root], c);
+    if (same) {
+      act = false;
+      root = -1 - (int)(threadIdx.x & 31);
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, root);
+    if (act && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&area_all[root], __popc(peers));
   }
-  unsigned peers = __match_any_sync(0xffffffffu, root);
-  if (act && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&area[root], __popc(peers));
 }
 
-// cls==1: remove foreground components with area < thr; cls==0: fill background components with area < thr
+// cls==1: remove foreground components with area < thr; cls==0: fill background components with area < thr.
+// mark == 0: write the new class; else write the transient mark (2: fg -> bg, 3: bg -> fg; value & 1 is the class)
+// that the incremental merge kernels look for.
 __global__ void __launch_bounds__(256)
     k_ccl_apply(uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
                 const int* __restrict__ area_all, int cls, int mark) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
-  if (g >= total) return;
-  const SegSlide sl = sb.slides[s];
-  const int idx = (int)(g - sb.px_base[s]);
-  uint8_t* mask = mask_all + sl.mask_off;
-  const int thr = cls ? sl.min_obj : sl.min_hole;
-  if (thr <= 0) return;
-  // L may not be fully flattened for pixels processed by other blocks of the fused flatten/area pass
-  // when this kernel runs (it is: separate launch), so one lookup suffices.
-  // mark == 0: write the new class; else write the transient mark (2: fg -> bg, 3: bg -> fg; value & 1 is the class)
-  // that the incremental merge kernels look for
-  if (mask[idx] == cls && area_all[sl.lab_off + L_all[sl.lab_off + idx]] < thr) mask[idx] = mark ? mark : 1 - cls;
+  const long long first = (long long)blockIdx.x * PX_CTA;
+  const int s0 = cta_slide(sb.px_base, sb.n, first);
+#pragma unroll
+  for (int it = 0; it < PXT; ++it) {
+    const long long g = first + it * 256 + threadIdx.x;
+    if (g >= total) continue;
+    const int s = advance_slide(sb.px_base, sb.n, s0, g);
+    const SegSlide sl = sb.slides[s];
+    const int idx = (int)(g - sb.px_base[s]);
+    uint8_t* mask = mask_all + sl.mask_off;
+    const int thr = cls ? sl.min_obj : sl.min_hole;
+    if (thr <= 0) continue;
+    if (mask[idx] == cls && area_all[sl.lab_off + L_all[sl.lab_off + idx]] < thr) mask[idx] = mark ? mark : 1 - cls;
+  }
 }
 
 // Incremental relabelling: pixels that just changed class (value == mark) join the neighbouring components of their new
@@ -654,24 +674,29 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     k_ccl_merge_flipped(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int mark,
                         int* __restrict__ L_all) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
-  if (g >= total) return;
-  const SegSlide sl = sb.slides[s];
-  const int idx = (int)(g - sb.px_base[s]);
-  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
-  if (mask[idx] != mark) return;
-  int* __restrict__ L = L_all + sl.lab_off;
-  const int H = sl.H, W = sl.W, cls = mark & 1;
-  const int gy = idx / W, gx = idx - gy * W;
-  auto link = [&](int q) {
-    const uint8_t m = mask[q];
-    if (m != mark && (m & 1) == cls) uf_union(L, idx, q);
-  };
-  if (gx > 0) link(idx - 1);
-  if (gx < W - 1) link(idx + 1);
-  if (gy > 0) link(idx - W);
-  if (gy < H - 1) link(idx + W);
+  const long long first = (long long)blockIdx.x * PX_CTA;
+  const int s0 = cta_slide(sb.px_base, sb.n, first);
+#pragma unroll
+  for (int it = 0; it < PXT; ++it) {
+    const long long g = first + it * 256 + threadIdx.x;
+    if (g >= total) continue;
+    const int s = advance_slide(sb.px_base, sb.n, s0, g);
+    const SegSlide sl = sb.slides[s];
+    const int idx = (int)(g - sb.px_base[s]);
+    const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+    if (mask[idx] != mark) continue;
+    int* __restrict__ L = L_all + sl.lab_off;
+    const int H = sl.H, W = sl.W, cls = mark & 1;
+    const int gy = idx / W, gx = idx - gy * W;
+    auto link = [&](int q) {
+      const uint8_t m = mask[q];
+      if (m != mark && (m & 1) == cls) uf_union(L, idx, q);
+    };
+    if (gx > 0) link(idx - 1);
+    if (gx < W - 1) link(idx + 1);
+    if (gy > 0) link(idx - W);
+    if (gy < H - 1) link(idx + W);
+  }
 }
 
 // From the 4-connected labelling of both classes to the one the outermost test needs: filled holes (mark 3) join the
@@ -679,33 +704,38 @@ __global__ void __launch_bounds__(256)
 // tied to the frame node (one union per run of border background).
 __global__ void __launch_bounds__(256)
     k_ccl_outer_links(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, int* __restrict__ L_all) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
-  if (g >= total) return;
-  const SegSlide sl = sb.slides[s];
-  const int idx = (int)(g - sb.px_base[s]);
-  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
-  int* __restrict__ L = L_all + sl.lab_off;
-  const int H = sl.H, W = sl.W;
-  const int gy = idx / W, gx = idx - gy * W;
-  const uint8_t m = mask[idx];
-  auto fg = [&](int q) { return (mask[q] & 1) != 0; };
-  if (m & 1) {
-    if (m == 3) {
-      if (gx > 0 && mask[idx - 1] == 1) uf_union(L, idx, idx - 1);
-      if (gx < W - 1 && mask[idx + 1] == 1) uf_union(L, idx, idx + 1);
-      if (gy > 0 && mask[idx - W] == 1) uf_union(L, idx, idx - W);
-      if (gy < H - 1 && mask[idx + W] == 1) uf_union(L, idx, idx + W);
+  const long long first = (long long)blockIdx.x * PX_CTA;
+  const int s0 = cta_slide(sb.px_base, sb.n, first);
+#pragma unroll
+  for (int it = 0; it < PXT; ++it) {
+    const long long g = first + it * 256 + threadIdx.x;
+    if (g >= total) continue;
+    const int s = advance_slide(sb.px_base, sb.n, s0, g);
+    const SegSlide sl = sb.slides[s];
+    const int idx = (int)(g - sb.px_base[s]);
+    const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+    int* __restrict__ L = L_all + sl.lab_off;
+    const int H = sl.H, W = sl.W;
+    const int gy = idx / W, gx = idx - gy * W;
+    const uint8_t m = mask[idx];
+    auto fg = [&](int q) { return (mask[q] & 1) != 0; };
+    if (m & 1) {
+      if (m == 3) {
+        if (gx > 0 && mask[idx - 1] == 1) uf_union(L, idx, idx - 1);
+        if (gx < W - 1 && mask[idx + 1] == 1) uf_union(L, idx, idx + 1);
+        if (gy > 0 && mask[idx - W] == 1) uf_union(L, idx, idx - W);
+        if (gy < H - 1 && mask[idx + W] == 1) uf_union(L, idx, idx + W);
+      }
+      if (gy > 0 && !fg(idx - W)) {
+        if (gx > 0 && fg(idx - W - 1) && !fg(idx - 1)) uf_union(L, idx, idx - W - 1);
+        if (gx < W - 1 && fg(idx - W + 1) && !fg(idx + 1)) uf_union(L, idx, idx - W + 1);
+      }
+    } else {
+      bool tie = false;
+      if (gy == 0 || gy == H - 1) tie = gx == 0 || fg(idx - 1);
+      if (!tie && (gx == 0 || gx == W - 1)) tie = gy == 0 || fg(idx - W);
+      if (tie) uf_union(L, idx, H * W);
     }
-    if (gy > 0 && !fg(idx - W)) {
-      if (gx > 0 && fg(idx - W - 1) && !fg(idx - 1)) uf_union(L, idx, idx - W - 1);
-      if (gx < W - 1 && fg(idx - W + 1) && !fg(idx + 1)) uf_union(L, idx, idx - W + 1);
-    }
-  } else {
-    bool tie = false;
-    if (gy == 0 || gy == H - 1) tie = gx == 0 || fg(idx - 1);
-    if (!tie && (gx == 0 || gx == W - 1)) tie = gy == 0 || fg(idx - W);
-    if (tie) uf_union(L, idx, H * W);
   }
 }
 
@@ -720,50 +750,50 @@ __global__ void __launch_bounds__(256) k_mask_norm(uint8_t* __restrict__ mask, l
 __global__ void __launch_bounds__(256)
     k_outer_flag(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
                  int* __restrict__ flag_all) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
-  if (g >= total) return;
-  const SegSlide sl = sb.slides[s];
-  const int idx = (int)(g - sb.px_base[s]);
-  const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
-  if (mask[idx] != 1) return;
-  const int* __restrict__ L = L_all + sl.lab_off;
-  const int H = sl.H, W = sl.W;
-  const int gy = idx / W, gx = idx - gy * W;
-  bool o = gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1;
-  if (!o) {
-    const int fr = uf_find(L, H * W);
-    o = (mask[idx - 1] == 0 && L[idx - 1] == fr) || (mask[idx + 1] == 0 && L[idx + 1] == fr) ||
-        (mask[idx - W] == 0 && L[idx - W] == fr) || (mask[idx + W] == 0 && L[idx + W] == fr);
+  const long long first = (long long)blockIdx.x * PX_CTA;
+  const int s0 = cta_slide(sb.px_base, sb.n, first);
+#pragma unroll
+  for (int it = 0; it < PXT; ++it) {
+    const long long g = first + it * 256 + threadIdx.x;
+    if (g >= total) continue;
+    const int s = advance_slide(sb.px_base, sb.n, s0, g);
+    const SegSlide sl = sb.slides[s];
+    const int idx = (int)(g - sb.px_base[s]);
+    const uint8_t* __restrict__ mask = mask_all + sl.mask_off;
+    if (mask[idx] != 1) continue;
+    const int* __restrict__ L = L_all + sl.lab_off;
+    const int H = sl.H, W = sl.W;
+    const int gy = idx / W, gx = idx - gy * W;
+    bool o = gx == 0 || gy == 0 || gx == W - 1 || gy == H - 1;
+    if (!o) {
+      // only a pixel with a background 4-neighbour can touch the frame-connected background
+      const bool b0 = mask[idx - 1] == 0, b1 = mask[idx + 1] == 0, b2 = mask[idx - W] == 0, b3 = mask[idx + W] == 0;
+      if (b0 || b1 || b2 || b3) {
+        const int fr = uf_find(L, H * W);
+        o = (b0 && L[idx - 1] == fr) || (b1 && L[idx + 1] == fr) || (b2 && L[idx - W] == fr) || (b3 && L[idx + W] == fr);
+      }
+    }
+    if (o) flag_all[sl.lab_off + L[idx]] = 1;
   }
-  if (o) flag_all[sl.lab_off + L[idx]] = 1;
 }
+
 __global__ void __launch_bounds__(256)
     k_outer_apply(const uint8_t* __restrict__ mask_all, SegBatch sb, long long total, const int* __restrict__ L_all,
                   const int* __restrict__ flag_all, uint8_t* __restrict__ outer_all, int* __restrict__ info) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  int key = -1 - (int)(threadIdx.x & 31);
-  const int s = find_slide_cta(sb.px_base, sb.n, g < total ? g : total - 1);
-  if (g < total) {
+  const long long first = (long long)blockIdx.x * PX_CTA;
+  const int s0 = cta_slide(sb.px_base, sb.n, first);
+#pragma unroll
+  for (int it = 0; it < PXT; ++it) {
+    const long long g = first + it * 256 + threadIdx.x;
+    if (g >= total) continue;
+    const int s = advance_slide(sb.px_base, sb.n, s0, g);
     const SegSlide sl = sb.slides[s];
     const int idx = (int)(g - sb.px_base[s]);
     const uint8_t m = (mask_all + sl.mask_off)[idx];
     (outer_all + sl.mask_off)[idx] = (m == 1 && flag_all[sl.lab_off + L_all[sl.lab_off + idx]]) ? 1 : 0;
-    if (m == 1) key = s;
-  }
-  if (info) {
-    // per-slide "the mask has tissue" flag (replaces a host-side mask.any()): one store per warp in the common case
-    // of a warp inside one slide, one per lane otherwise
-    const unsigned live = __ballot_sync(0xffffffffu, key >= 0);
-    if (live) {
-      const int k0 = __shfl_sync(0xffffffffu, key, __ffs(live) - 1);
-      const bool uniform = __all_sync(0xffffffffu, key < 0 || key == k0);
-      if (uniform) {
-        if ((int)(threadIdx.x & 31) == __ffs(live) - 1) info[4 * k0 + 1] = 1;
-      } else if (key >= 0) {
-        info[4 * key + 1] = 1;
-      }
-    }
+    // per-slide "the mask has tissue" flag (replaces a host-side mask.any()): the store of a slide's FIRST tissue
+    // pixel in this thread's stripe is enough -- benign same-value stores, no warp collectives
+    if (info && m == 1 && (idx == 0 || (mask_all + sl.mask_off)[idx - 1] != 1)) info[4 * s + 1] = 1;
   }
 }
 
@@ -1016,17 +1046,18 @@ static int seg_outermost(const SegBatch& sb, const BatchLayout& bl, uint8_t* d_m
   int* aux = (int*)(ws + bl.off_aux);
   const long long total = bl.npx;
   const size_t lab_bytes = ((size_t)bl.npx + sb.n) * sizeof(int);
-  const int nb = wsi_cdiv(total, 256);
+  const int nb = wsi_cdiv(total, 256), nbp = wsi_cdiv(total, PX_CTA);
+  (void)nb;
   if (have_base) {
-    k_ccl_outer_links<<<nb, 256, 0, stream>>>(d_mask, sb, total, L);
+    k_ccl_outer_links<<<nbp, 256, 0, stream>>>(d_mask, sb, total, L);
     wsi_count_launch(1);
   } else {
     seg_label(sb, bl, d_mask, 1, 1, L, stream);
   }
-  k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
+  k_ccl_flatten_area<<<nbp, 256, 0, stream>>>(d_mask, sb, total, -1, L, aux);
   WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
-  k_outer_flag<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux);
-  k_outer_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer, d_info);
+  k_outer_flag<<<nbp, 256, 0, stream>>>(d_mask, sb, total, L, aux);
+  k_outer_apply<<<nbp, 256, 0, stream>>>(d_mask, sb, total, L, aux, d_outer, d_info);
   wsi_count_launch(3);
   return WSI_OK;
 }
@@ -1069,7 +1100,8 @@ int wsi_seg_tissue_batch_ex(const uint8_t* d_rgb, int n, const int* h_H, const i
   int* info = d_info ? d_info : (int*)(ws + bl.off_info);
   const long long total = bl.npx;
   const size_t lab_bytes = ((size_t)bl.npx + n) * sizeof(int);
-  const int nb = wsi_cdiv(total, 256);
+  const int nb = wsi_cdiv(total, 256), nbp = wsi_cdiv(total, PX_CTA);
+  (void)nb;
   const bool legacy = seg_legacy();
   int launches = 0;
   WSI_CUDA_CHECK(cudaMemsetAsync(info, 0, sizeof(int) * 4 * (size_t)n, stream));
@@ -1119,8 +1151,8 @@ int wsi_seg_tissue_batch_ex(const uint8_t* d_rgb, int n, const int* h_H, const i
       if (!(cls ? any_obj : any_hole)) continue;
       seg_label(sb, bl, d_mask, 0, 0, L, stream);
       WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
-      k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, cls, L, aux);
-      k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls, 0);
+      k_ccl_flatten_area<<<nbp, 256, 0, stream>>>(d_mask, sb, total, cls, L, aux);
+      k_ccl_apply<<<nbp, 256, 0, stream>>>(d_mask, sb, total, L, aux, cls, 0);
       launches += 2;
     }
   } else if (any_obj || any_hole || d_outer) {
@@ -1130,16 +1162,16 @@ int wsi_seg_tissue_batch_ex(const uint8_t* d_rgb, int n, const int* h_H, const i
     bool marks = false;
     if (any_obj) {
       WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
-      k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, 1, L, aux);
-      k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, 1, 2);
-      k_ccl_merge_flipped<<<nb, 256, 0, stream>>>(d_mask, sb, total, 2, L);
+      k_ccl_flatten_area<<<nbp, 256, 0, stream>>>(d_mask, sb, total, 1, L, aux);
+      k_ccl_apply<<<nbp, 256, 0, stream>>>(d_mask, sb, total, L, aux, 1, 2);
+      k_ccl_merge_flipped<<<nbp, 256, 0, stream>>>(d_mask, sb, total, 2, L);
       launches += 3;
       marks = true;
     }
     if (any_hole) {
       WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, lab_bytes, stream));
-      k_ccl_flatten_area<<<nb, 256, 0, stream>>>(d_mask, sb, total, 0, L, aux);     // folds the marks 2 -> 0
-      k_ccl_apply<<<nb, 256, 0, stream>>>(d_mask, sb, total, L, aux, 0, 3);
+      k_ccl_flatten_area<<<nbp, 256, 0, stream>>>(d_mask, sb, total, 0, L, aux);     // folds the marks 2 -> 0
+      k_ccl_apply<<<nbp, 256, 0, stream>>>(d_mask, sb, total, L, aux, 0, 3);
       launches += 2;
       marks = true;
     }
@@ -1212,7 +1244,7 @@ int wsi_ccl_label_u8(const uint8_t* d_mask, int H, int W, int conn8_fg, int fram
   int* aux = (int*)(ws + bl.off_aux);
   seg_label(sb, bl, d_mask, conn8_fg, frame, L, stream);
   if (area_cls >= 0) WSI_CUDA_CHECK(cudaMemsetAsync(aux, 0, ((size_t)bl.npx + 1) * sizeof(int), stream));
-  k_ccl_flatten_area<<<wsi_cdiv(bl.npx, 256), 256, 0, stream>>>(d_mask, sb, bl.npx, area_cls, L, aux);
+  k_ccl_flatten_area<<<wsi_cdiv(bl.npx, PX_CTA), 256, 0, stream>>>(d_mask, sb, bl.npx, area_cls, L, aux);
   wsi_count_launch(1);
   *d_L_out = L;
   if (d_area_out) *d_area_out = aux;
