@@ -279,6 +279,13 @@ int wsi_extract_patches_rgb(const uint8_t* d_slide_rgba, long long W, long long 
 int wsi_pack_patches_rgba(const uint8_t* d_rgb, int n, int patch_size, long long pitch_bytes, uint8_t* d_out_rgba,
                           void* stream);
 
+/* N4: Macenko stain normalisation of RGB patches, per pixel (HistomicsTK deconvolution_based_normalization as the
+ * reference calls it, wsinsight/modellib/data.py:293-300; matrix estimation wsinsight/modellib/run_inference.py:232-264).
+ * h_M9 = W_target . inv(normalised, complemented W_source), row major, float64 (host).  d_rgb u8 [n_pixels][3];
+ * in-place allowed.  HistomicsTK is not available offline: parity unpinned (oracle/stain.py restates it). */
+int wsi_stain_normalize_rgb(const uint8_t* d_rgb_in, uint8_t* d_rgb_out, long long n_pixels, const double* h_M9,
+                            void* stream);
+
 /* a13 / N3: batch step of the cell-model tile stitcher, fused.  Replaces
  * wsinsight/modellib/tilefuse.py:219-278 TileRemapStitcher.accumulate_batch_torch (softmax, bilinear
  * align_corners=False resize h -> S, hv * alpha, tp renormalisation, D2H and the Python paste loop) with one kernel

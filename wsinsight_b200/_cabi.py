@@ -103,6 +103,7 @@ _PROTOS = {
     "wsi_density_accumulate": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "wsi_extract_patches_rgb": (c_int, [c_void_p, c_ll, c_ll, c_ll, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "wsi_pack_patches_rgba": (c_int, [c_void_p, c_int, c_int, c_ll, c_void_p, c_void_p]),
+    "wsi_stain_normalize_rgb": (c_int, [c_void_p, c_void_p, c_ll, C.POINTER(C.c_double), c_void_p]),
     "wsi_tilefuse_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                         C.c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "wsi_cellpost_workspace_bytes": (C.c_size_t, [c_int, c_int, c_int, c_int]),

@@ -308,7 +308,9 @@ def do_infer(*, wsi_dir, results_dir, model_obj, slide_paths, slides, batch_size
     click.secho("\nRunning model inference.\n", fg="green")
     failed_patching, failed_inference = run_inference(
         wsi_dir=wsi_dir, slide_paths=slide_paths, results_dir=results_dir, model_info=model_obj,
-        batch_size=batch_size, num_workers=num_workers, slides=slides)
+        batch_size=batch_size, num_workers=num_workers, slides=slides,
+        # the reference reads this switch from the model's config.json (cli/infer.py:845)
+        stain_normalization=bool(model_obj.config.extras.get("stain_normalization")))
     if failed_patching:
         click.secho(f"\nPatching failed for {len(failed_patching)} slides", fg="yellow")
         click.secho("\n".join(failed_patching), fg="yellow")

@@ -33,9 +33,53 @@ __global__ void k_rgb_to_rgba_stack(const uint8_t* __restrict__ rgb, int ps, lon
   reinterpret_cast<uint32_t*>(out + ((size_t)n * ps + y) * pitch)[x] = p;
 }
 
+// Macenko stain normalisation of cached patches (N4): HistomicsTK's deconvolution_based_normalization(patch + 1e-8,
+// W_source, W_target) per pixel (wsinsight/modellib/data.py:293-300).  With x = (float)(u8 + 1e-8f) + 1 (the library's
+// optical-density form: white = 256), sda = -log(x / 256) * 255 / log(256); stains = inv(Wc) . sda; the library then
+// maps the stains back to "RGB" (256^(1 - s/255) - 1), forward again (+1, log) and multiplies by W_target: the round
+// trip is the identity up to rounding, so M = W_target . inv(Wc) is applied once.  out = trunc(clip(256^(1 - v/255) - 1,
+// 0, 255)).  float64 throughout, as numpy computes it.
+struct StainM { double m[9]; };
+
+__global__ void __launch_bounds__(256)
+    k_stain_normalize(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, long long npix, StainM M) {
+  const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= npix) return;
+  const double k = 255.0 / log(256.0);
+  double sda[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const float f = (float)in[3 * p + c] + 1e-8f;          // patch_arr.astype(float32) + EPSILON
+    const double x = fmax((double)f + 1.0, 1e-10);
+    sda[c] = -log(x / 256.0) * k;
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const double v = M.m[3 * c] * sda[0] + M.m[3 * c + 1] * sda[1] + M.m[3 * c + 2] * sda[2];
+    double r = pow(256.0, 1.0 - v / 255.0) - 1.0;
+    r = fmin(fmax(r, 0.0), 255.0);
+    out[3 * p + c] = (uint8_t)r;                             // astype(np.uint8): truncation
+  }
+}
+
 }  // namespace
 
 extern "C" {
+
+int wsi_stain_normalize_rgb(const uint8_t* d_rgb_in, uint8_t* d_rgb_out, long long n_pixels, const double* h_M9,
+                            void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_rgb_in && d_rgb_out && h_M9 && n_pixels >= 0, "wsi_stain_normalize_rgb: bad arguments");
+  if (n_pixels == 0) return WSI_OK;
+  StainM M;
+  for (int i = 0; i < 9; ++i) M.m[i] = h_M9[i];
+  const long long nb = (n_pixels + 255) / 256;
+  WSI_ARG_CHECK(nb < (1ll << 31), "wsi_stain_normalize_rgb: too many pixels for one call");
+  k_stain_normalize<<<(unsigned)nb, 256, 0, stream>>>(d_rgb_in, d_rgb_out, n_pixels, M);
+  wsi_count_launch(1);
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
 
 int wsi_extract_patches_rgb(const uint8_t* d_slide_rgba, long long W, long long H, long long pitch_bytes,
                             const int32_t* d_coords_xy, int n, int patch_size, uint8_t* d_out_rgb, void* stream_) {

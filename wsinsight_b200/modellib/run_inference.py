@@ -100,6 +100,28 @@ def classify_patches_from_images(images, net, transform, batch_size: int, probs_
     return probs
 
 
+def classify_patches_stain_normalized(slide, coords_xywh: np.ndarray, net, transform, batch_size: int, W_est, W_def,
+                                      chunk: int = 4096):
+    """Classification with Macenko stain normalisation (reference ``data.py:293-300``): patches are gathered from the
+    slide, normalised per pixel on the device (``wsi_stain_normalize_rgb``) and classified from the patch stack, chunk
+    by chunk.  Returns a CUDA fp32 (N, K) tensor."""
+    from ..patchlib.io import extract_patches_from_slide
+    from .stain import normalize_patches_device
+
+    torch = _cabi.require_cuda()
+    n = len(coords_xywh)
+    probs = torch.empty((n, net.num_classes), dtype=torch.float32, device=net.device)
+    if n == 0:
+        return probs
+    ps = int(coords_xywh[0, 2])
+    for s in range(0, n, chunk):
+        e = min(n, s + chunk)
+        px = extract_patches_from_slide(slide, coords_xywh[s:e, :2], ps)
+        normalize_patches_device(px, W_est, W_def, out=px)
+        classify_patches_from_images(px, net, transform, batch_size, probs_out=probs[s:e])
+    return probs
+
+
 def gather_probs(probs_local, n_total: int, rank: int, world: int):
     """Gather per-rank (N_r, K) probability shards on rank 0 (NCCL on GPUs, gloo on CPU).
 
@@ -219,9 +241,8 @@ def run_inference(
     Returns ``(failed_patching, failed_inference)`` like the reference.
     """
     if references_dir or qupath_detection_dir or qupath_geojson_detection_dir or qupath_geojson_annotation_dir \
-            or object_based or object_detection or stain_normalization:
-        raise NotImplementedError("QuPath / reference-annotation / object-based / stain-normalisation branches "
-                                  "are outside the B200 hot path")
+            or object_based or object_detection:
+        raise NotImplementedError("QuPath / reference-annotation / object-based branches are outside the B200 hot path")
     from ..patchlib.io import load_patch_file
 
     results_dir = Path(results_dir)
@@ -270,7 +291,17 @@ def run_inference(
 
                 net = B200Network.from_torchscript(model_info.model_path, model_info.config.num_classes,
                                                    input_size=S, max_batch=batch_size, device=slide.rgba.device)
-            if world > 1:
+            if stain_normalization:
+                # run_inference.py:232-264: one stain matrix per slide from a 256-patch sample, eosin / hematoxylin target
+                from .stain import default_target_matrix, estimate_slide_stain_matrix
+
+                W_est = estimate_slide_stain_matrix(slide, coords, 256, seed=0)
+                lo, hi = shard_range(len(coords), rank, world)
+                local = classify_patches_stain_normalized(slide, coords[lo:hi], net, transform, batch_size, W_est,
+                                                          default_target_matrix())
+                full = gather_probs(local, len(coords), rank, world)
+                probs = full.cpu().numpy() if full is not None else None
+            elif world > 1:
                 probs = classify_coords_sharded(slide, coords, net, transform, batch_size, rank, world)
             else:
                 probs = classify_patches_device(slide, coords, net, transform, batch_size).cpu().numpy()
