@@ -436,38 +436,57 @@ def stage_cohort64(dev, peaks, cfg, n_slides=64, check=4):
             "slide_generation_plus_thumbnail_s": t_gen}
 
 
-def stage_inceptionv4(slide, dev, peaks, B, seconds):
-    """BASELINE config 3 at N = 1: pancancer-lymphocytes-inceptionv4.tcga, 100 um patches of the same slide, >= `seconds`."""
+def stage_inceptionv4(slide, dev, peaks, B, seconds, rank=0, world=1):
+    """BASELINE config 3: pancancer-lymphocytes-inceptionv4.tcga, 100 um patches of the same slide sharded over the ranks
+    (contiguous x-bands of the patch list), >= `seconds` of back-to-back steps per rank, MAX over ranks."""
     import torch
+    import torch.distributed as dist
 
     from wsinsight_b200.modellib.data import PreprocessPlan
     from wsinsight_b200.modellib.engine import B200Network
     from wsinsight_b200.modellib.transforms import make_compose_from_transform_config
     from wsinsight_b200.patchlib import segment_and_patch_slides_device
 
+    from wsinsight_b200.modellib.run_inference import shard_range
+
     spec = ModelSpec("inceptionv4")
     cfg = spec.cfg
-    res = segment_and_patch_slides_device([slide], cfg["patch_size_pixels"], cfg["spacing_um_px"])[0]
-    coords = res.coords
-    ps = res.patch_size
-    nb = int(coords.shape[0]) // B
-    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(spec.make())), 2, input_size=spec.S,
-                                       max_batch=B, device=dev)
-    transform = make_compose_from_transform_config(cfg["transform"])
-    lay = net.input_layout
-    plan = PreprocessPlan(slide, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"],
-                          lay["plane_stride_px"], lay["channels"])
-    xin = net.alloc_input(B)
-    probs = torch.empty((B, 2), dtype=torch.float32, device=dev)
+    setup_err = None
+    try:
+        # everything that can fail on ONE rank happens before the first collective of this stage
+        res = segment_and_patch_slides_device([slide], cfg["patch_size_pixels"], cfg["spacing_um_px"])[0]
+        n_all = int(res.coords.shape[0])
+        lo, hi = shard_range(n_all, rank, world)
+        coords = res.coords[lo:hi].contiguous()
+        ps = res.patch_size
+        nb = int(coords.shape[0]) // B
+        assert nb >= 1, "not enough patches for one batch"
+        net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(spec.make())), 2, input_size=spec.S,
+                                           max_batch=B, device=dev)
+        transform = make_compose_from_transform_config(cfg["transform"])
+        lay = net.input_layout
+        plan = PreprocessPlan(slide, ps, transform, lay["out_H"], lay["out_W"], lay["pad_top"], lay["pad_left"],
+                              lay["plane_stride_px"], lay["channels"])
+        xin = net.alloc_input(B)
+        probs = torch.empty((B, 2), dtype=torch.float32, device=dev)
 
-    def step(i):
-        b = i % nb
-        plan.run(coords[b * B:(b + 1) * B], xin)
-        net.forward_into(xin, probs)
+        def step(i):
+            b = i % nb
+            plan.run(coords[b * B:(b + 1) * B], xin)
+            net.forward_into(xin, probs)
 
-    for i in range(3):
-        step(i)
-    torch.cuda.synchronize()
+        for i in range(3):
+            step(i)
+        torch.cuda.synchronize()
+    except Exception as e:  # noqa: BLE001
+        setup_err = e
+    if world > 1:
+        bad = torch.tensor([1 if setup_err is not None else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(bad, op=dist.ReduceOp.MAX)
+        if int(bad.item()):
+            raise RuntimeError(f"InceptionV4 stage skipped on all ranks: setup failed on a rank ({setup_err})")
+    elif setup_err is not None:
+        raise setup_err
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(4):
@@ -476,13 +495,23 @@ def stage_inceptionv4(slide, dev, peaks, B, seconds):
     torch.cuda.synchronize()
     per = e0.elapsed_time(e1) / 4
     n = max(8, int(seconds * 1e3 / per) + 1)
+    if world > 1:                      # every rank times the same number of steps
+        nn = torch.tensor([n], dtype=torch.int64, device=dev)
+        dist.all_reduce(nn, op=dist.ReduceOp.MAX)
+        n = int(nn.item())
+        torch.cuda.synchronize()
+        dist.barrier()
     e0.record()
     for i in range(n):
         step(7 + i)
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
-    value = n * B / (ms * 1e-3)
+    if world > 1:
+        tm = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ms = float(tm.item())
+    value = world * n * B / (ms * 1e-3)
     # conv time and traffic figures from a separate short pass with per-op events
     net.set_profiling(8)
     for i in range(8):
@@ -492,18 +521,31 @@ def stage_inceptionv4(slide, dev, peaks, B, seconds):
     cs = conv_summary(ops, nfwd, B)
     # algorithmic HBM bytes per image of the conv launches: every conv reads its input once and writes its output once
     alg = float(_cabi_call_double("wsi_net_conv_bytes_per_image", net)) if hasattr(net, "_h") else None
-    out = {"metric": spec.metric, "value": value, "unit": UNIT, "steps": n, "seconds": ms * 1e-3, "batch": B,
-           "ms_per_step": ms / n, "patch_px": ps, "in_tissue_patches": int(coords.shape[0]),
+    out = {"metric": spec.metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": n, "seconds": ms * 1e-3, "batch": B,
+           "ms_per_step": ms / n, "patch_px": ps, "in_tissue_patches": n_all,
            "conv_tflops": cs["achieved"], "conv_frac_of_sustained": cs["achieved"] / peaks["tf_sustained"],
            "conv_share_of_step": cs["conv_ms"] / nfwd / (ms / n), "pool_head_ms_per_step": cs["other_ms"] / nfwd,
-           "tensor_pipe_frac_of_step": value * spec.gflop * 1e9 / (peaks["tf_sustained"] * 1e12),
+           "tensor_pipe_frac_of_step": value / world * spec.gflop * 1e9 / (peaks["tf_sustained"] * 1e12),
            "conv_launches": cs["n_conv"], "launches_per_step": net.num_launches + 1,
            "conv_algorithmic_bytes_per_launch_avg": alg * B / cs["n_conv"] if alg else None,
+           "conv_dram_bytes_per_launch_avg_ncu": ncu_traffic("inceptionv4"),
            "workload": workload_name(slide.width, slide.height, slide.mpp, B, spec)}
     plan.close()
     net.close()
     torch.cuda.empty_cache()
     return out
+
+
+def ncu_traffic(model):
+    """DRAM bytes per conv launch (read + write) from the committed ncu capture of this command, newest round first."""
+    for name in ("r02_ncu_conv_traffic.json", "r01_ncu_conv_traffic.json"):
+        try:
+            v = json.load(open(ROOT / "profiles" / name)).get(model, {}).get("dram_bytes_per_launch_avg")
+            if v:
+                return v
+        except Exception:  # noqa: BLE001
+            continue
+    return None
 
 
 def _cabi_call_double(name, net):
@@ -805,6 +847,15 @@ def b200_arm(args, rank, world, local_rank):
     strong = None
     if not args.quick:
         strong = stage_strong_scaling(slide, thumb, spec, net, transform, B, rank, world, dev)
+    iv4 = None
+    if not args.quick and args.model == "resnet34":
+        try:
+            iv4 = stage_inceptionv4(slide, dev, peaks, B, 3.0, rank, world)
+        except Exception as e:  # noqa: BLE001 - an auxiliary stage must not lose the headline line
+            import traceback
+
+            traceback.print_exc(file=sys.stderr)
+            iv4 = {"error": f"{type(e).__name__}: {e}"}
     sampler.stop()
     clocks = sampler.summary(c0, c1)
     clocks_b = sampler.summary(b0, b1)
@@ -821,14 +872,7 @@ def b200_arm(args, rank, world, local_rank):
                              f"{o['flops_per_image'] / 1e9:7.4f}  TFLOP/s {tf:8.1f}\n")
     # ---- roofline of the dominant kernels: the tcgen05 convolutions (tensor pipe) ----
     # DRAM bytes per conv launch from the committed `ncu --set full` capture of this same command
-    traffic = None
-    for name in ("r02_ncu_conv_traffic.json", "r01_ncu_conv_traffic.json"):
-        try:
-            tj = json.load(open(ROOT / "profiles" / name))
-            traffic = tj.get(args.model, {}).get("dram_bytes_per_launch_avg")
-            break
-        except Exception:
-            continue
+    traffic = ncu_traffic(args.model)
     step_ms_b = sum(o["ms_total"] for o in ops) / nfwd + pp_ms / K
     roofline = {"kernel": ("tcgen05 conv kernels: convs::k_conv_stem + convf::k_conv_flat + convk::k_conv_igemm "
                            f"({cs['n_conv']} launches per step)"),
@@ -863,6 +907,8 @@ def b200_arm(args, rank, world, local_rank):
     }
     if strong is not None:
         stages["slide_strong_scaling"] = strong
+    if iv4 is not None:
+        stages["inceptionv4"] = iv4
 
     line = {
         "metric": spec.metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
@@ -900,7 +946,6 @@ def b200_arm(args, rank, world, local_rank):
                     lb["b200_e2e_over_cudnn_fp32_default_e2e"] = e2e["value"] / lb["fp32_torch_default"]["e2e_patches_per_s"]
         stages["cohort64"] = guarded("cohort", lambda: stage_cohort64(dev, peaks, cfg))
         if args.model == "resnet34":
-            stages["inceptionv4"] = guarded("iv4", lambda: stage_inceptionv4(slide, dev, peaks, B, 3.0))
 
             def parity():
                 sys.path.insert(0, str(ROOT / "tests"))

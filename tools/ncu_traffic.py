@@ -1,4 +1,5 @@
-"""Summarise an `ncu --set full` capture of the conv kernels into profiles/r01_ncu_conv_traffic.json.
+"""Summarise an `ncu --set full` capture of the conv kernels into profiles/<ROUND>_ncu_conv_traffic.json (ROUND from the
+environment variable WSI_ROUND, default r02).
 
 usage: python tools/ncu_traffic.py <model> <report.ncu-rep> [<csv out>]
 Reads dram__bytes_read.sum + dram__bytes_write.sum and gpu__time_duration.sum per launch (ncu --page raw --csv)
@@ -60,7 +61,7 @@ def main():
         d["time_s"] += t
         tot_b += b
         tot_t += t
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "profiles", "r01_ncu_conv_traffic.json")
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "profiles", os.environ.get("WSI_ROUND", "r02") + "_ncu_conv_traffic.json")
     try:
         j = json.load(open(path))
     except Exception:
