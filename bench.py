@@ -878,6 +878,7 @@ def b200_arm(args, rank, world, local_rank):
                            f"({cs['n_conv']} launches per step)"),
                 "bound": "tensor", "achieved": cs["achieved"], "peak": peaks["tf_burst"], "unit": "TFLOP/s",
                 "frac": cs["achieved"] / peaks["tf_burst"], "traffic": traffic,
+                "algorithmic_bytes_per_launch_avg": float(_cabi_call_double("wsi_net_conv_bytes_per_image", net)) * B / cs["n_conv"],
                 "peak_source": (f"{peaks['source']} bf16 BURST (best of 10 cuBLAS 8192^3): this window is "
                                 f"{K} steps = {ms_max * 1e-3:.2f} s, shorter than the power-capped regime"),
                 "frac_of_sustained_peak": cs["achieved"] / peaks["tf_sustained"],
