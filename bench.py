@@ -565,24 +565,42 @@ def stage_strong_scaling(slide, thumb, spec, net, transform, B, rank, world, dev
     from wsinsight_b200.modellib.run_inference import classify_slide_sharded
 
     cfg = spec.cfg
-    runs = []
     n_total = 0
-    for it in range(2):
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
-        coords_np, probs_np = classify_slide_sharded(slide, cfg["patch_size_pixels"], cfg["spacing_um_px"], net, transform,
-                                                     B, rank=rank, world=world, thumb=thumb)
-        torch.cuda.synchronize()
-        dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        runs.append(float(dt.item()))
-        if rank == 0:
-            n_total = len(coords_np)
-            assert probs_np.shape == (n_total, net.num_classes)
-    return {"ms_per_slide": min(runs), "ms_runs": runs, "patches": n_total, "ranks": world,
+    keep = {}
+
+    def timed(result_path, reps):
+        nonlocal n_total
+        runs = []
+        for it in range(reps):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            coords_np, probs_np = classify_slide_sharded(slide, cfg["patch_size_pixels"], cfg["spacing_um_px"], net,
+                                                         transform, B, rank=rank, world=world, thumb=thumb,
+                                                         result_path=result_path)
+            torch.cuda.synchronize()
+            dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            runs.append(float(dt.item()))
+            if rank == 0:
+                n_total = len(coords_np)
+                assert probs_np.shape == (n_total, net.num_classes)
+                keep[result_path] = probs_np
+        return runs
+
+    runs = timed("nccl", 2)
+    peer = None
+    if world > 1 and os.environ.get("WSI_B200_NO_PEER_STAGE") != "1":
+        # the same slide with the tail kernel storing into a rank-0 buffer mapped through CUDA IPC (no collective)
+        try:
+            pr = timed("peer", 2)
+            peer = {"ms_per_slide": min(pr), "ms_runs": pr,
+                    "identical_to_nccl_gather": bool(rank != 0 or (keep["peer"] == keep["nccl"]).all())}
+        except Exception as e:  # noqa: BLE001
+            peer = {"error": f"{type(e).__name__}: {e}"}
+    return {"ms_per_slide": min(runs), "ms_runs": runs, "patches": n_total, "ranks": world, "peer_store_result_path": peer,
             "patches_per_s": n_total / (min(runs) * 1e-3) if n_total else None,
             "includes": "seg + patchify (every rank), fused preprocess + forward of the rank's x-band, "
                         + ("NCCL gather of (N_r, K) shards to rank 0, " if world > 1 else "") + "(N, K) host array",

@@ -42,6 +42,16 @@ long long wsi_launch_count(void);
 /* device-to-device copy on `stream` (debug access to activations owned by the library) */
 int wsi_memcpy_d2d(void* d_dst, const void* d_src, size_t bytes, void* stream);
 
+/* Peer-visible result buffer: the multi-GPU result path without a gather collective.  The reference gathers per-GPU
+ * outputs inside nn.DataParallel (wsinsight/modellib/run_inference.py:173-174).  Here rank 0 creates the (N, K) fp32
+ * probability array, the other ranks of the node open it through CUDA IPC (handle64: 64 opaque bytes, sent by any
+ * side channel) and pass `mapped + row offset` as the output pointer of wsi_net_forward: the tail kernel stores its
+ * probabilities straight into rank 0's memory over NVLink. */
+int wsi_peer_buffer_create(size_t bytes, void** d_ptr, unsigned char* handle64);
+int wsi_peer_buffer_open(const unsigned char* handle64, void** d_ptr);
+int wsi_peer_buffer_close(void* d_ptr);
+int wsi_peer_buffer_free(void* d_ptr);
+
 /* ---- K1: tissue segmentation --------------------------------------------------------- */
 /* Replaces segment_tissue(), wsinsight/patchlib/segment.py:13-97:
  *   cv.cvtColor(RGB2HSV)[...,1] (:54,65) -> cv.medianBlur(k) (:77) -> cv.threshold (:80-83)

@@ -178,3 +178,10 @@ def test_cli_two_ranks_same_csv_as_one(tmp_path):
     a = (tmp_path / "one" / "model-outputs-csv" / "a.csv").read_bytes()
     b = (tmp_path / "two" / "model-outputs-csv" / "a.csv").read_bytes()
     assert len(a) > 1000 and a == b
+    # the same with the peer-store result path: the tail kernel writes into rank 0's buffer over NVLink, no gather
+    peer = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                           "--master-addr", "127.0.0.1", "--master-port", "29534", "-m", "wsinsight_b200", "run",
+                           "-o", str(tmp_path / "peer")] + common, env=dict(env, WSI_B200_RESULT_PATH="peer"),
+                          capture_output=True, text=True, cwd=ROOT)
+    assert peer.returncode == 0, peer.stdout + peer.stderr
+    assert (tmp_path / "peer" / "model-outputs-csv" / "a.csv").read_bytes() == a

@@ -75,3 +75,42 @@ def test_product_path_vs_fp32_oracle_on_spread_nets(arch, K, n, oracle_mode, bat
         assert st["median_abs_dp"] <= 1.25 * lib["median_abs_dp"], (path, st, lib)
     # 6. the floor: bf16 conv weights alone (fp32 activations and accumulation) already exceed north_star's 2e-3
     assert wq["max_abs_dp"] > 2e-3, wq
+
+
+def test_config1_end_to_end_vs_oracle():
+    """BASELINE configs[0]: breast-tumor-resnet34.tcga-brca on a synthetic 8192 x 8192 slide at 0.25 um/px (350-px patches),
+    batch 32 -- the reference's own CPU-runnable case.  Whole product path vs the oracle: identical tissue mask and patch
+    coordinates, probabilities within the measured bf16 bounds of the calibrated net."""
+    import numpy as np
+
+    from oracle import forward as oforward
+    from oracle import patchgrid, preprocess, segment
+    from wsinsight_b200.modellib.engine import B200Network
+    from wsinsight_b200.modellib.run_inference import classify_patches_device
+    from wsinsight_b200.modellib.transforms import make_compose_from_transform_config
+    from wsinsight_b200.patchlib import segment_and_patch_slides_device
+    from wsinsight_b200.wsi import DeviceSlide
+
+    cfg = oforward.BREAST_RESNET34_CONFIG
+    slide = DeviceSlide.synthetic(8192, 8192, mpp=0.25, seed=0)
+    res = segment_and_patch_slides_device([slide], cfg["patch_size_pixels"], cfg["spacing_um_px"])[0]
+    assert res.patch_size == 350 and res.half_patch_size == 175
+    thumb = slide.thumbnail_device((2048, 2048)).cpu().numpy()
+    want_mask = segment.segment_tissue(thumb, 7, 7, 6, res.min_object_size_px, res.min_hole_size_px)
+    assert np.array_equal(res.mask.cpu().numpy().astype(bool), want_mask)
+    want_xy = patchgrid.patch_coordinates(want_mask, 8192, 8192, 350, 175)
+    coords = res.coords.cpu().numpy().astype(np.int64)
+    assert np.array_equal(coords, np.asarray(want_xy).astype(np.int64)) and len(coords) > 100
+    xywh = np.concatenate([coords, np.full_like(coords, 350)], 1)
+    model = oforward.make_resnet34_calibrated(2, 0)
+    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(model)), 2, input_size=224, max_batch=32)
+    tf = make_compose_from_transform_config(cfg["transform"])
+    got = classify_patches_device(slide, xywh, net, tf, batch_size=32).cpu()
+    host = slide.rgba[:, :slide.width].cpu().numpy()
+    a = cfg["transform"][2]["arguments"]
+    x = preprocess.preprocess_batch_lib(host, xywh, 224, a["mean"], a["std"])
+    want = oforward.forward_probs(model, x)
+    d = (got - want).abs().max(1).values
+    _save({"patches": int(len(coords)), "max_abs_dp": float(d.max()), "median_abs_dp": float(d.median()),
+           "argmax_agreement": float((got.argmax(1) == want.argmax(1)).float().mean())}, "config1_8192")
+    assert float(d.max()) <= 8e-2 and float(d.median()) <= 1.5e-2, (float(d.max()), float(d.median()))

@@ -33,6 +33,10 @@ _PROTOS = {
     "wsi_version": (C.c_char_p, []),
     "wsi_launch_count": (c_ll, []),
     "wsi_memcpy_d2d": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+    "wsi_peer_buffer_create": (c_int, [c_size_t, C.POINTER(c_void_p), C.POINTER(C.c_ubyte)]),
+    "wsi_peer_buffer_open": (c_int, [C.POINTER(C.c_ubyte), C.POINTER(c_void_p)]),
+    "wsi_peer_buffer_close": (c_int, [c_void_p]),
+    "wsi_peer_buffer_free": (c_int, [c_void_p]),
     "wsi_seg_workspace_bytes": (c_size_t, [c_int, c_int]),
     "wsi_seg_tissue_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

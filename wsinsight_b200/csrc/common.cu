@@ -76,4 +76,42 @@ int wsi_memcpy_d2d(void* d_dst, const void* d_src, size_t bytes, void* stream) {
 
 long long wsi_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
+// ---- peer-visible result buffer (multi-GPU result path without a gather collective) ----
+// Rank 0 owns the (N, K) probability array; the other ranks map it through CUDA IPC and their tail kernel (GAP + FC +
+// softmax) stores its rows straight into it over NVLink -- the "compute step followed by a collective" of this path
+// becomes the compute step alone.
+int wsi_peer_buffer_create(size_t bytes, void** d_ptr, unsigned char* handle64) {
+  WSI_ARG_CHECK(d_ptr && handle64 && bytes > 0, "wsi_peer_buffer_create: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  WSI_CUDA_CHECK(cudaMalloc(d_ptr, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, *d_ptr);
+  if (e != cudaSuccess) {
+    cudaFree(*d_ptr);
+    *d_ptr = nullptr;
+    wsi_set_error("wsi_peer_buffer_create: cudaIpcGetMemHandle -> %s", cudaGetErrorString(e));
+    return WSI_ERR_CUDA;
+  }
+  memcpy(handle64, &h, 64);
+  return WSI_OK;
+}
+
+int wsi_peer_buffer_open(const unsigned char* handle64, void** d_ptr) {
+  WSI_ARG_CHECK(d_ptr && handle64, "wsi_peer_buffer_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  WSI_CUDA_CHECK(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return WSI_OK;
+}
+
+int wsi_peer_buffer_close(void* d_ptr) {
+  WSI_CUDA_CHECK(cudaIpcCloseMemHandle(d_ptr));
+  return WSI_OK;
+}
+
+int wsi_peer_buffer_free(void* d_ptr) {
+  WSI_CUDA_CHECK(cudaFree(d_ptr));
+  return WSI_OK;
+}
+
 }  // extern "C"

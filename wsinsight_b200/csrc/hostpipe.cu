@@ -14,12 +14,15 @@
 
 namespace {
 
+constexpr int HP_CHUNKS = 4;    // a batch is copied and preprocessed in this many pieces (pipeline fill = one piece)
+
 struct Slot {
   uint8_t* d_stage = nullptr;          // [max_batch * ps rows][pitch] RGBA u8
   __nv_bfloat16* d_input = nullptr;    // network input layout, borders zeroed once
   float* d_probs = nullptr;            // [max_batch][K]
   void* plan = nullptr;                // preprocess plan over d_stage seen as a (ps x max_batch*ps) image
   cudaEvent_t copied = nullptr;        // H2D finished
+  cudaEvent_t chunk_ev[HP_CHUNKS] = {nullptr, nullptr, nullptr, nullptr};   // H2D of piece c finished
   cudaEvent_t staged_free = nullptr;   // preprocess finished reading d_stage
   cudaEvent_t done = nullptr;          // D2H of the probabilities finished
   bool used = false;
@@ -30,6 +33,7 @@ struct HostPipe {
   int ps = 0, S = 0, K = 0, max_batch = 0, depth = 0;
   long long pitch = 0;
   int in_H = 0, in_W = 0;
+  long long patch_elems = 0;           // bf16 elements one patch occupies in the network input buffer (per plane)
   int32_t* d_coords = nullptr;         // (0, i*ps) for i < max_batch
   cudaStream_t s_copy = nullptr, s_comp = nullptr;
   std::vector<Slot> slots;
@@ -45,6 +49,8 @@ void destroy(HostPipe* p) {
     if (s.d_input) cudaFree(s.d_input);
     if (s.d_probs) cudaFree(s.d_probs);
     if (s.copied) cudaEventDestroy(s.copied);
+    for (auto e : s.chunk_ev)
+      if (e) cudaEventDestroy(e);
     if (s.staged_free) cudaEventDestroy(s.staged_free);
     if (s.done) cudaEventDestroy(s.done);
   }
@@ -109,6 +115,7 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
     return rc;
   }
   const long long plane_stride_px = lay[0] == 1 ? (((long long)lay[3] << 32) | (unsigned int)lay[2]) : 0;
+  p->patch_elems = plane_stride_px ? (long long)(hwc[0] / 2) * hwc[1] * 4 : (long long)hwc[0] * hwc[1] * hwc[2];
   for (auto& s : p->slots) {
     if (cudaMalloc(&s.d_stage, stage_bytes) != cudaSuccess || cudaMalloc(&s.d_input, input_bytes) != cudaSuccess ||
         cudaMalloc(&s.d_probs, (size_t)max_batch * p->K * sizeof(float)) != cudaSuccess)
@@ -118,6 +125,9 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
         cudaEventCreateWithFlags(&s.staged_free, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming) != cudaSuccess)
       return fail("event creation failed", WSI_ERR_CUDA);
+    for (auto& e : s.chunk_ev)
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess)
+        return fail("event creation failed", WSI_ERR_CUDA);
     rc = wsi_preproc_plan_create(s.d_stage, patch_size, (long long)max_batch * patch_size, patch_pitch_bytes,
                                  patch_size, out_size, mean, stdv, hwc[0], hwc[1], pad, pad, &s.plan);
     if (!rc) rc = wsi_preproc_plan_set_parity_layout(s.plan, plane_stride_px);
@@ -144,11 +154,23 @@ int wsi_hostpipe_submit(void* pipe, const uint8_t* h_rgba, int n, float* h_probs
     // the probabilities of that earlier batch must have left d_probs before it is rewritten
     WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_copy, s.staged_free, 0));
   }
-  WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_stage, h_rgba, in_bytes, cudaMemcpyHostToDevice, p->s_copy));
+  // The batch goes over in HP_CHUNKS pieces, each preprocessed as soon as it has landed: the copy of piece c + 1 overlaps
+  // the preprocessing of piece c, and what a cold pipeline exposes is one piece, not one batch (at N = 8 the first
+  // 126-MB copies of all ranks contend for the host's memory and PCIe root and were 5 % of a 20-step window).
+  const int C = n >= 64 * HP_CHUNKS ? HP_CHUNKS : 1;
+  const int per = (n + C - 1) / C;
+  const size_t patch_bytes = (size_t)p->ps * (size_t)p->pitch;
+  int rc = WSI_OK;
+  for (int c = 0, j0 = 0; j0 < n; ++c, j0 += per) {
+    const int m = n - j0 < per ? n - j0 : per;
+    WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_stage + (size_t)j0 * patch_bytes, h_rgba + (size_t)j0 * patch_bytes,
+                                   (size_t)m * patch_bytes, cudaMemcpyHostToDevice, p->s_copy));
+    WSI_CUDA_CHECK(cudaEventRecord(s.chunk_ev[c], p->s_copy));
+    WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_comp, s.chunk_ev[c], 0));
+    rc = wsi_preproc_run(s.plan, p->d_coords + 2 * (size_t)j0, m, s.d_input + (size_t)j0 * p->patch_elems, p->s_comp);
+    if (rc) return rc;
+  }
   WSI_CUDA_CHECK(cudaEventRecord(s.copied, p->s_copy));
-  WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_comp, s.copied, 0));
-  int rc = wsi_preproc_run(s.plan, p->d_coords, n, s.d_input, p->s_comp);
-  if (rc) return rc;
   WSI_CUDA_CHECK(cudaEventRecord(s.staged_free, p->s_comp));
   rc = wsi_net_forward(p->net, s.d_input, n, s.d_probs, p->s_comp);
   if (rc) return rc;

@@ -154,23 +154,117 @@ def dist_rank_world():
     return 0, 1
 
 
-def classify_coords_sharded(slide, coords_xywh: np.ndarray, net, transform, batch_size: int, rank=None, world=None):
+class PeerResultBuffer:
+    """The (N, K) fp32 probability array of one slide, owned by rank 0 and mapped into every rank of the node through
+    CUDA IPC (``wsi_peer_buffer_*``): each rank's tail kernel (GAP + FC + softmax) stores its rows straight into rank 0's
+    memory over NVLink, so the result path needs no gather collective -- only a barrier before rank 0 reads."""
+
+    def __init__(self, n: int, K: int, rank: int, world: int, device):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        torch = _cabi.require_cuda()
+        self.rank, self.world, self.n, self.K = rank, world, int(n), int(K)
+        self._ptr = C.c_void_p()
+        self.tensor = None
+        handle = (C.c_ubyte * 64)()
+        nbytes = max(1, self.n * self.K) * 4
+        err = None
+        with torch.cuda.device(device):
+            # every step that can fail on ONE rank is followed by a collective vote, so that either all ranks use the
+            # buffer or all ranks raise (a one-sided failure would leave the others waiting in a barrier)
+            if rank == 0:
+                try:
+                    _cabi.call("wsi_peer_buffer_create", nbytes, C.byref(self._ptr), handle)
+                except Exception as e:  # noqa: BLE001
+                    err = e
+            box = [bytes(handle)]
+            dist.broadcast_object_list(box, src=0)
+            if rank != 0 and err is None:
+                try:
+                    h = (C.c_ubyte * 64).from_buffer_copy(box[0])
+                    _cabi.call("wsi_peer_buffer_open", h, C.byref(self._ptr))
+                except Exception as e:  # noqa: BLE001
+                    err = e
+            if err is None:
+                try:
+                    class _Raw:      # zero-copy tensor view of the mapped memory
+                        pass
+
+                    raw = _Raw()
+                    raw.__cuda_array_interface__ = {"shape": (self.n, self.K), "typestr": "<f4",
+                                                    "data": (int(self._ptr.value), False), "version": 2}
+                    self.tensor = torch.as_tensor(raw)       # the device is read off the pointer; must be zero-copy
+                    if self.n and int(self.tensor.data_ptr()) != int(self._ptr.value):
+                        raise RuntimeError("the tensor view of the mapped buffer is not zero-copy")
+                except Exception as e:  # noqa: BLE001
+                    err = e
+            bad = torch.tensor([0 if err is None else 1], dtype=torch.int32, device=torch.device(device))
+            dist.all_reduce(bad, op=dist.ReduceOp.MAX)
+            if int(bad.item()):
+                self.tensor = None
+                if self._ptr.value:
+                    try:
+                        _cabi.call("wsi_peer_buffer_close" if rank != 0 else "wsi_peer_buffer_free", self._ptr)
+                    except Exception:  # noqa: BLE001
+                        pass
+                raise RuntimeError(f"peer result buffer unavailable on this node (rank {rank}: {err})")
+
+    def rows(self, lo: int, hi: int):
+        return self.tensor[lo:hi]
+
+    def collect(self):
+        """Barrier, then the (N, K) NumPy array on rank 0 (None elsewhere); releases the mapping / the buffer."""
+        import torch.distributed as dist
+
+        torch = _cabi.require_cuda()
+        torch.cuda.synchronize()
+        dist.barrier()                     # every rank's stores have landed
+        out = self.tensor.cpu().numpy().copy() if self.rank == 0 else None
+        self.tensor = None
+        if self.rank != 0:
+            _cabi.call("wsi_peer_buffer_close", self._ptr)
+        dist.barrier()                     # all mappings closed before the owner frees
+        if self.rank == 0:
+            _cabi.call("wsi_peer_buffer_free", self._ptr)
+        return out
+
+
+def _result_path(result_path=None) -> str:
+    import os
+
+    rp = (result_path or os.environ.get("WSI_B200_RESULT_PATH") or "nccl").lower()
+    if rp not in ("nccl", "peer"):
+        raise ValueError(f"result path must be 'nccl' or 'peer', got {rp!r}")
+    return rp
+
+
+def classify_coords_sharded(slide, coords_xywh: np.ndarray, net, transform, batch_size: int, rank=None, world=None,
+                            result_path=None):
     """ONE slide on all ranks of a ``torch.distributed`` job (replaces ``nn.DataParallel``, reference
     run_inference.py:173-174): rank r classifies ``shard_range(N, r, R)`` of the x-major patch list -- an x-band of
     the slide, no data-path collective -- and the ``(N_r, K)`` shards are gathered on rank 0 with one collective.
+
+    ``result_path="peer"`` (or ``WSI_B200_RESULT_PATH=peer``): no collective at all -- the probabilities are stored into
+    a rank-0 buffer mapped into every rank (:class:`PeerResultBuffer`); default ``"nccl"``.
 
     Returns the (N, K) float32 NumPy array on rank 0, ``None`` on the other ranks."""
     if rank is None or world is None:
         rank, world = dist_rank_world()
     n = len(coords_xywh)
     lo, hi = shard_range(n, rank, world)
+    if world > 1 and _result_path(result_path) == "peer":
+        buf = PeerResultBuffer(n, net.num_classes, rank, world, net.device)
+        classify_patches_device(slide, coords_xywh[lo:hi], net, transform, batch_size, probs_out=buf.rows(lo, hi))
+        return buf.collect()
     local = classify_patches_device(slide, coords_xywh[lo:hi], net, transform, batch_size)
     full = gather_probs(local, n, rank, world)
     return full.cpu().numpy() if full is not None else None
 
 
 def classify_slide_sharded(slide, patch_size_px: int, patch_spacing_um_px: float, net, transform, batch_size: int,
-                           rank=None, world=None, thumb=None, **seg_kwargs):
+                           rank=None, world=None, thumb=None, result_path=None, **seg_kwargs):
     """Whole-slide form: tissue segmentation + patchify run redundantly on every rank (about a millisecond; the
     coordinates then need no broadcast), then :func:`classify_coords_sharded`.
 
@@ -187,8 +281,13 @@ def classify_slide_sharded(slide, patch_size_px: int, patch_spacing_um_px: float
     lo, hi = shard_range(n, rank, world)
     cxy = res.coords.cpu().numpy().astype(np.int64)
     xywh = np.concatenate([cxy, np.full_like(cxy, res.patch_size)], 1)
-    local = classify_patches_device(slide, xywh[lo:hi], net, transform, batch_size,
-                                    device_coords=res.coords[lo:hi].contiguous())
+    dc = res.coords[lo:hi].contiguous()
+    if world > 1 and _result_path(result_path) == "peer":
+        buf = PeerResultBuffer(n, net.num_classes, rank, world, net.device)
+        classify_patches_device(slide, xywh[lo:hi], net, transform, batch_size, device_coords=dc,
+                                probs_out=buf.rows(lo, hi))
+        return xywh, buf.collect()
+    local = classify_patches_device(slide, xywh[lo:hi], net, transform, batch_size, device_coords=dc)
     full = gather_probs(local, n, rank, world)
     return xywh, (full.cpu().numpy() if full is not None else None)
 

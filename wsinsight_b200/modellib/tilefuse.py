@@ -46,6 +46,7 @@ class TileRemapStitcher:
         self.tiles_y = (self.slide_height + self.canvas_tile - 1) // self.canvas_tile
         # (ty, tx) -> (np (T, T), hv (T, T, 2), tp (T, T, K)) fp32 CUDA tensors, allocated on first touch
         self._tiles: Dict[Tuple[int, int], tuple] = {}
+        self._staging = None
 
     # -- canvases ---------------------------------------------------------------------------------------------
     def _tile_dims(self, ty: int, tx: int):
@@ -154,7 +155,9 @@ class TileRemapStitcher:
                                    f[2][lo:hi].data_ptr(), coords.data_ptr(), 2, hi - lo, self.n_classes, int(h), S,
                                    self.slide_halo_size, float(self.alpha), tw, th, npt.data_ptr(), hvt.data_ptr(),
                                    tpt.data_ptr(), _cabi.stream_ptr())
-        torch.cuda.current_stream().synchronize()      # the fp32 / int32 staging copies are released on return
+        # the fp32 staging copies and coordinate tensors must outlive the kernels that read them: they are kept until the
+        # next call (stream order then guarantees they are no longer in use) instead of synchronising after every batch
+        self._staging = (f, torch.cuda.current_stream())
 
     # -- finalize (tilefuse.py:280-415) ---------------------------------------------------------------------------
     @staticmethod
