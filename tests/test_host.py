@@ -231,3 +231,15 @@ def test_gather_world_size_2_gloo(tmp_path):
                               stderr=subprocess.STDOUT, text=True) for r in range(2)]
     outs = [p.communicate(timeout=180)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
+
+
+def test_result_path_selection(monkeypatch):
+    """Multi-GPU result path: NCCL gather by default, peer stores on request, anything else is rejected."""
+    from wsinsight_b200.modellib.run_inference import _result_path
+
+    monkeypatch.delenv("WSI_B200_RESULT_PATH", raising=False)
+    assert _result_path() == "nccl" and _result_path("peer") == "peer" and _result_path("NCCL") == "nccl"
+    monkeypatch.setenv("WSI_B200_RESULT_PATH", "peer")
+    assert _result_path() == "peer" and _result_path("nccl") == "nccl"
+    with pytest.raises(ValueError):
+        _result_path("smoke-signals")

@@ -10,6 +10,7 @@
 // overlaps the kernels of batch i.  Nothing here computes on the CPU.
 #include "common.cuh"
 #include "../../include/wsi_b200.h"
+#include <stdlib.h>
 #include <vector>
 
 namespace {
@@ -33,6 +34,7 @@ struct HostPipe {
   int ps = 0, S = 0, K = 0, max_batch = 0, depth = 0;
   long long pitch = 0;
   int in_H = 0, in_W = 0;
+  bool skip_h2d = false;
   long long patch_elems = 0;           // bf16 elements one patch occupies in the network input buffer (per plane)
   int32_t* d_coords = nullptr;         // (0, i*ps) for i < max_batch
   cudaStream_t s_copy = nullptr, s_comp = nullptr;
@@ -84,6 +86,10 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
   p->max_batch = max_batch;
   p->depth = depth;
   p->pitch = patch_pitch_bytes;
+  {
+    const char* e = getenv("WSI_B200_HP_NO_H2D");
+    p->skip_h2d = e && e[0] == '1';
+  }
   p->in_H = hwc[0];
   p->in_W = hwc[1];
   // symmetric stem padding (ResNet: 3); an odd difference is the one unused row/column that rounds an odd
@@ -163,8 +169,9 @@ int wsi_hostpipe_submit(void* pipe, const uint8_t* h_rgba, int n, float* h_probs
   int rc = WSI_OK;
   for (int c = 0, j0 = 0; j0 < n; ++c, j0 += per) {
     const int m = n - j0 < per ? n - j0 : per;
-    WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_stage + (size_t)j0 * patch_bytes, h_rgba + (size_t)j0 * patch_bytes,
-                                   (size_t)m * patch_bytes, cudaMemcpyHostToDevice, p->s_copy));
+    if (!p->skip_h2d)     // WSI_B200_HP_NO_H2D=1: timing experiment only (stale pixels), never set in production
+      WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_stage + (size_t)j0 * patch_bytes, h_rgba + (size_t)j0 * patch_bytes,
+                                     (size_t)m * patch_bytes, cudaMemcpyHostToDevice, p->s_copy));
     WSI_CUDA_CHECK(cudaEventRecord(s.chunk_ev[c], p->s_copy));
     WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_comp, s.chunk_ev[c], 0));
     rc = wsi_preproc_run(s.plan, p->d_coords + 2 * (size_t)j0, m, s.d_input + (size_t)j0 * p->patch_elems, p->s_comp);
