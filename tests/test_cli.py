@@ -185,3 +185,49 @@ def test_cli_two_ranks_same_csv_as_one(tmp_path):
                           capture_output=True, text=True, cwd=ROOT)
     assert peer.returncode == 0, peer.stdout + peer.stderr
     assert (tmp_path / "peer" / "model-outputs-csv" / "a.csv").read_bytes() == a
+
+
+@pytest.mark.gpu
+def test_cli_purple_slide_matches_reference_golden_csv(tmp_path, golden_purple):
+    """Mirror of the reference's integration test (tests/test_all.py:413-478 `test_cli_run_with_local_model`, :559-612
+    `test_patch_cli`): `run` on the uniform purple 4096 x 4096 slide at 0.25 um/px.  The slide is a flat PNG read through
+    PIL (decoders are out of scope); the coordinate columns must equal the reference's golden purple.csv row for row
+    (the probability columns need the real zoo weights and stay unpinned), and the 'patch' expectations of the
+    reference's grid formula hold for its five (patch size, spacing) pairs."""
+    import pandas as pd
+    from PIL import Image
+
+    from oracle import forward as oforward
+    from wsinsight_b200.cli import cli
+    from wsinsight_b200.patchlib.io import load_patch_file
+
+    wsi = tmp_path / "slides"
+    wsi.mkdir()
+    g = golden_purple["breast-tumor-resnet34.tcga-brca"]
+    Image.new("RGB", (4096, 4096), tuple(g["rgb"])).save(wsi / "purple.png")
+    _, cfg, pt = _bundle(tmp_path)
+    out = tmp_path / "inference"
+    res = CliRunner().invoke(cli, ["run", "--wsi-dir", str(wsi), "--results-dir", str(out), "--model-path", str(pt),
+                                   "--config", str(cfg), "--slide-mpp", "0.25"], catch_exceptions=False)
+    assert res.exit_code == 0, res.output
+    df = pd.read_csv(out / "model-outputs-csv" / "purple.csv")
+    assert list(df.columns) == g["columns"]
+    assert df[["minx", "miny"]].to_numpy().tolist() == g["coords"]
+    assert (df["width"] == g["patch_size"]).all() and (df["height"] == g["patch_size"]).all()
+    assert (out / "masks" / "purple.jpg").exists()
+    # 'patch' alone for the reference's five (patch_size, spacing) pairs: its expected grid (test_all.py:590-603)
+    for k, (psz, spacing) in enumerate([(256, 0.25), (256, 0.50), (350, 0.25), (100, 0.3), (100, 0.5)]):
+        c = dict(oforward.BREAST_RESNET34_CONFIG, patch_size_pixels=psz, spacing_um_px=spacing)
+        cp = tmp_path / f"cfg{k}.json"
+        cp.write_text(json.dumps(c))
+        sd = tmp_path / f"savedir{k}"
+        r = CliRunner().invoke(cli, ["patch", "--wsi-dir", str(wsi), "--results-dir", str(sd), "--model-path", str(pt),
+                                     "--config", str(cp), "--slide-mpp", "0.25"], catch_exceptions=False)
+        assert r.exit_code == 0, r.output
+        eps = round(psz * spacing / 0.25)
+        want = [[x, y] for x in range(0, 4096, eps) for y in range(0, 4096, eps)
+                if x + eps // 2 <= 4096 and y + eps // 2 <= 4096]
+        assert len(want) == round(4096 / eps) ** 2
+        d = load_patch_file(sd / "patches" / "purple.h5")
+        assert int(d["patch_size"]) == eps
+        assert np.asarray(d["coords"]).tolist() == want, (psz, spacing)
