@@ -728,18 +728,22 @@ def b200_arm(args, rank, world, local_rank):
     # (timed right after pass A, before the long sustained pass drives the GPU into its power cap: value and e2e see
     # the same thermal state)
     e2e = None
-    if not args.no_e2e:
+    e2e_rgba = None
+
+    def run_e2e(host_channels):
+        """K steps through wsi_hostpipe_* from pinned host patches (3: dense RGB as read_region().convert("RGB") yields,
+        4: padded RGBA rows), probabilities back on the host, per-rank results gathered on rank 0 inside the region."""
         depth = 3
-        hp = HostPatchClassifier(net, ps, transform, B, depth=depth)
+        hp = HostPatchClassifier(net, ps, transform, B, depth=depth, host_channels=host_channels)
         nbuf = min(4, nb_local)
         host = []
         for j in range(nbuf):
-            rgba, hprobs = hp.alloc_host_batch(B)
+            px, hprobs = hp.alloc_host_batch(B)
             cj = coords[j * B:(j + 1) * B].cpu().numpy()
             for i, (x, y) in enumerate(cj):
                 x1, y1 = min(x + ps, W), min(y + ps, H)
-                rgba[i, : y1 - y, : x1 - x].copy_(slide.rgba[y:y1, x:x1])
-            host.append((rgba, hprobs))
+                px[i, : y1 - y, : x1 - x].copy_(slide.rgba[y:y1, x:x1, :host_channels])
+            host.append((px, hprobs))
         torch.cuda.synchronize()
 
         def gather_results():
@@ -747,13 +751,9 @@ def b200_arm(args, rank, world, local_rank):
             if world == 1:
                 return None
             shard = torch.cat([h[1] for h in host], 0).to(dev, non_blocking=True)
-            g = gather_probs_equal(shard, rank, world)
-            return g.cpu() if g is not None else None
-
-        def gather_probs_equal(shard, r, R):
-            bufs = [torch.empty_like(shard) for _ in range(R)] if r == 0 else None
+            bufs = [torch.empty_like(shard) for _ in range(world)] if rank == 0 else None
             dist.gather(shard, bufs, dst=0)
-            return torch.cat(bufs, 0) if r == 0 else None
+            return torch.cat(bufs, 0).cpu() if rank == 0 else None
 
         for i in range(max(Wm, 3)):
             hp.submit(*host[i % nbuf])
@@ -783,14 +783,21 @@ def b200_arm(args, rank, world, local_rank):
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
         e_ms = float(t2.item())
         ref_p = probs[: nbuf * B].cpu() if Wm + K >= nbuf else None
-        e2e = {"value": world * K * B / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // K,
+        out = {"value": world * K * B / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // K,
                "d2h_bytes_per_step": (d2h1 - d2h0) // K, "ms_per_step": e_ms / K, "in_flight": depth,
+               "host_buffers": ("dense RGB u8 (n, ps, ps, 3): what read_region(...).convert('RGB') yields" if host_channels == 3
+                                else "RGBA u8 rows padded to 4 pixels: what read_region returns"),
                "collective_in_region": "one NCCL gather of the per-rank (N_r, K) results to rank 0" if world > 1 else "none (1 rank)"}
-        e2e["clocks"] = sampler.summary(ec0, ec1)
+        out["clocks"] = sampler.summary(ec0, ec1)
         if ref_p is not None:
             got = torch.cat([h[1] for h in host], 0)
-            e2e["max_abs_diff_vs_resident_path"] = float((got - ref_p).abs().max().item())
+            out["max_abs_diff_vs_resident_path"] = float((got - ref_p).abs().max().item())
         hp.close()
+        return out
+
+    if not args.no_e2e:
+        e2e = run_e2e(3)
+        e2e_rgba = run_e2e(4)
 
     # ---- pass B: the same K steps again with per-op CUDA events (roofline of the conv kernels, short window) ----
     net.set_profiling(K)
@@ -948,6 +955,7 @@ def b200_arm(args, rank, world, local_rank):
     }
     if e2e is not None:
         line["e2e"] = e2e
+        line["e2e_rgba_host_buffers"] = e2e_rgba
 
     def guarded(name, fn):
         try:

@@ -59,3 +59,61 @@ def test_classify_from_cache_identical_to_slide(arch):
     assert torch.equal(got_np, want)
     with pytest.raises(ValueError):
         classify_patches_from_images(np.zeros((2, 10, 12, 3), np.uint8), net, tf, 4)
+
+
+@pytest.mark.parametrize("ps", [175, 100, 37, 350])
+def test_fast_pack_equals_reference_pack(ps):
+    """wsi_pack_patches_rgba_fast (shared-memory staged, any first patch) == wsi_pack_patches_rgba, bit for bit."""
+    import torch
+
+    from wsinsight_b200 import _cabi
+
+    n = 9
+    g = torch.Generator().manual_seed(ps)
+    rgb = torch.randint(0, 256, (n * ps * ps * 3 + 64,), dtype=torch.uint8, generator=g).cuda()
+    pitch = (ps + 3) // 4 * 4 * 4
+    want = torch.zeros((n * ps, pitch), dtype=torch.uint8, device="cuda")
+    got = torch.zeros_like(want)
+    _cabi.call("wsi_pack_patches_rgba", rgb.data_ptr(), n, ps, pitch, want.data_ptr(), _cabi.stream_ptr())
+    _cabi.call("wsi_pack_patches_rgba_fast", rgb.data_ptr(), 0, 4, ps, pitch, got.data_ptr(), _cabi.stream_ptr())
+    _cabi.call("wsi_pack_patches_rgba_fast", rgb.data_ptr(), 4, n - 4, ps, pitch, got.data_ptr(), _cabi.stream_ptr())
+    assert torch.equal(got, want)
+
+
+def test_hostpipe_rgb_buffers_equal_resident_path():
+    """Host-buffer entry with dense RGB patches (host_channels = 3): same probabilities, bit for bit, as the slide-resident
+    path and as the RGBA host buffers."""
+    import torch
+
+    from oracle import forward as oforward
+    from wsinsight_b200.modellib.engine import B200Network
+    from wsinsight_b200.modellib.run_inference import HostPatchClassifier, classify_patches_device
+    from wsinsight_b200.modellib.transforms import make_compose_from_transform_config
+    from wsinsight_b200.patchlib.io import extract_patches_from_slide
+
+    s = _slide()
+    ps, n, B = 175, 300, 256        # 256 >= 4 * 64: the batch goes over in four pieces
+    rng = np.random.default_rng(1)
+    coords = np.stack([rng.integers(0, 3001 - ps, n), rng.integers(0, 2003 - ps, n)], 1).astype(np.int32)
+    coords[0] = (2950, 1950)
+    xywh = np.concatenate([coords, np.full_like(coords, ps)], 1)
+    tf = make_compose_from_transform_config(oforward.BREAST_RESNET34_CONFIG["transform"])
+    net = B200Network.from_torchscript(torch.jit.freeze(torch.jit.script(oforward.make_resnet34_calibrated(2, 0))), 2,
+                                       input_size=224, max_batch=B)
+    want = classify_patches_device(s, xywh, net, tf, batch_size=B).cpu()
+    rgb = extract_patches_from_slide(s, coords, ps).cpu()
+    for ch in (3, 4):
+        hp = HostPatchClassifier(net, ps, tf, B, depth=2, host_channels=ch)
+        out = torch.zeros((n, 2), dtype=torch.float32).pin_memory()
+        for lo in range(0, n, B):
+            hi = min(n, lo + B)
+            px, _ = hp.alloc_host_batch(hi - lo)
+            if ch == 3:
+                px.copy_(rgb[lo:hi])
+            else:
+                px[:, :, :ps, :3].copy_(rgb[lo:hi])
+                px[:, :, :ps, 3] = 255
+            hp.submit(px, out[lo:hi])
+            hp.sync()
+        hp.close()
+        assert torch.equal(out, want), f"host_channels={ch}: max diff {(out - want).abs().max()}"

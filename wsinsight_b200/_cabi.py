@@ -88,6 +88,7 @@ _PROTOS = {
     "wsi_preproc_plan_set_capacity": (c_int, [c_void_p, c_int]),
     "wsi_hostpipe_create": (c_int, [c_void_p, c_int, c_ll, c_int, c_float_p, c_float_p, c_int, c_int,
                                     C.POINTER(c_void_p)]),
+    "wsi_hostpipe_set_host_channels": (c_int, [c_void_p, c_int]),
     "wsi_hostpipe_submit": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "wsi_hostpipe_sync": (c_int, [c_void_p]),
     "wsi_hostpipe_compute_stream": (c_void_p, [c_void_p]),
@@ -107,6 +108,7 @@ _PROTOS = {
     "wsi_density_accumulate": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "wsi_extract_patches_rgb": (c_int, [c_void_p, c_ll, c_ll, c_ll, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "wsi_pack_patches_rgba": (c_int, [c_void_p, c_int, c_int, c_ll, c_void_p, c_void_p]),
+    "wsi_pack_patches_rgba_fast": (c_int, [c_void_p, c_int, c_int, c_int, c_ll, c_void_p, c_void_p]),
     "wsi_stain_normalize_rgb": (c_int, [c_void_p, c_void_p, c_ll, C.POINTER(C.c_double), c_void_p]),
     "wsi_tilefuse_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                         C.c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

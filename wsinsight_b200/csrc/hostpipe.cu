@@ -18,6 +18,7 @@ namespace {
 constexpr int HP_CHUNKS = 4;    // a batch is copied and preprocessed in this many pieces (pipeline fill = one piece)
 
 struct Slot {
+  uint8_t* d_rgb = nullptr;            // RGB host mode: [max_batch][ps][ps][3] u8 landing buffer (+ 16 bytes of slack)
   uint8_t* d_stage = nullptr;          // [max_batch * ps rows][pitch] RGBA u8
   __nv_bfloat16* d_input = nullptr;    // network input layout, borders zeroed once
   float* d_probs = nullptr;            // [max_batch][K]
@@ -35,6 +36,7 @@ struct HostPipe {
   long long pitch = 0;
   int in_H = 0, in_W = 0;
   bool skip_h2d = false;
+  int host_channels = 4;               // 4: RGBA rows of `pitch` bytes (what read_region returns); 3: dense RGB
   long long patch_elems = 0;           // bf16 elements one patch occupies in the network input buffer (per plane)
   int32_t* d_coords = nullptr;         // (0, i*ps) for i < max_batch
   cudaStream_t s_copy = nullptr, s_comp = nullptr;
@@ -48,6 +50,7 @@ void destroy(HostPipe* p) {
   for (auto& s : p->slots) {
     if (s.plan) wsi_preproc_plan_destroy(s.plan);
     if (s.d_stage) cudaFree(s.d_stage);
+    if (s.d_rgb) cudaFree(s.d_rgb);
     if (s.d_input) cudaFree(s.d_input);
     if (s.d_probs) cudaFree(s.d_probs);
     if (s.copied) cudaEventDestroy(s.copied);
@@ -148,12 +151,31 @@ int wsi_hostpipe_create(void* net, int patch_size, long long patch_pitch_bytes, 
   return WSI_OK;
 }
 
+int wsi_hostpipe_set_host_channels(void* pipe, int channels) {
+  HostPipe* p = (HostPipe*)pipe;
+  WSI_ARG_CHECK(p && (channels == 3 || channels == 4), "wsi_hostpipe_set_host_channels: channels must be 3 or 4");
+  WSI_ARG_CHECK(p->submitted == 0, "wsi_hostpipe_set_host_channels: call before the first submit");
+  if (channels == 3)
+    for (auto& s : p->slots)
+      if (!s.d_rgb) {
+        const size_t bytes = (size_t)p->max_batch * p->ps * p->ps * 3 + 64;
+        if (cudaMalloc(&s.d_rgb, bytes) != cudaSuccess) {
+          wsi_set_error("wsi_hostpipe_set_host_channels: cudaMalloc of the RGB landing buffer failed");
+          return WSI_ERR_NOMEM;
+        }
+        // the RGBA stack's pitch padding (columns >= ps) is never written by the pack kernel: clear it once
+        WSI_CUDA_CHECK(cudaMemset(s.d_stage, 0, (size_t)p->max_batch * p->ps * (size_t)p->pitch));
+      }
+  p->host_channels = channels;
+  return WSI_OK;
+}
+
 int wsi_hostpipe_submit(void* pipe, const uint8_t* h_rgba, int n, float* h_probs) {
   HostPipe* p = (HostPipe*)pipe;
   WSI_ARG_CHECK(p && h_rgba && h_probs, "wsi_hostpipe_submit: null pointer");
   WSI_ARG_CHECK(n >= 1 && n <= p->max_batch, "wsi_hostpipe_submit: batch %d out of range (max %d)", n, p->max_batch);
   Slot& s = p->slots[(size_t)(p->submitted % p->depth)];
-  const size_t in_bytes = (size_t)n * p->ps * (size_t)p->pitch;
+  const size_t in_bytes = p->host_channels == 3 ? (size_t)n * p->ps * p->ps * 3 : (size_t)n * p->ps * (size_t)p->pitch;
   const size_t out_bytes = (size_t)n * p->K * sizeof(float);
   if (s.used) {
     // the staging buffer may be overwritten once the preprocess kernel that read it has finished;
@@ -166,14 +188,25 @@ int wsi_hostpipe_submit(void* pipe, const uint8_t* h_rgba, int n, float* h_probs
   const int C = n >= 64 * HP_CHUNKS ? HP_CHUNKS : 1;
   const int per = (n + C - 1) / C;
   const size_t patch_bytes = (size_t)p->ps * (size_t)p->pitch;
+  const size_t rgb_bytes = (size_t)p->ps * p->ps * 3;
   int rc = WSI_OK;
   for (int c = 0, j0 = 0; j0 < n; ++c, j0 += per) {
     const int m = n - j0 < per ? n - j0 : per;
-    if (!p->skip_h2d)     // WSI_B200_HP_NO_H2D=1: timing experiment only (stale pixels), never set in production
+    if (p->host_channels == 3) {
+      // dense RGB patches (25 % fewer bytes over PCIe): land in d_rgb, expanded to the RGBA stack on the device
+      if (!p->skip_h2d)
+        WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_rgb + (size_t)j0 * rgb_bytes, h_rgba + (size_t)j0 * rgb_bytes,
+                                       (size_t)m * rgb_bytes, cudaMemcpyHostToDevice, p->s_copy));
+    } else if (!p->skip_h2d) {   // WSI_B200_HP_NO_H2D=1: timing experiment only (stale pixels), never set in production
       WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_stage + (size_t)j0 * patch_bytes, h_rgba + (size_t)j0 * patch_bytes,
                                      (size_t)m * patch_bytes, cudaMemcpyHostToDevice, p->s_copy));
+    }
     WSI_CUDA_CHECK(cudaEventRecord(s.chunk_ev[c], p->s_copy));
     WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_comp, s.chunk_ev[c], 0));
+    if (p->host_channels == 3) {
+      rc = wsi_pack_patches_rgba_fast(s.d_rgb, j0, m, p->ps, p->pitch, s.d_stage, p->s_comp);
+      if (rc) return rc;
+    }
     rc = wsi_preproc_run(s.plan, p->d_coords + 2 * (size_t)j0, m, s.d_input + (size_t)j0 * p->patch_elems, p->s_comp);
     if (rc) return rc;
   }

@@ -33,6 +33,36 @@ __global__ void k_rgb_to_rgba_stack(const uint8_t* __restrict__ rgb, int ps, lon
   reinterpret_cast<uint32_t*>(out + ((size_t)n * ps + y) * pitch)[x] = p;
 }
 
+// Same packing at memory speed (the host-buffer pipeline runs it on every batch): a CTA takes PK_ROWS rows of one
+// patch -- a contiguous run of bytes in the dense RGB stack -- loads it with aligned 16-byte vectors into shared
+// memory, and writes one RGBA word per pixel, coalesced along the row.
+constexpr int PK_ROWS = 16;
+
+__global__ void __launch_bounds__(256)
+    k_rgb_to_rgba_rows(const uint8_t* __restrict__ rgb, int patch0, int ps, long long pitch, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) uint8_t s_pk[];
+  const int n = patch0 + blockIdx.y, y0 = blockIdx.x * PK_ROWS;
+  const int rows = min(PK_ROWS, ps - y0);
+  const size_t first = ((size_t)n * ps + y0) * (size_t)ps * 3;       // first byte of the run
+  const size_t nbytes = (size_t)rows * ps * 3;
+  const size_t a0 = first & ~(size_t)15;                               // aligned load window
+  const int mis = (int)(first - a0);
+  const int nvec = (int)((mis + nbytes + 15) / 16);
+  const uint4* src = reinterpret_cast<const uint4*>(rgb + a0);
+  uint4* dst = reinterpret_cast<uint4*>(s_pk);
+  // the window may start up to 15 bytes before / end up to 15 bytes after the run: still inside the allocation except
+  // at the very end of the stack, where the caller guarantees 16 bytes of slack
+  for (int i = threadIdx.x; i < nvec; i += 256) dst[i] = __ldg(src + i);
+  __syncthreads();
+  const int npx = rows * ps;
+  for (int p = threadIdx.x; p < npx; p += 256) {
+    const int y = p / ps, x = p - y * ps;
+    const uint8_t* q = s_pk + mis + 3 * p;
+    const uint32_t v = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | 0xff000000u;
+    reinterpret_cast<uint32_t*>(out + ((size_t)n * ps + y0 + y) * pitch)[x] = v;
+  }
+}
+
 // Macenko stain normalisation of cached patches (N4): HistomicsTK's deconvolution_based_normalization(patch + 1e-8,
 // W_source, W_target) per pixel (wsinsight/modellib/data.py:293-300).  With x = (float)(u8 + 1e-8f) + 1 (the library's
 // optical-density form: white = 256), sda = -log(x / 256) * 255 / log(256); stains = inv(Wc) . sda; the library then
@@ -65,6 +95,29 @@ __global__ void __launch_bounds__(256)
 }  // namespace
 
 extern "C" {
+
+// Patches [first_patch, first_patch + n) of the dense RGB stack d_rgb ([..][ps][ps][3], base 16-byte aligned and followed
+// by >= 16 readable bytes: the aligned vector loads of the last run) -> the same patch slots of the RGBA stack.
+int wsi_pack_patches_rgba_fast(const uint8_t* d_rgb, int first_patch, int n, int patch_size, long long pitch_bytes,
+                               uint8_t* d_out_rgba, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  WSI_ARG_CHECK(d_rgb && d_out_rgba, "wsi_pack_patches_rgba_fast: null pointer");
+  WSI_ARG_CHECK(first_patch >= 0 && n >= 0 && n <= 65535 && patch_size >= 1 && patch_size <= 1024 && (pitch_bytes & 15) == 0 &&
+                    pitch_bytes >= (long long)patch_size * 4 && (((uintptr_t)d_rgb) & 15) == 0,
+                "wsi_pack_patches_rgba_fast: bad sizes / alignment");
+  if (n == 0) return WSI_OK;
+  const size_t smem = (size_t)PK_ROWS * patch_size * 3 + 32;
+  static bool attr_set = false;
+  if (!attr_set) {
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(k_rgb_to_rgba_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    attr_set = true;
+  }
+  dim3 grid((patch_size + PK_ROWS - 1) / PK_ROWS, n);
+  k_rgb_to_rgba_rows<<<grid, 256, smem, stream>>>(d_rgb, first_patch, patch_size, pitch_bytes, d_out_rgba);
+  wsi_count_launch(1);
+  WSI_CUDA_CHECK(cudaGetLastError());
+  return WSI_OK;
+}
 
 int wsi_stain_normalize_rgb(const uint8_t* d_rgb_in, uint8_t* d_rgb_out, long long n_pixels, const double* h_M9,
                             void* stream_) {

@@ -422,7 +422,10 @@ class HostPatchClassifier:
     streams with ``depth`` batches in flight.
     """
 
-    def __init__(self, net, patch_size: int, transform, max_batch: int, depth: int = 2):
+    def __init__(self, net, patch_size: int, transform, max_batch: int, depth: int = 2, host_channels: int = 4):
+        """``host_channels=3``: the host batches are dense RGB ``(n, ps, ps, 3)`` -- what
+        ``read_region(...).convert("RGB")`` yields (data.py:276-281) -- 25 % fewer bytes over PCIe, expanded to the RGBA
+        stack on the device; ``4`` (default): RGBA rows padded to a multiple of 4 pixels."""
         import ctypes as C
 
         torch = _cabi.require_cuda()
@@ -435,19 +438,25 @@ class HostPatchClassifier:
         with torch.cuda.device(net.device):
             _cabi.call("wsi_hostpipe_create", net._h, self.patch_size, self.pitch_px * 4, self.S, mean, std,
                        self.max_batch, int(depth), C.byref(self._h))
+            self.host_channels = int(host_channels)
+            if self.host_channels != 4:
+                _cabi.call("wsi_hostpipe_set_host_channels", self._h, self.host_channels)
 
     def alloc_host_batch(self, n: int = None):
         """Pinned ``(n, ps, pitch_px, 4)`` uint8 and ``(n, K)`` fp32 host tensors."""
         import torch
 
         n = self.max_batch if n is None else int(n)
-        return (torch.zeros((n, self.patch_size, self.pitch_px, 4), dtype=torch.uint8).pin_memory(),
+        shape = (n, self.patch_size, self.patch_size, 3) if self.host_channels == 3 else \
+            (n, self.patch_size, self.pitch_px, 4)
+        return (torch.zeros(shape, dtype=torch.uint8).pin_memory(),
                 torch.zeros((n, self.net.num_classes), dtype=torch.float32).pin_memory())
 
     def submit(self, rgba, probs):
         n = int(rgba.shape[0])
         assert rgba.dtype.is_floating_point is False and rgba.is_contiguous() and not rgba.is_cuda
-        assert tuple(rgba.shape[1:]) == (self.patch_size, self.pitch_px, 4)
+        assert tuple(rgba.shape[1:]) == ((self.patch_size, self.patch_size, 3) if self.host_channels == 3
+                                         else (self.patch_size, self.pitch_px, 4))
         assert probs.is_contiguous() and not probs.is_cuda and probs.numel() >= n * self.net.num_classes
         _cabi.call("wsi_hostpipe_submit", self._h, rgba.data_ptr(), n, probs.data_ptr())
 
