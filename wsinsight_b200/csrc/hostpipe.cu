@@ -201,12 +201,14 @@ int wsi_hostpipe_submit(void* pipe, const uint8_t* h_rgba, int n, float* h_probs
       WSI_CUDA_CHECK(cudaMemcpyAsync(s.d_stage + (size_t)j0 * patch_bytes, h_rgba + (size_t)j0 * patch_bytes,
                                      (size_t)m * patch_bytes, cudaMemcpyHostToDevice, p->s_copy));
     }
-    WSI_CUDA_CHECK(cudaEventRecord(s.chunk_ev[c], p->s_copy));
-    WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_comp, s.chunk_ev[c], 0));
     if (p->host_channels == 3) {
-      rc = wsi_pack_patches_rgba_fast(s.d_rgb, j0, m, p->ps, p->pitch, s.d_stage, p->s_comp);
+      // expansion to the RGBA stack on the COPY stream, right behind the piece's H2D: it runs in the shadow of the
+      // previous batch's convolutions instead of sitting on the compute stream's critical path
+      rc = wsi_pack_patches_rgba_fast(s.d_rgb, j0, m, p->ps, p->pitch, s.d_stage, p->s_copy);
       if (rc) return rc;
     }
+    WSI_CUDA_CHECK(cudaEventRecord(s.chunk_ev[c], p->s_copy));
+    WSI_CUDA_CHECK(cudaStreamWaitEvent(p->s_comp, s.chunk_ev[c], 0));
     rc = wsi_preproc_run(s.plan, p->d_coords + 2 * (size_t)j0, m, s.d_input + (size_t)j0 * p->patch_elems, p->s_comp);
     if (rc) return rc;
   }
