@@ -179,3 +179,48 @@ def test_finalize_empty_and_single_blob():
     wi, wp, wl = cellpost.finalize(npm, hv, tp, 20)
     assert len(ins) == len(wi) and all(np.array_equal(a, b) for a, b in zip(ins, wi))
     assert all(np.array_equal(a, b) for a, b in zip(ply, wl)) and np.abs(np.concatenate(prb) - np.concatenate(wp)).max() < 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["tiny", "all_foreground", "k16_min0", "single_row"])
+def test_finalize_edge_cases(case):
+    """Degenerate tiles: smaller than the Sobel kernel (reflect-101 folds more than once), one blob covering everything,
+    the maximum class count with min_object_size = 0, a one-pixel-high canvas."""
+    import torch
+
+    from wsinsight_b200.modellib.tilefuse import TileRemapStitcher
+
+    rng = np.random.default_rng(7)
+    if case == "tiny":
+        h, w, K, ms = 5, 7, 3, 2
+        npm = (rng.random((h, w)) > 0.4).astype(np.float32) * 0.9
+        hv = rng.normal(0, 0.3, (h, w, 2)).astype(np.float32)
+    elif case == "all_foreground":
+        h, w, K, ms = 40, 50, 2, 10
+        npm = np.full((h, w), 0.8, np.float32)
+        yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+        hv = np.stack([(xx % 13) / 6.5 - 1, (yy % 11) / 5.5 - 1], -1).astype(np.float32)
+    elif case == "k16_min0":
+        h, w, K, ms = 90, 110, 16, 0
+        npm, hv, _ = synth_nuclei(h, w, 21, K=4)
+    else:
+        h, w, K, ms = 1, 64, 3, 3
+        npm = (rng.random((h, w)) > 0.5).astype(np.float32)
+        hv = rng.normal(0, 0.3, (h, w, 2)).astype(np.float32)
+    tp = rng.random((h, w, K)).astype(np.float32)
+    tp /= tp.sum(-1, keepdims=True)
+    st = TileRemapStitcher(K, w, h, 16, 0, 1.0, 1.0, min_object_size=ms)
+    t = st._tile(0, 0)
+    t[0].copy_(torch.from_numpy(npm)); t[1].copy_(torch.from_numpy(hv)); t[2].copy_(torch.from_numpy(tp))
+    boxes, probs, pxy, poff, maps = st.finalize_arrays(return_inst_maps=True)
+    want = cellpost.proc_np_hv_stages(npm, hv, ms)["inst"]
+    got = maps[0]
+    assert np.array_equal(got > 0, want > 0)
+    same_partition = len(np.unique(np.stack([got[want > 0], want[want > 0]], 1), axis=0)) == len(np.unique(want[want > 0]))
+    wi, wp, wl = cellpost.stitching_worker(npm, hv, tp, 0, 0, (slice(0, h), slice(0, w)), ms, inst=want)
+    if same_partition and len(wi):
+        assert np.array_equal(boxes, np.concatenate(wi)) and np.abs(probs - np.concatenate(wp)).max() <= 1e-6
+        polys = [pxy[poff[i]:poff[i + 1]] for i in range(len(boxes)) if poff[i + 1] > poff[i]]
+        assert len(polys) == len(wl) and all(np.array_equal(a, b) for a, b in zip(polys, wl))
+    else:
+        assert len(boxes) == len(wi) or not same_partition
