@@ -159,6 +159,23 @@ class PeerResultBuffer:
     CUDA IPC (``wsi_peer_buffer_*``): each rank's tail kernel (GAP + FC + softmax) stores its rows straight into rank 0's
     memory over NVLink, so the result path needs no gather collective -- only a barrier before rank 0 reads."""
 
+    _cache = {}      # (K, world, device index) -> PeerResultBuffer kept mapped between slides
+
+    @classmethod
+    def get(cls, n: int, K: int, rank: int, world: int, device):
+        """A buffer with room for ``n`` rows: the mapped buffer of the previous slide when it is large enough (every rank
+        sees the same ``n``, so every rank takes the same branch), else a new one of twice the size."""
+        torch = _cabi.require_cuda()
+        key = (int(K), int(world), torch.device(device).index)
+        buf = cls._cache.get(key)
+        if buf is None or buf.capacity < n:
+            if buf is not None:
+                buf.release()
+            buf = cls(max(2 * int(n), 1 << 16), K, rank, world, device)
+            cls._cache[key] = buf
+        buf.n = int(n)
+        return buf
+
     def __init__(self, n: int, K: int, rank: int, world: int, device):
         import ctypes as C
 
@@ -166,6 +183,7 @@ class PeerResultBuffer:
 
         torch = _cabi.require_cuda()
         self.rank, self.world, self.n, self.K = rank, world, int(n), int(K)
+        self.capacity = int(n)
         self._ptr = C.c_void_p()
         self.tensor = None
         handle = (C.c_ubyte * 64)()
@@ -215,20 +233,28 @@ class PeerResultBuffer:
         return self.tensor[lo:hi]
 
     def collect(self):
-        """Barrier, then the (N, K) NumPy array on rank 0 (None elsewhere); releases the mapping / the buffer."""
+        """Barrier, then the first ``n`` rows as a NumPy array on rank 0 (None elsewhere).  The buffer stays mapped for the
+        next slide; a second barrier keeps the other ranks from overwriting it before rank 0 has copied."""
         import torch.distributed as dist
 
         torch = _cabi.require_cuda()
         torch.cuda.synchronize()
         dist.barrier()                     # every rank's stores have landed
-        out = self.tensor.cpu().numpy().copy() if self.rank == 0 else None
+        out = self.tensor[: self.n].cpu().numpy().copy() if self.rank == 0 else None
+        dist.barrier()                     # rank 0 has its copy: the rows may be rewritten
+        return out
+
+    def release(self):
+        """Unmap (ranks > 0) / free (rank 0) the buffer; collective."""
+        import torch.distributed as dist
+
         self.tensor = None
-        if self.rank != 0:
+        if self.rank != 0 and self._ptr.value:
             _cabi.call("wsi_peer_buffer_close", self._ptr)
         dist.barrier()                     # all mappings closed before the owner frees
-        if self.rank == 0:
+        if self.rank == 0 and self._ptr.value:
             _cabi.call("wsi_peer_buffer_free", self._ptr)
-        return out
+        self._ptr.value = None
 
 
 def _result_path(result_path=None) -> str:
@@ -255,7 +281,7 @@ def classify_coords_sharded(slide, coords_xywh: np.ndarray, net, transform, batc
     n = len(coords_xywh)
     lo, hi = shard_range(n, rank, world)
     if world > 1 and _result_path(result_path) == "peer":
-        buf = PeerResultBuffer(n, net.num_classes, rank, world, net.device)
+        buf = PeerResultBuffer.get(n, net.num_classes, rank, world, net.device)
         classify_patches_device(slide, coords_xywh[lo:hi], net, transform, batch_size, probs_out=buf.rows(lo, hi))
         return buf.collect()
     local = classify_patches_device(slide, coords_xywh[lo:hi], net, transform, batch_size)
@@ -283,7 +309,7 @@ def classify_slide_sharded(slide, patch_size_px: int, patch_spacing_um_px: float
     xywh = np.concatenate([cxy, np.full_like(cxy, res.patch_size)], 1)
     dc = res.coords[lo:hi].contiguous()
     if world > 1 and _result_path(result_path) == "peer":
-        buf = PeerResultBuffer(n, net.num_classes, rank, world, net.device)
+        buf = PeerResultBuffer.get(n, net.num_classes, rank, world, net.device)
         classify_patches_device(slide, xywh[lo:hi], net, transform, batch_size, device_coords=dc,
                                 probs_out=buf.rows(lo, hi))
         return xywh, buf.collect()
