@@ -551,7 +551,7 @@ CPLayout cp_layout(int H, int W, int K, int max_inst) {
     o += up256(bytes);
     return r;
   };
-  l.max_marks = (int)(n / 4 + 16);
+  l.max_marks = (int)(n / 2 + 16);      // a binary image has at most ceil(n / 2) 4-connected components
   l.ctr = take(sizeof(int) * C_INTS);
   l.mm64 = take(sizeof(unsigned long long) * 4);
   for (int i = 0; i < 6; ++i) l.u8[i] = take(n);
