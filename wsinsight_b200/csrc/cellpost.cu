@@ -149,13 +149,16 @@ __global__ void __launch_bounds__(256)
   const float vsc = (float)sc, vsh = (float)sh;
   const int y = p / t.W, x = p - y * t.W;
   const float* row = t.hv + (size_t)y * t.hv_pitch;
-  double sH = 0.0, sV = 0.0;
+  // OpenCV's separable filters evaluate symmetric / anti-symmetric kernels in the folded form
+  // k[0] * S[0] + sum_k k[k] * (S[+k] +- S[-k]): a derivative along an axis the image does not vary on is then exactly 0
+  auto hv_at = [&](int xx) { return *reinterpret_cast<const float2*>(row + 2 * (size_t)reflect101(xx, t.W)); };
+  const float2 c0 = hv_at(x);
+  double sH = 0.0, sV = c_ks[10] * (double)fmaf(c0.y, vsc, vsh);
 #pragma unroll
-  for (int i = 0; i < 21; ++i) {
-    const int xx = reflect101(x + i - 10, t.W);
-    const float2 hv = *reinterpret_cast<const float2*>(row + 2 * (size_t)xx);
-    sH += c_kd[i] * (double)fmaf(hv.x, hsc, hsh);
-    sV += c_ks[i] * (double)fmaf(hv.y, vsc, vsh);
+  for (int k = 1; k <= 10; ++k) {
+    const float2 a = hv_at(x + k), b = hv_at(x - k);
+    sH += c_kd[10 + k] * ((double)fmaf(a.x, hsc, hsh) - (double)fmaf(b.x, hsc, hsh));
+    sV += c_ks[10 + k] * ((double)fmaf(a.y, vsc, vsh) + (double)fmaf(b.y, vsc, vsh));
   }
   tmpH[p] = sH;
   tmpV[p] = sV;
@@ -172,12 +175,12 @@ __global__ void __launch_bounds__(256)
   unsigned long long a0 = ~0ull, a1 = 0ull, b0 = ~0ull, b1 = 0ull;
   if (p < n) {
     const int y = p / W, x = p - y * W;
-    double sH = 0.0, sV = 0.0;
+    double sH = c_ks[10] * tmpH[(size_t)y * W + x], sV = 0.0;
 #pragma unroll
-    for (int j = 0; j < 21; ++j) {
-      const int yy = reflect101(y + j - 10, H);
-      sH += c_ks[j] * tmpH[(size_t)yy * W + x];
-      sV += c_kd[j] * tmpV[(size_t)yy * W + x];
+    for (int k = 1; k <= 10; ++k) {
+      const size_t ia = (size_t)reflect101(y + k, H) * W + x, ib = (size_t)reflect101(y - k, H) * W + x;
+      sH += c_ks[10 + k] * (tmpH[ia] + tmpH[ib]);
+      sV += c_kd[10 + k] * (tmpV[ia] - tmpV[ib]);
     }
     sobH[p] = sH;
     sobV[p] = sV;
