@@ -1,0 +1,345 @@
+// K4a'': 3x3 / stride 1 convolution with Cout = 64 over the zero-padded flat layout of conv_flat.cuh, with the
+// three kernel COLUMNS kept in separate accumulators ("kw-split").
+//
+// Why: a tcgen05.mma reads its whole A tile (128 rows x 32 B per K step) from shared memory whatever N is, so with
+// N = 64 the operand port (128 B/clk/SM) and not the tensor pipe bounds the nine-tap kernel: 4 KB of A + 1 KB of B per
+// 32 clk of math even as a CTA pair (ncu r02: layer1 of ResNet34 at 67-69 % tensor-pipe active, sm throughput 90 %).
+// Here ONE MMA per tap ROW kh multiplies the slab rows x + (kh-1)*Wp by the weights of all three taps of that row,
+//     D[x][kw*64 + co] += sum_ci In[x + (kh-1)*Wp][ci] * W[co][ci][kh][kw]            (N = 192),
+// i.e. 12 MMAs of N = 192 per 128 rows instead of 36 of N = 64: the A tile is read once per three taps (7 KB per
+// 96 clk of math as a pair).  The column shift moves to the epilogue,
+//     out[p] = D[p-1][0:64] + D[p][64:128] + D[p+1][128:192],
+// where a row is a TMEM lane: the two neighbours come from warp shuffles, the three lane pairs that straddle two
+// warps of an epilogue group go through 1.5 KB of shared memory, and a tile of 128 MMA rows yields the 126 outputs
+// that have both neighbours (tiles advance by 126 flat positions).
+//
+// Warps: 0 TMA producer (weights once: 3*chunks k-blocks of 192 rows; one slab of 128 + 2*Wp rows per tile),
+// 1 MMA issuer, 2-5 / 6-9 two epilogue groups that take alternate tiles (group g <-> accumulator stage g).
+// Residual tiles are TMA-loaded into the output staging buffer and added in place, as in conv_flat.cuh.
+#pragma once
+#include "conv_flat.cuh"
+
+namespace convf3 {
+
+constexpr int THREADS = 320;
+constexpr int NC = 64;           // Cout
+constexpr int N3 = 3 * NC;       // UMMA N
+constexpr int TMO = 126;         // outputs per tile: MMA rows 1..126
+
+struct Args {
+  int Hp, Wp, H, W, B;          // stored geometry shared by input, output and residual; H x W = OUTPUT interior
+  int pad;                      // border of the output interior inside the stored geometry
+  int cluster;                  // 1 | 2 (CTA pairs, M = 256)
+  int ksteps;                   // K = 16 steps per 64-channel chunk: 4, or 2 when only 32 channels are real
+  long long total_rows;         // B * Hp * Wp flat positions
+  int num_tiles;                // tiles of TMO outputs
+  int chunks;                   // Cin / 64
+  int slab_rows, slab_loads, slab_box_rows;
+  int stagesA;
+  int relu, has_res;
+  int out_c_off;
+  const float* bias;
+};
+
+template <bool PAIR>
+__device__ __forceinline__ void umma1(uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc) {
+  if (PAIR) ptx::umma_bf16_lohi_2sm(d, a_lo, b_lo, hi, idesc, acc); else ptx::umma_bf16_lohi(d, a_lo, b_lo, hi, idesc, acc);
+}
+
+template <int CL>
+__global__ void __launch_bounds__(THREADS, 1)
+    k_conv_flat3(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
+                 const __grid_constant__ CUtensorMap tmapO, const __grid_constant__ CUtensorMap tmapR, const Args a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+  constexpr bool PAIR = CL == 2;
+  constexpr int b_bytes = (N3 / CL) * 128;               // per-CTA bytes of one weight k-block
+  const int slab_bytes = a.slab_rows * 128;
+  const int KB = 3 * a.chunks;
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + (size_t)a.stagesA * slab_bytes;
+  uint8_t* sOut = sB + (size_t)KB * b_bytes;             // [group][buffer] x 16 KB, 1024-aligned
+  float* sX = reinterpret_cast<float*>(sOut + 4 * 16384);   // [group][up | down][3 boundaries][64]
+  float* sBias = sX + 2 * 384;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + NC);
+  uint64_t* aFull = bars;
+  uint64_t* aEmpty = aFull + a.stagesA;
+  uint64_t* bFull = aEmpty + a.stagesA;
+  uint64_t* tfull = bFull + 1;
+  uint64_t* tempty = tfull + 2;
+  uint64_t* resFull = tempty + 2;                        // [group * 2 + buffer]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resFull + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t crank = PAIR ? ptx::cluster_ctarank() : 0u;
+  const int num_units = PAIR ? (a.num_tiles + 1) / 2 : a.num_tiles;
+  const int first_unit = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int unit_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  auto tile_of = [&](int u) { return PAIR ? min(2 * u + (int)crank, a.num_tiles - 1) : u; };
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmapA);
+    ptx::prefetch_tmap(&tmapB);
+    ptx::prefetch_tmap(&tmapO);
+    for (int s = 0; s < a.stagesA; ++s) {
+      ptx::mbar_init(&aFull[s], 1);
+      ptx::mbar_init(&aEmpty[s], 1);
+    }
+    ptx::mbar_init(bFull, 1);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], (uint32_t)(4 * CL));
+    }
+    for (int s = 0; s < 4; ++s) ptx::mbar_init(&resFull[s], 1);
+    ptx::fence_barrier_init();
+  }
+  if (PAIR) {
+    __syncthreads();
+    ptx::cluster_sync();
+  }
+  if (warp == 1) {
+    if (PAIR) {
+      ptx::tmem_alloc_2sm(tmem_slot, 512);
+      ptx::tmem_relinquish_2sm();
+    } else {
+      ptx::tmem_alloc(tmem_slot, 512);
+      ptx::tmem_relinquish();
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (PAIR) ptx::cluster_sync();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    const bool arm = !PAIR || crank == 0;          // pair mode: only the leader arms, for the bytes of BOTH CTAs
+    if (ptx::elect_one()) {
+      if (arm) ptx::mbar_arrive_expect_tx(bFull, (uint32_t)(KB * b_bytes * CL));
+      for (int kb = 0; kb < KB; ++kb) {
+        if (PAIR)
+          ptx::tma_load_2d_2sm(sB + (size_t)kb * b_bytes, &tmapB, ptx::leader_bar_addr(bFull), kb * 64, (int)crank * (N3 / 2));
+        else
+          ptx::tma_load_2d(sB + (size_t)kb * b_bytes, &tmapB, bFull, kb * 64, 0);
+      }
+    }
+    __syncwarp();
+    int sa = 0;
+    uint32_t pa = 0;
+    for (int u = first_unit; u < num_units; u += unit_step) {
+      const long long q0 = (long long)tile_of(u) * TMO;
+      const int row0 = (int)(q0 - 1 - a.Wp);         // slab row 0: flat position of MMA row 0 under tap row kh = 0
+      for (int c = 0; c < a.chunks; ++c) {
+        ptx::mbar_wait(&aEmpty[sa], pa ^ 1);
+        if (ptx::elect_one()) {
+          if (arm) ptx::mbar_arrive_expect_tx(&aFull[sa], (uint32_t)(slab_bytes * CL));
+          for (int i = 0; i < a.slab_loads; ++i) {
+            void* dst = sA + (size_t)sa * slab_bytes + (size_t)i * a.slab_box_rows * 128;
+            if (PAIR)
+              ptx::tma_load_2d_2sm(dst, &tmapA, ptx::leader_bar_addr(&aFull[sa]), c * 64, row0 + i * a.slab_box_rows);
+            else
+              ptx::tma_load_2d(dst, &tmapA, &aFull[sa], c * 64, row0 + i * a.slab_box_rows);
+          }
+        }
+        __syncwarp();
+        if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (pair mode: the leader CTA only) =====================
+    if (!PAIR || crank == 0) {
+      const uint32_t idesc = ptx::make_idesc_bf16(PAIR ? 256 : 128, N3);
+      const uint32_t hi = ptx::sw128_desc_hi();
+      const uint32_t sA_lo = ptx::desc_lo(ptx::smem_u32(sA)), sB_lo = ptx::desc_lo(ptx::smem_u32(sB));
+      const uint32_t slab_step = (uint32_t)slab_bytes >> 4, b_step = (uint32_t)b_bytes >> 4;
+      const uint32_t row_step = (uint32_t)a.Wp * 8u;   // one image row of the padded layout in descriptor units
+      const bool k4 = a.ksteps == 4;
+      ptx::mbar_wait(bFull, 0);
+      int sa = 0, k = 0;
+      uint32_t pa = 0;
+      for (int u = first_unit; u < num_units; u += unit_step, ++k) {
+        const int acc = k & 1;
+        ptx::mbar_wait(&tempty[acc], (uint32_t)(((k >> 1) & 1) ^ 1));
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N3);
+        for (int c = 0; c < a.chunks; ++c) {
+          ptx::mbar_wait(&aFull[sa], pa);
+          ptx::tc_fence_after();
+          const uint32_t slab_lo = sA_lo + (uint32_t)sa * slab_step;
+          if (ptx::elect_one()) {
+#pragma unroll
+            for (int kh = 0; kh < 3; ++kh) {
+              const uint32_t a_lo = slab_lo + (uint32_t)kh * row_step;
+              const uint32_t b_lo = sB_lo + (uint32_t)(kh * a.chunks + c) * b_step;
+              umma1<PAIR>(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)((c | kh) != 0));
+              umma1<PAIR>(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
+              if (k4) {
+                umma1<PAIR>(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
+                umma1<PAIR>(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
+              }
+            }
+            if (PAIR) ptx::umma_commit_2sm(&aEmpty[sa], (uint16_t)3); else ptx::umma_commit(&aEmpty[sa]);
+            if (c == a.chunks - 1) {
+              if (PAIR) ptx::umma_commit_2sm(&tfull[acc], (uint16_t)3); else ptx::umma_commit(&tfull[acc]);
+            }
+          }
+          __syncwarp();
+          if (++sa == a.stagesA) { sa = 0; pa ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue: group g takes every other tile (accumulator stage g) =====================
+    const int g = (warp - 2) >> 2;
+    const int q = warp & 3;                           // TMEM lane quarter of this warp
+    const int row = q * 32 + lane;                    // MMA row == TMEM lane
+    const bool leader = (((warp - 2) & 3) * 32 + lane) == 0;
+    for (int i = (int)threadIdx.x - 64; i < NC; i += 256) sBias[i] = a.bias[i];
+    ptx::named_bar_sync(3, 256);
+    const int img = a.Hp * a.Wp;
+    uint8_t* myOut = sOut + (size_t)g * 2 * 16384;
+    float* xup = sX + g * 384;                        // [3][64]: column block kw = 0 of row 32b + 31 (needed by row 32b + 32)
+    float* xdn = xup + 192;                           // [3][64]: column block kw = 2 of row 32b + 32 (needed by row 32b + 31)
+    uint64_t* rf = resFull + g * 2;
+    const int u0 = first_unit + g * unit_step, ustep = 2 * unit_step;
+    const bool has_row = row >= 1 && row <= TMO;
+    const int sr = row - 1;                           // staged row == output p - q0
+    if (a.has_res && leader && u0 < num_units) {
+      ptx::mbar_arrive_expect_tx(&rf[0], (uint32_t)(TMO * 128));
+      ptx::tma_load_2d(myOut, &tmapR, &rf[0], 0, (int)((long long)tile_of(u0) * TMO));
+    }
+    int kk = 0;
+    for (int u = u0; u < num_units; u += ustep, ++kk) {
+      const int ob = kk & 1;
+      const long long q0 = (long long)tile_of(u) * TMO;
+      bool valid = false;
+      if (has_row) {
+        const long long p = q0 + sr;
+        const int n = (int)(p / img);
+        const int rem = (int)(p - (long long)n * img);
+        const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
+        valid = (n < a.B) && (hp >= a.pad) && (hp < a.pad + a.H) && (wp >= a.pad) && (wp < a.pad + a.W);
+      }
+      if (a.has_res) {
+        // residual tile of the NEXT own tile into the other buffer, once the store issued from it has been read
+        const int un = u + ustep;
+        if (leader && un < num_units) {
+          ptx::bulk_wait_read<0>();
+          ptx::mbar_arrive_expect_tx(&rf[ob ^ 1], (uint32_t)(TMO * 128));
+          ptx::tma_load_2d(myOut + (size_t)(ob ^ 1) * 16384, &tmapR, &rf[ob ^ 1], 0, (int)((long long)tile_of(un) * TMO));
+        }
+      } else {
+        if (leader) ptx::bulk_wait_read<1>();
+        ptx::named_bar_sync(1 + g, 128);              // staging buffer ob is free again
+      }
+      ptx::mbar_wait(&tfull[g], (uint32_t)(kk & 1));
+      ptx::tc_fence_after();
+      const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * N3);
+      float v[NC];
+#pragma unroll
+      for (int sub = 0; sub < 4; ++sub) {
+        uint32_t d0[16], d1[16], d2[16];
+        ptx::tmem_ld_32x32b_x16(t0 + (uint32_t)(sub * 16), d0);
+        ptx::tmem_ld_32x32b_x16(t0 + (uint32_t)(NC + sub * 16), d1);
+        ptx::tmem_ld_32x32b_x16(t0 + (uint32_t)(2 * NC + sub * 16), d2);
+        ptx::tmem_ld_wait();
+        if (lane == 31 && q < 3) {
+          float4* dst = reinterpret_cast<float4*>(xup + q * 64 + sub * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[i] = make_float4(__uint_as_float(d0[4 * i]), __uint_as_float(d0[4 * i + 1]), __uint_as_float(d0[4 * i + 2]),
+                                 __uint_as_float(d0[4 * i + 3]));
+        }
+        if (lane == 0 && q > 0) {
+          float4* dst = reinterpret_cast<float4*>(xdn + (q - 1) * 64 + sub * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[i] = make_float4(__uint_as_float(d2[4 * i]), __uint_as_float(d2[4 * i + 1]), __uint_as_float(d2[4 * i + 2]),
+                                 __uint_as_float(d2[4 * i + 3]));
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float s = __shfl_up_sync(0xffffffffu, __uint_as_float(d0[i]), 1);     // row - 1, kw = 0
+          float t = __shfl_down_sync(0xffffffffu, __uint_as_float(d2[i]), 1);   // row + 1, kw = 2
+          if (lane == 0) s = 0.f;                      // previous warp's row: added after the exchange
+          if (lane == 31) t = 0.f;
+          v[sub * 16 + i] = (s + __uint_as_float(d1[i])) + t;
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {                                 // accumulator stage g fully read: hand it back
+        if (PAIR) ptx::mbar_arrive_cluster(&tempty[g], 0u); else ptx::mbar_arrive(&tempty[g]);
+      }
+      ptx::named_bar_sync(1 + g, 128);                // boundary rows published
+      if (lane == 0 && q > 0) {
+        const float4* src = reinterpret_cast<const float4*>(xup + (q - 1) * 64);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 x = src[i];
+          v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+        }
+      }
+      if (lane == 31 && q < 3) {
+        const float4* src = reinterpret_cast<const float4*>(xdn + q * 64);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 x = src[i];
+          v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+        }
+      }
+      if (a.has_res) ptx::mbar_wait(&rf[ob], (uint32_t)((kk >> 1) & 1));
+      if (has_row) {
+        const uint32_t row_base = ptx::smem_u32(myOut + (size_t)ob * 16384) + (uint32_t)sr * 128u;
+        const uint32_t sw = (uint32_t)sr & 7u;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4 b0 = *reinterpret_cast<const float4*>(sBias + 8 * c);
+          const float4 b1 = *reinterpret_cast<const float4*>(sBias + 8 * c + 4);
+          float v0 = v[8 * c + 0] + b0.x, v1 = v[8 * c + 1] + b0.y, v2 = v[8 * c + 2] + b0.z, v3 = v[8 * c + 3] + b0.w;
+          float v4 = v[8 * c + 4] + b1.x, v5 = v[8 * c + 5] + b1.y, v6 = v[8 * c + 6] + b1.z, v7 = v[8 * c + 7] + b1.w;
+          const uint32_t addr = row_base + (((uint32_t)c ^ sw) << 4);
+          if (a.has_res) {
+            const uint4 rv = ptx::ld_shared_v4(addr);
+            v0 += convk::bf16_lo(rv.x); v1 += convk::bf16_hi(rv.x); v2 += convk::bf16_lo(rv.y); v3 += convk::bf16_hi(rv.y);
+            v4 += convk::bf16_lo(rv.z); v5 += convk::bf16_hi(rv.z); v6 += convk::bf16_lo(rv.w); v7 += convk::bf16_hi(rv.w);
+          }
+          if (a.relu) {
+            v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f);
+            v4 = fmaxf(v4, 0.f); v5 = fmaxf(v5, 0.f); v6 = fmaxf(v6, 0.f); v7 = fmaxf(v7, 0.f);
+          }
+          uint32_t o0 = convk::pack_bf16(v0, v1), o1 = convk::pack_bf16(v2, v3), o2 = convk::pack_bf16(v4, v5),
+                   o3 = convk::pack_bf16(v6, v7);
+          if (!valid) o0 = o1 = o2 = o3 = 0u;          // border positions of the padded layout stay zero
+          ptx::st_shared_v4(addr, o0, o1, o2, o3);
+        }
+      }
+      ptx::fence_proxy_async();
+      ptx::named_bar_sync(1 + g, 128);                // tile staged
+      if (leader) {
+        ptx::tma_store_2d(&tmapO, myOut + (size_t)ob * 16384, a.out_c_off, (int)q0);
+        ptx::bulk_commit();
+      }
+    }
+    if (leader) ptx::bulk_wait<0>();
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (PAIR) ptx::cluster_sync();   // nobody leaves while the peer may still arrive here
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tc_fence_after();
+    if (PAIR) ptx::tmem_dealloc_2sm(tmem_base, 512); else ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+static inline size_t smem_fixed(int chunks, int cluster) {
+  return 1024 + (size_t)3 * chunks * (N3 / cluster) * 128 + 4 * 16384 + 2 * 384 * 4 + NC * 4 + 256;
+}
+static inline size_t smem_bytes(const Args& a) {
+  return smem_fixed(a.chunks, a.cluster) + (size_t)a.stagesA * a.slab_rows * 128;
+}
+
+}  // namespace convf3

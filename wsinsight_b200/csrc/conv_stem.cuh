@@ -28,6 +28,7 @@
 namespace convs {
 
 constexpr int THREADS = 320;
+constexpr int THREADS_POOL = 576;   // POOL: 16 epilogue warps -- (M-tile, 32-column half) x 4 TMEM lane quarters
 constexpr int T = 2;             // M-tiles per super-tile
 // Instantiations: KH = 7, JJ = 2 (7x7/2 pad 3: 7 tap rows x 2 pair-pairs = 14 K steps of 16) and KH = 3, JJ = 1
 // (3x3/2 pad 0, InceptionV4 conv2d_1a: the 3 taps of a row are pixels 2wo..2wo+2 = pairs wo, wo+1 -> one K step
@@ -72,6 +73,27 @@ __device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint3
       : "memory");
 }
 
+// Epilogue of one 32-column half of a 128-row accumulator tile for the fused-pool stem: TMEM -> +bias -> ReLU -> bf16 ->
+// the half's four 16-byte chunks of the swizzled [128 rows][64 ch] staging tile (layout of convk::epi_chunk64).
+__device__ __forceinline__ void epi_half32_relu(uint32_t t_addr, int row, uint32_t s_tile, int half, const float* s_bias) {
+  uint32_t r[32];
+  ptx::tmem_ld_32x32b_x32(t_addr, r);
+  ptx::tmem_ld_wait();
+  const uint32_t row_base = s_tile + (uint32_t)row * 128u;
+  const uint32_t sw = (uint32_t)row & 7u;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
+    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
+    const float v0 = fmaxf(__uint_as_float(r[8 * c + 0]) + b0.x, 0.f), v1 = fmaxf(__uint_as_float(r[8 * c + 1]) + b0.y, 0.f);
+    const float v2 = fmaxf(__uint_as_float(r[8 * c + 2]) + b0.z, 0.f), v3 = fmaxf(__uint_as_float(r[8 * c + 3]) + b0.w, 0.f);
+    const float v4 = fmaxf(__uint_as_float(r[8 * c + 4]) + b1.x, 0.f), v5 = fmaxf(__uint_as_float(r[8 * c + 5]) + b1.y, 0.f);
+    const float v6 = fmaxf(__uint_as_float(r[8 * c + 6]) + b1.z, 0.f), v7 = fmaxf(__uint_as_float(r[8 * c + 7]) + b1.w, 0.f);
+    ptx::st_shared_v4(row_base + ((((uint32_t)(half * 4 + c)) ^ sw) << 4), convk::pack_bf16(v0, v1), convk::pack_bf16(v2, v3),
+                      convk::pack_bf16(v4, v5), convk::pack_bf16(v6, v7));
+  }
+}
+
 // POOL = false: one super-tile = T*128 consecutive flat outputs, each written to the conv output tensor.
 // POOL = true : ReLU + the 3x3/2 max pooling that follows the stem in every ResNet are fused into the epilogue
 // (the unfused pair wrote and re-read 1.7 GB per 1024 patches: 0.48 + 0.66 ms of an 7.8 ms step).  A CTA walks
@@ -79,8 +101,12 @@ __device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint3
 // stage bias+ReLU'd bf16 rows in one of three 32 KB shared buffers, meet at a named barrier, and then 256 threads
 // reduce pooled row r from rows 2r-1 (second row of the previous tile's buffer), 2r, 2r+1 and store it
 // straight into the (padded) pooled tensor.  Post-ReLU values are >= 0, so a missing neighbour is a 0.
+// The POOL epilogue was latency-bound (ncu r02: tensor pipe 40 % active, sm throughput 60 %, ~2570 cycles per tile for
+// ~800 issue slots per scheduler): it runs 16 epilogue warps -- every (M-tile, 32-column half) has its own four --
+// so that 512 threads drain TMEM and each owns ONE pooled (column, channel octet) whose horizontal maximum of
+// row 2r+1 stays in registers for the next tile (6 instead of 9 shared loads per output).
 template <bool POOL, int KH, int JJ>
-__global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant__ CUtensorMap tmapO, const Args a) {
+__global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(const __grid_constant__ CUtensorMap tmapO, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -109,7 +135,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 8);
+      ptx::mbar_init(&tempty[s], POOL ? 16 : 8);
     }
     ptx::mbar_init(wfull, 1);
     ptx::fence_barrier_init();
@@ -194,15 +220,16 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
     }
   } else {
     // ===================== epilogue: group g = M-tile g of every super-tile =====================
-    const int g = (warp - 2) >> 2;                    // 0 | 1
+    const int g = POOL ? ((warp - 2) >> 2) & 1 : (warp - 2) >> 2;   // M-tile: 0 | 1
+    const int half = POOL ? (warp - 2) >> 3 : 0;      // POOL: 32-column half of the tile this warp drains
     const int q = warp & 3;                           // TMEM lane quarter of this warp
     const int row = q * 32 + lane;
     const int gt = ((warp - 2) & 3) * 32 + lane;      // 0..127 inside the group
     const bool leader = gt == 0;
-    if (g == 0 && gt < N) sBias[gt] = a.bias[gt];
-    ptx::named_bar_sync(3, 256);                      // bias staged (both groups)
+    if ((int)threadIdx.x - 64 < N) sBias[(int)threadIdx.x - 64] = a.bias[(int)threadIdx.x - 64];
+    ptx::named_bar_sync(3, POOL ? 512 : 256);         // bias staged (all epilogue warps)
     if (POOL) {
-      const int et = (int)threadIdx.x - 64;             // 0..255 over both groups
+      const int et = (int)threadIdx.x - 64;             // 0..511 over the four groups
       const int my_imgs = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
       const int items = a.pool_w * 8;                   // (pooled column, 16-byte channel octet)
       const uint32_t sbuf0 = ptx::smem_u32(sOut);
@@ -218,6 +245,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
       };
       int acc = 0, bsel = 0;
       uint32_t pacc = 0;
+      const bool carry = items <= 512;                  // one pooled output per thread: row 2r+1's maximum is carried
+      uint4 hprev = make_uint4(0u, 0u, 0u, 0u);
       for (int im = 0; im < my_imgs; ++im) {
         const int n = (int)blockIdx.x + im * (int)gridDim.x;
         __nv_bfloat16* oimg = a.pool_out + (((size_t)n * a.pool_Hp + a.pool_pad) * a.pool_Wp + a.pool_pad) * a.pool_C + a.pool_c_off;
@@ -227,12 +256,30 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv_stem(const __grid_constant_
           ptx::mbar_wait(&tfull[acc], pacc);
           ptx::tc_fence_after();
           const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * T + g) * N);
-          convk::epi_chunk64(t_addr, row, true, cur + (uint32_t)g * 16384u, 0u, sBias, 1);
+          epi_half32_relu(t_addr + (uint32_t)(half * 32), row, cur + (uint32_t)g * 16384u, half, sBias + half * 32);
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
-          ptx::named_bar_sync(1, 256);                  // rows 2r, 2r+1 staged by both groups
-          for (int i = et; i < items; i += 256) {
+          ptx::named_bar_sync(1, 512);                  // rows 2r, 2r+1 staged by all four groups
+          if (carry) {
+            if (et < items) {
+              const uint32_t pc = (uint32_t)et >> 3, oct = (uint32_t)et & 7u;
+              uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;     // horizontal maxima of rows 2r and 2r+1
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx) {
+                if (dx == 0 && pc == 0) continue;
+                const uint32_t col = 2u * pc + (uint32_t)dx - 1u;
+                vmax(h0, ldpos(cur, col, oct));
+                vmax(h1, ldpos(cur, P + col, oct));
+              }
+              uint4 m = h0;
+              vmax(m, h1);
+              if (r > 0) vmax(m, hprev);                // row 2r-1 of the same image
+              hprev = h1;
+              *reinterpret_cast<uint4*>(oimg + ((size_t)r * a.pool_Wp + pc) * a.pool_C + oct * 8) = m;
+            }
+          } else
+          for (int i = et; i < items; i += 512) {
             const uint32_t pc = (uint32_t)i >> 3, oct = (uint32_t)i & 7u;
             uint4 m = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll

@@ -5,6 +5,7 @@
 // the Python side walks the (frozen) TorchScript graph, hands folded conv weights/biases
 // to wsi_net_add_*, and every forward runs only kernels from this library.
 #include "conv_flat.cuh"
+#include "conv_flat3.cuh"
 #include "conv_stem.cuh"
 #include "../../include/wsi_b200.h"
 #include <math.h>
@@ -36,6 +37,8 @@ struct Op {
   convf::Args fa;
   convs::Args sa;
   bool flat = false;              // 3x3/s1/p1 over padded tensors -> convf::k_conv_flat
+  bool flat3 = false;             // ... with Cout = 64 and short rows -> convf3::k_conv_flat3 (kw-split accumulators)
+  convf3::Args f3;
   int fused_pool = -1;            // stem: index of the 3x3/2 max-pool op fused into its epilogue
   bool skip = false;              // pool op executed by the stem kernel
   int cin_real = 0;               // input channels that carry a non-zero weight (<= Cin)
@@ -77,6 +80,7 @@ struct Net {
   bool pool_ring = true;          // WSI_B200_NO_POOL_RING=1: 3x3 pools by the register-ring kernel (direct global loads)
   bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
+  bool kw3_enabled = true;        // WSI_B200_NO_KW3=1: Cout = 64 flat convs stay on the nine-tap kernel
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
   int prof_slots = 0;
@@ -568,6 +572,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->legacy_epi = le && le[0] == '1';
   const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
   n->stem_pool_enabled = !(nsp && nsp[0] == '1');
+  const char* nk3 = getenv("WSI_B200_NO_KW3");
+  n->kw3_enabled = !(nk3 && nk3[0] == '1');
   *net_out = n;
   return WSI_OK;
 }
@@ -891,6 +897,18 @@ int wsi_net_finalize(void* net) {
     }
     if (!conflict) break;
   }
+  // Cout = 64 flat convs over short rows (ResNet layer1): the kw-split kernel, whose slab (128 + 2*Wp rows) is one TMA box
+  for (auto& op : n->ops) {
+    op.flat3 = false;
+    if (!op.flat || !n->kw3_enabled || op.Cout != convf3::NC || op.Cin % 64 != 0) continue;
+    const Tensor& ti = n->tensors[op.in];
+    const int cl = (n->cluster_enabled && !n->no_flat_pair) ? 2 : 1;
+    const int rows = ((128 + 2 * ti.Wp() + 7) / 8) * 8;
+    if (rows > 256) continue;
+    const long long room = 227 * 1024 - (long long)convf3::smem_fixed(op.Cin / 64, cl);
+    if (room / ((long long)rows * 128) < 2) continue;
+    op.flat3 = true;
+  }
   // stem + ReLU + 3x3/2/pad-1 max pooling (every ResNet): fuse when the stem output has no other reader
   if (n->stem_pool_enabled)
     for (size_t i = 0; i < n->ops.size(); ++i) {
@@ -924,11 +942,23 @@ int wsi_net_finalize(void* net) {
     WSI_CUDA_CHECK(cudaMalloc(&t.ptr, bytes));
     WSI_CUDA_CHECK(cudaMemset(t.ptr, 0, bytes));
   }
-  int max_smem = 0, max_smem_flat = 0, max_smem_stem = 0, max_smem_stem_pool = 0;
+  int max_smem = 0, max_smem_flat = 0, max_smem_flat3 = 0, max_smem_stem = 0, max_smem_stem_pool = 0;
   for (auto& op : n->ops) {
     if (op.kind == OP_CONV) {
       const Tensor& ti = n->tensors[op.in];
       const Tensor& to = n->tensors[op.out];
+      if (op.flat3) {
+        // kw-split weight matrix [kw*64 + co][(kh*chunks + c)*64 + ci] from the tap-major [co][((kh*3 + kw)*chunks + c)*64 + ci]
+        const int chunks = op.Cin / 64, K3 = 3 * chunks * 64;
+        std::vector<__nv_bfloat16> w3((size_t)convf3::N3 * K3);
+        for (int kw = 0; kw < 3; ++kw)
+          for (int co = 0; co < convf3::NC; ++co)
+            for (int kh = 0; kh < 3; ++kh)
+              for (int c = 0; c < chunks * 64; ++c)
+                w3[(size_t)(kw * convf3::NC + co) * K3 + (size_t)(kh * chunks + c / 64) * 64 + c % 64] =
+                    op.h_w[(size_t)co * op.Ktot + (size_t)((kh * 3 + kw) * chunks + c / 64) * 64 + c % 64];
+        op.h_w.swap(w3);
+      }
       WSI_CUDA_CHECK(cudaMalloc(&op.d_w, op.h_w.size() * sizeof(__nv_bfloat16)));
       WSI_CUDA_CHECK(cudaMemcpy(op.d_w, op.h_w.data(), op.h_w.size() * sizeof(__nv_bfloat16),
                                 cudaMemcpyHostToDevice));
@@ -972,6 +1002,65 @@ int wsi_net_finalize(void* net) {
         int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
                                op.Cout == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
         if (rc) return rc;
+        continue;
+      }
+      if (op.flat3) {
+        convf3::Args& f = op.f3;
+        memset(&f, 0, sizeof(f));
+        f.Hp = ti.Hp(); f.Wp = ti.Wp(); f.H = to.H; f.W = to.W;
+        f.pad = to.pad;
+        f.chunks = op.Cin / 64;
+        f.ksteps = (f.chunks == 1 && op.cin_real <= 32) ? 2 : 4;
+        f.cluster = (n->cluster_enabled && !n->no_flat_pair) ? 2 : 1;
+        f.slab_rows = ((128 + 2 * f.Wp + 7) / 8) * 8;
+        f.slab_loads = 1;
+        f.slab_box_rows = f.slab_rows;
+        f.stagesA = (int)((227 * 1024 - (long long)convf3::smem_fixed(f.chunks, f.cluster)) / ((long long)f.slab_rows * 128));
+        if (f.stagesA > 4) f.stagesA = 4;
+        WSI_ARG_CHECK(f.stagesA >= 2, "wsi_net_finalize: kw-split conv does not fit shared memory");
+        f.relu = op.relu;
+        f.has_res = op.res >= 0;
+        f.bias = op.d_bias;
+        f.out_c_off = op.out_c_off;
+        const int K3 = 3 * f.chunks * 64;
+        uint32_t es[2] = {1, 1};
+        {
+          uint64_t dims[2] = {(uint64_t)K3, (uint64_t)convf3::N3};
+          uint64_t strides[1] = {(uint64_t)K3 * 2};
+          uint32_t box[2] = {64, (uint32_t)(convf3::N3 / f.cluster)};
+          int rc = wsi_make_tmap(&op.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op.d_w, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+        }
+        {
+          uint64_t dims[2] = {(uint64_t)op.Cin, (uint64_t)B * ti.Hp() * ti.Wp()};
+          uint64_t strides[1] = {(uint64_t)ti.C * 2};
+          uint32_t box[2] = {64, (uint32_t)f.slab_box_rows};
+          int rc = wsi_make_tmap(&op.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ti.ptr + op.in_c_off, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+        }
+        {
+          uint64_t dims[2] = {(uint64_t)to.C, (uint64_t)B * to.Hp() * to.Wp()};
+          uint64_t strides[1] = {(uint64_t)to.C * 2};
+          uint32_t box[2] = {64, (uint32_t)convf3::TMO};
+          int rc = wsi_make_tmap(&op.tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, to.ptr, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+        }
+        op.tmR = op.tmO;
+        op.tmO32 = op.tmO;
+        if (f.has_res) {
+          const Tensor& tr = n->tensors[op.res];
+          uint64_t dims[2] = {(uint64_t)tr.C, (uint64_t)B * tr.Hp() * tr.Wp()};
+          uint64_t strides[1] = {(uint64_t)tr.C * 2};
+          uint32_t box[2] = {64, (uint32_t)convf3::TMO};
+          int rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr, dims, strides, box, es,
+                                 CU_TENSOR_MAP_SWIZZLE_128B);
+          if (rc) return rc;
+        }
+        int smem = (int)convf3::smem_bytes(f);
+        if (smem > max_smem_flat3) max_smem_flat3 = smem;
         continue;
       }
       if (op.flat) {
@@ -1216,6 +1305,10 @@ int wsi_net_finalize(void* net) {
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
     WSI_CUDA_CHECK(cudaFuncSetAttribute(convf::k_conv_flat<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat));
   }
+  if (max_smem_flat3 > 0) {
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convf3::k_conv_flat3<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat3));
+    WSI_CUDA_CHECK(cudaFuncSetAttribute(convf3::k_conv_flat3<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_flat3));
+  }
   WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3s1_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3s1_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   WSI_CUDA_CHECK(cudaFuncSetAttribute(k_pool3_tma<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
@@ -1288,7 +1381,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         if (op.fused_pool >= 0) {
           sa.B = B;
           int grid = B < n->num_sms ? B : n->num_sms;
-          convs::k_conv_stem<true, 7, 2><<<grid, convs::THREADS, convs::smem_bytes(sa.slab_pairs, sa.stages, true), stream>>>(op.tmB, sa);
+          convs::k_conv_stem<true, 7, 2><<<grid, convs::THREADS_POOL, convs::smem_bytes(sa.slab_pairs, sa.stages, true), stream>>>(op.tmB, sa);
           continue;
         }
         int grid = sa.num_tiles < n->num_sms ? sa.num_tiles : n->num_sms;
@@ -1297,6 +1390,44 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         else
           convs::k_conv_stem<false, 3, 1><<<grid, convs::THREADS,
                                             convs::smem_bytes(sa.slab_pairs, sa.stages, false, 3 * op.Cout * 32), stream>>>(op.tmO, sa);
+        continue;
+      }
+      if (op.flat3) {
+        convf3::Args f = op.f3;
+        f.B = B;
+        f.total_rows = (long long)B * f.Hp * f.Wp;
+        f.num_tiles = (int)((f.total_rows + convf3::TMO - 1) / convf3::TMO);
+        if (f.cluster == 2) {
+          const long long units = (f.num_tiles + 1) / 2;
+          long long pairs = units < n->num_sms / 2 ? units : n->num_sms / 2;
+          cudaLaunchConfig_t cfg;
+          memset(&cfg, 0, sizeof(cfg));
+          cfg.blockDim = dim3(convf3::THREADS);
+          cfg.dynamicSmemBytes = convf3::smem_bytes(f);
+          cfg.stream = stream;
+          cudaLaunchAttribute attr[1];
+          attr[0].id = cudaLaunchAttributeClusterDimension;
+          attr[0].val.clusterDim.x = 2;
+          attr[0].val.clusterDim.y = 1;
+          attr[0].val.clusterDim.z = 1;
+          cfg.attrs = attr;
+          cfg.numAttrs = 1;
+          if (op.max_pairs == 0) {
+            int nclusters = 0;
+            cfg.gridDim = dim3((unsigned)(n->num_sms / 2 * 2));
+            if (cudaOccupancyMaxActiveClusters(&nclusters, convf3::k_conv_flat3<2>, &cfg) != cudaSuccess || nclusters <= 0) {
+              cudaGetLastError();
+              nclusters = n->num_sms / 2;
+            }
+            op.max_pairs = nclusters;
+          }
+          if (pairs > op.max_pairs) pairs = op.max_pairs;
+          cfg.gridDim = dim3((unsigned)(2 * pairs));
+          WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convf3::k_conv_flat3<2>, op.tmA, op.tmB, op.tmO, op.tmR, f));
+          continue;
+        }
+        int grid = f.num_tiles < n->num_sms ? f.num_tiles : n->num_sms;
+        convf3::k_conv_flat3<1><<<grid, convf3::THREADS, convf3::smem_bytes(f), stream>>>(op.tmA, op.tmB, op.tmO, op.tmR, f);
         continue;
       }
       if (op.flat) {
