@@ -13,6 +13,13 @@
 // warps of an epilogue group go through 1.5 KB of shared memory, and a tile of 128 MMA rows yields the 126 outputs
 // that have both neighbours (tiles advance by 126 flat positions).
 //
+// MEASURED (B200, profiles/r02_ncu_stem16_kw3_*.csv, r02_perop_kw3_ab.txt): correct (same tests as the nine-tap kernel)
+// but SLOWER -- 0.318 ms against 0.225 ms per layer1 conv.  The tensor pipe is 47-52 % active: the epilogue now executes
+// ~950 instructions per warp and tile (3x the TMEM loads, 128 shuffles, 128 + 64 adds, the boundary-lane exchange)
+// against ~250 before, and with two groups of four warps that is more than the 1152 cycles the MMAs of a tile take.
+// The operand-port saving is real (shared wavefronts 41-47 % of peak instead of 90 %) but the cost moved to the issue
+// slots.  Kept as an opt-in experiment (WSI_B200_KW3=1); the default stays the nine-tap kernel.
+//
 // Warps: 0 TMA producer (weights once: 3*chunks k-blocks of 192 rows; one slab of 128 + 2*Wp rows per tile),
 // 1 MMA issuer, 2-5 / 6-9 two epilogue groups that take alternate tiles (group g <-> accumulator stage g).
 // Residual tiles are TMA-loaded into the output staging buffer and added in place, as in conv_flat.cuh.

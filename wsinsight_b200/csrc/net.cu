@@ -80,7 +80,7 @@ struct Net {
   bool pool_ring = true;          // WSI_B200_NO_POOL_RING=1: 3x3 pools by the register-ring kernel (direct global loads)
   bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
-  bool kw3_enabled = true;        // WSI_B200_NO_KW3=1: Cout = 64 flat convs stay on the nine-tap kernel
+  bool kw3_enabled = false;       // WSI_B200_KW3=1: Cout = 64 flat convs on the kw-split kernel (measured slower, see conv_flat3.cuh)
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
   int prof_slots = 0;
@@ -572,8 +572,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->legacy_epi = le && le[0] == '1';
   const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
   n->stem_pool_enabled = !(nsp && nsp[0] == '1');
-  const char* nk3 = getenv("WSI_B200_NO_KW3");
-  n->kw3_enabled = !(nk3 && nk3[0] == '1');
+  const char* k3 = getenv("WSI_B200_KW3");
+  n->kw3_enabled = k3 && k3[0] == '1';
   *net_out = n;
   return WSI_OK;
 }
