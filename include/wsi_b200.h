@@ -186,6 +186,15 @@ int wsi_net_add_pool_bias(void* net, int in_id, int in_c_off, int C, int out_id,
 /* ReLU of the convolution added last only on its first `cols` output channels (multiple of 64): lets the bias-free,
  * ReLU-free 1x1 conv of a commuted pool branch ride in the same launch as its sibling 1x1 branch convs. */
 int wsi_net_set_conv_relu_cols(void* net, int cols);
+/* Residual of the convolution added last (added with residual_id = -1) = channels [res_c_off, res_c_off + Cout) of
+ * tensor `residual_id`: the `out += identity` of a torchvision BasicBlock (TorchScript graph run by
+ * run_inference.py:541) when `identity` is the downsample branch stored next to the block's first conv. */
+int wsi_net_set_conv_residual_slice(void* net, int residual_id, int res_c_off);
+/* Output channels >= cols of the convolution added last (odd kernel, 'same' padding) have weights at the centre tap
+ * only: a 1x1 / stride-s downsample convolution stacked under the 3x3 / stride-s / pad-1 convolution that reads the
+ * same block input.  Those channels get their own N tiles, for which only the centre tap is multiplied, so one launch
+ * reads the block input once and writes both branches (three launches fewer per ResNet34 forward). */
+int wsi_net_set_conv_center_cols(void* net, int cols);
 int wsi_net_add_head(void* net, int in_id, const float* h_fc_w, const float* h_fc_b, int K);
 int wsi_net_finalize(void* net);
 /* d_input: the external input tensor (bf16 NHWC, layout of wsi_preproc_run); d_probs: f32 [B][K]

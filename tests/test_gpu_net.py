@@ -328,6 +328,37 @@ def test_resnet34_layerwise_and_probs(monkeypatch):
     assert dp <= MAX_DP_BF16, f"max |dp| = {dp}"
 
 
+def test_downsample_merge_matches_separate_launches(monkeypatch):
+    """The 1x1/2 downsample conv of layer2.0 / layer3.0 / layer4.0 rides in the launch of the block's first 3x3/2 conv
+    (centre-tap-only N tiles, one tensor [main | downsample], conv2 reads its residual as a channel slice).  Same operands,
+    same k-block order, same rounding points as three separate launches: activations and probabilities are identical."""
+    from oracle.forward import make_resnet34_calibrated
+    from wsinsight_b200.modellib.engine import B200Network
+
+    m = make_resnet34_calibrated(2, 3)
+    B = 37                                             # ragged: partial pixel boxes in every stage
+    x = _resnet_inputs(B, 224, 5)
+    ts = torch.jit.freeze(torch.jit.script(m))
+    net = B200Network.from_torchscript(ts, 2, input_size=224, max_batch=40)
+    assert len(net.downsample_merges) == 3, net.downsample_merges
+    monkeypatch.setenv("WSI_B200_NO_DS_MERGE", "1")
+    sep = B200Network.from_torchscript(ts, 2, input_size=224, max_batch=40)
+    monkeypatch.delenv("WSI_B200_NO_DS_MERGE")
+    assert sep.downsample_merges == [] and sep.num_launches == net.num_launches + 3
+    assert abs(net.flops_per_image - sep.flops_per_image) < 1e-6 * sep.flops_per_image
+    p_m = net(net.pack_input(x), B).cpu()
+    p_s = sep(sep.pack_input(x), B).cpu()
+    for main, ds in net.downsample_merges:
+        for i in (main, ds):
+            c = net.nodes[i].shape[0]
+            a_m = net.activation(i, B)[..., net.channel_offset(i):net.channel_offset(i) + c].float().cpu()
+            a_s = sep.activation(i, B)[..., sep.channel_offset(i):sep.channel_offset(i) + c].float().cpu()
+            assert torch.equal(a_m, a_s), f"node {i}: merged launch differs from the separate conv"
+    assert torch.equal(p_m, p_s)
+    net.close()
+    sep.close()
+
+
 def _torch_bf16_probs(m, x):
     """The 'best library' comparator: the same model through PyTorch/cuDNN in bf16 channels_last."""
     import copy

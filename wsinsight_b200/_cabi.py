@@ -69,6 +69,8 @@ _PROTOS = {
     "wsi_net_add_pool_bias": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                       c_float_p, c_int]),
     "wsi_net_set_conv_relu_cols": (c_int, [c_void_p, c_int]),
+    "wsi_net_set_conv_residual_slice": (c_int, [c_void_p, c_int, c_int]),
+    "wsi_net_set_conv_center_cols": (c_int, [c_void_p, c_int]),
     "wsi_net_add_head": (c_int, [c_void_p, c_int, c_float_p, c_float_p, c_int]),
     "wsi_net_finalize": (c_int, [c_void_p]),
     "wsi_net_forward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),

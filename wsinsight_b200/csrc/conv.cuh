@@ -47,6 +47,8 @@ struct Args {
                                              // stages its own 128 activation rows and HALF of the weight k-block, so a
                                              // stage is 16 KB + N_tile*64 B and the ring is 1.5x deeper (the single-CTA
                                              // ring starved: ncu showed the MMA warp waiting on TMA data 26 % of the time)
+  int center_nt, center_kb0;                 // N tiles >= center_nt run only the cin_chunks k-blocks from center_kb0
+                                             // (channels whose weights are zero outside the centre tap); tiles_N = none
   int relu;
   int relu_cols;                             // TMA epilogue: ReLU on output channels < relu_cols (merged sibling convs
                                              // may end with a slice that has none); Cout or 0 for ordinary convs
@@ -235,10 +237,24 @@ __global__ void __launch_bounds__(THREADS, 1)
   const int total_units = m_units * a.tiles_N;
   const int first_unit = CL == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int unit_step = CL == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  auto unit_to_tile = [&](int u, int& nt, int& mt) {
-    nt = u % a.tiles_N;
-    mt = u / a.tiles_N;
+  // iteration i of this CTA (pair) -> (N tile, M tile); false when the CTA has run out of work.  Default order: unit
+  // u = first + i * step, N tile fastest (neighbouring CTAs share an A tile through L2 at the same time).  With
+  // centre-tap-only N tiles (center_nt < tiles_N: a few k-blocks instead of all) a CTA instead takes ALL N tiles of its
+  // M tile back to back, so every CTA gets the same mix of long and short units.
+  const bool by_mtile = a.center_nt < a.tiles_N;
+  auto unit_of_iter = [&](int i, int& nt, int& mt) -> bool {
+    if (by_mtile) {
+      mt = first_unit + (i / a.tiles_N) * unit_step;
+      if (mt >= m_units) return false;
+      nt = i % a.tiles_N;
+    } else {
+      const int u = first_unit + i * unit_step;
+      if (u >= total_units) return false;
+      nt = u % a.tiles_N;
+      mt = u / a.tiles_N;
+    }
     if (CL == 2) mt = min(2 * mt + (int)crank, m_tiles - 1);
+    return true;
   };
   const int num_kb = a.is_stem ? 7 : a.KH * a.KW * a.cin_chunks;
 
@@ -279,15 +295,16 @@ __global__ void __launch_bounds__(THREADS, 1)
     // ===================== TMA producer (whole warp loops, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
-    for (int u = first_unit; u < total_units; u += unit_step) {
+    for (int it = 0;; ++it) {
       int nt, mt;
-      unit_to_tile(u, nt, mt);
+      if (!unit_of_iter(it, nt, mt)) break;
       const int tw = mt % a.tiles_w;
       mt /= a.tiles_w;
       const int th = mt % a.tiles_h;
       const int tn = mt / a.tiles_h;
       const int wo0 = tw * a.bw, ho0 = th * a.bh, n0 = tn * a.bn;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const int kb0 = nt >= a.center_nt ? a.center_kb0 : 0, kb1 = nt >= a.center_nt ? kb0 + a.cin_chunks : num_kb;
+      for (int kb = kb0; kb < kb1; ++kb) {
         ptx::mbar_wait(&empty[stage], phase ^ 1);
         if (ptx::elect_one()) {
           // pair mode: only the leader arms its barrier, for the bytes of BOTH CTAs (2 x (16 KB + half B))
@@ -337,11 +354,14 @@ __global__ void __launch_bounds__(THREADS, 1)
     int acc = 0;
     uint32_t acc_phase = 0;
     if (!pair || crank == 0)
-    for (int u = first_unit; u < total_units; u += unit_step) {
+    for (int it = 0;; ++it) {
+      int nt_u, mt_u;
+      if (!unit_of_iter(it, nt_u, mt_u)) break;
       ptx::mbar_wait(&tempty[acc], acc_phase ^ 1);
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const int kb0 = nt_u >= a.center_nt ? a.center_kb0 : 0, kb1 = nt_u >= a.center_nt ? kb0 + a.cin_chunks : num_kb;
+      for (int kb = kb0; kb < kb1; ++kb) {
         ptx::mbar_wait(&full[stage], phase);
         ptx::tc_fence_after();
         const uint32_t a_lo = ptx::desc_lo(ptx::smem_u32(sA + (size_t)stage * A_BYTES));
@@ -349,21 +369,21 @@ __global__ void __launch_bounds__(THREADS, 1)
         if (ptx::elect_one()) {
           // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in 16-byte units
           if (pair) {
-            ptx::umma_bf16_lohi_2sm(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != 0));
+            ptx::umma_bf16_lohi_2sm(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != kb0));
             ptx::umma_bf16_lohi_2sm(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
             ptx::umma_bf16_lohi_2sm(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
             ptx::umma_bf16_lohi_2sm(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
             ptx::umma_commit_2sm(&empty[stage], (uint16_t)3);      // frees the slot in both CTAs
-            if (kb == num_kb - 1) ptx::umma_commit_2sm(&tfull[acc], (uint16_t)3);
+            if (kb == kb1 - 1) ptx::umma_commit_2sm(&tfull[acc], (uint16_t)3);
           } else {
-            ptx::umma_bf16_lohi(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != 0));
+            ptx::umma_bf16_lohi(d_tmem, a_lo, b_lo, hi, idesc, (uint32_t)(kb != kb0));
             ptx::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, hi, idesc, 1u);
             if (!a.is_stem) {
               ptx::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, hi, idesc, 1u);
               ptx::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, hi, idesc, 1u);
             }
             ptx::umma_commit(&empty[stage]);   // frees the smem slot once these MMAs retire
-            if (kb == num_kb - 1) ptx::umma_commit(&tfull[acc]);   // accumulator ready for the epilogue
+            if (kb == kb1 - 1) ptx::umma_commit(&tfull[acc]);     // accumulator ready for the epilogue
           }
         }
         __syncwarp();
@@ -400,11 +420,11 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int n_l = row / (a.bw * a.bh);
     int acc = 0, k = 0;
     uint32_t acc_phase = 0, res_phase = 0;
-    for (int u = first_unit; u < total_units; u += unit_step, ++k) {
+    for (;; ++k) {
+      int nt, mt;
+      if (!unit_of_iter(k, nt, mt)) break;
       const bool part = cn > 1 ? (g < cn) : ((k & 1) == g);
       if (part) {
-        int nt, mt;
-        unit_to_tile(u, nt, mt);
         const int tw = mt % a.tiles_w;
         mt /= a.tiles_w;
         const int th = mt % a.tiles_h;
@@ -517,9 +537,9 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int n_l = row / (a.bw * a.bh);
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int u = first_unit; u < total_units; u += unit_step) {
+    for (int it = 0;; ++it) {
       int nt, mt;
-      unit_to_tile(u, nt, mt);
+      if (!unit_of_iter(it, nt, mt)) break;
       const int tw = mt % a.tiles_w;
       mt /= a.tiles_w;
       const int th = mt % a.tiles_h;

@@ -46,6 +46,7 @@ struct Args {
   int out_C, out_c_off;         // channels of the destination tensor / concat offset
   int tma_epi;                  // N % 64 == 0: epilogue staged in smem and written by TMA stores
   int res_smem;                 // residual tiles are TMA-loaded into the output staging buffers (needs nOut == 2)
+  int res_C, res_c_off;         // channels of the residual tensor (row pitch) and the first one read: `residual` points at it
   int nOut, nRes;               // output staging buffers (16 KB each) PER epilogue group; nRes unused (residual
                                 // chunks are prefetched from global memory into registers one chunk ahead)
   const __nv_bfloat16* residual;
@@ -241,7 +242,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           // the epilogue reads this super-tile's residual rows stagesA slabs from now: have them in L2 by then
           // (HBM latency under load exceeds the one-tile lead of the register prefetch)
           const long long rows = a.total_rows - q0 < TM ? a.total_rows - q0 : TM;
-          ptx::bulk_prefetch_l2(a.residual + (size_t)q0 * a.N, (uint32_t)(rows * a.N * 2));
+          ptx::bulk_prefetch_l2(a.residual - a.res_c_off + (size_t)q0 * a.res_C, (uint32_t)(rows * a.res_C * 2));
         }
         __syncwarp();
         for (int c = 0; c < a.chunks; ++c) {
@@ -399,7 +400,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         if (a.has_res && first_unit < num_units) {
           const long long p0 = (long long)tile_of(first_unit) * TM + g * 128 + row;
           if (p0 < a.total_rows) {
-            const uint4* rb = reinterpret_cast<const uint4*>(a.residual + (size_t)p0 * a.N);
+            const uint4* rb = reinterpret_cast<const uint4*>(a.residual + (size_t)p0 * a.res_C);
 #pragma unroll
             for (int i = 0; i < 8; ++i)
               if (i < nv0) rv[i] = __ldg(rb + i);
@@ -413,10 +414,10 @@ __global__ void __launch_bounds__(THREADS, 1)
           const int hp = rem / a.Wp, wp = rem - hp * a.Wp;
           const bool valid = (n < a.B) && (hp >= a.pad) && (hp < a.pad + a.H) && (wp >= a.pad) && (wp < a.pad + a.W);
           const bool do_res = a.has_res && p < a.total_rows;
-          const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N);
+          const uint4* rbase = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.res_C);
           const int un = u + unit_step;
           const long long pn = un < num_units ? (long long)tile_of(un) * TM + g * 128 + row : a.total_rows;
-          const uint4* rnext = reinterpret_cast<const uint4*>(a.residual + (size_t)pn * a.N);
+          const uint4* rnext = reinterpret_cast<const uint4*>(a.residual + (size_t)pn * a.res_C);
           ptx::mbar_wait(&tfull[acc], pacc);
           ptx::tc_fence_after();
           for (int j = 0; j < cn; ++j, ++k) {
@@ -496,7 +497,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + b.w;
             }
             if (a.has_res) {
-              const uint4* rp = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.N + c0);
+              const uint4* rp = reinterpret_cast<const uint4*>(a.residual + (size_t)p * a.res_C + c0);
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 uint4 rv = __ldg(rp + i);

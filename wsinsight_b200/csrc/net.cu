@@ -52,6 +52,8 @@ struct Op {
   int Cin, Cout, KH, KW, stride, pad_h, pad_w, relu, out_c_off, is_stem;
   int in_c_off = 0;               // first input channel read (slice of a wider tensor)
   int relu_cols = -1;             // conv: ReLU only on output channels < relu_cols (-1: all, when relu is set)
+  int res_c_off = 0;              // residual = channels [res_c_off, res_c_off + Cout) of tensor `res`
+  int center_cols = -1;           // output channels >= center_cols carry weights at the centre tap only (-1: none)
   int pC = 0;                     // pool: channels pooled (slice [in_c_off, in_c_off + pC) of the input tensor)
   int Ktot;
   // pool
@@ -747,6 +749,52 @@ int wsi_net_set_conv_relu_cols(void* net, int cols) {
   return WSI_OK;
 }
 
+// Residual of the conv added last = channels [res_c_off, res_c_off + Cout) of tensor `residual_id` (the conv must have
+// been added without a residual).  Lets a BasicBlock's second conv add the downsample branch where it lies inside the
+// tensor it shares with the block's first conv (wsi_net_set_conv_center_cols).
+int wsi_net_set_conv_residual_slice(void* net, int residual_id, int res_c_off) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized && !n->ops.empty() && n->ops.back().kind == OP_CONV, "wsi_net_set_conv_residual_slice: no conv");
+  Op& op = n->ops.back();
+  WSI_ARG_CHECK(op.res < 0 && !op.is_stem && op.out_c_off == 0, "wsi_net_set_conv_residual_slice: conv already has a residual");
+  WSI_ARG_CHECK(residual_id >= 0 && residual_id < (int)n->tensors.size(), "wsi_net_set_conv_residual_slice: bad residual id");
+  const Tensor& tr = n->tensors[residual_id];
+  const Tensor& to = n->tensors[op.out];
+  WSI_ARG_CHECK(tr.H == to.H && tr.W == to.W && !tr.external && res_c_off >= 0 && res_c_off % 8 == 0 &&
+                    res_c_off + op.Cout <= tr.C,
+                "wsi_net_set_conv_residual_slice: channels [%d, %d) of a %dx%dx%d tensor do not match the %dx%dx%d output",
+                res_c_off, res_c_off + op.Cout, tr.H, tr.W, tr.C, to.H, to.W, op.Cout);
+  op.res = residual_id;
+  op.res_c_off = res_c_off;
+  return WSI_OK;
+}
+
+// Output channels >= cols of the conv added last have non-zero weights at the CENTRE tap only (a 1x1 / stride-s / pad-0
+// convolution embedded in a KxK / stride-s / pad-(K-1)/2 one that reads the same pixels: the downsample branch of a
+// ResNet BasicBlock next to the block's first conv).  The per-tap kernel gives those channels their own N tiles and
+// runs only the centre tap's k-blocks for them, so the block input is read by ONE launch.
+int wsi_net_set_conv_center_cols(void* net, int cols) {
+  Net* n = (Net*)net;
+  WSI_ARG_CHECK(n && !n->finalized && !n->ops.empty() && n->ops.back().kind == OP_CONV, "wsi_net_set_conv_center_cols: no conv");
+  Op& op = n->ops.back();
+  WSI_ARG_CHECK(!op.is_stem && (op.KH & 1) && (op.KW & 1) && op.pad_h == op.KH / 2 && op.pad_w == op.KW / 2,
+                "wsi_net_set_conv_center_cols: needs an odd kernel with 'same' padding");
+  WSI_ARG_CHECK(cols > 0 && cols < op.Cout && cols % 64 == 0 && (op.Cout - cols) % 64 == 0,
+                "wsi_net_set_conv_center_cols: bad column count %d of %d", cols, op.Cout);
+  const int chunks = (op.Cin + 63) / 64, ctap = op.pad_h * op.KW + op.pad_w;
+  for (int o = cols; o < op.Cout; ++o)
+    for (int t = 0; t < op.KH * op.KW; ++t) {
+      if (t == ctap) continue;
+      for (int k = 0; k < chunks * 64; ++k)
+        WSI_ARG_CHECK(__bfloat162float(op.h_w[(size_t)o * op.Ktot + (size_t)t * chunks * 64 + k]) == 0.f,
+                      "wsi_net_set_conv_center_cols: channel %d has a weight outside the centre tap", o);
+    }
+  op.center_cols = cols;
+  const Tensor& to = n->tensors[op.out];
+  op.flops_per_image = 2.0 * to.H * to.W * (double)op.Cin * ((double)cols * op.KH * op.KW + (double)(op.Cout - cols));
+  return WSI_OK;
+}
+
 // 3x3 / stride 1 AVERAGE pool followed by + bias[c] and optional ReLU.  conv1x1(avgpool(x)) == avgpool(conv1x1(x))
 // (both linear, the divisor depends on the position only), so the engine runs the 1x1 conv of an Inception pool branch
 // FIRST (without bias / ReLU) and pools its 4-8x narrower output here: the wide block input is no longer read and
@@ -837,7 +885,8 @@ int wsi_net_finalize(void* net) {
               op.Cin % 8 == 0 && op.Cout % 32 == 0 && op.Cout <= 128 && !ti.external && ti.W >= 24 &&
               ti.H >= 8;
     if (op.pad_h == 0 && getenv("WSI_B200_NO_FLAT_VALID")) ok = false;
-    if (op.res >= 0 && (n->tensors[op.res].C != op.Cout || n->tensors[op.res].external)) ok = false;
+    if (op.res >= 0 && n->tensors[op.res].external) ok = false;
+    if (op.center_cols >= 0) ok = false;
     op.flat = ok;
   }
   for (int round = 0; round < 64; ++round) {
@@ -1052,10 +1101,10 @@ int wsi_net_finalize(void* net) {
         op.tmO32 = op.tmO;
         if (f.has_res) {
           const Tensor& tr = n->tensors[op.res];
-          uint64_t dims[2] = {(uint64_t)tr.C, (uint64_t)B * tr.Hp() * tr.Wp()};
+          uint64_t dims[2] = {(uint64_t)op.Cout, (uint64_t)B * tr.Hp() * tr.Wp()};
           uint64_t strides[1] = {(uint64_t)tr.C * 2};
           uint32_t box[2] = {64, (uint32_t)convf3::TMO};
-          int rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr, dims, strides, box, es,
+          int rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr + op.res_c_off, dims, strides, box, es,
                                  CU_TENSOR_MAP_SWIZZLE_128B);
           if (rc) return rc;
         }
@@ -1110,6 +1159,8 @@ int wsi_net_finalize(void* net) {
         WSI_ARG_CHECK(f.stagesA >= 2 && f.slab_box_rows <= 256, "wsi_net_finalize: flat conv does not fit shared memory");
         f.relu = op.relu;
         f.has_res = op.res >= 0;
+        f.res_C = op.res >= 0 ? n->tensors[op.res].C : 0;
+        f.res_c_off = op.res_c_off;
         f.bias = op.d_bias;
         f.out_C = to.C; f.out_c_off = op.out_c_off;
         op.tmO = op.tmB;
@@ -1118,11 +1169,11 @@ int wsi_net_finalize(void* net) {
         f.res_smem = 0;
         if (f.has_res && f.tma_epi && f.nOut == 2 && op.Cout % 64 == 0 && n->res_smem_enabled) {
           const Tensor& tr = n->tensors[op.res];
-          uint64_t dims[2] = {(uint64_t)tr.C, (uint64_t)B * tr.Hp() * tr.Wp()};
+          uint64_t dims[2] = {(uint64_t)op.Cout, (uint64_t)B * tr.Hp() * tr.Wp()};
           uint64_t strides[1] = {(uint64_t)tr.C * 2};
           uint32_t box[2] = {64, 128};
           uint32_t es[2] = {1, 1};
-          int rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr, dims, strides, box, es,
+          int rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, tr.ptr + op.res_c_off, dims, strides, box, es,
                                  CU_TENSOR_MAP_SWIZZLE_128B);
           if (rc) return rc;
           f.res_smem = 1;
@@ -1176,7 +1227,12 @@ int wsi_net_finalize(void* net) {
       a.cin_chunks = (op.Cin + 63) / 64;
       a.is_stem = op.is_stem;
       a.N_tile = pick_ntile(op.Cout);
+      if (op.center_cols >= 0)                       // the centre-tap-only channels get N tiles of their own
+        for (a.N_tile = 256; a.N_tile > 64; a.N_tile -= 64)
+          if (op.center_cols % a.N_tile == 0 && (op.Cout - op.center_cols) % a.N_tile == 0) break;
       a.tiles_N = op.Cout / a.N_tile;
+      a.center_nt = op.center_cols >= 0 ? op.center_cols / a.N_tile : a.tiles_N;
+      a.center_kb0 = (op.pad_h * op.KW + op.pad_w) * ((op.Cin + 63) / 64);
       a.tma_epi = (a.N_tile % 64 == 0 || (a.N_tile % 32 == 0 && !n->legacy_epi)) ? 1 : 0;
       a.Cout = op.Cout;
       // CTA pairs (cta_group::2, M = 256): N must be a multiple of 32 there and each CTA's half of the weight
@@ -1218,9 +1274,9 @@ int wsi_net_finalize(void* net) {
         a.res_smem = 0;
         if (op.res >= 0 && a.N_tile % 64 == 0 && n->res_smem_enabled && op.KH * op.KW * a.cin_chunks >= 16) {
           const Tensor& tr = n->tensors[op.res];
-          uint64_t rdims[4] = {(uint64_t)tr.C, (uint64_t)tr.W, (uint64_t)tr.H, (uint64_t)B};
+          uint64_t rdims[4] = {(uint64_t)op.Cout, (uint64_t)tr.W, (uint64_t)tr.H, (uint64_t)B};
           uint64_t rstrides[3] = {(uint64_t)tr.C * 2, (uint64_t)tr.Wp() * tr.C * 2, (uint64_t)tr.Hp() * tr.Wp() * tr.C * 2};
-          rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, tr.ptr + tr.interior_offset(), rdims, rstrides,
+          rc = wsi_make_tmap(&op.tmR, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, tr.ptr + tr.interior_offset() + op.res_c_off, rdims, rstrides,
                              box, es, CU_TENSOR_MAP_SWIZZLE_128B);
           if (rc) return rc;
           a.res_smem = 1;
@@ -1436,7 +1492,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         f.total_rows = (long long)B * f.Hp * f.Wp;
         f.num_tiles = (int)((f.total_rows + f.T * 128 - 1) / (f.T * 128));
         f.out = to.ptr;
-        f.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
+        f.residual = op.res >= 0 ? n->tensors[op.res].ptr + op.res_c_off : nullptr;
         if (f.cluster == 2) {
           const long long units = (f.num_tiles + 1) / 2;
           long long pairs = units < n->num_sms / 2 ? units : n->num_sms / 2;
@@ -1475,7 +1531,7 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
       a.B = B;
       a.tiles_n = wsi_cdiv(B, a.bn);
       a.out = to.ptr;
-      a.residual = op.res >= 0 ? n->tensors[op.res].ptr : nullptr;
+      a.residual = op.res >= 0 ? n->tensors[op.res].ptr + op.res_c_off : nullptr;
       const long long total = (long long)a.tiles_w * a.tiles_h * a.tiles_n * a.tiles_N;
       int grid = (int)(total < n->num_sms ? total : n->num_sms);
       size_t smem = convk::smem_bytes(a.N_tile, a.stages, a.tma_epi, a.Cout, a.cluster);

@@ -170,13 +170,13 @@ class B200Network:
         # tensor and the consumers read channel slices of it, so the block input is read from HBM once per group
         # instead of once per branch (these 1x1 convs are HBM-bound: 384 -> 64 at 35x35 moves 1.1 GB for 0.05 GFLOP/img).
         merged_into, group_of = {}, {}
+        users = {}
+        for j, m in enumerate(nodes):
+            for p in m.inputs:
+                users.setdefault(p, []).append((j, "in"))
+            if getattr(m, "residual", None) is not None:
+                users.setdefault(m.residual, []).append((j, "res"))
         if os.environ.get("WSI_B200_NO_SIBLING_MERGE") != "1":
-            users = {}
-            for j, m in enumerate(nodes):
-                for p in m.inputs:
-                    users.setdefault(p, []).append((j, "in"))
-                if getattr(m, "residual", None) is not None:
-                    users.setdefault(m.residual, []).append((j, "res"))
             sibs = {}
             for i, n in enumerate(nodes):
                 if (n.kind == "conv" and i not in tensor_of and n is not stem and n.residual is None
@@ -209,6 +209,33 @@ class B200Network:
                     merged_into[i] = members[0]
                 group_of[members[0]] = members
         self.merged_groups = list(group_of.values())
+        # Downsample branch of a torchvision BasicBlock: conv1x1(stride s, no padding) reads the pixels the centre tap of
+        # the block's first conv3x3(stride s, padding 1) reads.  Its filters are stacked under the 3x3 ones (zero outside
+        # the centre tap; the kernel skips the other taps for those channels: wsi_net_set_conv_center_cols), one launch
+        # writes one tensor [main | downsample], and the block's second conv takes its input and its residual as the
+        # two channel slices of that tensor.  Same operands and rounding points as two launches.
+        ds_main, ds_of = {}, {}                       # downsample node -> main conv node, and the inverse
+        if os.environ.get("WSI_B200_NO_DS_MERGE") != "1":
+            for i, n in enumerate(nodes):
+                if not (n.kind == "conv" and i not in tensor_of and n is not stem and n.residual is None and not n.relu
+                        and tuple(n.weight.shape[2:]) == (1, 1) and int(n.stride) > 1 and tuple(n.pad) == (0, 0)
+                        and int(n.weight.shape[0]) % 64 == 0 and users.get(i)
+                        and all(how == "res" and nodes[j].kind == "conv" for j, how in users[i])):
+                    continue
+                for j, m in enumerate(nodes):
+                    if (j != i and m.kind == "conv" and m.inputs == n.inputs and j not in tensor_of and j not in ds_of
+                            and m is not stem and m.residual is None and m.relu
+                            and tuple(m.weight.shape[2:]) == (3, 3) and int(m.stride) == int(n.stride)
+                            and tuple(m.pad) == (1, 1) and tuple(m.shape[1:]) == tuple(n.shape[1:])
+                            and int(m.weight.shape[0]) % 64 == 0 and users.get(j)
+                            and all(how == "in" and nodes[k].kind == "conv" for k, how in users[j])):
+                        c, h, w = m.shape
+                        tid = self._add_tensor(h, w, int(m.weight.shape[0]) + int(n.weight.shape[0]))
+                        tensor_of[j], c_off[j] = tid, 0
+                        tensor_of[i], c_off[i] = tid, int(m.weight.shape[0])
+                        ds_main[i], ds_of[j] = j, i
+                        break
+        self.downsample_merges = sorted(ds_of.items())
         for i, n in enumerate(nodes):
             if n.kind in ("conv", "pool") and i not in tensor_of:
                 c, h, w = n.shape
@@ -224,7 +251,7 @@ class B200Network:
                 continue
             x = n.inputs[0]
             in_off = 0
-            if x in merged_into:
+            if x in merged_into or x in ds_of:
                 in_off = c_off[x]                  # slice of a merged sibling tensor (conv consumers only)
             elif c_off.get(x, 0) != 0 or (nodes[x].kind in ("conv", "pool") and
                                           nodes[x].shape[0] != self._tensor_channels(nodes, tensor_of, x)):
@@ -262,6 +289,27 @@ class B200Network:
                 if has_pool:
                     _cabi.call("wsi_net_set_conv_relu_cols", self._h, relu_c)
                 continue
+            if i in ds_main or i in ds_of:
+                # block conv1 + downsample: one launch, emitted with whichever node is visited first
+                import torch
+
+                j = i if i in ds_of else ds_main[i]
+                if j in emitted_groups:
+                    continue
+                emitted_groups.add(j)
+                mn, dn = nodes[j], nodes[ds_of[j]]
+                cm, cd, cin = int(mn.weight.shape[0]), int(dn.weight.shape[0]), int(mn.weight.shape[1])
+                wd = torch.zeros((cd, cin, 3, 3), dtype=torch.float32)
+                wd[:, :, 1, 1] = dn.weight[:, :, 0, 0]
+                w = torch.cat([mn.weight, wd], 0).contiguous()
+                b = torch.cat([mn.bias if mn.bias is not None else torch.zeros(cm),
+                               dn.bias if dn.bias is not None else torch.zeros(cd)], 0).contiguous()
+                self._keep += [w, b]
+                _cabi.call("wsi_net_add_conv_slice", self._h, tensor_of[x], int(in_off), tensor_of[j], 0, _fptr(w),
+                           _fptr(b), cin, cm + cd, 3, 3, int(mn.stride), 1, 1, 1, -1)
+                _cabi.call("wsi_net_set_conv_relu_cols", self._h, cm)
+                _cabi.call("wsi_net_set_conv_center_cols", self._h, cm)
+                continue
             if n.kind == "pool" and i in conv_of_pool:
                 cn = nodes[conv_of_pool[i]]
                 w = cn.weight.contiguous()
@@ -292,11 +340,14 @@ class B200Network:
                                1 if n.relu else 0)
                 else:
                     res = tensor_of[n.residual] if n.residual is not None else -1
-                    if n.residual is not None and c_off.get(n.residual, 0) != 0:
+                    res_slice = n.residual is not None and n.residual in ds_main
+                    if n.residual is not None and c_off.get(n.residual, 0) != 0 and not res_slice:
                         raise UnknownArchitectureError("residual read from a concat slice")
                     _cabi.call("wsi_net_add_conv_slice", self._h, tensor_of[x], int(in_off), tensor_of[i], out_off,
                                _fptr(w), _fptr(b), cin, cout, int(w.shape[2]), int(w.shape[3]), int(n.stride),
-                               int(n.pad[0]), int(n.pad[1]), 1 if n.relu else 0, res)
+                               int(n.pad[0]), int(n.pad[1]), 1 if n.relu else 0, -1 if res_slice else res)
+                    if res_slice:
+                        _cabi.call("wsi_net_set_conv_residual_slice", self._h, res, int(c_off[n.residual]))
             elif n.kind == "pool":
                 _cabi.call("wsi_net_add_pool", self._h, tensor_of[x], tensor_of[i], c_off[i], 1 if n.pool_max else 0,
                            int(n.k), int(n.pstride), int(n.ppad), 1 if n.count_include_pad else 0)
