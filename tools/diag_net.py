@@ -30,6 +30,7 @@ for (K, seed, B, maxb) in [(1, 3, 5, 8), (2, 0, 16, 16), (1, 3, 8, 8)]:
     for i, n in enumerate(net.nodes):
         if n.kind in ("conv", "pool"):
             a = net.activation(i, B).float().permute(0, 3, 1, 2).cpu()
+            a = a[:, net.channel_offset(i):net.channel_offset(i) + n.shape[0]]
             e = acts[i]
             d = (a - e).abs()
             rel = (d.mean() / (e.abs().mean() + 1e-9)).item()
