@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-2 GPU pass M (final state): full GPU suite, smoke, default bench + reference arm, launch list, ncu --set full of
+# final-state verification pass: full GPU suite, smoke, default bench + reference arm, launch list, ncu --set full of
 # the 33 ResNet34 conv launches of one forward (traffic JSON + summary)
 mkdir -p gpurun_out
 ( time timeout 1200 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider 2>&1 | tail -60 ) > gpurun_out/pytest_m.log 2>&1
