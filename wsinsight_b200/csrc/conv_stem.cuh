@@ -61,6 +61,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       : "memory");
 }
 
+__device__ __forceinline__ uint32_t convk_hmax2(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
 __device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
                                            uint32_t idesc, uint32_t accumulate) {
   asm volatile(
@@ -73,38 +78,30 @@ __device__ __forceinline__ void umma_lohi2(uint32_t tmem_d, uint32_t a_lo, uint3
       : "memory");
 }
 
-// Epilogue of one 32-column half of a 128-row accumulator tile for the fused-pool stem: TMEM -> +bias -> ReLU -> bf16 ->
-// the half's four 16-byte chunks of the swizzled [128 rows][64 ch] staging tile (layout of convk::epi_chunk64).
-__device__ __forceinline__ void epi_half32_relu(uint32_t t_addr, int row, uint32_t s_tile, int half, const float* s_bias) {
-  uint32_t r[32];
-  ptx::tmem_ld_32x32b_x32(t_addr, r);
-  ptx::tmem_ld_wait();
-  const uint32_t row_base = s_tile + (uint32_t)row * 128u;
-  const uint32_t sw = (uint32_t)row & 7u;
+// 16 fp32 accumulator columns -> + bias -> ReLU -> 8 packed bf16 pairs
+__device__ __forceinline__ void bias_relu_pack16(const uint32_t (&d)[16], const float* s_bias, uint32_t (&p)[8]) {
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + 8 * c);
-    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + 8 * c + 4);
-    const float v0 = fmaxf(__uint_as_float(r[8 * c + 0]) + b0.x, 0.f), v1 = fmaxf(__uint_as_float(r[8 * c + 1]) + b0.y, 0.f);
-    const float v2 = fmaxf(__uint_as_float(r[8 * c + 2]) + b0.z, 0.f), v3 = fmaxf(__uint_as_float(r[8 * c + 3]) + b0.w, 0.f);
-    const float v4 = fmaxf(__uint_as_float(r[8 * c + 4]) + b1.x, 0.f), v5 = fmaxf(__uint_as_float(r[8 * c + 5]) + b1.y, 0.f);
-    const float v6 = fmaxf(__uint_as_float(r[8 * c + 6]) + b1.z, 0.f), v7 = fmaxf(__uint_as_float(r[8 * c + 7]) + b1.w, 0.f);
-    ptx::st_shared_v4(row_base + ((((uint32_t)(half * 4 + c)) ^ sw) << 4), convk::pack_bf16(v0, v1), convk::pack_bf16(v2, v3),
-                      convk::pack_bf16(v4, v5), convk::pack_bf16(v6, v7));
+  for (int i = 0; i < 4; ++i) {
+    const float4 b = *reinterpret_cast<const float4*>(s_bias + 4 * i);
+    p[2 * i] = convk::pack_bf16(fmaxf(__uint_as_float(d[4 * i]) + b.x, 0.f), fmaxf(__uint_as_float(d[4 * i + 1]) + b.y, 0.f));
+    p[2 * i + 1] = convk::pack_bf16(fmaxf(__uint_as_float(d[4 * i + 2]) + b.z, 0.f), fmaxf(__uint_as_float(d[4 * i + 3]) + b.w, 0.f));
   }
 }
 
 // POOL = false: one super-tile = T*128 consecutive flat outputs, each written to the conv output tensor.
 // POOL = true : ReLU + the 3x3/2 max pooling that follows the stem in every ResNet are fused into the epilogue
 // (the unfused pair wrote and re-read 1.7 GB per 1024 patches: 0.48 + 0.66 ms of an 7.8 ms step).  A CTA walks
-// whole images; tile r of an image is output rows 2r, 2r+1 (2P <= 256 flat positions).  Both epilogue groups
-// stage bias+ReLU'd bf16 rows in one of three 32 KB shared buffers, meet at a named barrier, and then 256 threads
-// reduce pooled row r from rows 2r-1 (second row of the previous tile's buffer), 2r, 2r+1 and store it
-// straight into the (padded) pooled tensor.  Post-ReLU values are >= 0, so a missing neighbour is a 0.
-// The POOL epilogue was latency-bound (ncu r02: tensor pipe 40 % active, sm throughput 60 %, ~2570 cycles per tile for
-// ~800 issue slots per scheduler): it runs 16 epilogue warps -- every (M-tile, 32-column half) has its own four --
-// so that 512 threads drain TMEM and each owns ONE pooled (column, channel octet) whose horizontal maximum of
-// row 2r+1 stays in registers for the next tile (6 instead of 9 shared loads per output).
+// whole images; tile r of an image is output rows 2r (M-tile 0) and 2r+1 (M-tile 1), BOTH starting at column 0: the
+// second MMA's A window starts one image row (P pairs) below the first instead of 128 positions further, so TMEM lane
+// l of the two accumulators holds the two vertically adjacent outputs of column l (needs P <= 128).
+// 16 epilogue warps (4 TMEM lane quarters x 4 sixteen-channel quarters): a thread loads its column's 16 channels of
+// both rows, adds bias, ReLUs, packs to bf16 and takes the VERTICAL maximum of rows 2r-1 (carried in registers from the
+// previous tile), 2r, 2r+1 without touching shared memory; only that one row is staged (16 KB, double-buffered), and
+// after a named barrier 448 threads each reduce one pooled (column, channel octet) from three staged columns and store
+// it straight into the (padded) pooled tensor.  Post-ReLU values are >= 0, so a missing neighbour is a 0; the maximum
+// commutes with the (monotone) bf16 rounding, so the result equals pooling the rounded conv output.
+// History (ncu): 8 epilogue warps staging both rows and reading 9 positions per output: 529 us, tensor pipe 40 % active,
+// latency-bound; 16 warps + row 2r+1's horizontal maximum carried: 452 us, 48 %, 79 % of the shared-memory data pipe.
 template <bool POOL, int KH, int JJ>
 __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(const __grid_constant__ CUtensorMap tmapO, const Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -114,8 +111,8 @@ __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(
   const int N = a.N;
   const int W_BYTES = KSTEPS * N * 32;
   const int slab_bytes = a.slab_pairs * 16;           // one parity
-  uint8_t* sOut = smem;                               // 4 x 16 KB: [group][buffer], 1024-aligned (POOL: 3 x 32 KB)
-  uint8_t* sW = sOut + (POOL ? 6 : 4) * 16384;
+  uint8_t* sOut = smem;                               // 4 x 16 KB: [group][buffer], 1024-aligned (POOL: 2 x 16 KB)
+  uint8_t* sW = sOut + (POOL ? 2 : 4) * 16384;
   uint8_t* sA = sW + W_BYTES;                          // stages x 2 parities x slab_bytes
   float* sBias = reinterpret_cast<float*>(sA + (size_t)a.stages * 2 * slab_bytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + N_MAX);
@@ -209,7 +206,7 @@ __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(
           const uint32_t a_lo = s_lo + (uint32_t)(kh & 1) * par_step + (uint32_t)(kh >> 1) * P + (uint32_t)(2 * jj);
           const uint32_t b_lo = w_lo + (uint32_t)ks * (uint32_t)(N * 32 >> 4);
           umma_lohi2(d0, a_lo, a_hi, b_lo, b_hi, idesc, ks == 0 ? 0u : 1u);
-          umma_lohi2(d0 + (uint32_t)N, a_lo + 128u, a_hi, b_lo, b_hi, idesc, ks == 0 ? 0u : 1u);
+          umma_lohi2(d0 + (uint32_t)N, a_lo + (POOL ? P : 128u), a_hi, b_lo, b_hi, idesc, ks == 0 ? 0u : 1u);
         }
         ptx::umma_commit(&empty[stage]);
         ptx::umma_commit(&tfull[acc]);
@@ -220,22 +217,20 @@ __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(
     }
   } else {
     // ===================== epilogue: group g = M-tile g of every super-tile =====================
-    const int g = POOL ? ((warp - 2) >> 2) & 1 : (warp - 2) >> 2;   // M-tile: 0 | 1
-    const int half = POOL ? (warp - 2) >> 3 : 0;      // POOL: 32-column half of the tile this warp drains
+    const int g = (warp - 2) >> 2;                    // !POOL: M-tile 0 | 1.  POOL: 16-channel quarter 0..3
     const int q = warp & 3;                           // TMEM lane quarter of this warp
-    const int row = q * 32 + lane;
+    const int row = q * 32 + lane;                    // !POOL: flat position in the M-tile.  POOL: output column
     const int gt = ((warp - 2) & 3) * 32 + lane;      // 0..127 inside the group
     const bool leader = gt == 0;
     if ((int)threadIdx.x - 64 < N) sBias[(int)threadIdx.x - 64] = a.bias[(int)threadIdx.x - 64];
     ptx::named_bar_sync(3, POOL ? 512 : 256);         // bias staged (all epilogue warps)
     if (POOL) {
-      const int et = (int)threadIdx.x - 64;             // 0..511 over the four groups
+      const int et = (int)threadIdx.x - 64;             // 0..511
       const int my_imgs = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
       const int items = a.pool_w * 8;                   // (pooled column, 16-byte channel octet)
       const uint32_t sbuf0 = ptx::smem_u32(sOut);
-      const uint32_t P = (uint32_t)a.P;
-      auto ldpos = [&](uint32_t buf, uint32_t pos, uint32_t oct) {
-        return ptx::ld_shared_v4(buf + pos * 128u + ((oct ^ (pos & 7u)) << 4));
+      auto ldcol = [&](uint32_t buf, uint32_t col, uint32_t oct) {
+        return ptx::ld_shared_v4(buf + col * 128u + ((oct ^ (col & 7u)) << 4));
       };
       auto vmax = [](uint4& m, const uint4& x) {
         __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
@@ -245,54 +240,43 @@ __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(
       };
       int acc = 0, bsel = 0;
       uint32_t pacc = 0;
-      const bool carry = items <= 512;                  // one pooled output per thread: row 2r+1's maximum is carried
-      uint4 hprev = make_uint4(0u, 0u, 0u, 0u);
+      uint32_t carry[8];                                // row 2r-1 of this column, 16 channels (bf16 pairs)
       for (int im = 0; im < my_imgs; ++im) {
         const int n = (int)blockIdx.x + im * (int)gridDim.x;
         __nv_bfloat16* oimg = a.pool_out + (((size_t)n * a.pool_Hp + a.pool_pad) * a.pool_Wp + a.pool_pad) * a.pool_C + a.pool_c_off;
         for (int r = 0; r < a.row_pairs; ++r) {
-          const uint32_t cur = sbuf0 + (uint32_t)bsel * 32768u;
-          const uint32_t prev = sbuf0 + (uint32_t)(bsel == 0 ? 2 : bsel - 1) * 32768u;
+          const uint32_t buf = sbuf0 + (uint32_t)bsel * 16384u;
           ptx::mbar_wait(&tfull[acc], pacc);
           ptx::tc_fence_after();
-          const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((acc * T + g) * N);
-          epi_half32_relu(t_addr + (uint32_t)(half * 32), row, cur + (uint32_t)g * 16384u, half, sBias + half * 32);
+          const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * T * N + g * 16);
+          uint32_t d0[16], d1[16], p0[8], p1[8];
+          ptx::tmem_ld_32x32b_x16(t0, d0);                          // row 2r
+          ptx::tmem_ld_32x32b_x16(t0 + (uint32_t)N, d1);            // row 2r + 1
+          ptx::tmem_ld_wait();
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
-          ptx::named_bar_sync(1, 512);                  // rows 2r, 2r+1 staged by all four groups
-          if (carry) {
-            if (et < items) {
-              const uint32_t pc = (uint32_t)et >> 3, oct = (uint32_t)et & 7u;
-              uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;     // horizontal maxima of rows 2r and 2r+1
+          bias_relu_pack16(d0, sBias + g * 16, p0);
+          bias_relu_pack16(d1, sBias + g * 16, p1);
 #pragma unroll
-              for (int dx = 0; dx < 3; ++dx) {
-                if (dx == 0 && pc == 0) continue;
-                const uint32_t col = 2u * pc + (uint32_t)dx - 1u;
-                vmax(h0, ldpos(cur, col, oct));
-                vmax(h1, ldpos(cur, P + col, oct));
-              }
-              uint4 m = h0;
-              vmax(m, h1);
-              if (r > 0) vmax(m, hprev);                // row 2r-1 of the same image
-              hprev = h1;
-              *reinterpret_cast<uint4*>(oimg + ((size_t)r * a.pool_Wp + pc) * a.pool_C + oct * 8) = m;
-            }
-          } else
-          for (int i = et; i < items; i += 512) {
-            const uint32_t pc = (uint32_t)i >> 3, oct = (uint32_t)i & 7u;
-            uint4 m = make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-            for (int dx = 0; dx < 3; ++dx) {
-              if (dx == 0 && pc == 0) continue;
-              const uint32_t col = 2u * pc + (uint32_t)dx - 1u;
-              if (r > 0) vmax(m, ldpos(prev, P + col, oct));
-              vmax(m, ldpos(cur, col, oct));
-              vmax(m, ldpos(cur, P + col, oct));
-            }
+          for (int i = 0; i < 8; ++i) {
+            uint32_t m = convk_hmax2(p0[i], p1[i]);
+            if (r > 0) m = convk_hmax2(m, carry[i]);
+            carry[i] = p1[i];
+            p0[i] = m;
+          }
+          const uint32_t rb = buf + (uint32_t)row * 128u, sw = (uint32_t)row & 7u;
+          ptx::st_shared_v4(rb + ((((uint32_t)(2 * g)) ^ sw) << 4), p0[0], p0[1], p0[2], p0[3]);
+          ptx::st_shared_v4(rb + ((((uint32_t)(2 * g + 1)) ^ sw) << 4), p0[4], p0[5], p0[6], p0[7]);
+          ptx::named_bar_sync(1, 512);                  // vertical maxima of all 128 columns x 64 channels staged
+          if (et < items) {
+            const uint32_t pc = (uint32_t)et >> 3, oct = (uint32_t)et & 7u;
+            uint4 m = ldcol(buf, 2u * pc, oct);
+            vmax(m, ldcol(buf, 2u * pc + 1u, oct));
+            if (pc > 0) vmax(m, ldcol(buf, 2u * pc - 1u, oct));
             *reinterpret_cast<uint4*>(oimg + ((size_t)r * a.pool_Wp + pc) * a.pool_C + oct * 8) = m;
           }
-          if (++bsel == 3) bsel = 0;
+          bsel ^= 1;
           if (++acc == 2) { acc = 0; pacc ^= 1; }
         }
       }
@@ -338,7 +322,7 @@ __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(
 }
 
 static inline size_t smem_bytes(int slab_pairs, int stages, bool pool = false, int w_bytes = 14 * 64 * 32) {
-  return 1024 + (pool ? 6 : 4) * 16384 + w_bytes + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
+  return 1024 + (pool ? 2 : 4) * 16384 + w_bytes + (size_t)stages * 2 * slab_pairs * 16 + 256 + (size_t)(2 * stages + 5) * 8 + 16;
 }
 
 }  // namespace convs

@@ -973,7 +973,7 @@ int wsi_net_finalize(void* net) {
       }
       const Tensor& ts = n->tensors[op.out];
       const int P = n->tensors[op.in].H / 2;
-      if (readers == 1 && pool_idx >= 0 && ts.H % 2 == 0 && ts.W % 2 == 0 && 2 * P <= convs::T * 128 &&
+      if (readers == 1 && pool_idx >= 0 && ts.H % 2 == 0 && ts.W % 2 == 0 && P <= 128 && (ts.W / 2) * 8 <= 512 &&
           n->tensors[n->ops[pool_idx].out].C % 8 == 0) {
         op.fused_pool = pool_idx;
         n->ops[pool_idx].skip = true;
@@ -1030,7 +1030,7 @@ int wsi_net_finalize(void* net) {
         sa.bias = op.d_bias;
         if (op.fused_pool >= 0) {
           const Tensor& tp = n->tensors[n->ops[op.fused_pool].out];
-          sa.stages = 3;
+          sa.stages = 4;
           sa.row_pairs = to.H / 2;
           sa.pool_w = to.W / 2;
           sa.pool_out = tp.ptr;
