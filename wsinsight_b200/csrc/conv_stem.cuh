@@ -100,6 +100,8 @@ __device__ __forceinline__ void bias_relu_pack16(const uint32_t (&d)[16], const 
 // after a named barrier 448 threads each reduce one pooled (column, channel octet) from three staged columns and store
 // it straight into the (padded) pooled tensor.  Post-ReLU values are >= 0, so a missing neighbour is a 0; the maximum
 // commutes with the (monotone) bf16 rounding, so the result equals pooling the rounded conv output.
+// (Tried and dropped: 8 warps that only drain + 6 warps that only pool, handing the buffers over through named
+// barriers -- 0.66 ms against 0.44 ms: what the drain needs is MANY warps in flight, each is a dependent chain.)
 // History (ncu): 8 epilogue warps staging both rows and reading 9 positions per output: 529 us, tensor pipe 40 % active,
 // latency-bound; 16 warps + row 2r+1's horizontal maximum carried: 452 us, 48 %, 79 % of the shared-memory data pipe.
 template <bool POOL, int KH, int JJ>
