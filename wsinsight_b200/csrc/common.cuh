@@ -173,6 +173,13 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   return v;
 }
 
+// ---- programmatic dependent launch ----
+// launch_dependents: the next kernel of the stream (launched with programmaticStreamSerializationAllowed) may start
+// filling SMs as soon as every CTA of this grid has executed it or exited; wait: returns once the preceding grid has
+// completed and its memory operations are visible (a no-op when the kernel was launched without the attribute).
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- thread-block clusters ----
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;

@@ -227,6 +227,10 @@ __global__ void __launch_bounds__(THREADS, 1)
   if (CL == 2) ptx::cluster_sync();           // the peer's barriers are initialised before anything remote happens
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // barriers, tensor memory and descriptors are set up: only now wait for the producing kernel of the stream (its
+  // tail overlapped this prologue), and let the consuming kernel do the same with ours
+  ptx::pdl_wait();
+  ptx::pdl_launch_dependents();
 
   if (warp == 0) {
     // ===================== TMA producer =====================

@@ -147,6 +147,10 @@ __global__ void __launch_bounds__(POOL ? THREADS_POOL : THREADS, 1) k_conv_stem(
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // barriers, tensor memory and descriptors are set up: only now wait for the producing kernel of the stream (its
+  // tail overlapped this prologue), and let the consuming kernel do the same with ours
+  ptx::pdl_wait();
+  ptx::pdl_launch_dependents();
 
   if (warp == 0) {
     // ===================== producer: weights once, then one bulk copy per parity per super-tile =====================

@@ -82,6 +82,7 @@ struct Net {
   bool pool_ring = true;          // WSI_B200_NO_POOL_RING=1: 3x3 pools by the register-ring kernel (direct global loads)
   bool legacy_epi = false;        // WSI_B200_LEGACY_EPI=1: per-thread global stores for N tiles that are not multiples of 64
   bool stem_pool_enabled = true;  // WSI_B200_NO_STEM_POOL=1: stem conv and max pooling stay two kernels
+  bool pdl_enabled = true;        // WSI_B200_NO_PDL=1: conv kernels launched without programmatic dependent launch
   bool kw3_enabled = false;       // WSI_B200_KW3=1: Cout = 64 flat convs on the kw-split kernel (measured slower, see conv_flat3.cuh)
   int launches_per_forward = 0;
   // optional per-op CUDA-event timing (bench roofline): ring of `prof_slots` event sets
@@ -574,6 +575,8 @@ int wsi_net_create(int max_batch, void** net_out) {
   n->legacy_epi = le && le[0] == '1';
   const char* nsp = getenv("WSI_B200_NO_STEM_POOL");
   n->stem_pool_enabled = !(nsp && nsp[0] == '1');
+  const char* npdl = getenv("WSI_B200_NO_PDL");
+  n->pdl_enabled = !(npdl && npdl[0] == '1');
   const char* k3 = getenv("WSI_B200_KW3");
   n->kw3_enabled = k3 && k3[0] == '1';
   *net_out = n;
@@ -1437,7 +1440,18 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         if (op.fused_pool >= 0) {
           sa.B = B;
           int grid = B < n->num_sms ? B : n->num_sms;
-          convs::k_conv_stem<true, 7, 2><<<grid, convs::THREADS_POOL, convs::smem_bytes(sa.slab_pairs, sa.stages, true), stream>>>(op.tmB, sa);
+          cudaLaunchConfig_t cfg;
+          memset(&cfg, 0, sizeof(cfg));
+          cfg.gridDim = dim3((unsigned)grid);
+          cfg.blockDim = dim3(convs::THREADS_POOL);
+          cfg.dynamicSmemBytes = convs::smem_bytes(sa.slab_pairs, sa.stages, true);
+          cfg.stream = stream;
+          cudaLaunchAttribute attr[1];
+          attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+          attr[0].val.programmaticStreamSerializationAllowed = 1;
+          cfg.attrs = attr;
+          cfg.numAttrs = n->pdl_enabled ? 1 : 0;
+          WSI_CUDA_CHECK(cudaLaunchKernelEx(&cfg, convs::k_conv_stem<true, 7, 2>, op.tmB, sa));
           continue;
         }
         int grid = sa.num_tiles < n->num_sms ? sa.num_tiles : n->num_sms;
@@ -1461,13 +1475,15 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
           cfg.blockDim = dim3(convf3::THREADS);
           cfg.dynamicSmemBytes = convf3::smem_bytes(f);
           cfg.stream = stream;
-          cudaLaunchAttribute attr[1];
+          cudaLaunchAttribute attr[2];
           attr[0].id = cudaLaunchAttributeClusterDimension;
           attr[0].val.clusterDim.x = 2;
           attr[0].val.clusterDim.y = 1;
           attr[0].val.clusterDim.z = 1;
+          attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // prologue overlaps the previous conv's tail
+          attr[1].val.programmaticStreamSerializationAllowed = 1;
           cfg.attrs = attr;
-          cfg.numAttrs = 1;
+          cfg.numAttrs = n->pdl_enabled ? 2 : 1;
           if (op.max_pairs == 0) {
             int nclusters = 0;
             cfg.gridDim = dim3((unsigned)(n->num_sms / 2 * 2));
@@ -1501,13 +1517,15 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
           cfg.blockDim = dim3(convf::THREADS);
           cfg.dynamicSmemBytes = convf::smem_bytes(f);
           cfg.stream = stream;
-          cudaLaunchAttribute attr[1];
+          cudaLaunchAttribute attr[2];
           attr[0].id = cudaLaunchAttributeClusterDimension;
           attr[0].val.clusterDim.x = 2;
           attr[0].val.clusterDim.y = 1;
           attr[0].val.clusterDim.z = 1;
+          attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // prologue overlaps the previous conv's tail
+          attr[1].val.programmaticStreamSerializationAllowed = 1;
           cfg.attrs = attr;
-          cfg.numAttrs = 1;
+          cfg.numAttrs = n->pdl_enabled ? 2 : 1;
           if (op.max_pairs == 0) {
             // GPCs with an odd SM count cannot host a pair on every SM: size the persistent grid to what is co-resident
             int nclusters = 0;
@@ -1546,13 +1564,15 @@ int wsi_net_forward(void* net, const void* d_input, int B, float* d_probs, void*
         cfg.blockDim = dim3(convk::THREADS);
         cfg.dynamicSmemBytes = smem;
         cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2;
         attr[0].val.clusterDim.y = 1;
         attr[0].val.clusterDim.z = 1;
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // prologue overlaps the previous conv's tail
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = n->pdl_enabled ? 2 : 1;
         if (op.max_pairs == 0) {
           // GPCs with an odd SM count cannot host a pair on every SM: size the persistent grid to what is co-resident
           int nclusters = 0;
