@@ -119,6 +119,18 @@ size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int 
 int wsi_patch_grid(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, long long slide_h,
                    int half, int step, int32_t* d_coords_xy, int capacity, int* d_count,
                    int* h_tile_dim, void* d_ws, size_t ws_bytes, void* stream);
+/* Allocation-free variant of wsi_patch_grid.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The scratch lives in a file-scope `static __device__` array of the library (256 KB per GPU that loads the
+ * library, held until exit) sized for at most WSI_PATCH_GRID_STATIC_MAX_CANDIDATES candidate centroids
+ * (ni * nj of wsi_patch_grid); larger grids return WSI_ERR_ARG.  Inputs, outputs and results are those of
+ * wsi_patch_grid.  The call performs no cudaMalloc / cudaFree / allocating library call.  All calls on one device share
+ * the array: calls that overlap on the GPU (different streams) race -- keep them on one stream or serialise them.
+ * The first call on each device resolves the array's device address; make that call outside a graph capture. */
+#define WSI_PATCH_GRID_STATIC_MAX_CANDIDATES (1 << 24)
+int wsi_patch_grid_static(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, long long slide_h,
+                          int half, int step, int32_t* d_coords_xy, int capacity, int* d_count,
+                          int* h_tile_dim, void* stream);
 
 /* ---- K3: fused patch data path --------------------------------------------------------- */
 /* Replaces WholeSlideImagePatches._get_patch_from_wsi (wsinsight/modellib/data.py:270-281:

@@ -51,6 +51,8 @@ _PROTOS = {
     "wsi_patch_grid_workspace_bytes": (c_size_t, [c_ll, c_ll, c_int, c_int]),
     "wsi_patch_grid": (c_int, [c_void_p, c_int, c_int, c_ll, c_ll, c_int, c_int, c_void_p, c_int,
                                c_void_p, c_int_p, c_void_p, c_size_t, c_void_p]),
+    "wsi_patch_grid_static": (c_int, [c_void_p, c_int, c_int, c_ll, c_ll, c_int, c_int, c_void_p, c_int,
+                                      c_void_p, c_int_p, c_void_p]),
     "wsi_preproc_plan_create": (c_int, [c_void_p, c_ll, c_ll, c_ll, c_int, c_int, c_float_p, c_float_p,
                                         c_int, c_int, c_int, c_int, C.POINTER(c_void_p)]),
     "wsi_preproc_run": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),

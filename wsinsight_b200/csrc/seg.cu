@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include "../../include/wsi_b200.h"
 #include <stdlib.h>
+#include <mutex>
 #include <vector>
 
 namespace {
@@ -1252,6 +1253,32 @@ int wsi_ccl_label_u8(const uint8_t* d_mask, int H, int W, int conn8_fg, int fram
   return WSI_OK;
 }
 
+// ---- allocation-free patch grid (no counterpart in the reference) -------------------------------------------------
+// Scratch of wsi_patch_grid_static(): per-block counts / offsets of k_grid_count / k_grid_scan / k_grid_write for up to
+// WSI_PATCH_GRID_STATIC_MAX_CANDIDATES candidate centroids.  256 KB of device memory on every GPU that loads the
+// library, held until the process exits.  In HOST code `g_grid_static` is only a stand-in for the symbol: the device
+// address comes from cudaGetSymbolAddress (grid_static_ptr below), once per device with that device current.
+constexpr int GRID_STATIC_MAX_BLOCKS = WSI_PATCH_GRID_STATIC_MAX_CANDIDATES / GRID_THREADS;
+static __device__ __align__(256) int g_grid_static[GRID_STATIC_MAX_BLOCKS + 64];
+
+static int grid_static_ptr(int** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static int* ptr_of[MAX_DEV] = {};
+  int dev = -1;
+  WSI_CUDA_CHECK(cudaGetDevice(&dev));
+  WSI_ARG_CHECK(dev >= 0 && dev < MAX_DEV, "wsi_patch_grid_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr_of[dev]) {
+    int* p = nullptr;
+    WSI_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_grid_static));
+    WSI_ARG_CHECK(p != nullptr, "wsi_patch_grid_static: no device address for the scratch array");
+    ptr_of[dev] = p;
+  }
+  *out = ptr_of[dev];
+  return WSI_OK;
+}
+
 size_t wsi_patch_grid_workspace_bytes(long long slide_w, long long slide_h, int half, int step) {
   if (step <= 0) return 0;
   long long ni = slide_w > half ? (slide_w - half + step - 1) / step : 0;
@@ -1293,6 +1320,29 @@ int wsi_patch_grid(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, lo
   wsi_count_launch(3);
   WSI_CUDA_CHECK(cudaGetLastError());
   return WSI_OK;
+}
+
+// wsi_patch_grid() with its scratch in the file-scope device array above: no cudaMalloc / cudaFree / allocating call on
+// this path, for callers that cannot allocate (CUDA graph capture, tight serving loops).  Same kernels, same results.
+// Every call on a device shares the one array: calls that overlap on the GPU (different streams) race; calls on one
+// stream are ordered.  Nothing in the array has to start at zero -- k_grid_count overwrites every entry it later reads.
+// The first call on a device resolves the array's address (cudaGetSymbolAddress); make it before a graph capture.
+int wsi_patch_grid_static(const uint8_t* d_outer, int Ht, int Wt, long long slide_w, long long slide_h, int half,
+                          int step, int32_t* d_coords_xy, int capacity, int* d_count, int* h_tile_dim, void* stream_) {
+  WSI_ARG_CHECK(step > 0, "wsi_patch_grid: step must be positive (overlap must be in (-inf, 1))");
+  WSI_ARG_CHECK(half >= 0 && slide_w > 0 && slide_h > 0 && slide_w < (1ll << 30) && slide_h < (1ll << 30),
+                "wsi_patch_grid_static: bad geometry");
+  const long long ni = slide_w > half ? (slide_w - half + step - 1) / step : 0;
+  const long long nj = slide_h > half ? (slide_h - half + step - 1) / step : 0;
+  WSI_ARG_CHECK(ni * nj <= (long long)WSI_PATCH_GRID_STATIC_MAX_CANDIDATES,
+                "wsi_patch_grid_static: %lld candidate centroids exceed the static scratch (max %d); use wsi_patch_grid "
+                "with a caller-provided workspace",
+                ni * nj, WSI_PATCH_GRID_STATIC_MAX_CANDIDATES);
+  int* scratch = nullptr;
+  int rc = grid_static_ptr(&scratch);
+  if (rc) return rc;
+  return wsi_patch_grid(d_outer, Ht, Wt, slide_w, slide_h, half, step, d_coords_xy, capacity, d_count, h_tile_dim,
+                        scratch, sizeof(int) * (size_t)(GRID_STATIC_MAX_BLOCKS + 64), stream_);
 }
 
 }  // extern "C"
