@@ -359,6 +359,115 @@ def test_downsample_merge_matches_separate_launches(monkeypatch):
     sep.close()
 
 
+def _build_block(B, cin, cm, H, w_main, b_main, w_ds9, b_ds, w2, b2, center_cols=True):
+    """[main 3x3/2 + ReLU | downsample as centre-tap-only 3x3/2] in one conv op, then conv2 3x3/1 + residual slice + ReLU."""
+    import ctypes as C
+    from wsinsight_b200 import _cabi
+
+    net = C.c_void_p()
+    _cabi.call("wsi_net_create", B, C.byref(net))
+    fp = lambda t: C.cast(t.data_ptr(), _cabi.c_float_p)
+    Ho = (H + 2 - 3) // 2 + 1
+    tin, tmid, tout = C.c_int(), C.c_int(), C.c_int()
+    _cabi.call("wsi_net_add_tensor", net, H, H, cin, 0, C.byref(tin))
+    _cabi.call("wsi_net_add_tensor", net, Ho, Ho, 2 * cm, 0, C.byref(tmid))
+    _cabi.call("wsi_net_add_tensor", net, Ho, Ho, cm, 0, C.byref(tout))
+    w1 = torch.cat([w_main, w_ds9], 0).contiguous()
+    b1 = torch.cat([b_main, b_ds], 0).contiguous()
+    keep = [w1, b1, w2.contiguous(), b2.contiguous()]
+    _cabi.call("wsi_net_add_conv_slice", net, tin.value, 0, tmid.value, 0, fp(w1), fp(b1), cin, 2 * cm, 3, 3, 2, 1, 1, 1, -1)
+    _cabi.call("wsi_net_set_conv_relu_cols", net, cm)
+    if center_cols:
+        _cabi.call("wsi_net_set_conv_center_cols", net, cm)
+    _cabi.call("wsi_net_add_conv_slice", net, tmid.value, 0, tout.value, 0, fp(keep[2]), fp(keep[3]), cm, cm, 3, 3, 1, 1, 1, 1, -1)
+    _cabi.call("wsi_net_set_conv_residual_slice", net, tmid.value, cm)
+    return net, (tin.value, tmid.value, tout.value), keep, Ho
+
+
+@pytest.mark.parametrize("B,cin,cm,H", [(5, 64, 128, 30), (3, 128, 256, 28), (2, 64, 64, 57)])
+def test_center_tap_tiles_and_residual_slice_vs_torch(B, cin, cm, H):
+    """wsi_net_set_conv_center_cols / wsi_net_set_conv_residual_slice on a bare BasicBlock head (odd and even sizes,
+    N tiles of 64 / 128 / 256): against fp64 torch on bf16-rounded operands, and bit-identical to the same stacked
+    conv run WITHOUT the centre-tap shortcut (all nine taps multiplied, eight of them by zeros)."""
+    import ctypes as C
+    from wsinsight_b200 import _cabi
+
+    g = torch.Generator().manual_seed(B * 7 + cin + H)
+    x = bf16_round(torch.randn((B, cin, H, H), generator=g))
+    w_main = bf16_round(torch.randn((cm, cin, 3, 3), generator=g) / (cin * 9) ** 0.5)
+    w_ds = bf16_round(torch.randn((cm, cin, 1, 1), generator=g) / cin ** 0.5)
+    w2 = bf16_round(torch.randn((cm, cm, 3, 3), generator=g) / (cm * 9) ** 0.5)
+    b_main, b_ds, b2 = (torch.randn(cm, generator=g) * 0.1 for _ in range(3))
+    w_ds9 = torch.zeros((cm, cin, 3, 3))
+    w_ds9[:, :, 1, 1] = w_ds[:, :, 0, 0]
+    outs = []
+    for center in (True, False):
+        net, (tin, tmid, tout), keep, Ho = _build_block(B, cin, cm, H, w_main, b_main, w_ds9, b_ds, w2, b2, center)
+        try:
+            _cabi.call("wsi_net_finalize", net)
+            xd = x.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+            _cabi.call("wsi_net_write_tensor", net, tin, B, xd.data_ptr(), _cabi.stream_ptr())
+            _cabi.call("wsi_net_forward", net, None, B, None, _cabi.stream_ptr())
+            mid = torch.empty((B, Ho, Ho, 2 * cm), dtype=torch.bfloat16, device="cuda")
+            out = torch.empty((B, Ho, Ho, cm), dtype=torch.bfloat16, device="cuda")
+            _cabi.call("wsi_net_read_tensor", net, tmid, B, mid.data_ptr(), _cabi.stream_ptr())
+            _cabi.call("wsi_net_read_tensor", net, tout, B, out.data_ptr(), _cabi.stream_ptr())
+            torch.cuda.synchronize()
+            outs.append((mid.float().permute(0, 3, 1, 2).cpu(), out.float().permute(0, 3, 1, 2).cpu()))
+        finally:
+            _cabi.load().wsi_net_destroy(net)
+    (mid_c, out_c), (mid_f, out_f) = outs
+    assert torch.equal(mid_c, mid_f) and torch.equal(out_c, out_f), "centre-tap-only tiles differ from the nine-tap product"
+    a = conv_reference(x, w_main, b_main, 2, 1, relu=True)
+    d = conv_reference(x, w_ds, b_ds, 2, 0)
+    _check(mid_c[:, :cm], a, "main 3x3/2")
+    _check(mid_c[:, cm:], d, "downsample 1x1/2 as centre-tap tiles")
+    want = conv_reference(bf16_round(mid_c[:, :cm]), w2, b2, 1, 1, relu=True, residual=bf16_round(mid_c[:, cm:]))
+    _check(out_c, want, "conv2 + residual slice + relu")
+
+
+def test_center_cols_and_residual_slice_reject_bad_arguments():
+    import ctypes as C
+    from wsinsight_b200 import _cabi
+    from wsinsight_b200._cabi import WsiKernelError
+
+    g = torch.Generator().manual_seed(5)
+    cin, cm, H, B = 64, 64, 30, 2
+    w_main = torch.randn((cm, cin, 3, 3), generator=g)
+    w_bad = torch.zeros((cm, cin, 3, 3))
+    w_bad[:, :, 1, 1] = 1.0
+    w_bad[3, 5, 0, 2] = 0.25                                   # a weight outside the centre tap
+    z = torch.zeros(cm)
+    w2 = torch.randn((cm, cm, 3, 3), generator=g)
+    net = C.c_void_p()
+    fp = lambda t: C.cast(t.data_ptr(), _cabi.c_float_p)
+    _cabi.call("wsi_net_create", B, C.byref(net))
+    try:
+        tin, tmid, tout, tsmall = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _cabi.call("wsi_net_add_tensor", net, H, H, cin, 0, C.byref(tin))
+        _cabi.call("wsi_net_add_tensor", net, 15, 15, 2 * cm, 0, C.byref(tmid))
+        _cabi.call("wsi_net_add_tensor", net, 15, 15, cm, 0, C.byref(tout))
+        _cabi.call("wsi_net_add_tensor", net, 14, 14, cm, 0, C.byref(tsmall))
+        w1 = torch.cat([w_main, w_bad], 0).contiguous()
+        b1 = torch.cat([z, z], 0).contiguous()
+        _cabi.call("wsi_net_add_conv_slice", net, tin.value, 0, tmid.value, 0, fp(w1), fp(b1), cin, 2 * cm, 3, 3, 2, 1, 1, 1, -1)
+        with pytest.raises(WsiKernelError, match="outside the centre tap"):
+            _cabi.call("wsi_net_set_conv_center_cols", net, cm)
+        with pytest.raises(WsiKernelError, match="bad column count"):
+            _cabi.call("wsi_net_set_conv_center_cols", net, 32)
+        w2c, b2c = w2.contiguous(), z.contiguous()
+        _cabi.call("wsi_net_add_conv_slice", net, tmid.value, 0, tout.value, 0, fp(w2c), fp(b2c), cm, cm, 3, 3, 1, 1, 1, 1, -1)
+        with pytest.raises(WsiKernelError, match="do not match"):
+            _cabi.call("wsi_net_set_conv_residual_slice", net, tsmall.value, 0)       # 14 x 14 residual for a 15 x 15 output
+        with pytest.raises(WsiKernelError, match="do not match"):
+            _cabi.call("wsi_net_set_conv_residual_slice", net, tmid.value, cm + 8)    # slice runs past the tensor
+        _cabi.call("wsi_net_set_conv_residual_slice", net, tmid.value, cm)
+        with pytest.raises(WsiKernelError, match="already has a residual"):
+            _cabi.call("wsi_net_set_conv_residual_slice", net, tmid.value, 0)
+    finally:
+        _cabi.load().wsi_net_destroy(net)
+
+
 def _torch_bf16_probs(m, x):
     """The 'best library' comparator: the same model through PyTorch/cuDNN in bf16 channels_last."""
     import copy
